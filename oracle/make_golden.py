@@ -1,0 +1,106 @@
+"""TEST INFRASTRUCTURE ONLY -- writes tests/golden/*.npz from the REAL reference modules.
+
+Run in the build container (needs /root/reference):  python -m oracle.make_golden
+Each fixture stores: the flat config, the (name, shape) list of the reference
+state_dict (weights are rebuilt from oracle/weights_recipe.py, so none are stored), the
+input recipe and the reference outputs.  The reference holds no golden vectors of its
+own, so these are outputs of the reference code itself run here.
+"""
+import json
+import os
+import sys
+from unittest import mock
+
+import numpy as np
+import torch
+
+from . import configs as C
+from . import ref_loader as R
+from .weights_recipe import recipe_input
+
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+SEED = 0
+
+
+def _names_shapes(model):
+    return [(k, list(v.shape)) for k, v in model.state_dict().items()]
+
+
+def _save(name, cfg, model, arrays):
+    os.makedirs(OUT, exist_ok=True)
+    meta = dict(cfg=cfg, names_shapes=_names_shapes(model), seed=SEED)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"), meta=json.dumps(meta),
+                        **{k: np.ascontiguousarray(v) for k, v in arrays.items()})
+    print("wrote", name, {k: tuple(np.shape(v)) for k, v in arrays.items()})
+
+
+def _sd(model):
+    return {k: v.detach().clone() for k, v in model.state_dict().items()}
+
+
+@torch.no_grad()
+def offline_and_stream(name, cfg, B, T, chunk=None, x_seed=1234, with_stream=True):
+    model = R.build_reference(cfg)
+    R.fill_deterministic(model, SEED)
+    x = torch.from_numpy(recipe_input((B, 1, T), x_seed))
+    arrays = dict(x_seed=np.int64(x_seed), x_shape=np.array([B, 1, T]))
+    noise = None
+    if cfg.get("noise", False):
+        L = T // cfg["n_band"]
+        noise = torch.from_numpy(recipe_input((B, L // 8, cfg["n_band"], 8), 7, uniform=True))
+        arrays["noise_seed"] = np.int64(7)
+        with mock.patch("torch.rand_like", side_effect=lambda t: (noise + 1) / 2):
+            z = model.encode(x)
+            y = model.decode(z)
+    else:
+        z = model.encode(x)
+        y = model.decode(z)
+    arrays.update(z=z.numpy(), y=y.numpy())
+    if with_stream and not cfg.get("noise", False):
+        ms = R.build_reference(cfg, streaming=True)
+        ms.load_state_dict(_sd(model), strict=False)
+        zs, ys = [], []
+        for c in range(T // chunk):
+            xc = x[..., c * chunk:(c + 1) * chunk]
+            zc = ms.encode(xc)
+            zs.append(zc)
+            ys.append(ms.decode(zc))
+        arrays.update(chunk=np.int64(chunk), z_stream=torch.cat(zs, -1).numpy(),
+                      y_stream=torch.cat(ys, -1).numpy())
+    if cfg.get("encoder_type") == "discrete":
+        zq = torch.from_numpy(recipe_input((4, cfg["latent_size"], 64), 99, scale=1.0))
+        idx = model.encoder.rvq.encode(zq)
+        acc = model.encoder.rvq.decode(idx)
+        arrays.update(rvq_z_seed=np.int64(99), rvq_idx=idx.numpy(), rvq_dec=acc.numpy())
+    _save(name, cfg, model, arrays)
+
+
+def pqmf_fixture():
+    pq = R.load("pqmf").CachedPQMF(attenuation=100, n_band=16)
+    os.makedirs(OUT, exist_ok=True)
+    np.savez_compressed(os.path.join(OUT, "pqmf_bank.npz"), h=pq.h.numpy(), hk=pq.hk.numpy(),
+                        wf=pq.forward_conv.weight.detach().numpy(),
+                        wi=pq.inverse_conv.weight.detach().numpy())
+    print("wrote pqmf_bank", tuple(pq.hk.shape))
+
+
+def main():
+    if not R.available():
+        sys.exit("reference tree not available; golden files can only be made in the build container")
+    torch.manual_seed(0)
+    pqmf_fixture()
+    offline_and_stream("v2_c8", C.v2(8), 2, 16384, 2048)
+    offline_and_stream("v2causal_c8", C.v2(8, causal=True), 2, 16384, 2048)
+    offline_and_stream("v3_c8", C.v3(8), 2, 16384, 2048)
+    offline_and_stream("v3causal_c8", C.v3(8, causal=True), 1, 8192, 2048)
+    offline_and_stream("discrete_c8", C.discrete(8), 1, 8192, 2048)
+    offline_and_stream("v2noise_c8", C.v2(8, noise=True), 2, 8192, None)
+    offline_and_stream("v1_c8", C.v1(8), 1, 8192, 2048)
+    offline_and_stream("raspberry_c16", C.raspberry(16), 1, 8192, 1024)
+    offline_and_stream("raspberry_causal_c16", C.raspberry(16, causal=True), 1, 8192, 1024)
+    # the real sizes of BASELINE.json configs[0] (fp32, B=1), shortened to 2^15 samples
+    offline_and_stream("v2_c64", C.v2(64), 1, 32768, None, with_stream=False)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,174 @@
+"""Pins the CPU oracle: (1) against the committed golden fixtures (outputs of the real
+reference modules, made by oracle/make_golden.py); (2) where /root/reference exists,
+against the real modules live, including the reference's own tests/test_residual.py
+identities that pin the restated cached_conv."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import configs as C
+from oracle import rave_oracle as O
+from oracle import ref_loader as R
+from oracle.model import OracleRAVE
+from oracle.weights_recipe import recipe_input
+
+from .util import golden_input, golden_state_dict, load_golden, rel_l2
+
+FIXTURES = ["v2_c8", "v2causal_c8", "v3_c8", "v3causal_c8", "discrete_c8", "v2noise_c8",
+            "v1_c8", "raspberry_c16", "raspberry_causal_c16", "v2_c64"]
+needs_ref = pytest.mark.skipif(not R.available(), reason="reference tree not present")
+
+
+def test_pqmf_design_matches_reference_bank():
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "pqmf_bank.npz"))
+    h, hk = O.pqmf_bank(100, 16)
+    wf, wi = O.pqmf_conv_weights(hk)
+    assert hk.shape == (16, 512) and wf.shape == (16, 1, 513) and wi.shape == (16, 16, 33)
+    assert rel_l2(h.numpy(), d["h"]) < 1e-6
+    assert rel_l2(hk.numpy(), d["hk"]) < 1e-6
+    assert rel_l2(wf.numpy(), d["wf"]) < 1e-6
+    assert rel_l2(wi.numpy(), d["wi"]) < 1e-6
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_oracle_offline_matches_golden(name):
+    meta, a = load_golden(name)
+    cfg = meta["cfg"]
+    o = OracleRAVE(cfg, golden_state_dict(meta))
+    x = torch.from_numpy(golden_input(a))
+    z = o.encode(x)
+    assert rel_l2(z.numpy(), a["z"]) < 2e-5
+    noise = None
+    if cfg.get("noise"):
+        B, _, T = x.shape
+        noise = torch.from_numpy(recipe_input((B, T // 16 // 8, 16, 8), int(a["noise_seed"].item()), uniform=True))
+    y = o.decode(torch.from_numpy(a["z"]), noise)
+    assert y.shape == x.shape                      # reference tests/test_configs.py:68
+    assert rel_l2(y.numpy(), a["y"]) < 5e-5
+
+
+@pytest.mark.parametrize("name", [f for f in FIXTURES if f not in ("v2noise_c8", "v2_c64")])
+def test_oracle_streaming_matches_golden(name):
+    meta, a = load_golden(name)
+    o = OracleRAVE(meta["cfg"], golden_state_dict(meta), streaming=True)
+    x = torch.from_numpy(golden_input(a))
+    n = int(a["chunk"].item())
+    zs, ys = [], []
+    for c in range(x.shape[-1] // n):
+        z = o.encode(x[..., c * n:(c + 1) * n])
+        zs.append(z)
+        ys.append(o.decode(z))
+    assert rel_l2(torch.cat(zs, -1).numpy(), a["z_stream"]) < 2e-5
+    assert rel_l2(torch.cat(ys, -1).numpy(), a["y_stream"]) < 5e-5
+
+
+def test_causal_stream_equals_offline_after_delay():
+    """causal v2 -- encoder stream == offline; decoder stream == offline
+    delayed by 58 sub-band samples = 928 audio samples, past the start-up transient."""
+    meta, a = load_golden("v2causal_c8")
+    zs, ys, z, y = a["z_stream"], a["y_stream"], a["z"], a["y"]
+    assert rel_l2(zs, z) < 1e-5
+    d = 928
+    assert rel_l2(ys[..., 14336:], y[..., 14336 - d:-d]) < 1e-5   # transient: 4e-2 @4096, 1e-4 @12288
+
+
+def test_rvq_oracle_matches_golden_bit_exact():
+    meta, a = load_golden("discrete_c8")
+    o = OracleRAVE(meta["cfg"], golden_state_dict(meta))
+    zq = torch.from_numpy(recipe_input((4, 128, 64), int(a["rvq_z_seed"].item()), scale=1.0))
+    idx = o.rvq_encode(zq)
+    assert idx.dtype == torch.int64 and tuple(idx.shape) == (4, 16, 64)
+    assert np.array_equal(idx.numpy(), a["rvq_idx"])
+    dec = o.rvq_decode(torch.from_numpy(a["rvq_idx"]))
+    assert rel_l2(dec.numpy(), a["rvq_dec"]) < 1e-6
+
+
+# ---------------------------------------------------------------- live reference (container only)
+
+@needs_ref
+@pytest.mark.reference
+@pytest.mark.parametrize("ratio", [2, 4, 8])
+def test_ref_upsample_layer_stream_identity(ratio):
+    """reference tests/test_residual.py:98-122 on the restated cached_conv."""
+    from oracle import cached_conv_restated as cc
+    blocks = R.load("blocks")
+    torch.manual_seed(0)
+    x = torch.randn(1, 16, 32)
+    cc.use_cached_conv(False)
+    reg = blocks.UpsampleLayer(16, 16, ratio)
+    cc.use_cached_conv(True)
+    stream = blocks.UpsampleLayer(16, 16, ratio)
+    cc.use_cached_conv(False)
+    for p1, p2 in zip(reg.parameters(), stream.parameters()):
+        p2.data.copy_(p1.data)
+    delay = stream.cumulative_delay
+    with torch.no_grad():
+        y_r, y_s = reg(x), stream(x)
+    if delay:
+        y_r, y_s = y_r[..., delay:-delay], y_s[..., 2 * delay:]
+    assert torch.allclose(y_r, y_s, 1e-3, 1e-4)
+
+
+@needs_ref
+@pytest.mark.reference
+@pytest.mark.parametrize("k,dil", [(1, [1, 1]), (3, [1, 1]), (1, [3, 1]), (3, [3, 1])])
+def test_ref_residual_layer_stream_identity(k, dil):
+    """reference tests/test_residual.py:71-95."""
+    from oracle import cached_conv_restated as cc
+    blocks = R.load("blocks")
+    torch.manual_seed(0)
+    x = torch.randn(1, 16, 32)
+    cc.use_cached_conv(False)
+    reg = blocks.ResidualLayer(16, k, dil)
+    cc.use_cached_conv(True)
+    stream = blocks.ResidualLayer(16, k, dil)
+    cc.use_cached_conv(False)
+    for p1, p2 in zip(reg.parameters(), stream.parameters()):
+        p2.data.copy_(p1.data)
+    delay = stream.cumulative_delay
+    with torch.no_grad():
+        y_r, y_s = reg(x), stream(x)
+    if delay:
+        y_r, y_s = y_r[..., delay:-delay], y_s[..., 2 * delay:]
+    assert torch.allclose(y_r, y_s, 1e-4, 1e-4)
+
+
+@needs_ref
+@pytest.mark.reference
+def test_ref_residual_stack_stream_identity():
+    """reference tests/test_residual.py:37-68."""
+    from oracle import cached_conv_restated as cc
+    blocks = R.load("blocks")
+    torch.manual_seed(0)
+    x = torch.randn(1, 16, 32)
+    kw = dict(dim=16, kernel_sizes=[3], dilations_list=[[1, 1], [3, 1], [5, 1]])
+    cc.use_cached_conv(False)
+    reg = blocks.ResidualStack(**kw)
+    cc.use_cached_conv(True)
+    stream = blocks.ResidualStack(**kw)
+    cc.use_cached_conv(False)
+    for p1, p2 in zip(reg.parameters(), stream.parameters()):
+        p2.data.copy_(p1.data)
+    delay = stream.cumulative_delay
+    with torch.no_grad():
+        y_r, y_s = reg(x), stream(x)
+    y_r, y_s = y_r[..., delay:-delay], y_s[..., 2 * delay:]
+    assert torch.allclose(y_r, y_s, 1e-4, 1e-4)
+
+
+@needs_ref
+@pytest.mark.reference
+@pytest.mark.parametrize("name", ["v2", "v3", "discrete", "v1"])
+def test_oracle_matches_live_reference(name):
+    cfg = C.NAMED[name](4)
+    m = R.build_reference(cfg)
+    R.fill_deterministic(m, 3)
+    o = OracleRAVE(cfg, {k: v.detach().clone() for k, v in m.state_dict().items()})
+    x = torch.from_numpy(recipe_input((1, 1, 4096), 11))
+    with torch.no_grad():
+        z = m.encode(x)
+        y = m.decode(z)
+    assert rel_l2(o.encode(x).numpy(), z.numpy()) < 2e-5
+    assert rel_l2(o.decode(z).numpy(), y.numpy()) < 5e-5
