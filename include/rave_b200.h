@@ -1,0 +1,164 @@
+/* rave_b200.h -- C-ABI of the B200-native RAVE encode/decode engine.
+ *
+ * Drop-in boundary for the hot path of abargum/RAVE (paths relative to the reference):
+ *   rave/model.py:594-634      RAVE.encode / decode / forward
+ *   rave/pqmf.py:234-284       CachedPQMF.forward / inverse
+ *   rave/blocks.py:508-710     EncoderV2 / GeneratorV2 (and :321-497 v1 Encoder / Generator)
+ *   rave/quantization.py:302-318  ResidualVectorQuantization.encode / decode
+ *   cached_conv (un-vendored)  streaming state of every conv (scripts/export.py:542-594)
+ *
+ * The reference is pure Python, so there is no FFI to match symbol for symbol; the
+ * Python shim rave_b200/model.py is the one caller and mirrors the reference's method
+ * names.  One C call per public method.  Plain pointers and sizes only -- no torch
+ * types.  All functions return 0 on success or a negative rb_status; none throws or
+ * exits; rb_last_error() gives the thread-local message.  All device work is enqueued
+ * on the caller's stream (a cudaStream_t passed as void*); device-pointer entry points
+ * never synchronise.  There is no CPU fallback: every entry point needs a CUDA device.
+ */
+#ifndef RAVE_B200_H
+#define RAVE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RB_ABI_VERSION 1
+
+typedef enum rb_status {
+  RB_OK = 0,
+  RB_ERR_INVALID = -1,     /* bad argument / shape / config  -> ValueError in the shim   */
+  RB_ERR_CUDA = -2,        /* CUDA runtime error             -> RuntimeError in the shim */
+  RB_ERR_STATE = -3,       /* call order (weights missing, streams not allocated, busy)  */
+  RB_ERR_UNSUPPORTED = -4
+} rb_status;
+
+typedef enum rb_dtype { RB_F32 = 0, RB_BF16 = 1 } rb_dtype;
+
+/* Activation applied to a conv's INPUT (the reference always activates before a conv:
+ * blocks.py:94-107, :557, :644, :669).  act(0) == 0 for both, so it commutes with
+ * zero padding. */
+typedef enum rb_act { RB_ACT_NONE = 0, RB_ACT_LEAKY = 1, RB_ACT_SNAKE = 2 } rb_act;
+
+typedef enum rb_op_kind {
+  RB_OP_CONV = 1,        /* cc.Conv1d / cc.ConvTranspose1d (as r phase-convs), fused pre-act,
+                            bias, residual add                                            */
+  RB_OP_PQMF_FWD = 2,    /* CachedPQMF.forward  pqmf.py:269-273                            */
+  RB_OP_PQMF_INV = 3,    /* CachedPQMF.inverse  pqmf.py:275-284                            */
+  RB_OP_AFFINE = 4,      /* AdaIN transfer blocks.py:885-891 as per-(stream,channel) a*x+b */
+  RB_OP_HEAD_V2 = 5,     /* GeneratorV2.forward tail blocks.py:699-707                     */
+  RB_OP_HEAD_V1 = 6,     /* Generator.forward tail blocks.py:412-417                       */
+  RB_OP_NOISE_V2 = 7,    /* NoiseGeneratorV2 tail blocks.py:281-291 (+ core.py:66,95-129)  */
+  RB_OP_CONCAT_COND = 8  /* model.py:618-620: append the constant conditioning channels    */
+} rb_op_kind;
+
+/* A tensor slot: activations [B, channels, frames * per_frame] (time innermost in the
+ * fp32 engine, channels innermost in the bf16 engine).  `hist` = samples of left
+ * context kept across rb_stream_step calls (the cached_conv state), 0 when offline. */
+typedef struct rb_slot {
+  int32_t channels;
+  int32_t per_frame;     /* samples of this tensor per latent frame                       */
+  int32_t hist;
+  int32_t reserved;
+} rb_slot;
+
+typedef struct rb_op {
+  int32_t kind;          /* rb_op_kind                                                     */
+  int32_t src;           /* input slot                                                     */
+  int32_t dst;           /* output slot                                                    */
+  int32_t res;           /* residual slot added to the output, or -1 (blocks.py:44-46)     */
+  int32_t src2;          /* second input (HEAD_V2: noise, HEAD_V1: loudness) or -1          */
+  int32_t c_in, c_out;   /* conv channels (c_out counts phase-stacked channels if ileave>1) */
+  int32_t k, stride, dilation;
+  int32_t off;           /* left offset: out[t] = sum_j W[j] x[t*stride + j*dilation - off] */
+  int32_t ileave;        /* >1: out channel c = ph*(c_out/ileave)+co is stored at
+                            [co][t*ileave+ph] (transposed conv phases)                     */
+  int32_t pre_act;       /* rb_act on the input                                            */
+  int32_t res_delay;     /* streaming: residual read at t - res_delay (AlignBranches)      */
+  int32_t has_bias;
+  int32_t n_band;        /* PQMF ops: number of bands M; PQMF_FWD: c_out = bands kept      */
+  int32_t src_ch_off;    /* first input channel read from src (noise / split heads)        */
+  int32_t reserved[3];
+} rb_op;
+
+typedef struct rb_netspec {
+  int32_t abi_version;   /* RB_ABI_VERSION                                                 */
+  int32_t n_slots;
+  const rb_slot* slots;
+  int32_t n_enc_ops;     /* ops [0, n_enc_ops) = encode program, the rest = decode program */
+  int32_t n_ops;
+  const rb_op* ops;
+  int32_t enc_in_slot, enc_out_slot;   /* audio [B,1,T] -> latent [B,Cz,F]                 */
+  int32_t dec_in_slot, dec_out_slot;   /* latent [B,Cz',F] -> audio [B,1,T]                */
+  int32_t samples_per_frame;           /* total ratio: PQMF bands * prod(ratios)           */
+  int32_t streaming;                   /* cc.use_cached_conv flag at construction          */
+  int32_t cond_channels;               /* speaker (+pitch) channels appended by encode     */
+  int32_t noise_slot;                  /* slot holding injected U(-1,1) noise, or -1       */
+  /* RVQ (discrete config), 0 when absent */
+  int32_t rvq_quantizers, rvq_codebook_size, rvq_dim;
+  int32_t reserved[4];
+} rb_netspec;
+
+/* Parameter roles for rb_load_weights. */
+typedef enum rb_role {
+  RB_W_CONV = 0,      /* folded conv weight, fp32 [c_out][c_in][k] of the op as declared    */
+  RB_W_BIAS = 1,      /* [c_out]                                                            */
+  RB_W_ALPHA = 2,     /* Snake alpha of the op's pre-activation, [c_in]                     */
+  RB_W_AFFINE_A = 3,  /* AFFINE scale  [max_streams][C]                                     */
+  RB_W_AFFINE_B = 4,  /* AFFINE shift  [max_streams][C]                                     */
+  RB_W_COND = 5,      /* conditioning vector [cond_channels] (op = CONCAT_COND)             */
+  RB_W_CODEBOOK = 6   /* RVQ codebooks [Q][codebook_size][dim] (op index ignored)           */
+} rb_role;
+
+typedef struct rb_tensor_desc {
+  int32_t op;          /* index into rb_netspec.ops                                         */
+  int32_t role;        /* rb_role                                                           */
+  const float* data;   /* HOST pointer, fp32, dense                                         */
+  int64_t numel;
+} rb_tensor_desc;
+
+typedef struct rb_handle rb_handle;
+
+int rb_create(const rb_netspec* spec, int device, rb_handle** out);
+int rb_destroy(rb_handle* h);
+int rb_load_weights(rb_handle* h, const rb_tensor_desc* tensors, int n);
+
+/* Offline entry points.  x: [B,1,T], z: [B,Cz,F], y: [B,1,T], device pointers, dense,
+ * dtype = element type of BOTH pointers and the engine that runs (fp32 CUDA-core engine
+ * or bf16 tensor-core engine).  T must be a multiple of samples_per_frame. */
+int rb_encode(rb_handle* h, const void* x, int B, int T, int dtype, void* z, void* stream);
+int rb_decode(rb_handle* h, const void* z, int B, int F, int dtype, void* y, void* stream);
+int rb_forward(rb_handle* h, const void* x, int B, int T, int dtype, void* y, void* stream);
+
+/* Same path with HOST buffers (fp32): host->device copy, forward, device->host copy,
+ * synchronous.  This is what a non-torch caller binds. */
+int rb_forward_host(rb_handle* h, const float* x, int B, int T, int dtype, float* y);
+
+/* Uniform noise U(-1,1) for the noise branch, [B, L/8, n_band, 8] fp32 device pointer
+ * (the reference draws it unseeded, blocks.py:287); NULL = engine-generated (Philox). */
+int rb_set_noise(rb_handle* h, const float* noise, int64_t numel);
+
+/* Discrete boundary (scripts/export.py:503-517). z fp32 [B,D,F]; idx int64 [B,Q,F]. */
+int rb_rvq_encode(rb_handle* h, const float* z, int B, int F, int64_t* idx, void* stream);
+int rb_rvq_decode(rb_handle* h, const int64_t* idx, int B, int F, float* zq, void* stream);
+
+/* Streaming (cached_conv semantics): state row i <-> stream i, zero after alloc/reset. */
+int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype);
+int rb_stream_reset(rb_handle* h, const int32_t* stream_ids, int n);   /* NULL = all */
+int rb_stream_encode(rb_handle* h, const void* x, int B, int n, void* z, void* stream);
+int rb_stream_decode(rb_handle* h, const void* z, int B, int frames, void* y, void* stream);
+int rb_stream_step(rb_handle* h, const void* x, int B, int n, void* y, void* stream);
+int rb_stream_state_elements(rb_handle* h, int64_t* per_stream);
+
+int rb_workspace_bytes(rb_handle* h, int B, int T, int dtype, size_t* bytes);
+int rb_kernel_launches(rb_handle* h, int64_t* count);   /* launches issued so far */
+int rb_set_microbatch(rb_handle* h, int streams);       /* 0 = automatic */
+const char* rb_last_error(void);
+int rb_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RAVE_B200_H */

@@ -1,0 +1,515 @@
+// engine.cu -- C-ABI entry points, weight packing, workspace planning and the op
+// interpreter of the fp32 engine.  Host C++; every device operation goes through the
+// launch_* functions of kernels_f32.cu / rvq.cu / (bf16) tc_engine.cu.
+#include <stdarg.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "engine.h"
+
+namespace rb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+struct BusyGuard {
+  rb_handle* h;
+  bool ok;
+  explicit BusyGuard(rb_handle* h_) : h(h_), ok(!h_->busy.test_and_set()) {}
+  ~BusyGuard() { if (ok) h->busy.clear(); }
+};
+
+static int upload(const float* host, size_t n, float** dev) {
+  if (*dev) { cudaFree(*dev); *dev = nullptr; }
+  RB_CUDA(cudaMalloc((void**)dev, std::max<size_t>(n, 1) * sizeof(float)));
+  RB_CUDA(cudaMemcpy(*dev, host, n * sizeof(float), cudaMemcpyHostToDevice));
+  return RB_OK;
+}
+
+
+// ------------------------------------------------------------------ offline workspace pool
+static int pool_get(rb_handle* h, size_t bytes, int* idx) {
+  int best = -1;
+  for (size_t i = 0; i < h->pool.size(); ++i)
+    if (!h->pool[i].busy && h->pool[i].bytes >= bytes &&
+        (best < 0 || h->pool[i].bytes < h->pool[best].bytes)) best = (int)i;
+  if (best < 0) {
+    // grow the largest free buffer if there is one, else add a new one
+    for (size_t i = 0; i < h->pool.size(); ++i)
+      if (!h->pool[i].busy && (best < 0 || h->pool[i].bytes > h->pool[best].bytes)) best = (int)i;
+    if (best >= 0) {
+      RB_CUDA(cudaFree(h->pool[best].p));
+      h->pool[best].p = nullptr;
+    } else {
+      h->pool.push_back(PoolBuf());
+      best = (int)h->pool.size() - 1;
+    }
+    RB_CUDA(cudaMalloc(&h->pool[best].p, bytes));
+    h->pool[best].bytes = bytes;
+  }
+  h->pool[best].busy = true;
+  *idx = best;
+  return RB_OK;
+}
+
+// ------------------------------------------------------------------------- op interpreter
+int exec_op_f32(RunCtx& c, int oi) {
+  const rb_op& op = c.h->ops[oi];
+  const OpWeights& w = c.h->w[oi];
+  const View& x = c.v[op.src];
+  const View& y = c.v[op.dst];
+  const int lo = c.streaming ? -x.hist : 0;
+  switch (op.kind) {
+    case RB_OP_CONV: {
+      ConvArgs a;
+      a.x = x; a.y = y;
+      a.res = op.res >= 0 ? c.v[op.res] : View();
+      a.w = w.w; a.bias = op.has_bias ? w.bias : nullptr; a.alpha = w.alpha;
+      a.B = c.B; a.c_in = op.c_in; a.c_out = op.c_out; a.k = op.k; a.stride = op.stride;
+      a.dil = op.dilation; a.off = op.off; a.ileave = op.ileave; a.pre_act = op.pre_act;
+      a.res_delay = op.res_delay; a.lo = lo;
+      RB_CHECK(op.pre_act != RB_ACT_SNAKE || w.alpha, RB_ERR_STATE, "op %d: Snake alpha not loaded", oi);
+      return launch_conv_f32(a, c.s);
+    }
+    case RB_OP_PQMF_FWD:
+      return launch_pqmf_fwd_f32(x, y, w.w, c.B, op.c_out, op.n_band, op.k, op.off, lo, c.s);
+    case RB_OP_PQMF_INV:
+      return launch_pqmf_inv_f32(x, y, w.w, c.B, op.n_band, op.k, op.off, lo, c.s);
+    case RB_OP_AFFINE:
+      RB_CHECK(w.aff_a && w.aff_b, RB_ERR_STATE, "op %d: AdaIN statistics not loaded", oi);
+      RB_CHECK(c.B <= w.aff_rows, RB_ERR_INVALID,
+               "batch %d exceeds the %d rows of AdaIN statistics (cc.MAX_BATCH_SIZE)", c.B, w.aff_rows);
+      return launch_affine_f32(x, w.aff_a, w.aff_b, c.B, c.s);
+    case RB_OP_HEAD_V2:
+      return launch_head_v2_f32(x, op.src2 >= 0 ? c.v[op.src2] : View(), y, c.B, op.c_out, op.k, c.s);
+    case RB_OP_HEAD_V1:
+      return launch_head_v1_f32(x, c.v[op.src2], y, c.B, op.c_out, c.s);
+    case RB_OP_NOISE_V2:
+      return launch_noise_v2_f32(x, c.noise, c.noise_bstride, y, c.B, op.c_out,
+                                 c.h->noise_seed++, c.s);
+    case RB_OP_CONCAT_COND:
+      RB_CHECK(w.cond, RB_ERR_STATE, "conditioning vector (speaker embedding) not loaded");
+      return launch_concat_f32(x, y, w.cond, c.B, op.c_in, op.c_out - op.c_in, c.s);
+  }
+  set_error("op %d: unknown kind %d", oi, op.kind);
+  return RB_ERR_INVALID;
+}
+
+// bf16 tensor-core engine (tc_engine.cu)
+int tc_run_program(rb_handle* h, int op_begin, int op_end, const void* in, void* out, int B, int F,
+                   cudaStream_t s);
+int tc_pack_weights(rb_handle* h);
+void tc_free(rb_handle* h);
+
+static size_t slot_bytes_f32(const rb_handle* h, int slot, int B, int F) {
+  const rb_slot& s = h->slots[slot];
+  return (size_t)B * s.channels * round4(s.per_frame * F) * sizeof(float);
+}
+
+// Runs ops [op_begin, op_end) offline on fp32 device buffers. `in` is the program input
+// slot's tensor, `out` the output slot's, both dense [B][C][n].
+static int run_offline_f32(rb_handle* h, int op_begin, int op_end, int in_slot, int out_slot,
+                           const float* in, float* out, int B, int F, cudaStream_t s) {
+  const int ns = (int)h->slots.size();
+  std::vector<int> last_use(ns, -1), buf_of(ns, -1);
+  for (int i = op_begin; i < op_end; ++i) {
+    const rb_op& op = h->ops[i];
+    last_use[op.src] = i;
+    if (op.res >= 0) last_use[op.res] = i;
+    if (op.src2 >= 0) last_use[op.src2] = i;
+    last_use[op.dst] = std::max(last_use[op.dst], i);
+  }
+  // microbatch so that the live activations stay within a budget (and mostly inside L2)
+  int mb = h->microbatch;
+  if (mb <= 0) {
+    size_t per_stream = 0;
+    for (int sl = 0; sl < ns; ++sl) per_stream = std::max(per_stream, slot_bytes_f32(h, sl, 1, F));
+    const size_t budget = (size_t)768 << 20;            // per live buffer
+    mb = (int)std::max<size_t>(1, std::min<size_t>(B, budget / std::max<size_t>(per_stream, 1)));
+  }
+  for (int b0 = 0; b0 < B; b0 += mb) {
+    const int nb = std::min(mb, B - b0);
+    RunCtx c{h, nb, F, std::vector<View>(ns), s, false, nullptr, 0};
+    for (auto& pb : h->pool) pb.busy = false;
+    std::fill(buf_of.begin(), buf_of.end(), -1);
+    auto make_view = [&](int sl, float* p) {
+      View v;
+      v.p = p; v.C = h->slots[sl].channels; v.n = h->slots[sl].per_frame * F;
+      v.ld = v.n; v.hist = 0;
+      return v;
+    };
+    c.v[in_slot] = make_view(in_slot, const_cast<float*>(in) +
+                                          (size_t)b0 * h->slots[in_slot].channels * h->slots[in_slot].per_frame * F);
+    c.v[out_slot] = make_view(out_slot, out + (size_t)b0 * h->slots[out_slot].channels *
+                                                  h->slots[out_slot].per_frame * F);
+    if (h->spec.noise_slot >= 0 && h->noise) {
+      const rb_slot& nsl = h->slots[h->spec.noise_slot];
+      c.noise_bstride = (int64_t)nsl.channels * nsl.per_frame * F;
+      RB_CHECK(h->noise_numel >= (int64_t)B * c.noise_bstride, RB_ERR_INVALID,
+               "noise tensor has %lld elements, need %lld", (long long)h->noise_numel,
+               (long long)B * c.noise_bstride);
+      c.noise = h->noise + (size_t)b0 * c.noise_bstride;
+    }
+    for (int i = op_begin; i < op_end; ++i) {
+      const rb_op& op = h->ops[i];
+      if (!c.v[op.dst].p) {
+        int bi;
+        int rc = pool_get(h, slot_bytes_f32(h, op.dst, nb, F), &bi);
+        if (rc) return rc;
+        buf_of[op.dst] = bi;
+        c.v[op.dst] = make_view(op.dst, (float*)h->pool[bi].p);
+        c.v[op.dst].ld = round4(c.v[op.dst].n);
+      }
+      if (op.src2 >= 0 && op.kind != RB_OP_NOISE_V2)
+        RB_CHECK(c.v[op.src2].p, RB_ERR_STATE, "op %d reads slot %d before it is written", i, op.src2);
+      RB_CHECK(c.v[op.src].p, RB_ERR_STATE, "op %d reads slot %d before it is written", i, op.src);
+      int rc = exec_op_f32(c, i);
+      if (rc) return rc;
+      const int used[3] = {op.src, op.res, op.src2};
+      for (int u : used)
+        if (u >= 0 && last_use[u] == i && buf_of[u] >= 0) {
+          h->pool[buf_of[u]].busy = false;
+          buf_of[u] = -1;
+        }
+    }
+  }
+  return RB_OK;
+}
+
+}  // namespace rb
+
+using namespace rb;
+
+// ================================================================================ C-ABI
+extern "C" {
+
+const char* rb_last_error(void) { return g_err; }
+int rb_abi_version(void) { return RB_ABI_VERSION; }
+
+int rb_create(const rb_netspec* spec, int device, rb_handle** out) {
+  RB_CHECK(spec && out, RB_ERR_INVALID, "rb_create: null argument");
+  RB_CHECK(spec->abi_version == RB_ABI_VERSION, RB_ERR_INVALID, "ABI version %d, library has %d",
+           spec->abi_version, RB_ABI_VERSION);
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  RB_CHECK(e == cudaSuccess && ndev > 0, RB_ERR_CUDA,
+           "no CUDA device: rave_b200 has no CPU fallback (%s)", cudaGetErrorString(e));
+  RB_CHECK(device >= 0 && device < ndev, RB_ERR_INVALID, "device %d out of range", device);
+  RB_CUDA(cudaSetDevice(device));
+  RB_CHECK(spec->n_slots > 0 && spec->n_ops > 0 && spec->n_enc_ops <= spec->n_ops, RB_ERR_INVALID,
+           "empty or inconsistent netspec");
+  rb_handle* h = new rb_handle();
+  h->device = device;
+  h->spec = *spec;
+  h->slots.assign(spec->slots, spec->slots + spec->n_slots);
+  h->ops.assign(spec->ops, spec->ops + spec->n_ops);
+  h->spec.slots = h->slots.data();
+  h->spec.ops = h->ops.data();
+  h->w.resize(h->ops.size());
+  for (size_t i = 0; i < h->ops.size(); ++i) {
+    const rb_op& op = h->ops[i];
+    bool ok = op.src >= 0 && op.src < spec->n_slots && op.dst >= 0 && op.dst < spec->n_slots &&
+              op.res < spec->n_slots && op.src2 < spec->n_slots && op.kind >= RB_OP_CONV &&
+              op.kind <= RB_OP_CONCAT_COND;
+    if (!ok) {
+      delete h;
+      set_error("op %zu is malformed", i);
+      return RB_ERR_INVALID;
+    }
+  }
+  *out = h;
+  return RB_OK;
+}
+
+int rb_destroy(rb_handle* h) {
+  if (!h) return RB_OK;
+  cudaSetDevice(h->device);
+  tc_free(h);
+  for (auto& w : h->w) {
+    cudaFree(w.w); cudaFree(w.bias); cudaFree(w.alpha); cudaFree(w.aff_a); cudaFree(w.aff_b);
+    cudaFree(w.cond);
+  }
+  cudaFree(h->codebooks); cudaFree(h->cb_norms); cudaFree(h->rvq_ws);
+  for (auto& p : h->pool) cudaFree(p.p);
+  for (void* p : h->sbuf) cudaFree(p);
+  if (h->stage_in) cudaFreeHost(h->stage_in);
+  if (h->stage_out) cudaFreeHost(h->stage_out);
+  cudaFree(h->dev_in); cudaFree(h->dev_out);
+  delete h;
+  return RB_OK;
+}
+
+int rb_load_weights(rb_handle* h, const rb_tensor_desc* t, int n) {
+  RB_CHECK(h && (t || n == 0), RB_ERR_INVALID, "rb_load_weights: null argument");
+  RB_CUDA(cudaSetDevice(h->device));
+  for (int i = 0; i < n; ++i) {
+    const rb_tensor_desc& d = t[i];
+    RB_CHECK(d.data && d.numel > 0, RB_ERR_INVALID, "tensor %d is empty", i);
+    if (d.role == RB_W_CODEBOOK) {
+      const int64_t want = (int64_t)h->spec.rvq_quantizers * h->spec.rvq_codebook_size * h->spec.rvq_dim;
+      RB_CHECK(want > 0 && d.numel == want, RB_ERR_INVALID, "codebooks: %lld elements, expected %lld",
+               (long long)d.numel, (long long)want);
+      int rc = upload(d.data, d.numel, &h->codebooks);
+      if (rc) return rc;
+      const int rows = h->spec.rvq_quantizers * h->spec.rvq_codebook_size;
+      cudaFree(h->cb_norms);
+      RB_CUDA(cudaMalloc((void**)&h->cb_norms, rows * sizeof(float)));
+      rc = launch_rvq_norms(h->codebooks, rows, h->spec.rvq_dim, h->cb_norms, 0);
+      if (rc) return rc;
+      RB_CUDA(cudaDeviceSynchronize());
+      continue;
+    }
+    RB_CHECK(d.op >= 0 && d.op < (int)h->ops.size(), RB_ERR_INVALID, "tensor %d: op %d out of range", i, d.op);
+    const rb_op& op = h->ops[d.op];
+    OpWeights& w = h->w[d.op];
+    int rc = RB_OK;
+    switch (d.role) {
+      case RB_W_CONV: {
+        if (op.kind == RB_OP_PQMF_FWD) {
+          // analysis weight [M][1][k] -> [k][8] (bands kept, zero padded)
+          RB_CHECK(d.numel == (int64_t)op.n_band * op.k, RB_ERR_INVALID, "pqmf analysis weight size");
+          std::vector<float> p((size_t)op.k * 8, 0.f);
+          for (int m = 0; m < op.c_out && m < 8; ++m)
+            for (int j = 0; j < op.k; ++j) p[(size_t)j * 8 + m] = d.data[(size_t)m * op.k + j];
+          rc = upload(p.data(), p.size(), &w.w);
+        } else if (op.kind == RB_OP_PQMF_INV) {
+          // synthesis weight [m][c][j] -> [c][j][m]
+          const int M = op.n_band;
+          RB_CHECK(d.numel == (int64_t)M * M * op.k, RB_ERR_INVALID, "pqmf synthesis weight size");
+          std::vector<float> p((size_t)M * M * op.k);
+          for (int m = 0; m < M; ++m)
+            for (int c = 0; c < M; ++c)
+              for (int j = 0; j < op.k; ++j)
+                p[((size_t)c * op.k + j) * M + m] = d.data[((size_t)m * M + c) * op.k + j];
+          rc = upload(p.data(), p.size(), &w.w);
+        } else {
+          RB_CHECK(op.kind == RB_OP_CONV, RB_ERR_INVALID, "op %d takes no conv weight", d.op);
+          RB_CHECK(d.numel == (int64_t)op.c_out * op.c_in * op.k, RB_ERR_INVALID,
+                   "op %d: conv weight has %lld elements, expected %d*%d*%d", d.op, (long long)d.numel,
+                   op.c_out, op.c_in, op.k);
+          std::vector<float> p((size_t)d.numel);
+          for (int co = 0; co < op.c_out; ++co)
+            for (int ci = 0; ci < op.c_in; ++ci)
+              for (int j = 0; j < op.k; ++j)
+                p[((size_t)ci * op.k + j) * op.c_out + co] = d.data[((size_t)co * op.c_in + ci) * op.k + j];
+          rc = upload(p.data(), p.size(), &w.w);
+          w.w_host.assign(d.data, d.data + d.numel);
+        }
+        break;
+      }
+      case RB_W_BIAS:
+        RB_CHECK(d.numel == op.c_out / std::max(op.ileave, 1), RB_ERR_INVALID, "op %d: bias size", d.op);
+        rc = upload(d.data, d.numel, &w.bias);
+        break;
+      case RB_W_ALPHA:
+        RB_CHECK(d.numel == op.c_in, RB_ERR_INVALID, "op %d: alpha size", d.op);
+        rc = upload(d.data, d.numel, &w.alpha);
+        break;
+      case RB_W_AFFINE_A:
+      case RB_W_AFFINE_B: {
+        RB_CHECK(op.kind == RB_OP_AFFINE && d.numel % op.c_in == 0, RB_ERR_INVALID, "op %d: affine size", d.op);
+        w.aff_rows = (int)(d.numel / op.c_in);
+        rc = upload(d.data, d.numel, d.role == RB_W_AFFINE_A ? &w.aff_a : &w.aff_b);
+        break;
+      }
+      case RB_W_COND:
+        RB_CHECK(op.kind == RB_OP_CONCAT_COND && d.numel == op.c_out - op.c_in, RB_ERR_INVALID,
+                 "conditioning vector size");
+        rc = upload(d.data, d.numel, &w.cond);
+        break;
+      default:
+        set_error("tensor %d: unknown role %d", i, d.role);
+        return RB_ERR_INVALID;
+    }
+    if (rc) return rc;
+  }
+  // every op that needs a weight must have one before the model can run
+  bool all = true;
+  for (size_t i = 0; i < h->ops.size(); ++i) {
+    const rb_op& op = h->ops[i];
+    if ((op.kind == RB_OP_CONV || op.kind == RB_OP_PQMF_FWD || op.kind == RB_OP_PQMF_INV) && !h->w[i].w) all = false;
+    if (op.kind == RB_OP_CONV && op.has_bias && !h->w[i].bias) all = false;
+  }
+  h->weights_loaded = all;
+  if (all) {
+    int rc = tc_pack_weights(h);
+    if (rc) return rc;
+  }
+  return RB_OK;
+}
+
+static int check_ready(rb_handle* h) {
+  RB_CHECK(h, RB_ERR_INVALID, "null handle");
+  RB_CHECK(h->weights_loaded, RB_ERR_STATE, "weights are not (fully) loaded");
+  RB_CUDA(cudaSetDevice(h->device));
+  return RB_OK;
+}
+
+static int run_any(rb_handle* h, int ob, int oe, int in_slot, int out_slot, const void* in, void* out,
+                   int B, int F, int dtype, cudaStream_t s) {
+  const long long before = g_launches;
+  int rc;
+  if (dtype == RB_F32)
+    rc = run_offline_f32(h, ob, oe, in_slot, out_slot, (const float*)in, (float*)out, B, F, s);
+  else if (dtype == RB_BF16)
+    rc = tc_run_program(h, ob, oe, in, out, B, F, s);
+  else {
+    set_error("unknown dtype %d", dtype);
+    rc = RB_ERR_INVALID;
+  }
+  h->launches += g_launches - before;
+  return rc;
+}
+
+int rb_encode(rb_handle* h, const void* x, int B, int T, int dtype, void* z, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  RB_CHECK(x && z && B > 0 && T > 0, RB_ERR_INVALID, "rb_encode: bad arguments");
+  RB_CHECK(T % h->spec.samples_per_frame == 0, RB_ERR_INVALID,
+           "T=%d is not a multiple of the model ratio %d", T, h->spec.samples_per_frame);
+  RB_CHECK(!h->spec.streaming, RB_ERR_STATE, "model was built with streaming=True: use rb_stream_*");
+  BusyGuard g(h);
+  RB_CHECK(g.ok, RB_ERR_STATE, "handle is busy on another thread");
+  return run_any(h, 0, h->spec.n_enc_ops, h->spec.enc_in_slot, h->spec.enc_out_slot, x, z, B,
+                 T / h->spec.samples_per_frame, dtype, (cudaStream_t)stream);
+}
+
+int rb_decode(rb_handle* h, const void* z, int B, int F, int dtype, void* y, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  RB_CHECK(z && y && B > 0 && F > 0, RB_ERR_INVALID, "rb_decode: bad arguments");
+  RB_CHECK(!h->spec.streaming, RB_ERR_STATE, "model was built with streaming=True: use rb_stream_*");
+  BusyGuard g(h);
+  RB_CHECK(g.ok, RB_ERR_STATE, "handle is busy on another thread");
+  return run_any(h, h->spec.n_enc_ops, h->spec.n_ops, h->spec.dec_in_slot, h->spec.dec_out_slot, z, y, B,
+                 F, dtype, (cudaStream_t)stream);
+}
+
+int rb_forward(rb_handle* h, const void* x, int B, int T, int dtype, void* y, void* stream) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  RB_CHECK(x && y && B > 0 && T > 0, RB_ERR_INVALID, "rb_forward: bad arguments");
+  RB_CHECK(T % h->spec.samples_per_frame == 0, RB_ERR_INVALID,
+           "T=%d is not a multiple of the model ratio %d", T, h->spec.samples_per_frame);
+  RB_CHECK(!h->spec.streaming, RB_ERR_STATE, "model was built with streaming=True: use rb_stream_*");
+  const rb_slot& zo = h->slots[h->spec.enc_out_slot];
+  const rb_slot& zi = h->slots[h->spec.dec_in_slot];
+  RB_CHECK(zo.channels == zi.channels, RB_ERR_INVALID,
+           "encode yields %d channels but the decoder takes %d (model.py:620 vs core.py:78)",
+           zo.channels, zi.channels);
+  BusyGuard g(h);
+  RB_CHECK(g.ok, RB_ERR_STATE, "handle is busy on another thread");
+  const int F = T / h->spec.samples_per_frame;
+  const size_t esz = dtype == RB_BF16 ? 2 : 4;
+  // latent scratch lives in a dedicated buffer (small)
+  const size_t zbytes = (size_t)B * zo.channels * ((F + 3) & ~3) * esz;
+  if (h->rvq_ws_bytes < zbytes) {
+    cudaFree(h->rvq_ws);
+    h->rvq_ws = nullptr;
+    RB_CUDA(cudaMalloc((void**)&h->rvq_ws, zbytes));
+    h->rvq_ws_bytes = zbytes;
+  }
+  rc = run_any(h, 0, h->spec.n_enc_ops, h->spec.enc_in_slot, h->spec.enc_out_slot, x, h->rvq_ws, B, F,
+               dtype, (cudaStream_t)stream);
+  if (rc) return rc;
+  return run_any(h, h->spec.n_enc_ops, h->spec.n_ops, h->spec.dec_in_slot, h->spec.dec_out_slot,
+                 h->rvq_ws, y, B, F, dtype, (cudaStream_t)stream);
+}
+
+int rb_forward_host(rb_handle* h, const float* x, int B, int T, int dtype, float* y) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  RB_CHECK(x && y && B > 0 && T > 0, RB_ERR_INVALID, "rb_forward_host: bad arguments");
+  const size_t n = (size_t)B * T;
+  if (h->stage_elems < n) {
+    if (h->stage_in) cudaFreeHost(h->stage_in);
+    if (h->stage_out) cudaFreeHost(h->stage_out);
+    cudaFree(h->dev_in); cudaFree(h->dev_out);
+    h->stage_in = h->stage_out = nullptr; h->dev_in = h->dev_out = nullptr; h->stage_elems = 0;
+    RB_CUDA(cudaMallocHost((void**)&h->stage_in, n * sizeof(float)));
+    RB_CUDA(cudaMallocHost((void**)&h->stage_out, n * sizeof(float)));
+    RB_CUDA(cudaMalloc(&h->dev_in, n * sizeof(float)));
+    RB_CUDA(cudaMalloc(&h->dev_out, n * sizeof(float)));
+    h->stage_elems = n;
+  }
+  RB_CHECK(dtype == RB_F32, RB_ERR_UNSUPPORTED, "rb_forward_host takes fp32 host buffers; for the bf16 "
+           "engine convert on the device (rave_b200.RAVE does)");
+  memcpy(h->stage_in, x, n * sizeof(float));
+  RB_CUDA(cudaMemcpyAsync(h->dev_in, h->stage_in, n * sizeof(float), cudaMemcpyHostToDevice, 0));
+  rc = rb_forward(h, h->dev_in, B, T, dtype, h->dev_out, nullptr);
+  if (rc) return rc;
+  RB_CUDA(cudaMemcpyAsync(h->stage_out, h->dev_out, n * sizeof(float), cudaMemcpyDeviceToHost, 0));
+  RB_CUDA(cudaStreamSynchronize(0));
+  memcpy(y, h->stage_out, n * sizeof(float));
+  return RB_OK;
+}
+
+int rb_set_noise(rb_handle* h, const float* noise, int64_t numel) {
+  RB_CHECK(h, RB_ERR_INVALID, "null handle");
+  h->noise = noise;
+  h->noise_numel = noise ? numel : 0;
+  return RB_OK;
+}
+
+int rb_set_microbatch(rb_handle* h, int streams) {
+  RB_CHECK(h && streams >= 0, RB_ERR_INVALID, "rb_set_microbatch: bad arguments");
+  h->microbatch = streams;
+  return RB_OK;
+}
+
+int rb_kernel_launches(rb_handle* h, int64_t* count) {
+  RB_CHECK(h && count, RB_ERR_INVALID, "null argument");
+  *count = h->launches;
+  return RB_OK;
+}
+
+int rb_workspace_bytes(rb_handle* h, int B, int T, int dtype, size_t* bytes) {
+  RB_CHECK(h && bytes && B > 0 && T > 0, RB_ERR_INVALID, "rb_workspace_bytes: bad arguments");
+  RB_CHECK(T % h->spec.samples_per_frame == 0, RB_ERR_INVALID, "T is not a multiple of the model ratio");
+  const int F = T / h->spec.samples_per_frame;
+  size_t mx = 0;
+  for (size_t s = 0; s < h->slots.size(); ++s) mx = std::max(mx, slot_bytes_f32(h, (int)s, 1, F));
+  if (dtype == RB_BF16) mx /= 2;
+  // at most four activations are live at once (x, conv3 out, residual, dst)
+  *bytes = 4 * mx * (size_t)std::min(B, std::max(1, h->microbatch > 0 ? h->microbatch : B));
+  return RB_OK;
+}
+
+// ------------------------------------------------------------------------------ RVQ
+int rb_rvq_encode(rb_handle* h, const float* z, int B, int F, int64_t* idx, void* stream) {
+  RB_CHECK(h && z && idx && B > 0 && F > 0, RB_ERR_INVALID, "rb_rvq_encode: bad arguments");
+  RB_CHECK(h->codebooks, RB_ERR_STATE, "RVQ codebooks are not loaded (not a discrete model?)");
+  RB_CUDA(cudaSetDevice(h->device));
+  const size_t need = (size_t)B * F * h->spec.rvq_dim * sizeof(float);
+  if (h->rvq_ws_bytes < need) {
+    cudaFree(h->rvq_ws);
+    h->rvq_ws = nullptr;
+    RB_CUDA(cudaMalloc((void**)&h->rvq_ws, need));
+    h->rvq_ws_bytes = need;
+  }
+  const long long before = g_launches;
+  int rc = launch_rvq_encode(z, B, h->spec.rvq_dim, F, h->codebooks, h->cb_norms, h->spec.rvq_quantizers,
+                             h->spec.rvq_codebook_size, idx, h->rvq_ws, (cudaStream_t)stream);
+  h->launches += g_launches - before;
+  return rc;
+}
+
+int rb_rvq_decode(rb_handle* h, const int64_t* idx, int B, int F, float* zq, void* stream) {
+  RB_CHECK(h && zq && idx && B > 0 && F > 0, RB_ERR_INVALID, "rb_rvq_decode: bad arguments");
+  RB_CHECK(h->codebooks, RB_ERR_STATE, "RVQ codebooks are not loaded (not a discrete model?)");
+  RB_CUDA(cudaSetDevice(h->device));
+  const long long before = g_launches;
+  int rc = launch_rvq_decode(idx, B, h->spec.rvq_dim, F, h->codebooks, h->spec.rvq_quantizers,
+                             h->spec.rvq_codebook_size, zq, (cudaStream_t)stream);
+  h->launches += g_launches - before;
+  return rc;
+}
+
+}  // extern "C"

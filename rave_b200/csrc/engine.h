@@ -1,0 +1,85 @@
+// engine.h -- host-side state of one rb_handle (not part of the C-ABI).
+#pragma once
+#include <atomic>
+#include <map>
+#include <vector>
+
+#include "common.cuh"
+
+struct rb_handle;
+
+namespace rb {
+
+static inline int round4(int v) { return (v + 3) & ~3; }
+
+struct RunCtx {
+  rb_handle* h;
+  int B, F;                      // streams in this (micro)batch, latent frames
+  std::vector<View> v;           // per slot
+  cudaStream_t s;
+  bool streaming;
+  const float* noise;            // for this microbatch
+  int64_t noise_bstride;
+};
+
+int exec_op_f32(RunCtx& c, int oi);
+
+struct OpWeights {
+  float* w = nullptr;       // fp32 engine packing ([c_in][k][c_out]; PQMF: see engine.cu)
+  float* bias = nullptr;
+  float* alpha = nullptr;
+  float* aff_a = nullptr;   // [rows][C]
+  float* aff_b = nullptr;
+  int aff_rows = 0;
+  float* cond = nullptr;
+  // bf16 tensor-core engine packing (tc_engine.cu)
+  void* w_tc = nullptr;
+  int tc_kpad = 0;
+  std::vector<float> w_host;   // folded fp32 [c_out][c_in][k] kept for the bf16 packer
+};
+
+struct PoolBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+  bool busy = false;
+};
+
+}  // namespace rb
+
+struct rb_handle {
+  int device = 0;
+  rb_netspec spec{};
+  std::vector<rb_slot> slots;
+  std::vector<rb_op> ops;
+  std::vector<rb::OpWeights> w;
+  bool weights_loaded = false;
+
+  float* codebooks = nullptr;   // [Q][K][D]
+  float* cb_norms = nullptr;    // [Q][K]
+  float* rvq_ws = nullptr;
+  size_t rvq_ws_bytes = 0;
+
+  const float* noise = nullptr;  // user noise, device
+  int64_t noise_numel = 0;
+  unsigned long long noise_seed = 0x1234;
+
+  std::vector<rb::PoolBuf> pool;  // offline activation workspace
+  int microbatch = 0;
+
+  // streaming state arena: one persistent buffer per slot
+  bool stream_ready = false;
+  int stream_dtype = RB_F32;
+  int max_streams = 0, max_frames = 0;
+  std::vector<void*> sbuf;
+  std::vector<int> s_ld, s_hist;
+
+  // pinned staging for rb_forward_host
+  float* stage_in = nullptr;
+  float* stage_out = nullptr;
+  void* dev_in = nullptr;
+  void* dev_out = nullptr;
+  size_t stage_elems = 0;
+
+  std::atomic_flag busy = ATOMIC_FLAG_INIT;
+  long long launches = 0;
+};

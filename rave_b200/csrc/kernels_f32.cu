@@ -1,0 +1,477 @@
+// kernels_f32.cu -- fp32 CUDA-core engine: the exact-parity path (rel-L2 <= 1e-3 gate).
+//
+// Activations are [B][C][ld] fp32, time innermost (the reference's own layout), so the
+// dilated / strided taps of cc.Conv1d are shifted coalesced reads.  Every kernel fuses
+// what the reference runs as separate launches around a conv: the pre-activation
+// (LeakyReLU(0.2) blocks.py:91 / Snake :845-853), F.pad zero padding (cached_conv Conv1d),
+// bias, the Residual add (blocks.py:44-46) and the transposed-conv phase interleave.
+#include "common.cuh"
+
+namespace rb {
+
+thread_local long long g_launches = 0;
+
+__device__ __forceinline__ float act_apply(float v, int kind, float alpha) {
+  if (kind == RB_ACT_LEAKY) return v > 0.f ? v : 0.2f * v;
+  if (kind == RB_ACT_SNAKE) {
+    float s = sinf(alpha * v);
+    return v + (1.0f / (alpha + 1e-9f)) * (s * s);
+  }
+  return v;
+}
+
+// ---------------------------------------------------------------------------------- conv
+// Output tile: 64 output channels x 128 output times per CTA, 256 threads, each thread
+// 4 channels x 8 times (times strided by 16 so a warp reads consecutive smem words).
+constexpr int CONV_TC = 64;
+constexpr int CONV_TT = 128;
+
+__global__ void __launch_bounds__(256)
+conv1d_f32_kernel(ConvArgs a, int ci_chunk, int span, int span_pad) {
+  extern __shared__ float smem[];
+  float* xs = smem;                                   // [ci_chunk][span_pad]
+  float* ws = smem + (size_t)ci_chunk * span_pad;     // [ci_chunk][k][64]
+  const int b = blockIdx.z;
+  const int co0 = blockIdx.y * CONV_TC;
+  const int t0 = blockIdx.x * CONV_TT;
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int T_in = a.x.n, T_out = a.y.n / a.ileave;
+  const float* xb = a.x.p + (size_t)b * a.x.C * a.x.ld + a.x.hist;
+  float acc[4][8];
+#pragma unroll
+  for (int c = 0; c < 4; ++c)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[c][i] = 0.f;
+
+  const int in0 = t0 * a.stride - a.off;
+  for (int ci0 = 0; ci0 < a.c_in; ci0 += ci_chunk) {
+    const int nci = min(ci_chunk, a.c_in - ci0);
+    for (int idx = tid; idx < nci * span; idx += 256) {
+      int ci = idx / span, u = idx - ci * span;
+      int ti = in0 + u;
+      float v = 0.f;
+      if (ti >= a.lo && ti < T_in) {
+        v = __ldg(xb + (size_t)(ci0 + ci) * a.x.ld + ti);
+        v = act_apply(v, a.pre_act, a.alpha ? __ldg(a.alpha + ci0 + ci) : 1.f);
+      }
+      xs[ci * span_pad + u] = v;
+    }
+    const int wn = nci * a.k * CONV_TC;
+    for (int idx = tid; idx < wn; idx += 256) {
+      int co = idx & (CONV_TC - 1);
+      int cj = idx >> 6;                               // ci*k + j
+      float v = 0.f;
+      if (co0 + co < a.c_out) v = __ldg(a.w + ((size_t)ci0 * a.k + cj) * a.c_out + co0 + co);
+      ws[idx] = v;
+    }
+    __syncthreads();
+    for (int ci = 0; ci < nci; ++ci) {
+      const float* xr = xs + ci * span_pad + tx * a.stride;
+      const float* wr = ws + (size_t)ci * a.k * CONV_TC + ty * 4;
+      for (int j = 0; j < a.k; ++j) {
+        const float4 wv = *reinterpret_cast<const float4*>(wr + j * CONV_TC);
+        const float* xj = xr + j * a.dil;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float xv = xj[i * 16 * a.stride];
+          acc[0][i] = fmaf(wv.x, xv, acc[0][i]);
+          acc[1][i] = fmaf(wv.y, xv, acc[1][i]);
+          acc[2][i] = fmaf(wv.z, xv, acc[2][i]);
+          acc[3][i] = fmaf(wv.w, xv, acc[3][i]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  const int cpp = a.c_out / a.ileave;                  // channels per phase
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int co = co0 + ty * 4 + c;
+    if (co >= a.c_out) continue;
+    const float bv = a.bias ? __ldg(a.bias + (a.ileave > 1 ? co % cpp : co)) : 0.f;
+    int ch = co, ph = 0;
+    if (a.ileave > 1) { ph = co / cpp; ch = co - ph * cpp; }
+    float* yb = a.y.p + ((size_t)b * a.y.C + ch) * a.y.ld + a.y.hist;
+    const float* rb_ = a.res.p ? a.res.p + ((size_t)b * a.res.C + co) * a.res.ld + a.res.hist - a.res_delay
+                               : nullptr;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int t = t0 + tx + 16 * i;
+      if (t >= T_out) continue;
+      float v = acc[c][i] + bv;
+      if (rb_) v += rb_[t];
+      yb[t * a.ileave + ph] = v;
+    }
+  }
+}
+
+int launch_conv_f32(const ConvArgs& a, cudaStream_t s) {
+  const int T_out = a.y.n / a.ileave;
+  if (T_out <= 0 || a.B <= 0) return RB_OK;
+  int ci_chunk = 32 / a.k;
+  if (ci_chunk < 4) ci_chunk = 4;
+  if (ci_chunk > 32) ci_chunk = 32;
+  if (ci_chunk > a.c_in) ci_chunk = a.c_in;
+  const int span = (CONV_TT - 1) * a.stride + (a.k - 1) * a.dil + 1;
+  const int span_pad = span | 1;
+  size_t smem = ((size_t)ci_chunk * span_pad + (size_t)ci_chunk * a.k * CONV_TC) * sizeof(float);
+  RB_CHECK(smem <= 200 * 1024, RB_ERR_UNSUPPORTED, "conv tile needs %zu B of shared memory", smem);
+  static bool attr_set = false;
+  if (!attr_set) {
+    RB_CUDA(cudaFuncSetAttribute(conv1d_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 200 * 1024));
+    attr_set = true;
+  }
+  dim3 grid((T_out + CONV_TT - 1) / CONV_TT, (a.c_out + CONV_TC - 1) / CONV_TC, a.B);
+  conv1d_f32_kernel<<<grid, 256, smem, s>>>(a, ci_chunk, span, span_pad);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// --------------------------------------------------------------------------- PQMF analysis
+// CachedPQMF.forward (pqmf.py:269-273): Conv1d(1 -> M, k, stride M) + reverse_half, of which
+// RAVE.encode keeps bands [0, n_keep) (model.py:613).  Polyphase form: the input window is
+// stored phase-major in smem so that lane t reads xs[p][t+q] (conflict-free), and each
+// thread produces all kept bands of one output time (x reused n_keep times from a register).
+constexpr int PQ_TT = 128;
+
+__global__ void __launch_bounds__(PQ_TT)
+pqmf_fwd_f32_kernel(View x, View y, const float* __restrict__ w, int n_keep, int M, int k, int off,
+                    int lo) {
+  extern __shared__ float smem[];
+  const int Q = (k + M - 1) / M;                       // taps per phase (33 for k=513, M=16)
+  const int pitch = PQ_TT + Q + 1;
+  float* xs = smem;                                    // [M][pitch]
+  float* ws = smem + M * pitch;                        // [Q*M][8]  (j = q*M + p)
+  const int b = blockIdx.y, t0 = blockIdx.x * PQ_TT, tid = threadIdx.x;
+  const float* xb = x.p + (size_t)b * x.C * x.ld + x.hist;
+  const int in0 = t0 * M - off;
+  const int nwin = (PQ_TT + Q) * M;
+  for (int idx = tid; idx < nwin; idx += PQ_TT) {
+    int ti = in0 + idx;
+    float v = (ti >= lo && ti < x.n) ? __ldg(xb + ti) : 0.f;
+    xs[(idx % M) * pitch + idx / M] = v;
+  }
+  for (int idx = tid; idx < Q * M * 8; idx += PQ_TT) ws[idx] = (idx >> 3) < k ? __ldg(w + idx) : 0.f;
+  __syncthreads();
+  float acc[8];
+#pragma unroll
+  for (int m = 0; m < 8; ++m) acc[m] = 0.f;
+  for (int q = 0; q < Q; ++q) {
+    for (int p = 0; p < M; ++p) {
+      const float xv = xs[p * pitch + tid + q];
+      const float4 w0 = *reinterpret_cast<const float4*>(ws + (q * M + p) * 8);
+      const float4 w1 = *reinterpret_cast<const float4*>(ws + (q * M + p) * 8 + 4);
+      acc[0] = fmaf(w0.x, xv, acc[0]); acc[1] = fmaf(w0.y, xv, acc[1]);
+      acc[2] = fmaf(w0.z, xv, acc[2]); acc[3] = fmaf(w0.w, xv, acc[3]);
+      acc[4] = fmaf(w1.x, xv, acc[4]); acc[5] = fmaf(w1.y, xv, acc[5]);
+      acc[6] = fmaf(w1.z, xv, acc[6]); acc[7] = fmaf(w1.w, xv, acc[7]);
+    }
+  }
+  const int t = t0 + tid;
+  if (t < y.n) {
+#pragma unroll
+    for (int m = 0; m < 8; ++m) {
+      if (m < n_keep) {
+        float v = acc[m];
+        if ((m & 1) && !(t & 1)) v = -v;               // reverse_half, pqmf.py:13-17
+        y.p[((size_t)b * y.C + m) * y.ld + y.hist + t] = v;
+      }
+    }
+  }
+}
+
+// Bands beyond 8 (all 16 bands, used when a caller wants the full analysis) go through
+// n_keep <= 8 per launch with a band offset folded into `w` and `y` by the caller.
+int launch_pqmf_fwd_f32(const View& x, const View& y, const float* w, int B, int n_keep, int n_band,
+                        int k, int off, int lo, cudaStream_t s) {
+  if (y.n <= 0 || B <= 0) return RB_OK;
+  RB_CHECK(n_keep <= 8, RB_ERR_UNSUPPORTED, "pqmf analysis keeps at most 8 bands per launch");
+  const int Q = (k + n_band - 1) / n_band;
+  size_t smem = ((size_t)n_band * (PQ_TT + Q + 1) + (size_t)Q * n_band * 8) * sizeof(float);
+  dim3 grid((y.n + PQ_TT - 1) / PQ_TT, B);
+  pqmf_fwd_f32_kernel<<<grid, PQ_TT, smem, s>>>(x, y, w, n_keep, n_band, k, off, lo);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// -------------------------------------------------------------------------- PQMF synthesis
+// CachedPQMF.inverse (pqmf.py:275-284): reverse_half, Conv1d(M -> M, k), *M, channel flip and
+// time interleave, fused: out[t*M + (M-1-m)] = M * sum_c sum_j w[m][c][j] xr[c][t + j - off].
+// M = 16 only (the kernel maps 4 threads x 4 bands onto each output time).
+constexpr int PI_TT = 64;
+
+__global__ void __launch_bounds__(256)
+pqmf_inv_f32_kernel(View x, View y, const float* __restrict__ w, int k, int off, int lo) {
+  extern __shared__ float smem[];
+  constexpr int M = 16;
+  const int pitch = PI_TT + k;                          // window = PI_TT + k - 1
+  float* xs = smem;                                     // [16][pitch]
+  float* ws = smem + M * pitch;                         // [c][j][m]
+  const int b = blockIdx.y, t0 = blockIdx.x * PI_TT, tid = threadIdx.x;
+  const int win = PI_TT + k - 1;
+  for (int idx = tid; idx < M * win; idx += 256) {
+    int c = idx / win, u = idx - c * win;
+    int ti = t0 - off + u;
+    float v = 0.f;
+    if (ti >= lo && ti < x.n) {
+      v = __ldg(x.p + ((size_t)b * x.C + c) * x.ld + x.hist + ti);
+      // reverse_half on absolute sub-band time: in streaming the chunk start is even
+      // (chunks are multiples of the total ratio), so parity of ti is the absolute parity.
+      if ((c & 1) && !(ti & 1)) v = -v;
+    }
+    xs[c * pitch + u] = v;
+  }
+  for (int idx = tid; idx < M * k * M; idx += 256) ws[idx] = __ldg(w + idx);
+  __syncthreads();
+  const int tl = tid & (PI_TT - 1), g = tid >> 6;       // 4 band groups of 4
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int c = 0; c < M; ++c) {
+    const float* xr = xs + c * pitch + tl;
+    const float* wr = ws + (size_t)c * k * M + g * 4;
+    for (int j = 0; j < k; ++j) {
+      const float xv = xr[j];
+      const float4 wv = *reinterpret_cast<const float4*>(wr + j * M);
+      acc[0] = fmaf(wv.x, xv, acc[0]); acc[1] = fmaf(wv.y, xv, acc[1]);
+      acc[2] = fmaf(wv.z, xv, acc[2]); acc[3] = fmaf(wv.w, xv, acc[3]);
+    }
+  }
+  const int t = t0 + tl;
+  if (t < x.n) {
+    // bands m = 4g..4g+3 land at output phases 15-4g .. 12-4g (descending): one float4
+    float4 o = make_float4(acc[3] * M, acc[2] * M, acc[1] * M, acc[0] * M);
+    float* yp = y.p + (size_t)b * y.C * y.ld + y.hist + (size_t)t * M + (12 - 4 * g);
+    *reinterpret_cast<float4*>(yp) = o;
+  }
+}
+
+int launch_pqmf_inv_f32(const View& x, const View& y, const float* w, int B, int n_band, int k, int off,
+                        int lo, cudaStream_t s) {
+  if (x.n <= 0 || B <= 0) return RB_OK;
+  RB_CHECK(n_band == 16, RB_ERR_UNSUPPORTED, "pqmf synthesis kernel is specialised to 16 bands");
+  RB_CHECK(((size_t)y.p % 16) == 0 && (y.ld % 4) == 0 && (y.hist % 4) == 0, RB_ERR_INVALID,
+           "pqmf synthesis output must be 16-byte aligned");
+  size_t smem = ((size_t)16 * (PI_TT + k) + (size_t)16 * k * 16) * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    RB_CUDA(cudaFuncSetAttribute(pqmf_inv_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 100 * 1024));
+    attr_set = true;
+  }
+  dim3 grid((x.n + PI_TT - 1) / PI_TT, B);
+  pqmf_inv_f32_kernel<<<grid, 256, smem, s>>>(x, y, w, k, off, lo);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// ------------------------------------------------------------------------- small fused ops
+__global__ void affine_f32_kernel(View x, const float* __restrict__ a, const float* __restrict__ bb) {
+  const int row = blockIdx.y;                            // b*C + c
+  float* p = x.p + (size_t)row * x.ld + x.hist;
+  const float av = a[row], bv = bb[row];
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < x.n; t += gridDim.x * blockDim.x)
+    p[t] = fmaf(p[t], av, bv);
+}
+
+int launch_affine_f32(const View& x, const float* a, const float* b, int B, cudaStream_t s) {
+  if (x.n <= 0 || B <= 0) return RB_OK;
+  dim3 grid(min((x.n + 255) / 256, 64), B * x.C);
+  affine_f32_kernel<<<grid, 256, 0, s>>>(x, a, b);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// GeneratorV2.forward tail (blocks.py:699-707): x, amp = split; tanh(x*sigmoid(amp) + noise)
+__global__ void head_v2_f32_kernel(View w, View nz, View y, int data, int am) {
+  const int b = blockIdx.z, c = blockIdx.y;
+  const float* xp = w.p + ((size_t)b * w.C + c) * w.ld + w.hist;
+  const float* ap = xp + (size_t)data * w.ld;
+  const float* np_ = nz.p ? nz.p + ((size_t)b * nz.C + c) * nz.ld + nz.hist : nullptr;
+  float* yp = y.p + ((size_t)b * y.C + c) * y.ld + y.hist;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < y.n; t += gridDim.x * blockDim.x) {
+    float v = xp[t];
+    if (am) v = v * (1.f / (1.f + expf(-ap[t])));
+    if (np_) v += np_[t];
+    yp[t] = tanhf(v);
+  }
+}
+
+int launch_head_v2_f32(const View& w, const View& noise, const View& y, int B, int data, int am,
+                       cudaStream_t s) {
+  if (y.n <= 0 || B <= 0) return RB_OK;
+  dim3 grid(min((y.n + 255) / 256, 64), data, B);
+  head_v2_f32_kernel<<<grid, 256, 0, s>>>(w, noise, y, data, am);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// Generator.forward tail (blocks.py:412): tanh(waveform) * mod_sigmoid(loudness), core.py:66-67
+__global__ void head_v1_f32_kernel(View wv, View ld, View y) {
+  const int b = blockIdx.z, c = blockIdx.y;
+  const float* xp = wv.p + ((size_t)b * wv.C + c) * wv.ld + wv.hist;
+  const float* lp = ld.p + (size_t)b * ld.C * ld.ld + ld.hist;
+  float* yp = y.p + ((size_t)b * y.C + c) * y.ld + y.hist;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < y.n; t += gridDim.x * blockDim.x) {
+    float sg = 1.f / (1.f + expf(-lp[t]));
+    yp[t] = tanhf(xp[t]) * (2.f * powf(sg, 2.3f) + 1e-7f);
+  }
+}
+
+int launch_head_v1_f32(const View& wave, const View& loud, const View& y, int B, int data, cudaStream_t s) {
+  if (y.n <= 0 || B <= 0) return RB_OK;
+  dim3 grid(min((y.n + 255) / 256, 64), data, B);
+  head_v1_f32_kernel<<<grid, 256, 0, s>>>(wave, loud, y);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// NoiseGeneratorV2.forward tail (blocks.py:281-291) with amp_to_impulse_response and
+// fft_convolve (core.py:95-129) in closed form: 5 real bins -> 8-tap IR (irfft as a cosine
+// sum), centred, Hann-windowed, and a causal 8-tap FIR inside each block of 8 samples.
+// One thread per (stream, block q, band d).  noise: [B][L/8][data][8] U(-1,1) or nullptr
+// (then a counter-based hash generator is used; parity tests always inject).
+__device__ __forceinline__ float hash_uniform(unsigned long long seed, unsigned long long i) {
+  unsigned long long z = seed + i * 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(z >> 40) * (2.0f / 16777216.0f) - 1.0f;
+}
+
+__global__ void noise_v2_f32_kernel(View amp, const float* __restrict__ noise, long long nbs, View y,
+                                    int data, int nblk, unsigned long long seed) {
+  const int b = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;   // q*data + d
+  if (i >= nblk * data) return;
+  const int q = i / data, d = i - q * data;
+  float a[5];
+#pragma unroll
+  for (int n = 0; n < 5; ++n) {
+    float h = amp.p[((size_t)b * amp.C + d * 5 + n) * amp.ld + amp.hist + q] - 5.f;
+    float sg = 1.f / (1.f + expf(-h));
+    a[n] = 2.f * powf(sg, 2.3f) + 1e-7f;                  // mod_sigmoid
+  }
+  float ir[8];
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    // irfft(5 bins)[u] at u = (t + 4) mod 8 after roll(+4), window, roll(-4):
+    // final[t] = hann[(t+4)%8] * irfft[t]   (the two rolls cancel on the index of irfft)
+    const float c1 = cospif(t * 0.25f), c2 = cospif(t * 0.5f), c3 = cospif(t * 0.75f);
+    const float c4 = (t & 1) ? -1.f : 1.f;
+    float v = (a[0] + 2.f * (a[1] * c1 + a[2] * c2 + a[3] * c3) + a[4] * c4) * 0.125f;
+    const int u = (t + 4) & 7;
+    const float hann = 0.5f * (1.f - cospif(u * 0.25f));
+    ir[t] = v * hann;
+  }
+  float nz[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    nz[j] = noise ? noise[(size_t)b * nbs + ((size_t)q * data + d) * 8 + j]
+                  : hash_uniform(seed, ((unsigned long long)b * nblk + q) * data * 8 + d * 8 + j);
+  float* yp = y.p + ((size_t)b * y.C + d) * y.ld + y.hist + (size_t)q * 8;
+#pragma unroll
+  for (int t = 0; t < 8; ++t) {
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j <= t; ++j) s = fmaf(nz[j], ir[t - j], s);
+    yp[t] = s;
+  }
+}
+
+int launch_noise_v2_f32(const View& amp, const float* noise, int64_t nbs, const View& y, int B, int data,
+                        unsigned long long seed, cudaStream_t s) {
+  const int nblk = amp.n;
+  if (nblk <= 0 || B <= 0) return RB_OK;
+  dim3 grid((nblk * data + 127) / 128, B);
+  noise_v2_f32_kernel<<<grid, 128, 0, s>>>(amp, noise, nbs, y, data, nblk, seed);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// model.py:618-620: z = cat(z, speaker.repeat(B, 1, F))
+__global__ void concat_f32_kernel(View z, View y, const float* __restrict__ cond, int c_z) {
+  const int b = blockIdx.z, c = blockIdx.y;
+  float* yp = y.p + ((size_t)b * y.C + c) * y.ld + y.hist;
+  const float* zp = c < c_z ? z.p + ((size_t)b * z.C + c) * z.ld + z.hist : nullptr;
+  const float cv = c < c_z ? 0.f : cond[c - c_z];
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < y.n; t += gridDim.x * blockDim.x)
+    yp[t] = zp ? zp[t] : cv;
+}
+
+int launch_concat_f32(const View& z, const View& y, const float* cond, int B, int c_z, int c_cond,
+                      cudaStream_t s) {
+  if (y.n <= 0 || B <= 0) return RB_OK;
+  dim3 grid(min((y.n + 127) / 128, 64), c_z + c_cond, B);
+  concat_f32_kernel<<<grid, 128, 0, s>>>(z, y, cond, c_z);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+__global__ void copy_rows_f32_kernel(const float* __restrict__ src, int src_ld, float* __restrict__ dst,
+                                     int dst_ld, int n) {
+  const int r = blockIdx.y;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x)
+    dst[(size_t)r * dst_ld + t] = src[(size_t)r * src_ld + t];
+}
+
+int launch_copy_rows_f32(const float* src, int src_ld, float* dst, int dst_ld, int rows, int n,
+                         cudaStream_t s) {
+  if (rows <= 0 || n <= 0) return RB_OK;
+  for (int r0 = 0; r0 < rows; r0 += 65535) {
+    int nr = min(65535, rows - r0);
+    dim3 grid(min((n + 255) / 256, 256), nr);
+    copy_rows_f32_kernel<<<grid, 256, 0, s>>>(src + (size_t)r0 * src_ld, src_ld,
+                                              dst + (size_t)r0 * dst_ld, dst_ld, n);
+    ++g_launches;
+  }
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+// Streaming state update (cached_conv CachedPadding1d: `pad = x[..., -P:]`): the last `hist`
+// samples of each row become the left context of the next call.  One warp per row; rows
+// are read completely before being written so overlapping moves (n < hist) are safe.
+__global__ void roll_f32_kernel(float* p, int rows, int ld, int hist, int n) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float* r = p + (size_t)row * ld;
+  for (int base = 0; base < hist; base += 32 * 8) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int u = base + i * 32 + lane;
+      v[i] = u < hist ? r[n + u] : 0.f;
+    }
+    __syncwarp();
+    // a later source element (index >= n + base + 256) may alias a destination written now
+    // only when n < 256; handle by processing chunks in order: dest [base, base+256) aliases
+    // sources [base - n, ...) which were already read (smaller index) -> safe for n >= 0.
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      int u = base + i * 32 + lane;
+      if (u < hist) r[u] = v[i];
+    }
+    __syncwarp();
+  }
+}
+
+int launch_roll_f32(float* p, int rows, int ld, int hist, int n, cudaStream_t s) {
+  if (rows <= 0 || hist <= 0 || n <= 0) return RB_OK;
+  dim3 grid((rows + 7) / 8);
+  roll_f32_kernel<<<grid, 256, 0, s>>>(p, rows, ld, hist, n);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+}  // namespace rb

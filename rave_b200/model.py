@@ -1,0 +1,263 @@
+"""`RAVE`: drop-in for the reference's `rave.RAVE` on the encode/decode inference path.
+
+Same three methods and shapes as rave/model.py:594-634 --
+    encode(x[B,1,T]) -> z[B, latent+speaker, T/ratio];  decode(z) -> y[B,1,T];  forward(x)
+-- and the attribute names its callers read (scripts/export.py:162-164,394-405,503-517:
+`.pqmf`, `.encoder`, `.decoder`, `.sr`, `.latent_size`, `.encoder.rvq.encode/decode`,
+`.latent_pca/.latent_mean/.fidelity`).  No Lightning, no training code.  Construction
+follows the reference: parse gin files, then build (`RAVE.from_gin`), with
+`streaming=True` standing for `cc.use_cached_conv(True)` before construction
+(export.py:543), then `load_state_dict(ckpt["state_dict"])` (export.py:566-569).
+
+All arithmetic runs in librave_b200.so through the C-ABI (include/rave_b200.h); torch is
+used for device memory and the current CUDA stream only.  CPU tensors raise: there is
+no fallback path.
+"""
+import ctypes as C
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+from . import capi, gin_lite
+from .netspec import NetSpec, build_netspec
+from .pqmf_design import design as pqmf_design
+from .weights import collect
+
+MAX_BATCH_SIZE = 64   # cached_conv.MAX_BATCH_SIZE: default number of stream rows
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _RVQ:
+    """`model.encoder.rvq` (quantization.ResidualVectorQuantization inference surface)."""
+
+    def __init__(self, owner):
+        self._o = owner
+
+    def encode(self, z: torch.Tensor) -> torch.Tensor:
+        o = self._o
+        z = o._check_input(z, o.spec.rvq["dim"], "rvq.encode", force_f32=True)
+        B, _, F = z.shape
+        idx = torch.empty(B, o.spec.rvq["num_quantizers"], F, dtype=torch.int64, device=z.device)
+        capi.check(o._lib.rb_rvq_encode(o._h, z.data_ptr(), B, F, idx.data_ptr(), _stream_ptr()))
+        return idx
+
+    def decode(self, q_indices: torch.Tensor) -> torch.Tensor:
+        o = self._o
+        if not q_indices.is_cuda:
+            raise ValueError("rvq.decode: indices must live on the CUDA device (no CPU path)")
+        if q_indices.dtype != torch.int64 or q_indices.dim() != 3 or \
+                q_indices.shape[1] != o.spec.rvq["num_quantizers"]:
+            raise ValueError("rvq.decode expects int64 [B, num_quantizers, F]")
+        q_indices = q_indices.contiguous()
+        B, _, F = q_indices.shape
+        zq = torch.empty(B, o.spec.rvq["dim"], F, dtype=torch.float32, device=q_indices.device)
+        capi.check(o._lib.rb_rvq_decode(o._h, q_indices.data_ptr(), B, F, zq.data_ptr(), _stream_ptr()))
+        return zq
+
+
+class RAVE:
+    def __init__(self, spec: NetSpec, device="cuda:0", dtype=torch.float32):
+        if not torch.cuda.is_available():
+            raise RuntimeError("rave_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        if dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("dtype must be torch.float32 or torch.bfloat16")
+        self.spec = spec
+        self.device = torch.device(device)
+        self.dtype = dtype
+        self._rb_dtype = capi.RB_F32 if dtype == torch.float32 else capi.RB_BF16
+        self._lib = capi.load_library()
+        self._h = C.c_void_p()
+        self._keep = []
+        slots = (capi.RbSlot * len(spec.slots))(*[capi.RbSlot(s.channels, s.per_frame, s.hist, 0) for s in spec.slots])
+        ops = (capi.RbOp * len(spec.ops))()
+        for i, o in enumerate(spec.ops):
+            for name, _ in capi.RbOp._fields_[:-1]:
+                setattr(ops[i], name, int(getattr(o, name)))
+        ns = capi.RbNetSpec()
+        ns.abi_version = capi.ABI_VERSION
+        ns.n_slots, ns.slots = len(spec.slots), slots
+        ns.n_enc_ops, ns.n_ops, ns.ops = spec.n_enc_ops, len(spec.ops), ops
+        ns.enc_in_slot, ns.enc_out_slot = spec.enc_in, spec.enc_out
+        ns.dec_in_slot, ns.dec_out_slot = spec.dec_in, spec.dec_out
+        ns.samples_per_frame = spec.samples_per_frame
+        ns.streaming = int(spec.streaming)
+        ns.cond_channels = spec.cond_channels
+        ns.noise_slot = spec.noise_slot
+        if spec.rvq:
+            ns.rvq_quantizers = spec.rvq["num_quantizers"]
+            ns.rvq_codebook_size = spec.rvq["codebook_size"]
+            ns.rvq_dim = spec.rvq["dim"]
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        capi.check(self._lib.rb_create(C.byref(ns), idx, C.byref(self._h)))
+        # attribute surface of the reference model
+        self.sr = spec.sr
+        self.latent_size = spec.latent_size
+        self.cond_channels = spec.cond_channels
+        h, hk, wa, ws = pqmf_design(spec.attenuation, spec.n_band)
+        self.pqmf = SimpleNamespace(n_band=spec.n_band, h=h, hk=hk, forward_conv_weight=wa,
+                                    inverse_conv_weight=ws)
+        self.encoder = SimpleNamespace(noise_augmentation=0, enabled=int(spec.rvq is not None),
+                                       rvq=_RVQ(self) if spec.rvq else None, kind=spec.encoder_type)
+        self.decoder = SimpleNamespace(latent_size=spec.dec_latent_size)
+        self.speaker_encoder = None   # SpeakerRAVE is upstream of the path
+        self.latent_pca = np.eye(spec.latent_size, dtype=np.float32)
+        self.latent_mean = np.zeros(spec.latent_size, dtype=np.float32)
+        self.fidelity = np.zeros(spec.latent_size, dtype=np.float32)
+        self._streams_ready = False
+        self._noise = None
+        # PQMF filters do not depend on the checkpoint: load them now
+        self._load([(i, capi.RB_W_CONV, w) for i, o in enumerate(spec.ops)
+                    for w in ([wa] if o.kind == 2 else [ws] if o.kind == 3 else [])])
+
+    # ------------------------------------------------------------------ construction
+    @classmethod
+    def from_gin(cls, config_files, bindings=None, streaming=False, device="cuda:0",
+                 dtype=torch.float32, search_paths=None):
+        cfg = gin_lite.parse_config_files_and_bindings(config_files, bindings, search_paths)
+        return cls(build_netspec(cfg, streaming=streaming), device=device, dtype=dtype)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None) and self._h.value:
+                self._lib.rb_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def _load(self, items):
+        if not items:
+            return
+        arr = (capi.RbTensorDesc * len(items))()
+        keep = []
+        for j, (op, role, a) in enumerate(items):
+            a = np.ascontiguousarray(a, dtype=np.float32)
+            keep.append(a)
+            arr[j].op, arr[j].role = int(op), int(role)
+            arr[j].data = a.ctypes.data_as(C.POINTER(C.c_float))
+            arr[j].numel = a.size
+        capi.check(self._lib.rb_load_weights(self._h, arr, len(items)))
+
+    def load_state_dict(self, state_dict, strict=True):
+        """Accepts a reference checkpoint's `state_dict` (weight-norm pairs or folded)."""
+        self._load(collect(self.spec, state_dict, (self.pqmf.forward_conv_weight,
+                                                   self.pqmf.inverse_conv_weight), strict=strict))
+        return self
+
+    def set_speaker(self, emb):
+        """`self.speaker` of the reference (model.py:246-247): the fixed [1, S, 1] embedding."""
+        self.load_state_dict({"speaker": emb}, strict=False)
+
+    def eval(self):
+        return self
+
+    def set_noise(self, noise):
+        """Inject the U(-1,1) draw of the noise branch ([B, L/8, n_band, 8]); None = internal RNG."""
+        if noise is None:
+            self._noise = None
+            capi.check(self._lib.rb_set_noise(self._h, None, 0))
+            return
+        if not noise.is_cuda:
+            raise ValueError("noise must live on the CUDA device")
+        self._noise = noise.contiguous().float()
+        capi.check(self._lib.rb_set_noise(self._h, self._noise.data_ptr(), self._noise.numel()))
+
+    # ------------------------------------------------------------------ checks
+    def _check_input(self, x, channels, what, force_f32=False):
+        if not isinstance(x, torch.Tensor):
+            raise ValueError(f"{what}: expected a torch.Tensor")
+        if not x.is_cuda:
+            raise ValueError(f"{what}: tensor must live on the CUDA device (no CPU path)")
+        if x.dim() != 3 or x.shape[1] != channels:
+            raise ValueError(f"{what}: expected shape [B, {channels}, T], got {tuple(x.shape)}")
+        if not x.is_contiguous():
+            raise ValueError(f"{what}: tensor must be contiguous")
+        want = torch.float32 if force_f32 else self.dtype
+        return x if x.dtype == want else x.to(want)
+
+    def _ensure_streams(self, B, n):
+        if not self._streams_ready:
+            self.alloc_streams(max(B, MAX_BATCH_SIZE), n)
+
+    # ------------------------------------------------------------------ public surface
+    def alloc_streams(self, max_streams, max_chunk):
+        capi.check(self._lib.rb_stream_alloc(self._h, int(max_streams), int(max_chunk), self._rb_dtype))
+        self._streams_ready = True
+
+    def reset_streams(self, stream_ids=None):
+        if stream_ids is None:
+            capi.check(self._lib.rb_stream_reset(self._h, None, 0))
+        else:
+            ids = (C.c_int32 * len(stream_ids))(*stream_ids)
+            capi.check(self._lib.rb_stream_reset(self._h, ids, len(stream_ids)))
+
+    @torch.no_grad()
+    def encode(self, x):
+        x = self._check_input(x, 1, "encode")
+        B, _, T = x.shape
+        spf = self.spec.samples_per_frame
+        if T % spf:
+            raise ValueError(f"encode: T={T} must be a multiple of the model ratio {spf}")
+        cz = self.spec.slots[self.spec.enc_out].channels
+        z = torch.empty(B, cz, T // spf, dtype=self.dtype, device=x.device)
+        if self.spec.streaming:
+            self._ensure_streams(B, T)
+            capi.check(self._lib.rb_stream_encode(self._h, x.data_ptr(), B, T, z.data_ptr(), _stream_ptr()))
+        else:
+            capi.check(self._lib.rb_encode(self._h, x.data_ptr(), B, T, self._rb_dtype, z.data_ptr(), _stream_ptr()))
+        return z
+
+    @torch.no_grad()
+    def decode(self, z):
+        z = self._check_input(z, self.spec.dec_latent_size, "decode")
+        B, _, F = z.shape
+        y = torch.empty(B, 1, F * self.spec.samples_per_frame, dtype=self.dtype, device=z.device)
+        if self.spec.streaming:
+            self._ensure_streams(B, F * self.spec.samples_per_frame)
+            capi.check(self._lib.rb_stream_decode(self._h, z.data_ptr(), B, F, y.data_ptr(), _stream_ptr()))
+        else:
+            capi.check(self._lib.rb_decode(self._h, z.data_ptr(), B, F, self._rb_dtype, y.data_ptr(), _stream_ptr()))
+        return y
+
+    @torch.no_grad()
+    def forward(self, x):
+        x = self._check_input(x, 1, "forward")
+        B, _, T = x.shape
+        if T % self.spec.samples_per_frame:
+            raise ValueError(f"forward: T={T} must be a multiple of the model ratio {self.spec.samples_per_frame}")
+        y = torch.empty_like(x)
+        if self.spec.streaming:
+            self._ensure_streams(B, T)
+            capi.check(self._lib.rb_stream_step(self._h, x.data_ptr(), B, T, y.data_ptr(), _stream_ptr()))
+        else:
+            capi.check(self._lib.rb_forward(self._h, x.data_ptr(), B, T, self._rb_dtype, y.data_ptr(), _stream_ptr()))
+        return y
+
+    __call__ = forward
+
+    def forward_host(self, x: np.ndarray) -> np.ndarray:
+        """Host-buffer entry (rb_forward_host): H2D copy, forward, D2H copy, synchronous."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        if x.ndim != 3 or x.shape[1] != 1:
+            raise ValueError("forward_host expects [B, 1, T]")
+        y = np.empty_like(x)
+        capi.check(self._lib.rb_forward_host(self._h, x.ctypes.data_as(C.c_void_p), x.shape[0], x.shape[2],
+                                             capi.RB_F32, y.ctypes.data_as(C.c_void_p)))
+        return y
+
+    # ------------------------------------------------------------------ introspection
+    def kernel_launches(self):
+        n = C.c_int64()
+        capi.check(self._lib.rb_kernel_launches(self._h, C.byref(n)))
+        return n.value
+
+    def stream_state_elements(self):
+        n = C.c_int64()
+        capi.check(self._lib.rb_stream_state_elements(self._h, C.byref(n)))
+        return n.value
+
+    def set_microbatch(self, streams):
+        capi.check(self._lib.rb_set_microbatch(self._h, int(streams)))

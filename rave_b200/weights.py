@@ -1,0 +1,122 @@
+"""Reference state_dict -> folded fp32 tensors for rb_load_weights.
+
+Accepts the key names of a reference checkpoint, with or without
+weight-norm pairs (`weight_g`/`weight_v` vs `weight`; scripts/export.py:598-600 removes
+them before export).  Folding done here, once, at load time:
+  * weight norm  w = g * v / ||v||, norm over every dim but 0 (torch weight_norm default;
+    for ConvTranspose1d dim 0 is the INPUT channel) -- rave/blocks.py:17-24;
+  * eval-mode BatchNorm1d of the v1 encoder (blocks.py:445-446) into the conv before it;
+  * ConvTranspose1d(C, C', 2r, stride r, padding r//2) into r phase-convs (netspec.py);
+  * AdaIN transfer (blocks.py:885-891) into a per-(row, channel) scale/shift.
+"""
+import numpy as np
+
+from . import capi
+from .netspec import OP_AFFINE, OP_CONCAT, OP_CONV, OP_PQMF_FWD, OP_PQMF_INV, NetSpec
+
+
+def _np(t):
+    if hasattr(t, "detach"):
+        t = t.detach().to("cpu").float().numpy()
+    return np.ascontiguousarray(np.asarray(t), dtype=np.float32)
+
+
+def _folded(sd, prefix, norm=True):
+    if prefix + "weight_g" in sd:
+        # fp32 like the reference: weight_norm computes g * v / ||v|| in the parameter dtype
+        v, g = _np(sd[prefix + "weight_v"]), _np(sd[prefix + "weight_g"])
+        nrm = np.sqrt((v.reshape(v.shape[0], -1) ** 2).sum(1, dtype=np.float32))
+        w = v * (g / nrm.reshape((-1,) + (1,) * (v.ndim - 1)))
+    elif prefix + "weight" in sd:
+        w = _np(sd[prefix + "weight"])
+    else:
+        raise KeyError(f"state_dict has neither {prefix}weight nor {prefix}weight_g/_v")
+    b = _np(sd[prefix + "bias"]) if prefix + "bias" in sd else None
+    return np.ascontiguousarray(w, dtype=np.float32), b
+
+
+def _phase_pack(w, r, p, k_taps):
+    """ConvTranspose1d weight [c_in][c_out][2r] -> equivalent conv weight [r*c_out][c_in][k_taps].
+
+    Output phase ph of y[t*r + ph] reads input offsets m (tap index m + 1) with kernel tap
+    j = ph + p - r*m (netspec._Builder.conv_transpose)."""
+    c_in, c_out, k = w.shape
+    assert k == 2 * r
+    out = np.zeros((r * c_out, c_in, k_taps), dtype=np.float32)
+    for ph in range(r):
+        for tap in range(k_taps):
+            m = tap - 1
+            j = ph + p - r * m
+            if 0 <= j < k:
+                out[ph * c_out:(ph + 1) * c_out, :, tap] = w[:, :, j].T
+    return out
+
+
+def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True):
+    """Returns a list of (op_index, role, float32 ndarray) for everything found in `sd`."""
+    out = []
+    missing = []
+    if spec.arch == "v1" and "decoder.warmed_up" in sd and "decoder.synth.branches.2.net.0.weight" in sd \
+            and int(np.asarray(_np(sd["decoder.warmed_up"])).reshape(-1)[0]) != 0:
+        raise NotImplementedError("v1 Generator with an active NoiseGenerator branch (warmed_up=1)")
+    for i, op in enumerate(spec.ops):
+        P = op.params
+        try:
+            if op.kind == OP_CONV and "conv" in P:
+                w, b = _folded(sd, P["conv"])
+                if "bn" in P:
+                    bn = P["bn"]
+                    scale = _np(sd[bn + "weight"]) / np.sqrt(_np(sd[bn + "running_var"]) + np.float32(1e-5))
+                    w = w * scale[:, None, None]
+                    b = (b - _np(sd[bn + "running_mean"])) * scale + _np(sd[bn + "bias"])
+                out.append((i, capi.RB_W_CONV, w))
+                if op.has_bias:
+                    if b is None:
+                        raise KeyError(P["conv"] + "bias")
+                    out.append((i, capi.RB_W_BIAS, b))
+            elif op.kind == OP_CONV and "convt" in P:
+                w, b = _folded(sd, P["convt"])
+                out.append((i, capi.RB_W_CONV, _phase_pack(w, P["r"], P["p"], op.k)))
+                if op.has_bias:
+                    if b is None:
+                        raise KeyError(P["convt"] + "bias")
+                    out.append((i, capi.RB_W_BIAS, b))
+            elif op.kind in (OP_PQMF_FWD, OP_PQMF_INV):
+                key = ("pqmf.forward_conv.weight" if op.kind == OP_PQMF_FWD else "pqmf.inverse_conv.weight")
+                if key in sd:
+                    w = _np(sd[key])
+                elif pqmf_weights is not None:
+                    w = pqmf_weights[0 if op.kind == OP_PQMF_FWD else 1]
+                else:
+                    raise KeyError(key)
+                out.append((i, capi.RB_W_CONV, w))
+            elif op.kind == OP_AFFINE:
+                p = P["adain"]
+                mx, sx = _np(sd[p + "mean_x"])[..., 0], _np(sd[p + "std_x"])[..., 0]
+                my, sy = _np(sd[p + "mean_y"])[..., 0], _np(sd[p + "std_y"])[..., 0]
+                active = float(_np(sd[p + "num_update_x"]).reshape(-1)[0]) and \
+                    float(_np(sd[p + "num_update_y"]).reshape(-1)[0])
+                if active:
+                    a = sy / (sx + np.float32(1e-5))
+                    bsh = my - mx * a
+                else:
+                    a, bsh = np.ones_like(mx), np.zeros_like(mx)
+                out.append((i, capi.RB_W_AFFINE_A, a))
+                out.append((i, capi.RB_W_AFFINE_B, bsh))
+            elif op.kind == OP_CONCAT:
+                if "speaker" in sd:
+                    out.append((i, capi.RB_W_COND, _np(sd["speaker"]).reshape(-1)))
+            if "alpha" in P:
+                out.append((i, capi.RB_W_ALPHA, _np(sd[P["alpha"]]).reshape(-1)))
+        except KeyError as e:
+            missing.append(str(e))
+    if spec.rvq is not None:
+        keys = [f"{spec.rvq['prefix']}layers.{q}._codebook.embed" for q in range(spec.rvq["num_quantizers"])]
+        if all(k in sd for k in keys):
+            out.append((0, capi.RB_W_CODEBOOK, np.stack([_np(sd[k]) for k in keys], 0)))
+        else:
+            missing.append("RVQ codebooks")
+    if missing and strict:
+        raise KeyError("missing keys in state_dict: " + ", ".join(missing[:8]) +
+                       (" ..." if len(missing) > 8 else ""))
+    return [(i, r, np.ascontiguousarray(a, dtype=np.float32)) for i, r, a in out]

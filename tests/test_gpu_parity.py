@@ -1,0 +1,163 @@
+"""-m gpu parity tests: the CUDA path (through the C-ABI) against the CPU oracle on the same
+seeded inputs and against the committed golden fixtures.  Tolerances are the ones
+BASELINE.json states: rel-L2 <= 1e-3 for the fp32 engine (the tests hold it to 1e-4),
+<= 1e-2 for bf16, RVQ indices bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from .util import golden_input, golden_state_dict, load_golden, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+GIN = {"v2_c8": (["v2.gin"], ["CAPACITY=8"]), "v2causal_c8": (["v2.gin", "causal.gin"], ["CAPACITY=8"]),
+       "v3_c8": (["v3.gin"], ["CAPACITY=8"]), "v3causal_c8": (["v3.gin", "causal.gin"], ["CAPACITY=8"]),
+       "discrete_c8": (["discrete.gin"], ["CAPACITY=8"]), "v2noise_c8": (["v2.gin", "noise.gin"], ["CAPACITY=8"]),
+       "v1_c8": (["v1.gin"], ["CAPACITY=8"]), "raspberry_c16": (["raspberry.gin"], []),
+       "raspberry_causal_c16": (["raspberry.gin", "causal.gin"], []), "v2_c64": (["v2.gin"], [])}
+F32_TOL = 1e-4
+
+
+def _model(name, streaming=False, dtype=torch.float32):
+    from rave_b200 import RAVE
+    meta, a = load_golden(name)
+    files, binds = GIN[name]
+    m = RAVE.from_gin(files, binds, streaming=streaming, dtype=dtype)
+    m.load_state_dict(golden_state_dict(meta))
+    return m, meta, a
+
+
+@pytest.mark.parametrize("name", list(GIN))
+def test_offline_matches_golden(name):
+    m, meta, a = _model(name)
+    x = torch.from_numpy(golden_input(a)).cuda()
+    if meta["cfg"].get("noise"):
+        from oracle.weights_recipe import recipe_input
+        B, _, T = x.shape
+        m.set_noise(torch.from_numpy(recipe_input((B, T // 16 // 8, 16, 8), int(a["noise_seed"].item()),
+                                                  uniform=True)).cuda())
+    z = m.encode(x)
+    assert tuple(z.shape) == a["z"].shape
+    assert rel_l2(z.cpu().numpy(), a["z"]) < F32_TOL
+    y = m.decode(torch.from_numpy(a["z"]).cuda())
+    assert y.shape == x.shape                       # reference tests/test_configs.py:68
+    assert rel_l2(y.cpu().numpy(), a["y"]) < F32_TOL
+    y2 = m(x)                                        # forward == decode(encode(x)), model.py:634
+    assert rel_l2(y2.cpu().numpy(), a["y"]) < 2 * F32_TOL
+
+
+@pytest.mark.parametrize("name", [n for n in GIN if n not in ("v2noise_c8", "v2_c64")])
+def test_streaming_matches_golden_chunk_by_chunk(name):
+    m, meta, a = _model(name, streaming=True)
+    x = torch.from_numpy(golden_input(a)).cuda()
+    n = int(a["chunk"].item())
+    zs, ys = [], []
+    for c in range(x.shape[-1] // n):
+        z = m.encode(x[..., c * n:(c + 1) * n].contiguous())
+        zs.append(z)
+        ys.append(m.decode(z))
+    assert rel_l2(torch.cat(zs, -1).cpu().numpy(), a["z_stream"]) < F32_TOL
+    assert rel_l2(torch.cat(ys, -1).cpu().numpy(), a["y_stream"]) < F32_TOL
+    # fused encode->decode step on a fresh state gives the same audio
+    m.reset_streams()
+    ys2 = [m(x[..., c * n:(c + 1) * n].contiguous()) for c in range(x.shape[-1] // n)]
+    assert rel_l2(torch.cat(ys2, -1).cpu().numpy(), a["y_stream"]) < F32_TOL
+
+
+def test_streaming_ragged_chunks_and_reset():
+    """Chunk sizes may vary call to call (multiples of the ratio); reset zeroes one stream."""
+    from oracle.model import OracleRAVE
+    m, meta, a = _model("v2causal_c8", streaming=True)
+    o = OracleRAVE(meta["cfg"], golden_state_dict(meta), streaming=True)
+    x = torch.from_numpy(golden_input(a))
+    m.alloc_streams(4, 4096)
+    pos = 0
+    for n in (1024, 3072, 2048, 1024, 4096):
+        xc = x[..., pos:pos + n].contiguous()
+        pos += n
+        y = m(xc.cuda())
+        yo = o.forward(xc)
+        assert rel_l2(y.cpu().numpy(), yo.numpy()) < F32_TOL
+    m.reset_streams([1])
+    o2 = OracleRAVE(meta["cfg"], golden_state_dict(meta), streaming=True)
+    xc = x[..., :2048].contiguous()
+    y = m(xc.cuda())
+    assert rel_l2(y[1].cpu().numpy(), o2.forward(xc)[1].numpy()) < F32_TOL      # fresh state
+    assert rel_l2(y[0].cpu().numpy(), o.forward(xc)[0].numpy()) < F32_TOL       # carried state
+
+
+def test_causal_stream_equals_offline_after_delay_gpu():
+    m, meta, a = _model("v2causal_c8", streaming=True)
+    x = torch.from_numpy(golden_input(a)).cuda()
+    ys = torch.cat([m(x[..., c * 2048:(c + 1) * 2048].contiguous()) for c in range(8)], -1).cpu().numpy()
+    d = 928
+    assert rel_l2(ys[..., 14336:], a["y"][..., 14336 - d:-d]) < 1e-4
+
+
+def test_rvq_indices_bit_exact_and_decode():
+    from oracle.weights_recipe import recipe_input
+    m, meta, a = _model("discrete_c8")
+    zq = torch.from_numpy(recipe_input((4, 128, 64), int(a["rvq_z_seed"].item()), scale=1.0)).cuda()
+    idx = m.encoder.rvq.encode(zq)
+    assert idx.dtype == torch.int64
+    assert np.array_equal(idx.cpu().numpy(), a["rvq_idx"])
+    dec = m.encoder.rvq.decode(idx)
+    assert rel_l2(dec.cpu().numpy(), a["rvq_dec"]) < 1e-6
+
+
+def test_rvq_bit_exact_vs_oracle_large_and_ragged():
+    """131072 vectors (the C4 size) plus ragged shapes, live against the oracle."""
+    from oracle.model import OracleRAVE
+    from oracle.weights_recipe import recipe_input
+    m, meta, _ = _model("discrete_c8")
+    o = OracleRAVE(meta["cfg"], golden_state_dict(meta))
+    for shape, seed in (((1, 128, 1), 1), ((3, 128, 7), 2), ((5, 128, 65), 3), ((512, 128, 256), 4)):
+        z = torch.from_numpy(recipe_input(shape, seed, scale=1.0))
+        ref = o.rvq_encode(z)
+        got = m.encoder.rvq.encode(z.cuda()).cpu()
+        assert torch.equal(got, ref), f"{shape}: {(got != ref).sum().item()} mismatching indices"
+        assert rel_l2(m.encoder.rvq.decode(got.cuda()).cpu().numpy(), o.rvq_decode(ref).numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("B,T", [(1, 1024), (3, 5120), (2, 131072)])
+def test_v2_ragged_sizes_vs_oracle(B, T):
+    """Smallest legal input (one frame), odd batch, and BASELINE configs[0] length 2^17."""
+    from oracle.model import OracleRAVE
+    from oracle.weights_recipe import recipe_input
+    m, meta, _ = _model("v2_c8")
+    o = OracleRAVE(meta["cfg"], golden_state_dict(meta))
+    x = torch.from_numpy(recipe_input((B, 1, T), 77))
+    y = m(x.cuda())
+    assert rel_l2(y.cpu().numpy(), o.forward(x).numpy()) < F32_TOL
+
+
+def test_error_conventions():
+    from rave_b200 import RAVE
+    m, meta, a = _model("v2_c8")
+    with pytest.raises(ValueError):
+        m.encode(torch.zeros(1, 1, 1000).cuda())                 # not a multiple of the ratio
+    with pytest.raises(ValueError):
+        m.encode(torch.zeros(1, 1, 1024))                        # CPU tensor: no fallback
+    with pytest.raises(ValueError):
+        m.decode(torch.zeros(1, 64, 4).cuda())                   # wrong latent width
+    with pytest.raises(ValueError):
+        m.encode(torch.zeros(1, 2048, 1).cuda().transpose(1, 2))  # non-contiguous
+    raw = RAVE.from_gin(["v2.gin"], ["CAPACITY=8"])
+    with pytest.raises(RuntimeError):
+        raw.encode(torch.zeros(1, 1, 1024).cuda())               # weights not loaded
+    with pytest.raises(KeyError):
+        raw.load_state_dict({})
+
+
+def test_streams_are_independent_at_full_length():
+    """Size-independent property at the BASELINE configs[1] length (2^18 samples): a stream's
+    output does not depend on its batch neighbours or its row (bitwise), which is what lets
+    the batch be sharded across GPUs with no exchange."""
+    from oracle.weights_recipe import recipe_input
+    m, meta, _ = _model("v2_c8")
+    x = torch.from_numpy(recipe_input((3, 1, 2 ** 18), 5)).cuda()
+    y = m(x)
+    y1 = m(x[1:2].contiguous())
+    assert torch.equal(y[1:2], y1)
+    yp = m(x.flip(0).contiguous())
+    assert torch.equal(yp.flip(0), y)

@@ -1,0 +1,153 @@
+"""CPU-side tests: gin reader, netspec builder, weight folding, C-ABI library exports."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from rave_b200 import capi, gin_lite, netspec
+from rave_b200.weights import _phase_pack, collect
+
+from .util import ROOT, golden_state_dict, load_golden
+
+REF = "/root/reference/rave/configs"
+
+
+def _spec(files, bindings=(), streaming=False, search=None):
+    cfg = gin_lite.parse_config_files_and_bindings(list(files), list(bindings), search_paths=search)
+    return netspec.build_netspec(cfg, streaming=streaming)
+
+
+def test_get_padding_matches_cached_conv_rule():
+    assert netspec.get_padding(1) == (0, 0)
+    assert netspec.get_padding(3) == (1, 1)
+    assert netspec.get_padding(3, dilation=9) == (9, 9)
+    assert netspec.get_padding(8, 4) == (3, 4)            # stride ignored
+    assert netspec.get_padding(8, 4, mode="causal") == (7, 0)
+    assert netspec.get_padding(513) == (256, 256)
+    assert netspec.get_padding(513, mode="causal") == (512, 0)
+    with pytest.raises(ValueError):
+        netspec.get_padding(3, mode="bogus")
+
+
+def test_gin_lite_syntax():
+    cfg = gin_lite.Config().parse_string('''
+A = 3  # comment
+B = [%A, 2,
+     1]
+mod.Cls.x = %B
+scope/mod.Cls.y = @other.Thing
+mod.Fn:
+    p = {'a': 1,
+         'b': (5, 1)}
+    q = @mod.fn()
+''')
+    assert cfg.macro("A") == 3
+    assert cfg.params("Cls")["x"] == [3, 2, 1]
+    assert "y" not in cfg.params("Cls")
+    assert cfg.params("Cls", "scope")["y"].name == "Thing"
+    assert cfg.params("Fn")["p"] == {"a": 1, "b": (5, 1)}
+    assert cfg.params("Fn")["q"].evaluate
+
+
+def test_v2_macs_and_state_match_survey():
+    s = _spec(["v2.gin"])
+    m = s.macs_per_frame()
+    # enc 19.243 M + 0.197 M PQMF(6 bands); dec 20.775 M + 0.541 M
+    assert m["enc"] == 19_440_000 and m["dec"] == 21_315_584
+    assert s.samples_per_frame == 1024 and s.slots[s.enc_out].channels == 320
+    st = _spec(["v2.gin"], streaming=True)
+    assert 40_000 < sum(sl.hist * sl.channels for sl in st.slots) < 43_000    # ~42 K elements
+
+
+@pytest.mark.parametrize("stack", [["v1"], ["v2"], ["v2", "adain"], ["v2", "wasserstein"], ["v2", "spherical"],
+                                   ["discrete"], ["discrete", "snake"], ["discrete", "snake", "adain"],
+                                   ["discrete", "noise"], ["v3"], ["raspberry"], ["onnx"], ["discrete_v3"]])
+@pytest.mark.parametrize("causal", [False, True])
+def test_config_stacks_build(stack, causal):
+    """The config stacks of the reference's tests/test_configs.py:15-31 (+causal) all build,
+    offline and streaming, with CAPACITY=2 as in test_configs.py:58."""
+    files = [s + ".gin" for s in stack] + (["causal.gin"] if causal else [])
+    for streaming in (False, True):
+        s = _spec(files, ["CAPACITY=2"], streaming)
+        assert s.causal == causal and s.slots[s.dec_out].per_frame == s.samples_per_frame
+
+
+@pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not present")
+@pytest.mark.parametrize("name", ["v1", "v2", "v3", "discrete", "raspberry", "discrete_v3"])
+def test_reference_gin_files_give_same_program(name):
+    """Parsing the reference's own .gin files yields the same program as the in-repo subset."""
+    sp = ["/root/reference", "/root/reference/rave", REF]
+    a = _spec([f"{REF}/{name}.gin"], search=sp)
+    b = _spec([f"{name}.gin"])
+    assert [(o.kind, o.c_in, o.c_out, o.k, o.stride, o.dilation, o.off, o.pre_act, o.name) for o in a.ops] == \
+           [(o.kind, o.c_in, o.c_out, o.k, o.stride, o.dilation, o.off, o.pre_act, o.name) for o in b.ops]
+
+
+def test_unsupported_and_invalid_configs_raise():
+    with pytest.raises(ValueError):
+        _spec(["v2.gin"], ["rave.RAVE.encoder=@blocks.NoSuchEncoder"])
+    with pytest.raises(Exception):
+        _spec(["v2.gin"], ["blocks.normalization.mode='spectral'"])
+    with pytest.raises(ValueError):
+        _spec(["v2.gin"], ["cc.get_padding.mode='reflect'"])
+
+
+def test_phase_pack_equals_conv_transpose():
+    import torch
+    import torch.nn.functional as F
+    torch.manual_seed(0)
+    for r in (2, 4, 8):
+        w = torch.randn(5, 3, 2 * r)
+        x = torch.randn(2, 5, 11)
+        ref = F.conv_transpose1d(x, w, None, r, r // 2)
+        weq = torch.from_numpy(_phase_pack(w.numpy(), r, r // 2, 3))
+        y = F.conv1d(F.pad(x, (1, 1)), weq)                       # [B, r*3, 11]
+        y = y.reshape(2, r, 3, 11).permute(0, 2, 3, 1).reshape(2, 3, 11 * r)
+        assert torch.allclose(y, ref, atol=1e-5)
+
+
+def test_weight_collection_covers_every_op():
+    meta, _ = load_golden("v3_c8")
+    cfg = gin_lite.parse_config_files_and_bindings(["v3.gin"], ["CAPACITY=8"])
+    s = netspec.build_netspec(cfg)
+    items = collect(s, golden_state_dict(meta), pqmf_weights=(np.zeros((16, 1, 513)), np.zeros((16, 16, 33))))
+    have = {(i, r) for i, r, _ in items}
+    for i, op in enumerate(s.ops):
+        if op.kind == netspec.OP_CONV:
+            assert (i, capi.RB_W_CONV) in have
+            if op.has_bias:
+                assert (i, capi.RB_W_BIAS) in have
+            if op.pre_act == netspec.ACT_SNAKE:
+                assert (i, capi.RB_W_ALPHA) in have
+    with pytest.raises(KeyError):
+        collect(s, {}, None)
+
+
+def test_library_exports_every_symbol_of_the_header():
+    """The C-ABI library loads and exports every function include/rave_b200.h declares."""
+    hdr = open(os.path.join(ROOT, "include", "rave_b200.h")).read()
+    declared = set(re.findall(r"\b(rb_[a-z_0-9]+)\s*\(", hdr))
+    assert declared == set(capi.EXPORTS), declared ^ set(capi.EXPORTS)
+    assert os.path.exists(capi.LIB_PATH), "build with python -m rave_b200.build"
+    lib = ctypes.CDLL(capi.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), name
+    lib.rb_abi_version.restype = ctypes.c_int
+    assert lib.rb_abi_version() == capi.ABI_VERSION
+
+
+def test_struct_layouts_match_header_sizes():
+    assert ctypes.sizeof(capi.RbSlot) == 16
+    assert ctypes.sizeof(capi.RbOp) == 4 * 20
+    assert ctypes.sizeof(capi.RbTensorDesc) == 24
+
+
+def test_no_cuda_device_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from rave_b200 import RAVE
+    with pytest.raises(RuntimeError):
+        RAVE.from_gin(["v2.gin"], ["CAPACITY=2"])
