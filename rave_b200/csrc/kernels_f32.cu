@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(256)
 conv1d_f32_kernel(ConvArgs a, int ci_chunk, int span, int span_pad) {
   extern __shared__ float smem[];
   float* xs = smem;                                   // [ci_chunk][span_pad]
-  float* ws = smem + (size_t)ci_chunk * span_pad;     // [ci_chunk][k][64]
+  float* ws = smem + (((size_t)ci_chunk * span_pad + 3) & ~(size_t)3);   // [ci_chunk][k][64], 16B aligned
   const int b = blockIdx.z;
   const int co0 = blockIdx.y * CONV_TC;
   const int t0 = blockIdx.x * CONV_TT;
@@ -115,7 +115,7 @@ int launch_conv_f32(const ConvArgs& a, cudaStream_t s) {
   if (ci_chunk > a.c_in) ci_chunk = a.c_in;
   const int span = (CONV_TT - 1) * a.stride + (a.k - 1) * a.dil + 1;
   const int span_pad = span | 1;
-  size_t smem = ((size_t)ci_chunk * span_pad + (size_t)ci_chunk * a.k * CONV_TC) * sizeof(float);
+  size_t smem = ((((size_t)ci_chunk * span_pad + 3) & ~(size_t)3) + (size_t)ci_chunk * a.k * CONV_TC) * sizeof(float);
   RB_CHECK(smem <= 200 * 1024, RB_ERR_UNSUPPORTED, "conv tile needs %zu B of shared memory", smem);
   static bool attr_set = false;
   if (!attr_set) {

@@ -141,7 +141,7 @@ def test_error_conventions():
     with pytest.raises(ValueError):
         m.decode(torch.zeros(1, 64, 4).cuda())                   # wrong latent width
     with pytest.raises(ValueError):
-        m.encode(torch.zeros(1, 2048, 1).cuda().transpose(1, 2))  # non-contiguous
+        m.encode(torch.zeros(2, 1, 4096).cuda()[:, :, ::2])      # non-contiguous
     raw = RAVE.from_gin(["v2.gin"], ["CAPACITY=8"])
     with pytest.raises(RuntimeError):
         raw.encode(torch.zeros(1, 1, 1024).cuda())               # weights not loaded
