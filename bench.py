@@ -1,0 +1,279 @@
+#!/usr/bin/env python
+"""bench.py -- audio-seconds per wall-second of v2 encode+decode (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--dtype bf16|f32]
+
+A step = one pass of RAVE.forward (encode -> decode) over the synthetic batch of
+BASELINE.json configs[1]: 512 streams x 2^18 samples @44.1 kHz, random-init v2 weights
+(name-keyed recipe, oracle/weights_recipe.py), streams sharded over the N ranks with no
+exchange; the only collective is the final NCCL all-gather of the outputs (inside the
+timed region).  Prints ONE JSON line on rank 0.
+
+--impl reference: the reference's own CPU path (the oracle port of its PyTorch modules --
+the reference itself is not importable) on the host cores, each step a
+bounded sample (2 streams x 2^17 samples) of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SR = 44100
+STREAMS = 512
+SAMPLES = 2 ** 18
+METRIC = "audio-sec/sec v2 encode+decode"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sus=d["bf16_tflops_sustained"],
+                    src="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sus=1400.0, src="fallback (B200_PROFILING.md)")
+
+
+def _state_dict():
+    from tests.util import golden_state_dict, load_golden
+    meta, _ = load_golden("v2_c64")            # only the (name, shape) list is read from the fixture
+    return meta, golden_state_dict(meta)
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop = index, [], False
+
+    def run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
+        mx = max((int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()), default=None)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_baseline(meta, sd, budget_s=20.0):
+    """Oracle (port of the reference's PyTorch CPU path) on BASELINE configs[0]: B=1, 2^17, fp32."""
+    import torch
+    from oracle.model import OracleRAVE
+    from oracle.weights_recipe import recipe_input
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    o = OracleRAVE(meta["cfg"], sd)
+    x = torch.from_numpy(recipe_input((1, 1, 2 ** 17), 1234))
+    o.forward(x)
+    times, t_end = [], time.time() + budget_s
+    while len(times) < 5 or (time.time() < t_end and len(times) < 20):
+        t0 = time.perf_counter()
+        o.forward(x)
+        times.append(time.perf_counter() - t0)
+    times.sort()
+    med = times[len(times) // 2]
+    return {"value": (2 ** 17 / SR) / med, "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+            "sample": f"v2 fp32 B=1 T=2^17 (configs[0]), median of {len(times)} calls after 1 warm-up"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from oracle.model import OracleRAVE
+    from oracle.weights_recipe import recipe_input
+    meta, sd = _state_dict()
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    o = OracleRAVE(meta["cfg"], sd)
+    B, T = 2, 2 ** 17
+    x = torch.from_numpy(recipe_input((B, 1, T), 1234))
+    for _ in range(max(args.warmup, 1)):
+        o.forward(x)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        o.forward(x)
+    dt = time.perf_counter() - t0
+    val = args.steps * B * T / SR / dt
+    sample = f"each step = {B} streams x 2^17 samples of the {STREAMS} x 2^18 workload, fp32, torch CPU"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "audio-sec/sec", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": f"v2 encode+decode, {STREAMS} streams x 2^18 samples", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "audio-sec/sec", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from rave_b200 import RAVE
+    from oracle.weights_recipe import recipe_input
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    esz = 2 if args.dtype == "bf16" else 4
+    streams, T = args.streams, args.samples
+    assert streams % world == 0
+    B = streams // world
+    meta, sd = _state_dict()
+    m = RAVE.from_gin(["v2.gin"], device=f"cuda:{local}", dtype=dtype)
+    m.load_state_dict(sd)
+    if args.microbatch:
+        m.set_microbatch(args.microbatch)
+    # synthetic audio: one seeded second-long pattern per stream row, resident in HBM
+    base = torch.from_numpy(recipe_input((64, 1, T), 1234 + rank)).cuda()
+    x = base.repeat((B + 63) // 64, 1, 1)[:B].contiguous().to(dtype)
+    x += (0.001 * torch.arange(B, device="cuda").view(B, 1, 1)).to(dtype)
+    gathered = torch.empty(world * B, 1, T, dtype=dtype, device="cuda") if world > 1 else None
+
+    def step():
+        y = m(x)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, y)
+        return y
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = m.kernel_launches()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = m.kernel_launches() - l0
+    sampler.stop = True
+    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    audio_s = streams * T / SR
+    value = args.steps * audio_s / (ms / 1e3)
+
+    # ---- per-op device times (CUDA events around every op on the launching stream)
+    macs = m.spec.macs_per_frame()
+    flops_step = 2.0 * (macs["enc"] + macs["dec"]) * (B * T // m.spec.samples_per_frame)
+    m.profile_ops(True)
+    m(x)
+    torch.cuda.synchronize()
+    op_ms = m.op_times_ms()
+    m.profile_ops(False)
+    conv_ms = conv_flops = 0.0
+    frames = B * T // m.spec.samples_per_frame
+    for op, t_ms in zip(m.spec.ops, op_ms):
+        if op.kind == 1:
+            conv_ms += t_ms
+            pf = m.spec.slots[op.dst].per_frame
+            mac = pf * (2 * op.c_in * (op.c_out // op.ileave) if op.ileave > 1 else op.c_in * op.c_out * op.k)
+            conv_flops += 2.0 * mac * frames
+    n_conv = sum(1 for op in m.spec.ops if op.kind == 1)
+    pk = _peaks()
+    achieved = conv_flops / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
+    roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["tf_sus"], "unit": "TFLOP/s",
+                "frac": achieved / pk["tf_sus"], "traffic": None,
+                "kernel": "conv (all %d conv launches of one step: %.1f of %.1f ms)" % (n_conv, conv_ms, sum(op_ms)),
+                "peak_source": pk["src"] + ", sustained bf16",
+                "whole_path_frac": (flops_step * world / (ms / args.steps / 1e3) / 1e12) / (pk["tf_sus"] * world)}
+
+    # ---- end to end through the public API with HOST buffers (pinned), H2D + D2H inside
+    xh = x.float().cpu().pin_memory() if esz == 4 else x.cpu().pin_memory()
+    yh = torch.empty_like(xh).pin_memory()
+    e2e_steps = max(2, min(args.steps, 5))
+
+    def e2e_step():
+        xd = xh.to("cuda", non_blocking=True)
+        y = m(xd)
+        yh.copy_(y, non_blocking=True)
+
+    e2e_step()
+    barrier()
+    ev0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    ev1.record()
+    barrier()
+    t = torch.tensor([ev0.elapsed_time(ev1)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_val = e2e_steps * audio_s / (float(t.item()) / 1e3)
+
+    if rank == 0:
+        sampler.join(timeout=2)
+        out = {
+            "metric": METRIC, "value": value, "unit": "audio-sec/sec", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": f"v2 encode+decode, {streams} streams x {T} samples @44.1 kHz, "
+                                   f"{B} streams per GPU, final NCCL all-gather of outputs",
+                       "l2": f"inputs {B * T * esz >> 20} MiB per GPU > 126 MB L2, no flush needed",
+                       "weights": "random-init (name-keyed recipe), CAPACITY=64"},
+            "clocks": sampler.summary(),
+            "e2e": {"value": e2e_val, "unit": "audio-sec/sec", "h2d_bytes_per_step": B * T * esz * world,
+                    "d2h_bytes_per_step": B * T * esz * world, "steps": e2e_steps},
+            "gpu_launches": int(launches),
+            "roofline": roofline,
+        }
+        if world == 1 and not args.no_cpu:
+            out["cpu_baseline"] = cpu_baseline(meta, sd)
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--dtype", default=os.environ.get("RAVE_BENCH_DTYPE", "f32"), choices=["bf16", "f32"])
+    ap.add_argument("--streams", type=int, default=STREAMS)
+    ap.add_argument("--samples", type=int, default=SAMPLES)
+    ap.add_argument("--microbatch", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -155,6 +155,11 @@ int rb_stream_state_elements(rb_handle* h, int64_t* per_stream);
 int rb_workspace_bytes(rb_handle* h, int B, int T, int dtype, size_t* bytes);
 int rb_kernel_launches(rb_handle* h, int64_t* count);   /* launches issued so far */
 int rb_set_microbatch(rb_handle* h, int streams);       /* 0 = automatic */
+/* Per-op device timing (CUDA events on the launching stream around every op of the
+ * program).  enable!=0 starts recording; rb_op_times synchronises, writes the accumulated
+ * milliseconds per op (n = number of ops) and clears the record. */
+int rb_profile_ops(rb_handle* h, int enable);
+int rb_op_times(rb_handle* h, float* ms, int n);
 const char* rb_last_error(void);
 int rb_abi_version(void);
 

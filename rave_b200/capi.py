@@ -62,6 +62,8 @@ EXPORTS = {
     "rb_workspace_bytes": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)],
     "rb_kernel_launches": [C.c_void_p, C.POINTER(C.c_int64)],
     "rb_set_microbatch": [C.c_void_p, C.c_int],
+    "rb_profile_ops": [C.c_void_p, C.c_int],
+    "rb_op_times": [C.c_void_p, C.POINTER(C.c_float), C.c_int],
     "rb_last_error": [],
     "rb_abi_version": [],
 }

@@ -59,6 +59,18 @@ static int pool_get(rb_handle* h, size_t bytes, int* idx) {
   return RB_OK;
 }
 
+OpTimer::OpTimer(rb_handle* h_, int oi_, cudaStream_t s_) : h(h_), s(s_), oi(oi_), on(h_->profile) {
+  if (!on) return;
+  rb_handle::Ev e{oi, nullptr, nullptr};
+  cudaEventCreate(&e.a);
+  cudaEventCreate(&e.b);
+  cudaEventRecord(e.a, s);
+  h->events.push_back(e);
+}
+OpTimer::~OpTimer() {
+  if (on) cudaEventRecord(h->events.back().b, s);
+}
+
 // ------------------------------------------------------------------------- op interpreter
 int exec_op_f32(RunCtx& c, int oi) {
   const rb_op& op = c.h->ops[oi];
@@ -170,7 +182,11 @@ static int run_offline_f32(rb_handle* h, int op_begin, int op_end, int in_slot, 
       if (op.src2 >= 0 && op.kind != RB_OP_NOISE_V2)
         RB_CHECK(c.v[op.src2].p, RB_ERR_STATE, "op %d reads slot %d before it is written", i, op.src2);
       RB_CHECK(c.v[op.src].p, RB_ERR_STATE, "op %d reads slot %d before it is written", i, op.src);
-      int rc = exec_op_f32(c, i);
+      int rc;
+      {
+        OpTimer tm(h, i, s);
+        rc = exec_op_f32(c, i);
+      }
       if (rc) return rc;
       const int used[3] = {op.src, op.res, op.src2};
       for (int u : used)
@@ -455,6 +471,27 @@ int rb_set_noise(rb_handle* h, const float* noise, int64_t numel) {
   RB_CHECK(h, RB_ERR_INVALID, "null handle");
   h->noise = noise;
   h->noise_numel = noise ? numel : 0;
+  return RB_OK;
+}
+
+int rb_profile_ops(rb_handle* h, int enable) {
+  RB_CHECK(h, RB_ERR_INVALID, "null handle");
+  h->profile = enable != 0;
+  return RB_OK;
+}
+
+int rb_op_times(rb_handle* h, float* ms, int n) {
+  RB_CHECK(h && ms && n == (int)h->ops.size(), RB_ERR_INVALID, "rb_op_times: n must equal the op count");
+  for (int i = 0; i < n; ++i) ms[i] = 0.f;
+  for (auto& e : h->events) {
+    float t = 0.f;
+    RB_CUDA(cudaEventSynchronize(e.b));
+    RB_CUDA(cudaEventElapsedTime(&t, e.a, e.b));
+    ms[e.op] += t;
+    cudaEventDestroy(e.a);
+    cudaEventDestroy(e.b);
+  }
+  h->events.clear();
   return RB_OK;
 }
 

@@ -24,6 +24,13 @@ struct RunCtx {
 
 int exec_op_f32(RunCtx& c, int oi);
 
+// RAII: records a start/stop event pair for op `oi` when profiling is on
+struct OpTimer {
+  rb_handle* h; cudaStream_t s; int oi; bool on;
+  OpTimer(rb_handle* h, int oi, cudaStream_t s);
+  ~OpTimer();
+};
+
 struct OpWeights {
   float* w = nullptr;       // fp32 engine packing ([c_in][k][c_out]; PQMF: see engine.cu)
   float* bias = nullptr;
@@ -79,6 +86,11 @@ struct rb_handle {
   void* dev_in = nullptr;
   void* dev_out = nullptr;
   size_t stage_elems = 0;
+
+  // per-op profiling (rb_profile_ops)
+  bool profile = false;
+  struct Ev { int op; cudaEvent_t a, b; };
+  std::vector<Ev> events;
 
   std::atomic_flag busy = ATOMIC_FLAG_INIT;
   long long launches = 0;

@@ -259,5 +259,14 @@ class RAVE:
         capi.check(self._lib.rb_stream_state_elements(self._h, C.byref(n)))
         return n.value
 
+    def profile_ops(self, enable=True):
+        capi.check(self._lib.rb_profile_ops(self._h, int(enable)))
+
+    def op_times_ms(self):
+        n = len(self.spec.ops)
+        buf = (C.c_float * n)()
+        capi.check(self._lib.rb_op_times(self._h, buf, n))
+        return list(buf)
+
     def set_microbatch(self, streams):
         capi.check(self._lib.rb_set_microbatch(self._h, int(streams)))
