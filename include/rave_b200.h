@@ -161,6 +161,23 @@ int rb_set_microbatch(rb_handle* h, int streams);       /* 0 = automatic */
 int rb_profile_ops(rb_handle* h, int enable);
 int rb_op_times(rb_handle* h, float* ms, int n);
 const char* rb_last_error(void);
+
+/* Testing hook (tests/test_gpu_tc_conv.py): one conv op of the bf16 tensor-core engine, or
+ * a conv + 1x1-conv pair (a DilatedUnit, fused when the planner fuses it), on HOST fp32
+ * data.  Not part of the drop-in surface. */
+typedef struct rb_debug_conv {
+  rb_op op[2];            /* kind/src/dst/res are filled in by the library                  */
+  int32_t n_ops;          /* 1, or 2: op[1] is the 1x1 conv whose residual is op[0]'s input */
+  int32_t B, n_in;        /* streams, input samples per stream                              */
+  const float* w[2];      /* folded fp32 [c_out][c_in][k]                                   */
+  const float* bias[2];   /* [c_out / ileave] or NULL                                       */
+  const float* alpha[2];  /* Snake alpha [c_in] or NULL                                     */
+  const float* x;         /* [B][c_in][n_in]                                                */
+  const float* res;       /* n_ops == 1: optional residual [B][c_out][n_out]                */
+  float* y;               /* [B][c_out / ileave][n_out]                                     */
+  int32_t* fused_out;     /* optional: set to 1 when the pair ran as one fused kernel       */
+} rb_debug_conv;
+int rb_debug_conv_bf16(const rb_debug_conv* d);
 int rb_abi_version(void);
 
 #ifdef __cplusplus

@@ -42,7 +42,16 @@ class RbTensorDesc(C.Structure):
                 ("numel", C.c_int64)]
 
 
+class RbDebugConv(C.Structure):
+    _fields_ = [("op", RbOp * 2), ("n_ops", C.c_int32), ("B", C.c_int32), ("n_in", C.c_int32),
+                ("w", C.POINTER(C.c_float) * 2), ("bias", C.POINTER(C.c_float) * 2),
+                ("alpha", C.POINTER(C.c_float) * 2), ("x", C.POINTER(C.c_float)),
+                ("res", C.POINTER(C.c_float)), ("y", C.POINTER(C.c_float)),
+                ("fused_out", C.POINTER(C.c_int32))]
+
+
 EXPORTS = {
+    "rb_debug_conv_bf16": [C.POINTER(RbDebugConv)],
     "rb_create": [C.POINTER(RbNetSpec), C.c_int, C.POINTER(C.c_void_p)],
     "rb_destroy": [C.c_void_p],
     "rb_load_weights": [C.c_void_p, C.POINTER(RbTensorDesc), C.c_int],

@@ -35,7 +35,7 @@ static int upload(const float* host, size_t n, float** dev) {
 
 
 // ------------------------------------------------------------------ offline workspace pool
-static int pool_get(rb_handle* h, size_t bytes, int* idx) {
+int pool_get(rb_handle* h, size_t bytes, int* idx) {
   int best = -1;
   for (size_t i = 0; i < h->pool.size(); ++i)
     if (!h->pool[i].busy && h->pool[i].bytes >= bytes &&
@@ -295,6 +295,7 @@ int rb_load_weights(rb_handle* h, const rb_tensor_desc* t, int n) {
           for (int m = 0; m < op.c_out && m < 8; ++m)
             for (int j = 0; j < op.k; ++j) p[(size_t)j * 8 + m] = d.data[(size_t)m * op.k + j];
           rc = upload(p.data(), p.size(), &w.w);
+          w.w_host.assign(d.data, d.data + d.numel);
         } else if (op.kind == RB_OP_PQMF_INV) {
           // synthesis weight [m][c][j] -> [c][j][m]
           const int M = op.n_band;
@@ -305,6 +306,7 @@ int rb_load_weights(rb_handle* h, const rb_tensor_desc* t, int n) {
               for (int j = 0; j < op.k; ++j)
                 p[((size_t)c * op.k + j) * M + m] = d.data[((size_t)m * M + c) * op.k + j];
           rc = upload(p.data(), p.size(), &w.w);
+          w.w_host.assign(d.data, d.data + d.numel);
         } else {
           RB_CHECK(op.kind == RB_OP_CONV, RB_ERR_INVALID, "op %d takes no conv weight", d.op);
           RB_CHECK(d.numel == (int64_t)op.c_out * op.c_in * op.k, RB_ERR_INVALID,
@@ -323,10 +325,12 @@ int rb_load_weights(rb_handle* h, const rb_tensor_desc* t, int n) {
       case RB_W_BIAS:
         RB_CHECK(d.numel == op.c_out / std::max(op.ileave, 1), RB_ERR_INVALID, "op %d: bias size", d.op);
         rc = upload(d.data, d.numel, &w.bias);
+        w.bias_host.assign(d.data, d.data + d.numel);
         break;
       case RB_W_ALPHA:
         RB_CHECK(d.numel == op.c_in, RB_ERR_INVALID, "op %d: alpha size", d.op);
         rc = upload(d.data, d.numel, &w.alpha);
+        w.alpha_host.assign(d.data, d.data + d.numel);
         break;
       case RB_W_AFFINE_A:
       case RB_W_AFFINE_B: {
@@ -423,6 +427,9 @@ int rb_forward(rb_handle* h, const void* x, int B, int T, int dtype, void* y, vo
   BusyGuard g(h);
   RB_CHECK(g.ok, RB_ERR_STATE, "handle is busy on another thread");
   const int F = T / h->spec.samples_per_frame;
+  if (dtype == RB_BF16)   // one program: the latent stays on the device in the engine's layout
+    return run_any(h, 0, h->spec.n_ops, h->spec.enc_in_slot, h->spec.dec_out_slot, x, y, B, F, dtype,
+                   (cudaStream_t)stream);
   const size_t esz = dtype == RB_BF16 ? 2 : 4;
   // latent scratch lives in a dedicated buffer (small)
   const size_t zbytes = (size_t)B * zo.channels * ((F + 3) & ~3) * esz;

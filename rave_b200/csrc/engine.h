@@ -23,6 +23,7 @@ struct RunCtx {
 };
 
 int exec_op_f32(RunCtx& c, int oi);
+int pool_get(rb_handle* h, size_t bytes, int* idx);   // offline workspace pool (engine.cu)
 
 // RAII: records a start/stop event pair for op `oi` when profiling is on
 struct OpTimer {
@@ -39,10 +40,9 @@ struct OpWeights {
   float* aff_b = nullptr;
   int aff_rows = 0;
   float* cond = nullptr;
-  // bf16 tensor-core engine packing (tc_engine.cu)
-  void* w_tc = nullptr;
-  int tc_kpad = 0;
-  std::vector<float> w_host;   // folded fp32 [c_out][c_in][k] kept for the bf16 packer
+  // host copies kept for the bf16 tensor-core packer (tc_engine.cu)
+  std::vector<float> w_host;   // folded fp32 [c_out][c_in][k] (PQMF: as loaded)
+  std::vector<float> bias_host, alpha_host;
 };
 
 struct PoolBuf {
@@ -91,6 +91,8 @@ struct rb_handle {
   bool profile = false;
   struct Ev { int op; cudaEvent_t a, b; };
   std::vector<Ev> events;
+
+  void* tc = nullptr;           // rb::tc::Plan of the bf16 engine (tc_engine.cu)
 
   std::atomic_flag busy = ATOMIC_FLAG_INIT;
   long long launches = 0;

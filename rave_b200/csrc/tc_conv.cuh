@@ -1,0 +1,70 @@
+// tc_conv.cuh -- parameters of the tcgen05 implicit-GEMM convolution kernel (tc_conv.cu).
+//
+// Every convolution of the path (cc.Conv1d, strided cc.Conv1d, cc.ConvTranspose1d as r
+// phase-convs, both PQMF banks) is expressed in the bf16 engine as a ROW-SHIFT GEMM over
+// channels-last activations [stream][row][channel]:
+//
+//     D[t, n] = sum_taps j  sum_c  A[t + j*dil - off, c] * W_j[n, c]
+//
+// where a "row" is one time step of the (possibly reshaped) tensor: a stride-s conv reads
+// its input as [T/s][s*C] and a transposed conv writes its output as [T][r*C'] -- the same
+// bytes in memory, so striding and phase interleave cost nothing.  M = 128 rows (time) per
+// MMA, N = output channels, K = input channels of one tap.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rb {
+namespace tc {
+
+constexpr int TC_MAX_NT = 8;        // output-channel tiles per layer
+constexpr int TC_THREADS = 320;     // warps 0-3 epilogue, 4-7 A loaders, 8 MMA issuer, 9 W producer
+
+// [stream][ld rows][C] bf16; element (b, t, c) at p[((size_t)b*ld + hist + t)*C + c], t in [lo, n)
+struct TcView {
+  const __nv_bfloat16* p;
+  int C, ld, hist, n, lo;
+};
+
+struct TcParams {
+  TcView x;                 // input (row view)
+  TcView y;                 // output (row view); written rows [0, y.n)
+  TcView res;               // residual added to the output (res.p == nullptr: none)
+  int res_delay;            // residual row = t - res_delay (AlignBranches delay, streaming)
+  const __nv_bfloat16* w;   // packed weight blocks, consumption order (see tc_engine.cu)
+  const uint64_t* masks;    // [n_ntiles][n_kchunks] active-tap bit masks
+  const float* bias;        // [N_total] or nullptr
+  const float* alpha;       // Snake alpha of the pre-activation per view channel, or nullptr
+  const float* aff_a;       // AdaIN scale  [rows][c_in] applied before the pre-activation, or nullptr
+  const float* aff_b;       // AdaIN shift
+  int aff_C;                // channels of the affine tables (un-reshaped tensor)
+  int pre_act;              // rb_act on the input
+  int B;
+  int n_taps, dil, off;     // row taps: shift_j = j*dil - off
+  int KC, n_kchunks;        // input channels per K chunk (multiple of 16), chunks per row
+  int N_TILE, n_ntiles;     // output channels per tile (multiple of 16, <= 256)
+  int nt_base[TC_MAX_NT + 1];   // first weight block of each n-tile
+  int MT;                   // 128-row sub-tiles per work item (1 or 2)
+  int R, R_ALLOC;           // A rows per stage (MT*128 + max shift), allocated (odd)
+  int w_resident;           // all blocks live in smem for the whole kernel
+  int SA, SW, SD;           // A stages, W stages (streamed), accumulator stages
+  int out_mask;             // 1: negate odd channels at even rows (pqmf.py:13-17 reverse_half)
+  int tiles_per_stream, n_work;
+  // fused DilatedUnit (blocks.py:84-113 + Residual :32-46): second GEMM k=1 on act(D1 + bias)
+  int fused;
+  int act2;                 // activation between the two convs
+  const float* bias2;
+  const float* alpha2;
+  int n_blk1;               // weight blocks of GEMM1 (GEMM2 blocks follow)
+  int SH;                   // h stages
+  // shared memory carve-up (bytes from the 1024-aligned base)
+  uint32_t off_bias, off_a, off_w, off_h, smem_bytes;
+  uint32_t a_stage_bytes, w_blk_bytes, h_stage_bytes;
+  uint32_t tmem_cols;       // power of two >= 32
+};
+
+int launch_tc_conv(const TcParams& p, cudaStream_t s);
+
+}  // namespace tc
+}  // namespace rb

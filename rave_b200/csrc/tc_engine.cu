@@ -1,15 +1,821 @@
-// tc_engine.cu -- bf16 tensor-core engine (tcgen05 / TMEM / TMA implicit-GEMM convolutions).
-// Placeholder until the tcgen05 path lands: the bf16 dtype fails loudly, it never falls back.
+// tc_engine.cu -- bf16 tensor-core engine: layer planning / weight packing for the tcgen05
+// implicit-GEMM kernel (tc_conv.cu), the small channels-last elementwise kernels, and the
+// op interpreter for dtype == RB_BF16.
+//
+// Activation layout: channels-last  [stream][row][Cp]  bf16, Cp = channels rounded up to 16
+// (audio slots: Cp = 1).  A stride-s conv reads its input through the view [rows/s][s*Cp],
+// a transposed conv writes its output through [rows][r*Cp'] -- same bytes, no copies -- so
+// every conv of the path becomes a stride-1 row-shift GEMM (tc_conv.cuh).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
 #include "engine.h"
+#include "tc_conv.cuh"
 
 namespace rb {
+namespace tc {
 
-int tc_pack_weights(rb_handle*) { return RB_OK; }
-void tc_free(rb_handle*) {}
+static inline int round16(int v) { return (v + 15) & ~15; }
+static inline int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 
-int tc_run_program(rb_handle*, int, int, const void*, void*, int, int, cudaStream_t) {
-  set_error("the bf16 tensor-core engine is not built into this library");
-  return RB_ERR_UNSUPPORTED;
+// One convolution-like op, planned: geometry in VIEW units + packed device weights.
+struct Layer {
+  bool valid = false;
+  int fin = 1, fout = 1;          // view factors of the input / output slot
+  int cin_v = 0;                  // view input channels (fin * Cp_in)
+  int n_taps = 1, dil = 1, off = 0;
+  int N_total = 0, N_TILE = 0, n_ntiles = 0;
+  int KC = 0, n_kchunks = 0;
+  int out_mask = 0;
+  std::vector<int> nt_base;       // [n_ntiles + 1]
+  int total_blocks = 0;
+  uint32_t blk_bytes = 0;
+  __nv_bfloat16* w = nullptr;     // device, packed blocks
+  uint64_t* masks = nullptr;      // device [n_ntiles][n_kchunks]
+  float* bias = nullptr;          // device [N_total] (nullptr: none)
+  float* alpha = nullptr;         // device [cin_v]   (Snake pre-activation)
+  // fused DilatedUnit: this layer also carries the 1x1 conv that follows it
+  bool fused = false;
+  int fused_with = -1;            // op index of the 1x1 conv
+  float* bias2 = nullptr;
+  float* alpha2 = nullptr;
+  int act2 = 0;
+};
+
+struct Plan {
+  std::vector<Layer> layers;      // per op
+  std::vector<int> skip;          // op is the tail of a fused pair
+  std::vector<int> cp;            // per slot channel pitch
+};
+
+static int slot_cp(const rb_handle* h, int sl) {
+  if (sl == h->spec.enc_in_slot || sl == h->spec.dec_out_slot) return 1;   // audio [B][T]
+  return round16(h->slots[sl].channels);
+}
+
+template <typename T>
+static int dev_upload(const std::vector<T>& v, T** dev) {
+  RB_CUDA(cudaMalloc((void**)dev, std::max<size_t>(v.size(), 1) * sizeof(T)));
+  RB_CUDA(cudaMemcpy(*dev, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return RB_OK;
+}
+
+static inline __nv_bfloat16 f2bf(float f) { return __float2bfloat16_rn(f); }
+
+// View-space weight of one op: Wv[n][c][j], n < N_total, c < cin_v, j < n_taps (zero padded).
+struct ViewWeight {
+  int N_total, cin_v, n_taps, dil, off, fin, fout, out_mask;
+  std::vector<float> w;
+  std::vector<float> bias;    // [N_total] (empty: none)
+  std::vector<float> alpha;   // [cin_v]   (empty: none)
+  float& at(int n, int c, int j) { return w[((size_t)n * cin_v + c) * n_taps + j]; }
+};
+
+// conv geometry -> view geometry.  x index of tap j at output t: t*stride + j*dil - off.
+static void view_geometry(int k, int stride, int dil, int off, ViewWeight& v) {
+  if (stride == 1) {
+    v.n_taps = k; v.dil = dil; v.off = off;
+  } else {
+    const int jmin = floordiv(-off, stride), jmax = floordiv((k - 1) * dil - off, stride);
+    v.n_taps = jmax - jmin + 1; v.dil = 1; v.off = -jmin;
+  }
+}
+
+static int build_view_weight(const rb_handle* h, int oi, const Plan& pl, ViewWeight& v) {
+  const rb_op& op = h->ops[oi];
+  const OpWeights& ow = h->w[oi];
+  const int cp_in = pl.cp[op.src];
+  RB_CHECK(op.src_ch_off == 0, RB_ERR_UNSUPPORTED, "op %d: src_ch_off is not supported by the bf16 engine", oi);
+  if (op.kind == RB_OP_CONV) {
+    const int r = std::max(op.ileave, 1);
+    const int c_out_ph = op.c_out / r;                 // channels per phase
+    const int cpo = round16(c_out_ph);
+    RB_CHECK(pl.cp[op.dst] == cpo, RB_ERR_INVALID, "op %d: output pitch mismatch", oi);
+    v.fin = op.stride; v.fout = r; v.out_mask = 0;
+    v.cin_v = op.stride * cp_in;
+    v.N_total = r * cpo;
+    view_geometry(op.k, op.stride, op.dilation, op.off, v);
+    v.w.assign((size_t)v.N_total * v.cin_v * v.n_taps, 0.f);
+    RB_CHECK(ow.w_host.size() == (size_t)op.c_out * op.c_in * op.k, RB_ERR_STATE, "op %d: no host weight", oi);
+    const int jmin = op.stride == 1 ? 0 : floordiv(-op.off, op.stride);
+    for (int co = 0; co < op.c_out; ++co) {
+      const int ph = co / c_out_ph, cc = co - ph * c_out_ph;
+      const int n = ph * cpo + cc;
+      for (int ci = 0; ci < op.c_in; ++ci)
+        for (int j = 0; j < op.k; ++j) {
+          const float wv = ow.w_host[((size_t)co * op.c_in + ci) * op.k + j];
+          if (op.stride == 1) {
+            v.at(n, ci, j) = wv;
+          } else {
+            const int q = j * op.dilation - op.off;
+            const int row = floordiv(q, op.stride), sub = q - row * op.stride;
+            v.at(n, sub * cp_in + ci, row - jmin) = wv;
+          }
+        }
+    }
+    if (op.has_bias) {
+      RB_CHECK((int)ow.bias_host.size() == c_out_ph, RB_ERR_STATE, "op %d: no host bias", oi);
+      v.bias.assign(v.N_total, 0.f);
+      for (int ph = 0; ph < r; ++ph)
+        for (int cc = 0; cc < c_out_ph; ++cc) v.bias[ph * cpo + cc] = ow.bias_host[cc];
+    }
+    if (op.pre_act == RB_ACT_SNAKE) {
+      RB_CHECK((int)ow.alpha_host.size() == op.c_in, RB_ERR_STATE, "op %d: Snake alpha not loaded", oi);
+      v.alpha.assign(v.cin_v, 1.f);
+      for (int sub = 0; sub < op.stride; ++sub)
+        for (int ci = 0; ci < op.c_in; ++ci) v.alpha[sub * cp_in + ci] = ow.alpha_host[ci];
+    }
+    return RB_OK;
+  }
+  if (op.kind == RB_OP_PQMF_FWD) {
+    // Conv1d(1 -> M, k, stride M) on the audio viewed as [T/M][M]; keep c_out bands; the
+    // reverse_half sign flip (pqmf.py:13-17) is the epilogue's out_mask.
+    const int M = op.n_band;
+    RB_CHECK(ow.w_host.size() == (size_t)M * op.k, RB_ERR_STATE, "pqmf analysis weight missing");
+    v.fin = M; v.fout = 1; v.out_mask = 1;
+    v.cin_v = M * cp_in;                       // cp_in == 1
+    v.N_total = round16(op.c_out);
+    view_geometry(op.k, M, 1, op.off, v);
+    v.w.assign((size_t)v.N_total * v.cin_v * v.n_taps, 0.f);
+    const int jmin = floordiv(-op.off, M);
+    for (int m = 0; m < op.c_out; ++m)
+      for (int j = 0; j < op.k; ++j) {
+        const int q = j - op.off, row = floordiv(q, M), sub = q - row * M;
+        v.at(m, sub, row - jmin) = ow.w_host[(size_t)m * op.k + j];
+      }
+    return RB_OK;
+  }
+  if (op.kind == RB_OP_PQMF_INV) {
+    // out[t*M + (M-1-m)] = M * sum_c sum_j w[m][c][j] xr[c][t + j - off]  (pqmf.py:275-284);
+    // xr = reverse_half(x) is written by the head kernels (the only producers of this slot).
+    const int M = op.n_band;
+    RB_CHECK(ow.w_host.size() == (size_t)M * M * op.k, RB_ERR_STATE, "pqmf synthesis weight missing");
+    RB_CHECK(cp_in == M, RB_ERR_UNSUPPORTED, "pqmf synthesis expects %d-channel input", M);
+    v.fin = 1; v.fout = M; v.out_mask = 0;
+    v.cin_v = cp_in;
+    v.N_total = M;
+    view_geometry(op.k, 1, 1, op.off, v);
+    v.w.assign((size_t)v.N_total * v.cin_v * v.n_taps, 0.f);
+    for (int m = 0; m < M; ++m)
+      for (int c = 0; c < M; ++c)
+        for (int j = 0; j < op.k; ++j)
+          v.at(M - 1 - m, c, j) = (float)M * ow.w_host[((size_t)m * M + c) * op.k + j];
+    return RB_OK;
+  }
+  set_error("op %d is not a convolution", oi);
+  return RB_ERR_INVALID;
+}
+
+static int largest_div16(int v, int cap) {
+  int best = 16;
+  for (int d = 16; d <= cap && d <= v; d += 16)
+    if (v % d == 0) best = d;
+  return best;
+}
+
+static void free_layer(Layer& L) {
+  cudaFree(L.w); cudaFree(L.masks); cudaFree(L.bias); cudaFree(L.alpha); cudaFree(L.bias2); cudaFree(L.alpha2);
+  L = Layer();
+}
+
+// Pack Wv into [N_TILE][KC] blocks (UMMA K-major no-swizzle core-matrix order) in the order
+// the kernel consumes them: n-tile, K chunk, active tap.  `extra` (fused 1x1 conv) appended.
+static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, Layer& L) {
+  L.fin = v.fin; L.fout = v.fout; L.cin_v = v.cin_v; L.n_taps = v.n_taps; L.dil = v.dil; L.off = v.off;
+  L.N_total = v.N_total; L.out_mask = v.out_mask;
+  RB_CHECK(v.n_taps <= 64, RB_ERR_UNSUPPORTED, "conv with %d row taps (max 64)", v.n_taps);
+  L.N_TILE = largest_div16(v.N_total, 256);
+  L.n_ntiles = v.N_total / L.N_TILE;
+  RB_CHECK(L.n_ntiles <= TC_MAX_NT, RB_ERR_UNSUPPORTED, "too many output-channel tiles");
+  L.KC = largest_div16(v.cin_v, kc_cap);
+  L.n_kchunks = v.cin_v / L.KC;
+  L.blk_bytes = (uint32_t)L.N_TILE * L.KC * 2;
+  std::vector<uint64_t> masks((size_t)L.n_ntiles * L.n_kchunks, 0);
+  for (int nt = 0; nt < L.n_ntiles; ++nt) {
+    bool any = false;
+    for (int kc = 0; kc < L.n_kchunks; ++kc) {
+      uint64_t m = 0;
+      for (int j = 0; j < v.n_taps; ++j) {
+        bool nz = false;
+        for (int n = nt * L.N_TILE; n < (nt + 1) * L.N_TILE && !nz; ++n)
+          for (int c = kc * L.KC; c < (kc + 1) * L.KC; ++c)
+            if (v.w[((size_t)n * v.cin_v + c) * v.n_taps + j] != 0.f) { nz = true; break; }
+        if (nz) m |= (uint64_t)1 << j;
+      }
+      masks[(size_t)nt * L.n_kchunks + kc] = m;
+      any |= m != 0;
+    }
+    if (!any) masks[(size_t)nt * L.n_kchunks] = 1;   // keep the accumulator defined
+  }
+  L.nt_base.assign(L.n_ntiles + 1, 0);
+  std::vector<__nv_bfloat16> blocks;
+  int nblk = 0;
+  for (int nt = 0; nt < L.n_ntiles; ++nt) {
+    L.nt_base[nt] = nblk;
+    for (int kc = 0; kc < L.n_kchunks; ++kc)
+      for (int j = 0; j < v.n_taps; ++j) {
+        if (!((masks[(size_t)nt * L.n_kchunks + kc] >> j) & 1)) continue;
+        const size_t base = blocks.size();
+        blocks.resize(base + (size_t)L.N_TILE * L.KC);
+        for (int n = 0; n < L.N_TILE; ++n)
+          for (int c = 0; c < L.KC; ++c)
+            blocks[base + (size_t)(c >> 3) * (L.N_TILE * 8) + (size_t)n * 8 + (c & 7)] =
+                f2bf(v.w[((size_t)(nt * L.N_TILE + n) * v.cin_v + kc * L.KC + c) * v.n_taps + j]);
+        ++nblk;
+      }
+  }
+  L.nt_base[L.n_ntiles] = nblk;
+  L.total_blocks = nblk;
+  if (extra) {
+    // 1x1 conv of the fused unit: K = N_TILE channels in chunks of KC, same block shape
+    for (int kc = 0; kc < L.N_TILE / L.KC; ++kc) {
+      const size_t base = blocks.size();
+      blocks.resize(base + (size_t)L.N_TILE * L.KC);
+      for (int n = 0; n < L.N_TILE; ++n)
+        for (int c = 0; c < L.KC; ++c)
+          blocks[base + (size_t)(c >> 3) * (L.N_TILE * 8) + (size_t)n * 8 + (c & 7)] =
+              f2bf(extra->w[((size_t)n * extra->cin_v + kc * L.KC + c) * extra->n_taps]);
+    }
+  }
+  int rc = dev_upload(blocks, &L.w);
+  if (rc) return rc;
+  if ((rc = dev_upload(masks, &L.masks))) return rc;
+  if (!v.bias.empty() && (rc = dev_upload(v.bias, &L.bias))) return rc;
+  if (!v.alpha.empty() && (rc = dev_upload(v.alpha, &L.alpha))) return rc;
+  L.valid = true;
+  return RB_OK;
+}
+
+// ------------------------------------------------------------------ buffers and launches
+// One activation tensor of the bf16 engine, in un-reshaped row units.
+struct Buf {
+  __nv_bfloat16* p = nullptr;
+  int cp = 0, ld = 0, hist = 0, n = 0, lo = 0;
+};
+
+static int make_view(const Buf& b, int f, TcView* v) {
+  RB_CHECK(b.ld % f == 0 && b.hist % f == 0 && b.n % f == 0, RB_ERR_INVALID,
+           "tensor rows (%d,%d,%d) not divisible by the view factor %d", b.ld, b.hist, b.n, f);
+  v->p = b.p; v->C = b.cp * f; v->ld = b.ld / f; v->hist = b.hist / f; v->n = b.n / f;
+  v->lo = floordiv(b.lo, f);
+  return RB_OK;
+}
+
+static uint32_t align_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
+
+static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Buf& src, const Buf& dst,
+                     const Buf* res, int B, cudaStream_t s) {
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  int rc = make_view(src, L.fin, &p.x);
+  if (rc) return rc;
+  if ((rc = make_view(dst, L.fout, &p.y))) return rc;
+  RB_CHECK(p.x.C == L.cin_v && p.y.C == L.N_total, RB_ERR_INVALID, "layer/view channel mismatch (%d vs %d, %d vs %d)",
+           p.x.C, L.cin_v, p.y.C, L.N_total);
+  const rb_op& rop = op2 ? *op2 : op;
+  if (res) {
+    if ((rc = make_view(*res, 1, &p.res))) return rc;
+    RB_CHECK(L.fout == 1 && p.res.C == L.N_total, RB_ERR_INVALID, "residual shape mismatch");
+    p.res_delay = rop.res_delay;
+  }
+  p.w = L.w; p.masks = L.masks; p.bias = L.bias; p.alpha = L.alpha;
+  p.pre_act = op.pre_act;
+  p.B = B;
+  p.n_taps = L.n_taps; p.dil = L.dil; p.off = L.off;
+  p.KC = L.KC; p.n_kchunks = L.n_kchunks;
+  p.N_TILE = L.N_TILE; p.n_ntiles = L.n_ntiles;
+  for (int i = 0; i <= L.n_ntiles; ++i) p.nt_base[i] = L.nt_base[i];
+  p.out_mask = L.out_mask;
+  p.fused = L.fused ? 1 : 0;
+  p.act2 = L.act2; p.bias2 = L.bias2; p.alpha2 = L.alpha2; p.n_blk1 = L.total_blocks;
+  const int halo = (L.n_taps - 1) * L.dil;
+  const uint32_t budget = 224u * 1024u;
+  const uint32_t w_total = (uint32_t)(L.total_blocks + (L.fused ? L.N_TILE / L.KC : 0)) * L.blk_bytes;
+  p.w_blk_bytes = L.blk_bytes;
+  p.off_bias = 256;
+  const uint32_t fixed = align_up(256 + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
+  p.SH = L.fused ? 2 : 0;
+  p.h_stage_bytes = L.fused ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
+  const uint32_t h_total = p.SH * p.h_stage_bytes;
+  // resident weights when the whole layer fits beside >= 2 A stages, else a streamed ring
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    const bool resident = attempt == 0 && (L.n_ntiles == 1) && w_total <= 160u * 1024u;
+    if (attempt == 0 && !resident) continue;
+    RB_CHECK(resident || !L.fused, RB_ERR_UNSUPPORTED, "fused unit does not fit in shared memory");
+    p.w_resident = resident ? 1 : 0;
+    p.MT = (!resident && p.y.n >= 256) ? 2 : 1;
+    p.R = p.MT * 128 + halo;
+    p.R_ALLOC = p.R | 1;
+    p.a_stage_bytes = align_up((uint32_t)(L.KC / 8) * p.R_ALLOC * 16u, 128);
+    p.SW = resident ? 0 : 4;
+    uint32_t w_bytes = resident ? align_up(w_total, 128) : p.SW * L.blk_bytes;
+    if (!resident && fixed + w_bytes + 2 * p.a_stage_bytes > budget) { p.SW = 2; w_bytes = p.SW * L.blk_bytes; }
+    if (fixed + w_bytes + h_total + p.a_stage_bytes > budget) {
+      RB_CHECK(resident, RB_ERR_UNSUPPORTED, "conv tile does not fit in shared memory");
+      continue;
+    }
+    const uint32_t room = budget - fixed - w_bytes - h_total;
+    p.SA = (int)std::min<uint32_t>(4, room / p.a_stage_bytes);
+    if (resident && p.SA < 2) continue;
+    p.off_a = fixed;
+    p.off_w = p.off_a + p.SA * p.a_stage_bytes;
+    p.off_h = p.off_w + w_bytes;
+    p.smem_bytes = p.off_h + h_total;
+    break;
+  }
+  RB_CHECK(p.SA >= 1, RB_ERR_UNSUPPORTED, "conv tile does not fit in shared memory");
+  const int acc_cols = L.fused ? 2 * L.N_TILE : p.MT * L.N_TILE;
+  p.SD = (2 * acc_cols <= 512) ? 2 : 1;
+  RB_CHECK(!L.fused || p.SD == 2, RB_ERR_UNSUPPORTED, "fused unit needs two accumulator stages");
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(p.SD * acc_cols)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.tiles_per_stream = (p.y.n + p.MT * 128 - 1) / (p.MT * 128);
+  p.n_work = L.n_ntiles * B * p.tiles_per_stream;
+  return launch_tc_conv(p, s);
+}
+
+// ------------------------------------------------------- channels-last elementwise kernels
+// All of these are bandwidth-bound single passes; one thread per (row, 8-channel group) or
+// per element, rows of all streams flattened.
+__device__ __forceinline__ size_t row_index(const Buf& b, int bi, int t) {
+  return ((size_t)bi * b.ld + b.hist + t) * b.cp;
+}
+
+// [B][C][n] (caller layout, dense) -> [B][n][Cp]
+__global__ void cf_to_cl_kernel(const __nv_bfloat16* __restrict__ src, Buf dst, int C, int B) {
+  const size_t total = (size_t)B * dst.n * dst.cp;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % dst.cp);
+    const size_t r = i / dst.cp;
+    const int t = (int)(r % dst.n), b = (int)(r / dst.n);
+    dst.p[row_index(dst, b, t) + c] = c < C ? src[((size_t)b * C + c) * dst.n + t] : __float2bfloat16_rn(0.f);
+  }
+}
+// [B][n][Cp] -> [B][C][n]
+__global__ void cl_to_cf_kernel(Buf src, __nv_bfloat16* __restrict__ dst, int C, int B) {
+  const size_t total = (size_t)B * C * src.n;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int t = (int)(i % src.n);
+    const size_t r = i / src.n;
+    const int c = (int)(r % C), b = (int)(r / C);
+    dst[i] = src.p[row_index(src, b, t) + c];
+  }
+}
+// model.py:618-620: z = cat(z, speaker.repeat(B, 1, F)) (+ zero pad channels)
+__global__ void concat_cl_kernel(Buf z, Buf y, const float* __restrict__ cond, int c_z, int c_cond, int B) {
+  const size_t total = (size_t)B * y.n * y.cp;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % y.cp);
+    const size_t r = i / y.cp;
+    const int t = (int)(r % y.n), b = (int)(r / y.n);
+    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+    if (c < c_z) v = z.p[row_index(z, b, t) + c];
+    else if (c < c_z + c_cond) v = __float2bfloat16_rn(cond[c - c_z]);
+    y.p[row_index(y, b, t) + c] = v;
+  }
+}
+// AdaIN transfer (blocks.py:885-891) as x = a[b][c]*x + b[b][c], in place
+__global__ void affine_cl_kernel(Buf x, const float* __restrict__ a, const float* __restrict__ bb, int C, int B) {
+  const size_t total = (size_t)B * x.n * C;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const size_t r = i / C;
+    const int t = (int)(r % x.n), b = (int)(r / x.n);
+    __nv_bfloat16* q = x.p + row_index(x, b, t) + c;
+    *q = __float2bfloat16_rn(fmaf(__bfloat162float(*q), a[(size_t)b * C + c], bb[(size_t)b * C + c]));
+  }
+}
+// GeneratorV2.forward tail (blocks.py:699-707) + reverse_half of the synthesis bank input
+__global__ void head_v2_cl_kernel(Buf w, Buf nz, Buf y, int data, int am, int B) {
+  const size_t total = (size_t)B * y.n * y.cp;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % y.cp);
+    const size_t r = i / y.cp;
+    const int t = (int)(r % y.n), b = (int)(r / y.n);
+    float v = 0.f;
+    if (c < data) {
+      const __nv_bfloat16* wp = w.p + row_index(w, b, t);
+      v = __bfloat162float(wp[c]);
+      if (am) v *= 1.f / (1.f + expf(-__bfloat162float(wp[data + c])));
+      if (nz.p) v += __bfloat162float(nz.p[row_index(nz, b, t) + c]);
+      v = tanhf(v);
+      if ((c & 1) && !(t & 1)) v = -v;
+    }
+    y.p[row_index(y, b, t) + c] = __float2bfloat16_rn(v);
+  }
+}
+// Generator.forward tail (blocks.py:412): tanh(waveform) * mod_sigmoid(loudness)
+__global__ void head_v1_cl_kernel(Buf wv, Buf ld, Buf y, int data, int B) {
+  const size_t total = (size_t)B * y.n * y.cp;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % y.cp);
+    const size_t r = i / y.cp;
+    const int t = (int)(r % y.n), b = (int)(r / y.n);
+    float v = 0.f;
+    if (c < data) {
+      const float sg = 1.f / (1.f + expf(-__bfloat162float(ld.p[row_index(ld, b, t)])));
+      v = tanhf(__bfloat162float(wv.p[row_index(wv, b, t) + c])) * (2.f * powf(sg, 2.3f) + 1e-7f);
+      if ((c & 1) && !(t & 1)) v = -v;
+    }
+    y.p[row_index(y, b, t) + c] = __float2bfloat16_rn(v);
+  }
+}
+// NoiseGeneratorV2.forward tail (blocks.py:281-291, core.py:66,95-129) in closed form; one
+// thread per (stream, block q, band d) -- see kernels_f32.cu for the derivation.
+__global__ void noise_v2_cl_kernel(Buf amp, const float* __restrict__ noise, long long nbs, Buf y, int data,
+                                   int nblk, unsigned long long seed, int B) {
+  const size_t total = (size_t)B * nblk * data;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int d = (int)(i % data);
+    const size_t r = i / data;
+    const int q = (int)(r % nblk), b = (int)(r / nblk);
+    float a[5];
+    const __nv_bfloat16* ap = amp.p + row_index(amp, b, q) + d * 5;
+#pragma unroll
+    for (int n = 0; n < 5; ++n) {
+      const float hh = __bfloat162float(ap[n]) - 5.f;
+      const float sg = 1.f / (1.f + expf(-hh));
+      a[n] = 2.f * powf(sg, 2.3f) + 1e-7f;
+    }
+    float ir[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const float c1 = cospif(t * 0.25f), c2 = cospif(t * 0.5f), c3 = cospif(t * 0.75f);
+      const float c4 = (t & 1) ? -1.f : 1.f;
+      const float v = (a[0] + 2.f * (a[1] * c1 + a[2] * c2 + a[3] * c3) + a[4] * c4) * 0.125f;
+      const int u = (t + 4) & 7;
+      ir[t] = v * 0.5f * (1.f - cospif(u * 0.25f));
+    }
+    float nzv[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (noise) {
+        nzv[j] = noise[(size_t)b * nbs + ((size_t)q * data + d) * 8 + j];
+      } else {
+        unsigned long long z = seed + (((unsigned long long)b * nblk + q) * data * 8 + d * 8 + j) * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        nzv[j] = (float)(z >> 40) * (2.0f / 16777216.0f) - 1.0f;
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      float sacc = 0.f;
+#pragma unroll
+      for (int j = 0; j <= t; ++j) sacc = fmaf(nzv[j], ir[t - j], sacc);
+      y.p[row_index(y, b, q * 8 + t) + d] = __float2bfloat16_rn(sacc);
+    }
+  }
+}
+__global__ void zero_pad_channels_kernel(Buf y, int C, int B) {
+  const int padc = y.cp - C;
+  const size_t total = (size_t)B * y.n * padc;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = C + (int)(i % padc);
+    const size_t r = i / padc;
+    y.p[row_index(y, (int)(r / y.n), (int)(r % y.n)) + c] = __float2bfloat16_rn(0.f);
+  }
+}
+
+static inline int ew_grid(size_t total) {
+  return (int)std::min<size_t>((total + 255) / 256, 148 * 16);
+}
+#define RB_LAUNCH_EW(kernel, total, s, ...)                          \
+  do {                                                                \
+    if ((total) > 0) {                                                \
+      kernel<<<ew_grid(total), 256, 0, s>>>(__VA_ARGS__);             \
+      ++g_launches;                                                   \
+      RB_CUDA(cudaGetLastError());                                    \
+    }                                                                 \
+  } while (0)
+
+}  // namespace tc
+
+using namespace tc;
+
+void tc_free(rb_handle* h) {
+  Plan* pl = (Plan*)h->tc;
+  if (!pl) return;
+  for (auto& L : pl->layers) free_layer(L);
+  delete pl;
+  h->tc = nullptr;
+}
+
+// Plans every conv-like op (called when all weights are present; re-run on every reload).
+int tc_pack_weights(rb_handle* h) {
+  tc_free(h);
+  Plan* pl = new Plan();
+  h->tc = pl;
+  const int nops = (int)h->ops.size();
+  pl->layers.resize(nops);
+  pl->skip.assign(nops, 0);
+  pl->cp.resize(h->slots.size());
+  for (size_t s = 0; s < h->slots.size(); ++s) pl->cp[s] = slot_cp(h, (int)s);
+  for (int i = 0; i < nops; ++i) {
+    const rb_op& op = h->ops[i];
+    if (pl->skip[i]) continue;
+    if (op.kind != RB_OP_CONV && op.kind != RB_OP_PQMF_FWD && op.kind != RB_OP_PQMF_INV) continue;
+    ViewWeight v;
+    int rc = build_view_weight(h, i, *pl, v);
+    if (rc) return rc;
+    // DilatedUnit fusion: conv(k, dil) -> act -> conv(1x1) + residual of the unit's input
+    bool fuse = false;
+    ViewWeight v2;
+    if (op.kind == RB_OP_CONV && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {
+      const rb_op& o2 = h->ops[i + 1];
+      fuse = o2.kind == RB_OP_CONV && o2.k == 1 && o2.stride == 1 && o2.ileave <= 1 && op.stride == 1 &&
+             op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 &&
+             v.N_total == v.cin_v && v.N_total <= 64 && pl->cp[o2.dst] == v.N_total;
+      if (fuse) {
+        rc = build_view_weight(h, i + 1, *pl, v2);
+        if (rc) return rc;
+      }
+    }
+    Layer& L = pl->layers[i];
+    rc = pack_layer(v, fuse ? 128 : 64, fuse ? &v2 : nullptr, L);
+    if (rc) return rc;
+    if (fuse) {
+      L.fused = true;
+      L.fused_with = i + 1;
+      L.act2 = h->ops[i + 1].pre_act;
+      if (!v2.bias.empty() && (rc = dev_upload(v2.bias, &L.bias2))) return rc;
+      if (!v2.alpha.empty() && (rc = dev_upload(v2.alpha, &L.alpha2))) return rc;
+      pl->skip[i + 1] = 1;
+    }
+  }
+  return RB_OK;
+}
+
+// ------------------------------------------------------------------- offline op interpreter
+static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int B, const float* noise,
+                      int64_t noise_bstride, cudaStream_t s) {
+  const rb_op& op = h->ops[i];
+  const Layer& L = pl->layers[i];
+  switch (op.kind) {
+    case RB_OP_CONV:
+    case RB_OP_PQMF_FWD:
+    case RB_OP_PQMF_INV: {
+      RB_CHECK(L.valid, RB_ERR_STATE, "op %d has no bf16 plan", i);
+      if (L.fused) {
+        const rb_op& o2 = h->ops[L.fused_with];
+        return run_layer(L, op, &o2, bufs[op.src], bufs[o2.dst], &bufs[o2.res], B, s);
+      }
+      return run_layer(L, op, nullptr, bufs[op.src], bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s);
+    }
+    case RB_OP_AFFINE: {
+      const OpWeights& w = h->w[i];
+      RB_CHECK(w.aff_a && w.aff_b, RB_ERR_STATE, "op %d: AdaIN statistics not loaded", i);
+      RB_CHECK(B <= w.aff_rows, RB_ERR_INVALID,
+               "batch %d exceeds the %d rows of AdaIN statistics (cc.MAX_BATCH_SIZE)", B, w.aff_rows);
+      const Buf& x = bufs[op.src];
+      RB_LAUNCH_EW(affine_cl_kernel, (size_t)B * x.n * op.c_in, s, x, w.aff_a, w.aff_b, op.c_in, B);
+      return RB_OK;
+    }
+    case RB_OP_HEAD_V2: {
+      const Buf& y = bufs[op.dst];
+      RB_LAUNCH_EW(head_v2_cl_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src],
+                   op.src2 >= 0 ? bufs[op.src2] : Buf(), y, op.c_out, op.k, B);
+      return RB_OK;
+    }
+    case RB_OP_HEAD_V1: {
+      const Buf& y = bufs[op.dst];
+      RB_LAUNCH_EW(head_v1_cl_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src], bufs[op.src2], y, op.c_out, B);
+      return RB_OK;
+    }
+    case RB_OP_NOISE_V2: {
+      const Buf& amp = bufs[op.src];
+      const Buf& y = bufs[op.dst];
+      if (y.cp > op.c_out) RB_LAUNCH_EW(zero_pad_channels_kernel, (size_t)B * y.n * (y.cp - op.c_out), s, y, op.c_out, B);
+      RB_LAUNCH_EW(noise_v2_cl_kernel, (size_t)B * amp.n * op.c_out, s, amp, noise, (long long)noise_bstride, y,
+                   op.c_out, amp.n, h->noise_seed++, B);
+      return RB_OK;
+    }
+    case RB_OP_CONCAT_COND: {
+      const OpWeights& w = h->w[i];
+      RB_CHECK(w.cond, RB_ERR_STATE, "conditioning vector (speaker embedding) not loaded");
+      const Buf& y = bufs[op.dst];
+      RB_LAUNCH_EW(concat_cl_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src], y, w.cond, op.c_in,
+                   op.c_out - op.c_in, B);
+      return RB_OK;
+    }
+  }
+  set_error("op %d: unknown kind %d", i, op.kind);
+  return RB_ERR_INVALID;
+}
+
+// Runs ops [ob, oe) on bf16 buffers.  `in` / `out` are in the CALLER's layout ([B,1,T] audio
+// or [B,C,F] latents, dense); a range that spans both programs keeps the latent on the
+// device in channels-last form (rb_forward).
+int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int B, int F, cudaStream_t s) {
+  Plan* pl = (Plan*)h->tc;
+  RB_CHECK(pl, RB_ERR_STATE, "bf16 engine: weights are not packed");
+  const int ns = (int)h->slots.size();
+  const int n_enc = h->spec.n_enc_ops;
+  const bool has_enc = ob < n_enc, has_dec = oe > n_enc;
+  const int in_slot = has_enc ? h->spec.enc_in_slot : h->spec.dec_in_slot;
+  const int out_slot = has_dec ? h->spec.dec_out_slot : h->spec.enc_out_slot;
+  if (has_enc && has_dec)
+    RB_CHECK(pl->cp[h->spec.enc_out_slot] == pl->cp[h->spec.dec_in_slot], RB_ERR_INVALID,
+             "encoder output and decoder input widths differ");
+  std::vector<int> last_use(ns, -1), buf_of(ns, -1);
+  for (int i = ob; i < oe; ++i) {
+    if (pl->skip[i]) continue;
+    const rb_op& op = h->ops[i];
+    const rb_op& ol = pl->layers[i].fused ? h->ops[pl->layers[i].fused_with] : op;
+    last_use[op.src] = i;
+    if (ol.res >= 0) last_use[ol.res] = i;
+    if (op.src2 >= 0) last_use[op.src2] = i;
+    last_use[ol.dst] = std::max(last_use[ol.dst], i);
+  }
+  if (has_enc && has_dec) last_use[h->spec.enc_out_slot] = std::max(last_use[h->spec.enc_out_slot], last_use[h->spec.dec_in_slot]);
+  auto slot_rows = [&](int sl) { return h->slots[sl].per_frame * F; };
+  auto slot_bytes = [&](int sl, int nb) { return (size_t)nb * slot_rows(sl) * pl->cp[sl] * sizeof(__nv_bfloat16); };
+  int mb = h->microbatch;
+  if (mb <= 0) {
+    size_t per_stream = 0;
+    for (int sl = 0; sl < ns; ++sl) per_stream = std::max(per_stream, slot_bytes(sl, 1));
+    const size_t budget = (size_t)128 << 20;
+    mb = (int)std::max<size_t>(1, std::min<size_t>(B, budget / std::max<size_t>(per_stream, 1)));
+  }
+  const int in_ch = h->slots[in_slot].channels, out_ch = h->slots[out_slot].channels;
+  for (int b0 = 0; b0 < B; b0 += mb) {
+    const int nb = std::min(mb, B - b0);
+    std::vector<Buf> bufs(ns);
+    for (auto& pb : h->pool) pb.busy = false;
+    std::fill(buf_of.begin(), buf_of.end(), -1);
+    auto alloc_slot = [&](int sl) -> int {
+      int bi;
+      int rc = pool_get(h, std::max<size_t>(slot_bytes(sl, nb), 256), &bi);
+      if (rc) return rc;
+      buf_of[sl] = bi;
+      Buf& b = bufs[sl];
+      b.p = (__nv_bfloat16*)h->pool[bi].p;
+      b.cp = pl->cp[sl]; b.n = slot_rows(sl); b.ld = b.n; b.hist = 0; b.lo = 0;
+      return RB_OK;
+    };
+    // program input
+    if (pl->cp[in_slot] == 1) {
+      Buf& b = bufs[in_slot];
+      b.p = (__nv_bfloat16*)in + (size_t)b0 * slot_rows(in_slot);
+      b.cp = 1; b.n = slot_rows(in_slot); b.ld = b.n;
+    } else {
+      int rc = alloc_slot(in_slot);
+      if (rc) return rc;
+      const Buf& b = bufs[in_slot];
+      RB_LAUNCH_EW(cf_to_cl_kernel, (size_t)nb * b.n * b.cp, s,
+                   (const __nv_bfloat16*)in + (size_t)b0 * in_ch * b.n, b, in_ch, nb);
+    }
+    if (pl->cp[out_slot] == 1) {
+      Buf& b = bufs[out_slot];
+      b.p = (__nv_bfloat16*)out + (size_t)b0 * slot_rows(out_slot);
+      b.cp = 1; b.n = slot_rows(out_slot); b.ld = b.n;
+    }
+    const float* noise = nullptr;
+    int64_t noise_bstride = 0;
+    if (h->spec.noise_slot >= 0 && h->noise) {
+      const rb_slot& nsl = h->slots[h->spec.noise_slot];
+      noise_bstride = (int64_t)nsl.channels * nsl.per_frame * F;
+      RB_CHECK(h->noise_numel >= (int64_t)B * noise_bstride, RB_ERR_INVALID, "noise tensor has %lld elements, need %lld",
+               (long long)h->noise_numel, (long long)B * noise_bstride);
+      noise = h->noise + (size_t)b0 * noise_bstride;
+    }
+    for (int i = ob; i < oe; ++i) {
+      if (i == n_enc && has_enc && has_dec) {      // latent stays on the device, channels-last
+        bufs[h->spec.dec_in_slot] = bufs[h->spec.enc_out_slot];
+        buf_of[h->spec.dec_in_slot] = buf_of[h->spec.enc_out_slot];
+        buf_of[h->spec.enc_out_slot] = -1;
+      }
+      if (pl->skip[i]) continue;
+      const rb_op& op = h->ops[i];
+      const rb_op& ol = pl->layers[i].fused ? h->ops[pl->layers[i].fused_with] : op;
+      if (!bufs[ol.dst].p) {
+        int rc = alloc_slot(ol.dst);
+        if (rc) return rc;
+      }
+      RB_CHECK(bufs[op.src].p, RB_ERR_STATE, "op %d reads slot %d before it is written", i, op.src);
+      if (op.src2 >= 0 && op.kind != RB_OP_NOISE_V2)
+        RB_CHECK(bufs[op.src2].p, RB_ERR_STATE, "op %d reads slot %d before it is written", i, op.src2);
+      int rc;
+      {
+        OpTimer tm(h, i, s);
+        rc = tc_exec_op(h, pl, i, bufs, nb, noise, noise_bstride, s);
+      }
+      if (rc) return rc;
+      const int used[3] = {op.src, ol.res, op.src2};
+      for (int u : used)
+        if (u >= 0 && last_use[u] == i && buf_of[u] >= 0) {
+          h->pool[buf_of[u]].busy = false;
+          buf_of[u] = -1;
+        }
+    }
+    if (pl->cp[out_slot] != 1) {
+      const Buf& b = bufs[out_slot];
+      RB_CHECK(b.p, RB_ERR_STATE, "program output was never written");
+      RB_LAUNCH_EW(cl_to_cf_kernel, (size_t)nb * out_ch * b.n, s, b,
+                   (__nv_bfloat16*)out + (size_t)b0 * out_ch * b.n, out_ch, nb);
+    }
+  }
+  return RB_OK;
 }
 
 }  // namespace rb
+
+// ------------------------------------------------------------------------- testing hook
+// Runs one conv op (or a conv + 1x1 conv pair, fused when the planner fuses it) of the bf16
+// engine on host fp32 data: x [B][c_in][n_in] -> y [B][c_out/ileave][n_out].  Used by
+// tests/test_gpu_tc_conv.py to check the tcgen05 kernel layer by layer against numpy.
+extern "C" int rb_debug_conv_bf16(const rb_debug_conv* d) {
+  using namespace rb;
+  RB_CHECK(d && d->n_ops >= 1 && d->n_ops <= 2 && d->x && d->y && d->w[0], RB_ERR_INVALID, "rb_debug_conv_bf16: bad arguments");
+  rb_handle hh;
+  rb_handle* h = &hh;
+  h->spec.enc_in_slot = h->spec.dec_out_slot = -1;
+  h->spec.n_enc_ops = 0;
+  h->spec.noise_slot = -1;
+  const rb_op& o0 = d->op[0];
+  const int r0 = std::max(o0.ileave, 1);
+  const int n_mid = d->n_in / o0.stride * r0;
+  // slots: 0 in, 1 out of op0, 2 out of op1, 3 explicit residual
+  h->slots.push_back({o0.c_in, d->n_in, 0, 0});
+  h->slots.push_back({o0.c_out / r0, n_mid, 0, 0});
+  if (d->n_ops == 2) h->slots.push_back({d->op[1].c_out, n_mid, 0, 0});
+  else h->slots.push_back({1, 1, 0, 0});
+  h->slots.push_back({o0.c_out / r0, n_mid, 0, 0});
+  for (int i = 0; i < d->n_ops; ++i) {
+    rb_op op = d->op[i];
+    op.kind = RB_OP_CONV;
+    op.src = i == 0 ? 0 : 1;
+    op.dst = i == 0 ? 1 : 2;
+    op.src2 = -1;
+    op.res = i == 1 ? 0 : (d->res ? 3 : -1);
+    op.src_ch_off = 0;
+    h->ops.push_back(op);
+  }
+  h->w.resize(h->ops.size());
+  for (int i = 0; i < d->n_ops; ++i) {
+    const rb_op& op = h->ops[i];
+    h->w[i].w_host.assign(d->w[i], d->w[i] + (size_t)op.c_out * op.c_in * op.k);
+    if (op.has_bias) {
+      RB_CHECK(d->bias[i], RB_ERR_INVALID, "bias missing");
+      h->w[i].bias_host.assign(d->bias[i], d->bias[i] + op.c_out / std::max(op.ileave, 1));
+    }
+    if (op.pre_act == RB_ACT_SNAKE) {
+      RB_CHECK(d->alpha[i], RB_ERR_INVALID, "alpha missing");
+      h->w[i].alpha_host.assign(d->alpha[i], d->alpha[i] + op.c_in);
+    }
+  }
+  int rc = tc_pack_weights(h);
+  if (rc) { tc_free(h); return rc; }
+  Plan* pl = (Plan*)h->tc;
+  const int B = d->B;
+  std::vector<Buf> bufs(h->slots.size());
+  std::vector<void*> to_free;
+  auto mk = [&](int sl, const float* host) -> int {
+    Buf& b = bufs[sl];
+    b.cp = pl->cp[sl]; b.n = h->slots[sl].per_frame; b.ld = b.n; b.hist = 0; b.lo = 0;
+    const size_t elems = (size_t)B * b.n * b.cp;
+    RB_CUDA(cudaMalloc((void**)&b.p, elems * 2));
+    to_free.push_back(b.p);
+    RB_CUDA(cudaMemset(b.p, 0xFF, elems * 2));     // NaN fill: unwritten outputs show up
+    if (host) {
+      const int C = h->slots[sl].channels;
+      std::vector<__nv_bfloat16> tmp(elems, __float2bfloat16_rn(0.f));
+      for (int bi = 0; bi < B; ++bi)
+        for (int c = 0; c < C; ++c)
+          for (int t = 0; t < b.n; ++t)
+            tmp[((size_t)bi * b.n + t) * b.cp + c] = __float2bfloat16_rn(host[((size_t)bi * C + c) * b.n + t]);
+      RB_CUDA(cudaMemcpy(b.p, tmp.data(), elems * 2, cudaMemcpyHostToDevice));
+    }
+    return RB_OK;
+  };
+  rc = mk(0, d->x);
+  if (!rc) rc = mk(1, nullptr);
+  if (!rc && d->n_ops == 2) rc = mk(2, nullptr);
+  if (!rc && d->res) rc = mk(3, d->res);
+  for (int i = 0; i < d->n_ops && !rc; ++i) {
+    if (pl->skip[i]) continue;
+    rc = tc_exec_op(h, pl, i, bufs, B, nullptr, 0, 0);
+  }
+  if (!rc) {
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { set_error("debug conv failed: %s", cudaGetErrorString(e)); rc = RB_ERR_CUDA; }
+  }
+  if (!rc) {
+    const int osl = d->n_ops == 2 ? 2 : 1;
+    const Buf& b = bufs[osl];
+    const int C = h->slots[osl].channels;
+    std::vector<__nv_bfloat16> tmp((size_t)B * b.n * b.cp);
+    cudaMemcpy(tmp.data(), b.p, tmp.size() * 2, cudaMemcpyDeviceToHost);
+    for (int bi = 0; bi < B; ++bi)
+      for (int c = 0; c < C; ++c)
+        for (int t = 0; t < b.n; ++t)
+          d->y[((size_t)bi * C + c) * b.n + t] = __bfloat162float(tmp[((size_t)bi * b.n + t) * b.cp + c]);
+    if (d->fused_out) *d->fused_out = pl->layers[0].fused ? 1 : 0;
+  }
+  for (void* p : to_free) cudaFree(p);
+  tc_free(h);
+  return rc;
+}

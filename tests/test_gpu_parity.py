@@ -161,3 +161,28 @@ def test_streams_are_independent_at_full_length():
     assert torch.equal(y[1:2], y1)
     yp = m(x.flip(0).contiguous())
     assert torch.equal(yp.flip(0), y)
+
+
+BF16_TOL = 1e-2
+
+
+@pytest.mark.parametrize("name", list(GIN))
+def test_offline_bf16_matches_golden(name):
+    """bf16 tensor-core engine (tcgen05) against the fp32 oracle goldens: rel-L2 <= 1e-2."""
+    m, meta, a = _model(name, dtype=torch.bfloat16)
+    x = torch.from_numpy(golden_input(a)).cuda().bfloat16()
+    if meta["cfg"].get("noise"):
+        from oracle.weights_recipe import recipe_input
+        B, _, T = x.shape
+        m.set_noise(torch.from_numpy(recipe_input((B, T // 16 // 8, 16, 8), int(a["noise_seed"].item()),
+                                                  uniform=True)).cuda())
+    z = m.encode(x)
+    assert z.dtype == torch.bfloat16 and tuple(z.shape) == a["z"].shape
+    nl = m.latent_size
+    assert rel_l2(z[:, :nl].float().cpu().numpy(), a["z"][:, :nl]) < BF16_TOL
+    assert rel_l2(z.float().cpu().numpy(), a["z"]) < BF16_TOL
+    y = m.decode(torch.from_numpy(a["z"]).cuda().bfloat16())
+    assert y.shape == x.shape
+    assert rel_l2(y.float().cpu().numpy(), a["y"]) < BF16_TOL
+    y2 = m(x)
+    assert rel_l2(y2.float().cpu().numpy(), a["y"]) < 2 * BF16_TOL
