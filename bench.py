@@ -203,6 +203,19 @@ def run_ours(args):
             pf = m.spec.slots[op.dst].per_frame
             mac = pf * (2 * op.c_in * (op.c_out // op.ileave) if op.ileave > 1 else op.c_in * op.c_out * op.k)
             conv_flops += 2.0 * mac * frames
+    if args.dump_ops and rank == 0:
+        rows = []
+        for op, t_ms in zip(m.spec.ops, op_ms):
+            pf = m.spec.slots[op.dst].per_frame
+            mac = 0
+            if op.kind == 1:
+                mac = pf * (2 * op.c_in * (op.c_out // op.ileave) if op.ileave > 1 else op.c_in * op.c_out * op.k)
+            rows.append({"name": op.name, "kind": op.kind, "c_in": op.c_in, "c_out": op.c_out, "k": op.k,
+                         "stride": op.stride, "dil": op.dilation, "ileave": op.ileave, "ms": t_ms,
+                         "gflop": 2e-9 * mac * frames,
+                         "out_mb": pf * frames * m.spec.slots[op.dst].channels * esz / 1e6})
+        os.makedirs(os.path.dirname(os.path.abspath(args.dump_ops)), exist_ok=True)
+        json.dump(rows, open(args.dump_ops, "w"), indent=1)
     n_conv = sum(1 for op in m.spec.ops if op.kind == 1)
     pk = _peaks()
     achieved = conv_flops / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
@@ -263,11 +276,12 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--dtype", default=os.environ.get("RAVE_BENCH_DTYPE", "f32"), choices=["bf16", "f32"])
+    ap.add_argument("--dtype", default=os.environ.get("RAVE_BENCH_DTYPE", "bf16"), choices=["bf16", "f32"])
     ap.add_argument("--streams", type=int, default=STREAMS)
     ap.add_argument("--samples", type=int, default=SAMPLES)
     ap.add_argument("--microbatch", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--dump-ops", default="", help="write per-op device times (JSON) to this file")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -1,20 +1,26 @@
 // tc_conv.cu -- the tcgen05 implicit-GEMM convolution kernel of the bf16 engine.
 //
-// One persistent CTA per SM, warp-specialised:
-//   warps 0-3  epilogue    TMEM -> registers (tcgen05.ld) -> bias / residual / activation -> HBM
-//                          (fused DilatedUnit: also writes act(conv3 + b) back to smem as the A
-//                          operand of the 1x1 conv -- the intermediate never leaves the SM)
-//   warps 4-7  A loaders   channels-last rows HBM -> registers -> pre-activation (LeakyReLU /
-//                          Snake / AdaIN affine, zero padding, stream edges) -> smem in the
-//                          UMMA K-major no-swizzle core-matrix layout
-//   warp  8    MMA issuer  one thread: tcgen05.mma (M=128, N=N_TILE, K=16) per tap and K step;
-//                          a dilated / shifted tap is only a different start row of the same
-//                          smem tile (start address + 16 B per row), accumulators in TMEM
-//   warp  9    W producer  weight blocks HBM/L2 -> smem with cp.async.bulk on an mbarrier ring,
-//                          or once for the whole kernel when the layer's weights fit
+// One persistent CTA per SM, warp-specialised (14 warps):
+//   warps 0-7   epilogue    TMEM -> registers (tcgen05.ld) -> bias / residual / sign mask -> HBM.
+//                           Warp w owns TMEM lanes 32*(w%4).. (hardware rule) and the 32-column
+//                           groups of parity w/4.  Fused DilatedUnit: also writes act(conv3 + b)
+//                           back to smem as the A operand of the 1x1 conv -- the intermediate
+//                           never leaves the SM.
+//   warps 8-11  A loaders   channels-last rows HBM -> smem by 16-byte cp.async (several chunks in
+//                           flight), zero padding / stream edges by zero-fill, then the
+//                           pre-activation (LeakyReLU / Snake) in place in smem, stored in the
+//                           UMMA K-major no-swizzle core-matrix layout
+//   warp  12    MMA issuer  one thread: tcgen05.mma (M=128, N=N_TILE, K=16) per tap and K step;
+//                           a dilated / shifted tap is only a different start row of the same
+//                           smem tile (descriptor start address + 16 B per row), fp32
+//                           accumulators in TMEM, double-buffered against the epilogue
+//   warp  13    W producer  weight blocks L2 -> smem with cp.async.bulk on an mbarrier ring,
+//                           or once for the whole kernel when the layer's weights fit
 // Stages hand over through mbarriers only; tcgen05.commit releases smem stages and publishes
 // accumulators.  smem A tile:  addr(row, c8) = c8*(R_ALLOC*16) + row*16   (c8 = 8-channel group)
 //        weight block [N][KC]: addr(n,   c8) = c8*(N*16)       + n*16
+// The activation kinds are template parameters so that each instantiation stays small
+// (the first version branched per element and thrashed the instruction cache).
 #include "common.cuh"
 #include "tc_conv.cuh"
 #include "tc_ptx.cuh"
@@ -27,12 +33,17 @@ namespace {
 enum { BAR_A_FULL = 0, BAR_A_EMPTY = 4, BAR_W_FULL = 8, BAR_W_EMPTY = 12, BAR_D_FULL = 16,
        BAR_D_EMPTY = 18, BAR_H_FULL = 20, BAR_H_EMPTY = 22, BAR_D2_FULL = 24, BAR_D2_EMPTY = 26,
        BAR_COUNT = 28 };
+constexpr int N_EPI = 256;       // epilogue threads
+constexpr int N_LOAD = 128;      // loader threads
+constexpr int W_LOAD0 = 8, W_MMA = 12, W_WPROD = 13;
 
-__device__ __forceinline__ float act_f(float v, int kind, float alpha) {
-  if (kind == RB_ACT_LEAKY) return v > 0.f ? v : 0.2f * v;
-  if (kind == RB_ACT_SNAKE) {
-    const float s = sinf(alpha * v);
-    return v + (1.0f / (alpha + 1e-9f)) * (s * s);
+template <int ACT>
+__device__ __forceinline__ float act_f(float v, float alpha) {
+  if (ACT == RB_ACT_LEAKY) return fmaxf(v, 0.2f * v);
+  if (ACT == RB_ACT_SNAKE) {
+    // x + sin^2(a x) / (a + 1e-9)   (blocks.py:845-853); bf16 storage: fast sine is ample
+    const float s = __sinf(alpha * v);
+    return fmaf(__fdividef(1.0f, alpha + 1e-9f), s * s, v);
   }
   return v;
 }
@@ -67,90 +78,159 @@ __device__ __forceinline__ Work decode(const TcParams& p, int w) {
 }
 
 // ------------------------------------------------------------------------------ A loader
-// Rows [t0 - off, t0 - off + R) x channels [kc*KC, kc*KC + KC) of stream b -> smem stage.
-__device__ __forceinline__ void load_a_chunk(const TcParams& p, const Work& wk, int kc, uint8_t* stage,
-                                             int tid) {
+struct ChunkRef {
+  int b, row0, kc;
+  uint32_t sa;
+};
+
+// (row, 8-channel group) units of one chunk, strided over the loader threads
+template <typename F>
+__device__ __forceinline__ void for_units(const TcParams& p, int tid, F&& f) {
   const int c8n = p.KC >> 3;
-  const int units = p.R * c8n;
-  const int row0 = wk.t0 - p.off;
-  const size_t sbase = ((size_t)wk.b * p.x.ld + p.x.hist) * p.x.C + (size_t)kc * p.KC;
-  const bool plain = p.pre_act == RB_ACT_NONE && p.aff_a == nullptr;
-  for (int u0 = tid; u0 < units; u0 += 128 * 4) {
-    uint4 v[4];
-    int row[4], c8[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int u = u0 + i * 128;
-      row[i] = u / c8n;
-      c8[i] = u - row[i] * c8n;
-      const int t = row0 + row[i];
-      v[i] = make_uint4(0u, 0u, 0u, 0u);
-      if (u < units && t >= p.x.lo && t < p.x.n)
-        v[i] = __ldg(reinterpret_cast<const uint4*>(p.x.p + sbase + (ptrdiff_t)t * p.x.C + c8[i] * 8));
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int u = u0 + i * 128;
-      if (u >= units) break;
-      if (!plain) {
-        float f[8];
-        unpack8(v[i], f);
-        const int ch = kc * p.KC + c8[i] * 8;            // view channel of f[0]
-        if (p.aff_a) {
-          const int t = row0 + row[i];
-          if (t >= p.x.lo && t < p.x.n) {                // padding stays zero (F.pad comes after AdaIN)
-            const int c0 = ch % p.aff_C;
-            const float* a = p.aff_a + (size_t)wk.b * p.aff_C + c0;
-            const float* bb = p.aff_b + (size_t)wk.b * p.aff_C + c0;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], __ldg(a + e), __ldg(bb + e));
-          }
-        }
-        if (p.pre_act == RB_ACT_LEAKY) {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) f[e] = f[e] > 0.f ? f[e] : 0.2f * f[e];
-        } else if (p.pre_act == RB_ACT_SNAKE) {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) f[e] = act_f(f[e], RB_ACT_SNAKE, __ldg(p.alpha + ch + e));
-        }
-        v[i] = pack8(f);
-      }
-      *reinterpret_cast<uint4*>(stage + (size_t)c8[i] * p.R_ALLOC * 16 + (size_t)row[i] * 16) = v[i];
+  if ((N_LOAD % c8n) == 0) {                     // c8n in {1,2,4,8,16}: fixed channel group per thread
+    const int c8 = tid % c8n, rstep = N_LOAD / c8n;
+#pragma unroll 2
+    for (int row = tid / c8n; row < p.R; row += rstep) f(row, c8);
+  } else {
+    const int units = p.R * c8n;
+    for (int u = tid; u < units; u += N_LOAD) {
+      const int row = u / c8n;
+      f(row, u - row * c8n);
     }
   }
 }
 
-// ----------------------------------------------------------------------------- epilogues
-// 16 accumulator columns of one row: + bias, + residual, optional sign mask -> 32 B of bf16.
-__device__ __forceinline__ void store16(const TcParams& p, const uint32_t* r, const float* bias_s, int cg,
-                                        int b, int t, bool valid) {
-  float v[16];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]) + bias_s[cg + i];
-  if (!valid) return;
-  if (p.res.p) {
-    const __nv_bfloat16* rp =
-        p.res.p + ((size_t)b * p.res.ld + p.res.hist + (t - p.res_delay)) * p.res.C + cg;
+__device__ __forceinline__ void issue_a_chunk(const TcParams& p, const ChunkRef& c, uint32_t stage, int tid) {
+  const __nv_bfloat16* base = p.x.p + ((size_t)c.b * p.x.ld + p.x.hist) * p.x.C + (size_t)c.kc * p.KC;
+  const uint32_t col = (uint32_t)p.R_ALLOC * 16u;
+  for_units(p, tid, [&](int row, int c8) {
+    const int t = c.row0 + row;
+    const bool ok = t >= p.x.lo && t < p.x.n;
+    const void* src = ok ? (const void*)(base + (ptrdiff_t)t * p.x.C + c8 * 8) : (const void*)p.x.p;
+    cp_async16(stage + (uint32_t)c8 * col + (uint32_t)row * 16u, src, ok ? 16u : 0u);
+  });
+  cp_async_commit();
+}
+
+template <int PRE>
+__device__ __forceinline__ void finish_a_chunk(const TcParams& p, const ChunkRef& c, uint8_t* stage, int tid) {
+  if (PRE == RB_ACT_NONE) return;
+  const size_t col = (size_t)p.R_ALLOC * 16;
+  for_units(p, tid, [&](int row, int c8) {
+    uint4* q = reinterpret_cast<uint4*>(stage + (size_t)c8 * col + (size_t)row * 16);
     float f[8];
-    unpack8(__ldg(reinterpret_cast<const uint4*>(rp)), f);
+    unpack8(*q, f);
+    if (PRE == RB_ACT_SNAKE) {
+      const float4* al = reinterpret_cast<const float4*>(p.alpha + c.kc * p.KC + c8 * 8);
+      const float4 a0 = __ldg(al), a1 = __ldg(al + 1);
+      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] += f[i];
-    unpack8(__ldg(reinterpret_cast<const uint4*>(rp + 8)), f);
+      for (int e = 0; e < 8; ++e) f[e] = act_f<PRE>(f[e], a[e]);
+    } else {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[8 + i] += f[i];
+      for (int e = 0; e < 8; ++e) f[e] = act_f<PRE>(f[e], 1.f);
+    }
+    *q = pack8(f);
+  });
+}
+
+// ----------------------------------------------------------------------------- epilogues
+// 32 accumulator columns (16 when ncol == 16) of one row from TMEM, + bias (smem, float4 reads).
+__device__ __forceinline__ void load_acc32(uint32_t taddr, int ncol, const float* bias_s, float* v) {
+  uint32_t r[32];
+  tmem_ld16(taddr, r);
+  if (ncol > 16) tmem_ld16(taddr + 16u, r + 16);
+  tmem_ld_wait();
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    const float4 b = *reinterpret_cast<const float4*>(bias_s + g * 4);
+    v[g * 4 + 0] = __uint_as_float(r[g * 4 + 0]) + b.x;
+    v[g * 4 + 1] = __uint_as_float(r[g * 4 + 1]) + b.y;
+    v[g * 4 + 2] = __uint_as_float(r[g * 4 + 2]) + b.z;
+    v[g * 4 + 3] = __uint_as_float(r[g * 4 + 3]) + b.w;
   }
-  if (p.out_mask && !(t & 1)) {
-#pragma unroll
-    for (int i = 1; i < 16; i += 2) v[i] = -v[i];
+}
+
+// Drains the 32-column groups of parity `half` of `MTn` sub-tiles x `NT` accumulator columns
+// (TMEM address `tbase`, lane base included) into y at channel offset ch0: + bias, + residual,
+// optional sign mask, bf16, 16-byte stores.  The residual of a group is loaded before the
+// accumulator barrier / the previous group's stores so that its latency overlaps.
+__device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
+                                      const float* bs, const Work& wk, int rit, int half, int ch0, int MTn,
+                                      int NT) {
+  const int gpr = (NT + 31) >> 5;                       // 32-column groups per row
+  const int G = MTn * gpr;
+  const bool has_res = p.res.p != nullptr;
+  auto res_ptr = [&](int g, bool& ok, int& ncol) -> const __nv_bfloat16* {
+    const int mt = g / gpr, c0 = (g - mt * gpr) * 32;
+    const int t = wk.t0 + mt * 128 + rit;
+    ncol = NT - c0 < 32 ? NT - c0 : 32;
+    ok = t < p.y.n;
+    return p.res.p + ((size_t)wk.b * p.res.ld + p.res.hist + (t - p.res_delay)) * p.res.C + ch0 + c0;
+  };
+  uint4 rr[4];
+  if (has_res && half < G) {
+    bool ok; int ncol;
+    const __nv_bfloat16* rp = res_ptr(half, ok, ncol);
+    if (ok) {
+      rr[0] = __ldg(reinterpret_cast<const uint4*>(rp));
+      rr[1] = __ldg(reinterpret_cast<const uint4*>(rp + 8));
+      if (ncol > 16) {
+        rr[2] = __ldg(reinterpret_cast<const uint4*>(rp + 16));
+        rr[3] = __ldg(reinterpret_cast<const uint4*>(rp + 24));
+      }
+    }
   }
-  __nv_bfloat16* yp =
-      const_cast<__nv_bfloat16*>(p.y.p) + ((size_t)b * p.y.ld + p.y.hist + t) * p.y.C + cg;
-  *reinterpret_cast<uint4*>(yp) = pack8(v);
-  *reinterpret_cast<uint4*>(yp + 8) = pack8(v + 8);
+  mbar_wait(bar_full, parity);
+  tc_fence_after();
+  for (int g = half; g < G; g += 2) {
+    const int mt = g / gpr, c0 = (g - mt * gpr) * 32;
+    const int t = wk.t0 + mt * 128 + rit;
+    const int ncol = NT - c0 < 32 ? NT - c0 : 32;
+    const bool valid = t < p.y.n;
+    float v[32];
+    load_acc32(tbase + (uint32_t)(mt * NT + c0), ncol, bs + ch0 + c0, v);
+    if (has_res && valid) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (q * 8 < ncol) {
+          float f[8];
+          unpack8(rr[q], f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[q * 8 + e] += f[e];
+        }
+      }
+    }
+    if (has_res && g + 2 < G) {                          // prefetch the next group's residual
+      bool ok; int n2;
+      const __nv_bfloat16* rp = res_ptr(g + 2, ok, n2);
+      if (ok) {
+        rr[0] = __ldg(reinterpret_cast<const uint4*>(rp));
+        rr[1] = __ldg(reinterpret_cast<const uint4*>(rp + 8));
+        if (n2 > 16) {
+          rr[2] = __ldg(reinterpret_cast<const uint4*>(rp + 16));
+          rr[3] = __ldg(reinterpret_cast<const uint4*>(rp + 24));
+        }
+      }
+    }
+    if (valid) {
+      if (p.out_mask && !(t & 1)) {
+#pragma unroll
+        for (int e = 1; e < 32; e += 2) v[e] = -v[e];
+      }
+      __nv_bfloat16* yp =
+          const_cast<__nv_bfloat16*>(p.y.p) + ((size_t)wk.b * p.y.ld + p.y.hist + t) * p.y.C + ch0 + c0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (q * 8 < ncol) *reinterpret_cast<uint4*>(yp + q * 8) = pack8(v + q * 8);
+    }
+  }
+  tc_fence_before();
 }
 
 }  // namespace
 
+template <int PRE, int ACT2, bool FUSED>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_constant__ TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
@@ -169,29 +249,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
 
   if (tid == 0) {
     for (int i = 0; i < 4; ++i) {
-      mbar_init(BAR(BAR_A_FULL + i), 128);
+      mbar_init(BAR(BAR_A_FULL + i), N_LOAD);
       mbar_init(BAR(BAR_A_EMPTY + i), 1);
       mbar_init(BAR(BAR_W_FULL + i), 1);
       mbar_init(BAR(BAR_W_EMPTY + i), 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(BAR(BAR_D_FULL + i), 1);
-      mbar_init(BAR(BAR_D_EMPTY + i), 128);
-      mbar_init(BAR(BAR_H_FULL + i), 128);
+      mbar_init(BAR(BAR_D_EMPTY + i), N_EPI);
+      mbar_init(BAR(BAR_H_FULL + i), N_EPI);
       mbar_init(BAR(BAR_H_EMPTY + i), 1);
       mbar_init(BAR(BAR_D2_FULL + i), 1);
-      mbar_init(BAR(BAR_D2_EMPTY + i), 128);
+      mbar_init(BAR(BAR_D2_EMPTY + i), N_EPI);
     }
     fence_mbar_init();
   }
   for (int i = tid; i < N_total; i += TC_THREADS) bias_s[i] = p.bias ? p.bias[i] : 0.f;
-  if (p.fused) {
+  if (FUSED) {
     for (int i = tid; i < p.N_TILE; i += TC_THREADS) {
       bias2_s[i] = p.bias2 ? p.bias2[i] : 0.f;
       alpha2_s[i] = p.alpha2 ? p.alpha2[i] : 1.f;
     }
   }
-  if (warp == 8) {
+  if (warp == W_MMA) {
     tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
     tmem_relinquish();
   }
@@ -204,29 +284,49 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
   const uint32_t lbo_w = (uint32_t)p.N_TILE * 16u;
   const int ksteps = p.KC >> 4;
   const int C2 = p.N_TILE;                        // fused: channels of the unit
+  const uint32_t d_stage_cols = FUSED ? 2u * C2 : (uint32_t)(p.MT * p.N_TILE);
 
-  if (warp >= 4 && warp < 8) {
+  if (warp >= W_LOAD0 && warp < W_MMA) {
     // ============================================================== A loaders (128 threads)
-    const int ltid = tid - 128;
+    // Software-pipelined: up to LA chunks are in flight (cp.async groups) before the oldest is
+    // finished (activation pass, proxy fence) and handed to the MMA warp.
+    const int ltid = tid - W_LOAD0 * 32;
+    const int LA = p.SA - 1 < 3 ? p.SA - 1 : 3;
+    ChunkRef pend[4] = {};
+    int n_pend = 0;
     uint32_t it = 0;
+    auto retire = [&]() {
+      const ChunkRef c = pend[0];
+      pend[0] = pend[1]; pend[1] = pend[2]; pend[2] = pend[3];
+      --n_pend;
+      cp_async_wait(n_pend);
+      finish_a_chunk<PRE>(p, c, a_smem + (size_t)c.sa * p.a_stage_bytes, ltid);
+      fence_proxy_async();
+      mbar_arrive(BAR(BAR_A_FULL + c.sa));
+    };
     for (int w = blockIdx.x; w < p.n_work; w += gridDim.x) {
       const Work wk = decode(p, w);
       for (int kc = 0; kc < p.n_kchunks; ++kc) {
         if (__ldg(p.masks + wk.nt * p.n_kchunks + kc) == 0) continue;
         const uint32_t sa = it % p.SA, ph = (it / p.SA) & 1;
         mbar_wait(BAR(BAR_A_EMPTY + sa), ph ^ 1);
-        load_a_chunk(p, wk, kc, a_smem + (size_t)sa * p.a_stage_bytes, ltid);
-        fence_proxy_async();
-        mbar_arrive(BAR(BAR_A_FULL + sa));
+        ChunkRef c{wk.b, wk.t0 - p.off, kc, sa};
+        issue_a_chunk(p, c, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes), ltid);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (k == n_pend) pend[k] = c;
+        ++n_pend;
         ++it;
+        if (n_pend > LA) retire();
       }
     }
-  } else if (warp == 9) {
+    while (n_pend > 0) retire();
+  } else if (warp == W_WPROD) {
     // =========================================================== W producer (one thread)
     if (lane == 0) {
       if (p.w_resident) {
         const uint32_t total = (uint32_t)p.nt_base[p.n_ntiles] * p.w_blk_bytes +
-                               (p.fused ? (uint32_t)(C2 / p.KC) * p.w_blk_bytes : 0u);
+                               (FUSED ? (uint32_t)(C2 / p.KC) * p.w_blk_bytes : 0u);
         mbar_expect_tx(BAR(BAR_W_FULL), total);
         for (uint32_t o = 0; o < total; o += 32768u) {
           const uint32_t n = total - o < 32768u ? total - o : 32768u;
@@ -239,8 +339,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
           int gblk = p.nt_base[wk.nt];
           for (int kc = 0; kc < p.n_kchunks; ++kc) {
             const uint64_t mask = __ldg(p.masks + wk.nt * p.n_kchunks + kc);
-            for (int j = 0; j < p.n_taps; ++j) {
-              if (!((mask >> j) & 1)) continue;
+            const int nb = __popcll(mask);
+            for (int j = 0; j < nb; ++j) {
               const uint32_t sw = it % p.SW, ph = (it / p.SW) & 1;
               mbar_wait(BAR(BAR_W_EMPTY + sw), ph ^ 1);
               mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
@@ -254,12 +354,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         }
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == W_MMA) {
     // =========================================================== MMA issuer (one thread)
     if (lane == 0) {
       const uint32_t idesc = make_idesc_bf16(128, p.N_TILE);
       const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem), h0 = smem_u32(h_smem);
-      const uint32_t d_stage_cols = p.fused ? 2u * C2 : (uint32_t)(p.MT * p.N_TILE);
+      // descriptor halves: hi is constant (SBO = 128 B, version 1); lo = start>>4 | LBO>>4 << 16
+      const uint32_t dhi = desc_hi(128u);
+      const uint32_t a_lbo_bits = ((lbo_a >> 4) & 0x3FFFu) << 16, w_lbo_bits = ((lbo_w >> 4) & 0x3FFFu) << 16;
+      const uint32_t a_kadd = (2u * lbo_a) >> 4, w_kadd = (2u * lbo_w) >> 4;   // one K=16 step
+      const uint32_t tap_add = (uint32_t)p.dil;                                // rows -> 16 B units
       uint32_t it_a = 0, it_w = 0;
       if (p.w_resident) {
         mbar_wait(BAR(BAR_W_FULL), 0);
@@ -272,46 +376,54 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols;
         uint32_t acc = 0;
-        int blk = 0;
+        uint32_t wres = ((w0 >> 4) & 0x3FFFu) | w_lbo_bits;      // resident: next block's desc.lo
+        const uint64_t* mrow = p.masks + wk.nt * p.n_kchunks;
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
-          const uint64_t mask = __ldg(p.masks + wk.nt * p.n_kchunks + kc);
+          uint64_t mask = __ldg(mrow + kc);
           if (mask == 0) continue;
           const uint32_t sa = it_a % p.SA, pha = (it_a / p.SA) & 1;
           mbar_wait(BAR(BAR_A_FULL + sa), pha);
           tc_fence_after();
-          const uint32_t abase = a0 + sa * p.a_stage_bytes;
-          for (int j = 0; j < p.n_taps; ++j) {
-            if (!((mask >> j) & 1)) continue;
-            uint32_t wbase, sw = 0;
+          const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
+          while (mask) {
+            const int j = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            uint32_t blo, sw = 0;
             if (p.w_resident) {
-              wbase = w0 + (uint32_t)blk * p.w_blk_bytes;
+              blo = wres;
+              wres += p.w_blk_bytes >> 4;
             } else {
               sw = it_w % p.SW;
               mbar_wait(BAR(BAR_W_FULL + sw), (it_w / p.SW) & 1);
               tc_fence_after();
-              wbase = w0 + sw * p.w_blk_bytes;
+              blo = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
             }
+            uint32_t alo = alo0 + (uint32_t)j * tap_add;
             for (int mt = 0; mt < p.MT; ++mt) {
-              const uint32_t arow = abase + (uint32_t)(j * p.dil + mt * 128) * 16u;
-              for (int kk = 0; kk < ksteps; ++kk) {
-                const uint64_t ad = make_desc(arow + (uint32_t)kk * 2u * lbo_a, lbo_a, 128u);
-                const uint64_t bd = make_desc(wbase + (uint32_t)kk * 2u * lbo_w, lbo_w, 128u);
-                mma_bf16(dcol + (uint32_t)(mt * p.N_TILE), ad, bd, idesc, acc | (uint32_t)kk);
+              uint32_t al = alo, bl = blo;
+              const uint32_t dc = dcol + (uint32_t)(mt * p.N_TILE);
+              mma_bf16_lohi(dc, al, bl, dhi, idesc, acc);
+#pragma unroll 4
+              for (int kk = 1; kk < ksteps; ++kk) {
+                al += a_kadd;
+                bl += w_kadd;
+                mma_bf16_lohi(dc, al, bl, dhi, idesc, 1u);
               }
+              alo += 128u;                                        // next 128-row sub-tile
             }
             acc = 1;
             if (!p.w_resident) {
               mma_commit(BAR(BAR_W_EMPTY + sw));
               ++it_w;
             }
-            ++blk;
           }
           mma_commit(BAR(BAR_A_EMPTY + sa));
           ++it_a;
         }
         mma_commit(BAR(BAR_D_FULL + sd));
       };
-      // GEMM2 (fused): D2 = h * W1^T
+      // GEMM2 (fused): D2 = h * W1^T  (h: [128][C2] core-matrix layout, LBO = 2048)
+      const uint32_t h_lbo_bits = ((2048u >> 4) & 0x3FFFu) << 16, h_kadd = (2u * 2048u) >> 4;
       auto gemm2 = [&](uint32_t i) {
         const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
         const uint32_t sh = i % p.SH, phh = (i / p.SH) & 1;
@@ -319,14 +431,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         mbar_wait(BAR(BAR_D2_EMPTY + sd), phd ^ 1);
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols + (uint32_t)C2;
-        const uint32_t hbase = h0 + sh * p.h_stage_bytes;
-        const int k16n = C2 >> 4;
-        for (int k16 = 0; k16 < k16n; ++k16) {
-          const int kc = k16 / ksteps, kk = k16 - kc * ksteps;
-          const uint64_t ad = make_desc(hbase + (uint32_t)k16 * 2u * 2048u, 2048u, 128u);
-          const uint64_t bd =
-              make_desc(w0 + (uint32_t)(p.n_blk1 + kc) * p.w_blk_bytes + (uint32_t)kk * 2u * lbo_w, lbo_w, 128u);
-          mma_bf16(dcol, ad, bd, idesc, (uint32_t)k16);
+        uint32_t al = (((h0 + sh * p.h_stage_bytes) >> 4) & 0x3FFFu) | h_lbo_bits;
+        const int nkc = C2 / p.KC;
+        uint32_t accum = 0;
+        for (int kc = 0; kc < nkc; ++kc) {
+          uint32_t bl = (((w0 + (uint32_t)(p.n_blk1 + kc) * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+#pragma unroll 4
+          for (int kk = 0; kk < ksteps; ++kk) {
+            mma_bf16_lohi(dcol, al, bl, dhi, idesc, accum);
+            accum = 1;
+            al += h_kadd;
+            bl += w_kadd;
+          }
         }
         mma_commit(BAR(BAR_H_EMPTY + sh));
         mma_commit(BAR(BAR_D2_FULL + sd));
@@ -334,30 +450,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       uint32_t i = 0;
       for (int w = blockIdx.x; w < p.n_work; w += gridDim.x, ++i) {
         gemm1(i, decode(p, w));
-        if (p.fused && i >= 1) gemm2(i - 1);
+        if (FUSED && i >= 1) gemm2(i - 1);
       }
-      if (p.fused && i >= 1) gemm2(i - 1);
+      if (FUSED && i >= 1) gemm2(i - 1);
     }
   } else {
-    // ============================================================ epilogue (warps 0-3)
-    const int rit = warp * 32 + lane;                       // row within a 128-row sub-tile
-    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-    const uint32_t d_stage_cols = p.fused ? 2u * C2 : (uint32_t)(p.MT * p.N_TILE);
+    // ============================================================ epilogue (warps 0-7)
+    const int rit = (warp & 3) * 32 + lane;                 // row within a 128-row sub-tile
+    const int half = warp >> 2;                             // parity of the 32-column groups owned
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     auto epi_plain = [&](uint32_t i, const Work& wk) {
       const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
-      mbar_wait(BAR(BAR_D_FULL + sd), phd);
-      tc_fence_after();
-      for (int mt = 0; mt < p.MT; ++mt) {
-        const int t = wk.t0 + mt * 128 + rit;
-        const bool valid = t < p.y.n;
-        for (int c0 = 0; c0 < p.N_TILE; c0 += 16) {
-          uint32_t r[16];
-          tmem_ld16(tmem + lane_base + sd * d_stage_cols + (uint32_t)(mt * p.N_TILE + c0), r);
-          tmem_ld_wait();
-          store16(p, r, bias_s, wk.nt * p.N_TILE + c0, wk.b, t, valid);
-        }
-      }
-      tc_fence_before();
+      drain(p, BAR(BAR_D_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols, bias_s, wk, rit, half,
+            wk.nt * p.N_TILE, p.MT, p.N_TILE);
       mbar_arrive(BAR(BAR_D_EMPTY + sd));
     };
     // fused E1: h = act2(D1 + bias) -> smem (A operand of the 1x1 conv)
@@ -368,16 +473,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       mbar_wait(BAR(BAR_H_EMPTY + sh), phh ^ 1);
       tc_fence_after();
       uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
-      for (int c0 = 0; c0 < C2; c0 += 16) {
-        uint32_t r[16];
-        tmem_ld16(tmem + lane_base + sd * d_stage_cols + (uint32_t)c0, r);
-        tmem_ld_wait();
-        float v[16];
+      for (int c0 = half * 32; c0 < C2; c0 += 64) {
+        const int ncol = C2 - c0 < 32 ? C2 - c0 : 32;
+        float v[32];
+        load_acc32(tmem + lane_base + sd * d_stage_cols + (uint32_t)c0, ncol, bias_s + c0, v);
 #pragma unroll
-        for (int e = 0; e < 16; ++e)
-          v[e] = act_f(__uint_as_float(r[e]) + bias_s[c0 + e], p.act2, alpha2_s[c0 + e]);
-        *reinterpret_cast<uint4*>(hb + (size_t)(c0 >> 3) * 2048) = pack8(v);
-        *reinterpret_cast<uint4*>(hb + (size_t)((c0 >> 3) + 1) * 2048) = pack8(v + 8);
+        for (int q = 0; q < 4; ++q) {
+          if (q * 8 < ncol) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              v[q * 8 + e] = act_f<ACT2>(v[q * 8 + e], ACT2 == RB_ACT_SNAKE ? alpha2_s[c0 + q * 8 + e] : 1.f);
+            *reinterpret_cast<uint4*>(hb + (size_t)((c0 >> 3) + q) * 2048) = pack8(v + q * 8);
+          }
+        }
       }
       fence_proxy_async();
       tc_fence_before();
@@ -387,24 +495,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
     // fused E2: y = D2 + bias2 + x
     auto epi_out = [&](uint32_t i, const Work& wk) {
       const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
-      mbar_wait(BAR(BAR_D2_FULL + sd), phd);
-      tc_fence_after();
-      const int t = wk.t0 + rit;
-      const bool valid = t < p.y.n;
-      for (int c0 = 0; c0 < C2; c0 += 16) {
-        uint32_t r[16];
-        tmem_ld16(tmem + lane_base + sd * d_stage_cols + (uint32_t)(C2 + c0), r);
-        tmem_ld_wait();
-        store16(p, r, bias2_s, c0, wk.b, t, valid);
-      }
-      tc_fence_before();
+      drain(p, BAR(BAR_D2_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols + (uint32_t)C2, bias2_s, wk, rit,
+            half, 0, 1, C2);
       mbar_arrive(BAR(BAR_D2_EMPTY + sd));
     };
     uint32_t i = 0;
     Work prev{0, 0, 0};
     for (int w = blockIdx.x; w < p.n_work; w += gridDim.x, ++i) {
       const Work wk = decode(p, w);
-      if (!p.fused) {
+      if (!FUSED) {
         epi_plain(i, wk);
       } else {
         epi_h(i);
@@ -412,32 +511,55 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         prev = wk;
       }
     }
-    if (p.fused && i >= 1) epi_out(i - 1, prev);
+    if (FUSED && i >= 1) epi_out(i - 1, prev);
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == W_MMA) {
     tc_fence_after();
     tmem_dealloc(tmem, p.tmem_cols);
   }
 }
 
+template <int PRE, int ACT2, bool FUSED>
+static int launch_variant(const TcParams& p, int grid, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 227 * 1024));
+    attr_set = true;
+  }
+  tc_conv_kernel<PRE, ACT2, FUSED><<<grid, TC_THREADS, p.smem_bytes, s>>>(p);
+  return RB_OK;
+}
+
 int launch_tc_conv(const TcParams& p, cudaStream_t s) {
   if (p.n_work <= 0) return RB_OK;
   static int n_sm = 0;
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!n_sm) {
     int dev = 0;
     RB_CUDA(cudaGetDevice(&dev));
     RB_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
   }
   RB_CHECK(p.smem_bytes <= 227u * 1024u, RB_ERR_UNSUPPORTED, "tc conv needs %u B of shared memory",
            p.smem_bytes);
   const int grid = p.n_work < n_sm ? p.n_work : n_sm;
-  tc_conv_kernel<<<grid, TC_THREADS, p.smem_bytes, s>>>(p);
+  int rc = RB_ERR_UNSUPPORTED;
+  if (!p.fused) {
+    if (p.pre_act == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false>(p, grid, s);
+    else if (p.pre_act == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_NONE, false>(p, grid, s);
+    else if (p.pre_act == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_NONE, false>(p, grid, s);
+  } else {
+    if (p.pre_act == RB_ACT_LEAKY && p.act2 == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_LEAKY, true>(p, grid, s);
+    else if (p.pre_act == RB_ACT_SNAKE && p.act2 == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_SNAKE, true>(p, grid, s);
+    else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, true>(p, grid, s);
+  }
+  if (rc == RB_ERR_UNSUPPORTED) {
+    set_error("tc conv: activation combination (%d, %d, fused=%d) has no kernel variant", p.pre_act, p.act2, p.fused);
+    return rc;
+  }
+  if (rc) return rc;
   ++g_launches;
   RB_CUDA(cudaGetLastError());
   return RB_OK;

@@ -19,7 +19,7 @@ namespace rb {
 namespace tc {
 
 constexpr int TC_MAX_NT = 8;        // output-channel tiles per layer
-constexpr int TC_THREADS = 320;     // warps 0-3 epilogue, 4-7 A loaders, 8 MMA issuer, 9 W producer
+constexpr int TC_THREADS = 448;     // warps 0-7 epilogue, 8-11 A loaders, 12 MMA issuer, 13 W producer
 
 // [stream][ld rows][C] bf16; element (b, t, c) at p[((size_t)b*ld + hist + t)*C + c], t in [lo, n)
 struct TcView {

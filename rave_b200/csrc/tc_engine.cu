@@ -527,7 +527,7 @@ int tc_pack_weights(rb_handle* h) {
     if (op.kind == RB_OP_CONV && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {
       const rb_op& o2 = h->ops[i + 1];
       fuse = o2.kind == RB_OP_CONV && o2.k == 1 && o2.stride == 1 && o2.ileave <= 1 && op.stride == 1 &&
-             op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 &&
+             op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 && o2.pre_act == op.pre_act &&
              v.N_total == v.cin_v && v.N_total <= 64 && pl->cp[o2.dst] == v.N_total;
       if (fuse) {
         rc = build_view_weight(h, i + 1, *pl, v2);
