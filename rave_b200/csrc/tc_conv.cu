@@ -89,7 +89,7 @@ __device__ __forceinline__ void for_units(const TcParams& p, int tid, F&& f) {
   const int c8n = p.KC >> 3;
   if ((N_LOAD % c8n) == 0) {                     // c8n in {1,2,4,8,16}: fixed channel group per thread
     const int c8 = tid % c8n, rstep = N_LOAD / c8n;
-#pragma unroll 2
+#pragma unroll 4
     for (int row = tid / c8n; row < p.R; row += rstep) f(row, c8);
   } else {
     const int units = p.R * c8n;
@@ -112,25 +112,37 @@ __device__ __forceinline__ void issue_a_chunk(const TcParams& p, const ChunkRef&
   cp_async_commit();
 }
 
+// LeakyReLU(0.2) on two packed bf16: max(x, 0.2 x).  0.2 is not a bf16, so the product is
+// formed as fma(x, c1, x * c2) with c1 + c2 = 0.2 to ~1e-6: one rounding of 0.2 x like the
+// fp32 reference followed by a bf16 store, at 3 packed instructions per pair.
+__device__ __forceinline__ uint32_t leaky2(uint32_t w) {
+  const __nv_bfloat162 x = *reinterpret_cast<const __nv_bfloat162*>(&w);
+  const __nv_bfloat162 c1 = __floats2bfloat162_rn(0.2001953125f, 0.2001953125f);
+  const __nv_bfloat162 c2 = __floats2bfloat162_rn(-0.0001953125f, -0.0001953125f);
+  const __nv_bfloat162 y = __hmax2(x, __hfma2(x, c1, __hmul2(x, c2)));
+  return *reinterpret_cast<const uint32_t*>(&y);
+}
+
 template <int PRE>
 __device__ __forceinline__ void finish_a_chunk(const TcParams& p, const ChunkRef& c, uint8_t* stage, int tid) {
   if (PRE == RB_ACT_NONE) return;
   const size_t col = (size_t)p.R_ALLOC * 16;
   for_units(p, tid, [&](int row, int c8) {
     uint4* q = reinterpret_cast<uint4*>(stage + (size_t)c8 * col + (size_t)row * 16);
-    float f[8];
-    unpack8(*q, f);
-    if (PRE == RB_ACT_SNAKE) {
+    if (PRE == RB_ACT_LEAKY) {
+      uint4 v = *q;
+      v.x = leaky2(v.x); v.y = leaky2(v.y); v.z = leaky2(v.z); v.w = leaky2(v.w);
+      *q = v;
+    } else {
+      float f[8];
+      unpack8(*q, f);
       const float4* al = reinterpret_cast<const float4*>(p.alpha + c.kc * p.KC + c8 * 8);
       const float4 a0 = __ldg(al), a1 = __ldg(al + 1);
       const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
       for (int e = 0; e < 8; ++e) f[e] = act_f<PRE>(f[e], a[e]);
-    } else {
-#pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] = act_f<PRE>(f[e], 1.f);
+      *q = pack8(f);
     }
-    *q = pack8(f);
   });
 }
 
@@ -229,6 +241,10 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
 }
 
 }  // namespace
+
+// issued by the elected lane of the MMA warp only
+#define MMA(...) do { if (leader) mma_bf16_lohi(__VA_ARGS__); } while (0)
+#define COMMIT(bar) do { if (leader) mma_commit(bar); } while (0)
 
 template <int PRE, int ACT2, bool FUSED>
 __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_constant__ TcParams p) {
@@ -355,8 +371,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       }
     }
   } else if (warp == W_MMA) {
-    // =========================================================== MMA issuer (one thread)
-    if (lane == 0) {
+    // ====================================== MMA issuer (warp-uniform control, elected lane issues)
+    {
+      const bool leader = elect_one();
       const uint32_t idesc = make_idesc_bf16(128, p.N_TILE);
       const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem), h0 = smem_u32(h_smem);
       // descriptor halves: hi is constant (SBO = 128 B, version 1); lo = start>>4 | LBO>>4 << 16
@@ -364,6 +381,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       const uint32_t a_lbo_bits = ((lbo_a >> 4) & 0x3FFFu) << 16, w_lbo_bits = ((lbo_w >> 4) & 0x3FFFu) << 16;
       const uint32_t a_kadd = (2u * lbo_a) >> 4, w_kadd = (2u * lbo_w) >> 4;   // one K=16 step
       const uint32_t tap_add = (uint32_t)p.dil;                                // rows -> 16 B units
+      const uint32_t blk_units = p.w_blk_bytes >> 4;
       uint32_t it_a = 0, it_w = 0;
       if (p.w_resident) {
         mbar_wait(BAR(BAR_W_FULL), 0);
@@ -385,13 +403,52 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
           mbar_wait(BAR(BAR_A_FULL + sa), pha);
           tc_fence_after();
           const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
+          const int j0 = __ffsll((long long)mask) - 1, n_act = __popcll(mask);
+          const bool run = (mask >> j0) == (n_act >= 64 ? ~0ull : ((1ull << n_act) - 1ull));
+          if (p.w_resident && run) {
+            // fast path (one run of active taps, weights in smem, MT == 1): adds between MMAs only
+            uint32_t al = alo0 + (uint32_t)j0 * tap_add, bl = wres;
+            if (ksteps == 1) {
+#pragma unroll 4
+              for (int j = 0; j < n_act; ++j) {
+                MMA(dcol, al, bl, dhi, idesc, acc | (uint32_t)j);
+                al += tap_add;
+                bl += blk_units;
+              }
+            } else if (ksteps == 4) {
+#pragma unroll 2
+              for (int j = 0; j < n_act; ++j) {
+                MMA(dcol, al, bl, dhi, idesc, acc | (uint32_t)j);
+                MMA(dcol, al + a_kadd, bl + w_kadd, dhi, idesc, 1u);
+                MMA(dcol, al + 2u * a_kadd, bl + 2u * w_kadd, dhi, idesc, 1u);
+                MMA(dcol, al + 3u * a_kadd, bl + 3u * w_kadd, dhi, idesc, 1u);
+                al += tap_add;
+                bl += blk_units;
+              }
+            } else {
+              for (int j = 0; j < n_act; ++j) {
+                uint32_t a2 = al, b2 = bl;
+                MMA(dcol, a2, b2, dhi, idesc, acc | (uint32_t)j);
+                for (int kk = 1; kk < ksteps; ++kk) {
+                  a2 += a_kadd;
+                  b2 += w_kadd;
+                  MMA(dcol, a2, b2, dhi, idesc, 1u);
+                }
+                al += tap_add;
+                bl += blk_units;
+              }
+            }
+            wres = bl;
+            acc = 1;
+            mask = 0;
+          }
           while (mask) {
             const int j = __ffsll((long long)mask) - 1;
             mask &= mask - 1;
             uint32_t blo, sw = 0;
             if (p.w_resident) {
               blo = wres;
-              wres += p.w_blk_bytes >> 4;
+              wres += blk_units;
             } else {
               sw = it_w % p.SW;
               mbar_wait(BAR(BAR_W_FULL + sw), (it_w / p.SW) & 1);
@@ -402,25 +459,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
             for (int mt = 0; mt < p.MT; ++mt) {
               uint32_t al = alo, bl = blo;
               const uint32_t dc = dcol + (uint32_t)(mt * p.N_TILE);
-              mma_bf16_lohi(dc, al, bl, dhi, idesc, acc);
+              MMA(dc, al, bl, dhi, idesc, acc);
 #pragma unroll 4
               for (int kk = 1; kk < ksteps; ++kk) {
                 al += a_kadd;
                 bl += w_kadd;
-                mma_bf16_lohi(dc, al, bl, dhi, idesc, 1u);
+                MMA(dc, al, bl, dhi, idesc, 1u);
               }
               alo += 128u;                                        // next 128-row sub-tile
             }
             acc = 1;
             if (!p.w_resident) {
-              mma_commit(BAR(BAR_W_EMPTY + sw));
+              COMMIT(BAR(BAR_W_EMPTY + sw));
               ++it_w;
             }
           }
-          mma_commit(BAR(BAR_A_EMPTY + sa));
+          COMMIT(BAR(BAR_A_EMPTY + sa));
           ++it_a;
         }
-        mma_commit(BAR(BAR_D_FULL + sd));
+        COMMIT(BAR(BAR_D_FULL + sd));
       };
       // GEMM2 (fused): D2 = h * W1^T  (h: [128][C2] core-matrix layout, LBO = 2048)
       const uint32_t h_lbo_bits = ((2048u >> 4) & 0x3FFFu) << 16, h_kadd = (2u * 2048u) >> 4;
@@ -438,14 +495,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
           uint32_t bl = (((w0 + (uint32_t)(p.n_blk1 + kc) * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
 #pragma unroll 4
           for (int kk = 0; kk < ksteps; ++kk) {
-            mma_bf16_lohi(dcol, al, bl, dhi, idesc, accum);
+            MMA(dcol, al, bl, dhi, idesc, accum);
             accum = 1;
             al += h_kadd;
             bl += w_kadd;
           }
         }
-        mma_commit(BAR(BAR_H_EMPTY + sh));
-        mma_commit(BAR(BAR_D2_FULL + sd));
+        COMMIT(BAR(BAR_H_EMPTY + sh));
+        COMMIT(BAR(BAR_D2_FULL + sd));
       };
       uint32_t i = 0;
       for (int w = blockIdx.x; w < p.n_work; w += gridDim.x, ++i) {

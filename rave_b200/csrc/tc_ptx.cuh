@@ -75,6 +75,21 @@ __device__ __forceinline__ void cp_async_wait(int n) {
   }
 }
 
+// One lane of the (fully active) warp gets true; lets ptxas issue warp-level instructions
+// (tcgen05.mma / commit) once without a per-thread uniformisation loop.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n"
+      ".reg .b32 rx;\n"
+      ".reg .pred px;\n"
+      "elect.sync rx|px, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, px;\n"
+      "}\n"
+      : "=r"(pred)::"memory");
+  return pred != 0;
+}
+
 // ------------------------------------------------------------------------------ tcgen05
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem),
