@@ -32,7 +32,7 @@ namespace {
 
 enum { BAR_A_FULL = 0, BAR_A_EMPTY = 4, BAR_W_FULL = 8, BAR_W_EMPTY = 12, BAR_D_FULL = 16,
        BAR_D_EMPTY = 18, BAR_H_FULL = 20, BAR_H_EMPTY = 22, BAR_D2_FULL = 24, BAR_D2_EMPTY = 26,
-       BAR_COUNT = 28 };
+       BAR_RAW_FULL = 28, BAR_COUNT = 32 };
 constexpr int N_EPI = 256;       // epilogue threads
 constexpr int N_LOAD = 128;      // loader threads
 constexpr int W_LOAD0 = 8, W_MMA = 12, W_WPROD = 13;
@@ -80,36 +80,86 @@ __device__ __forceinline__ Work decode(const TcParams& p, int w) {
 // ------------------------------------------------------------------------------ A loader
 struct ChunkRef {
   int b, row0, kc;
-  uint32_t sa;
+  uint32_t sa, ph;
 };
 
-// (row, 8-channel group) units of one chunk, strided over the loader threads
+// (row, 8-channel group) units of one chunk, strided over the loader threads: consecutive
+// threads take consecutive rows of one channel group (contiguous in the group-major layout).
 template <typename F>
 __device__ __forceinline__ void for_units(const TcParams& p, int tid, F&& f) {
   const int c8n = p.KC >> 3;
   if ((N_LOAD % c8n) == 0) {                     // c8n in {1,2,4,8,16}: fixed channel group per thread
-    const int c8 = tid % c8n, rstep = N_LOAD / c8n;
+    const int rthr = N_LOAD / c8n;
+    const int c8 = tid / rthr;
 #pragma unroll 4
-    for (int row = tid / c8n; row < p.R; row += rstep) f(row, c8);
+    for (int row = tid % rthr; row < p.R; row += rthr) f(row, c8);
   } else {
     const int units = p.R * c8n;
     for (int u = tid; u < units; u += N_LOAD) {
-      const int row = u / c8n;
-      f(row, u - row * c8n);
+      const int c8 = u / p.R;
+      f(u - c8 * p.R, c8);
     }
   }
 }
 
+__device__ __forceinline__ long long group_off(const TcView& v, int g) {
+  int hi, lo;
+  if (v.g1_shift >= 0) {
+    hi = g >> v.g1_shift;
+    lo = g & (v.G1 - 1);
+  } else {
+    hi = g / v.G1;
+    lo = g - hi * v.G1;
+  }
+  return (long long)lo * v.sA + (long long)hi * v.sB;
+}
+
 __device__ __forceinline__ void issue_a_chunk(const TcParams& p, const ChunkRef& c, uint32_t stage, int tid) {
-  const __nv_bfloat16* base = p.x.p + ((size_t)c.b * p.x.ld + p.x.hist) * p.x.C + (size_t)c.kc * p.KC;
+  const uint4* base = reinterpret_cast<const uint4*>(p.x.p) + (long long)c.b * p.x.sb + (long long)p.x.hist * p.x.sT;
   const uint32_t col = (uint32_t)p.R_ALLOC * 16u;
+  const int kg0 = c.kc * (p.KC >> 3);
   for_units(p, tid, [&](int row, int c8) {
     const int t = c.row0 + row;
     const bool ok = t >= p.x.lo && t < p.x.n;
-    const void* src = ok ? (const void*)(base + (ptrdiff_t)t * p.x.C + c8 * 8) : (const void*)p.x.p;
+    const void* src = ok ? (const void*)(base + group_off(p.x, kg0 + c8) + (long long)t * p.x.sT) : (const void*)p.x.p;
     cp_async16(stage + (uint32_t)c8 * col + (uint32_t)row * 16u, src, ok ? 16u : 0u);
   });
   cp_async_commit();
+}
+
+// Bulk path (views whose rows are contiguous per channel group, sT == 1): ONE thread issues a
+// cp.async.bulk per channel group for the valid row range; rows outside [lo, n) are zeroed by
+// the loader threads in the finish pass.
+__device__ __forceinline__ void valid_rows(const TcParams& p, const ChunkRef& c, int& r0, int& r1) {
+  r0 = p.x.lo - c.row0;
+  if (r0 < 0) r0 = 0;
+  r1 = p.x.n - c.row0;
+  if (r1 > p.R) r1 = p.R;
+  if (r1 < r0) r1 = r0;
+}
+__device__ __forceinline__ void issue_a_bulk(const TcParams& p, const ChunkRef& c, uint32_t stage, uint32_t bar) {
+  int r0, r1;
+  valid_rows(p, c, r0, r1);
+  const int c8n = p.KC >> 3;
+  const uint32_t bytes = (uint32_t)(r1 - r0) * 16u;
+  mbar_expect_tx(bar, bytes * (uint32_t)c8n);
+  if (bytes == 0) return;
+  const uint4* base = reinterpret_cast<const uint4*>(p.x.p) + (long long)c.b * p.x.sb +
+                      (long long)(p.x.hist + c.row0 + r0);
+  const uint32_t col = (uint32_t)p.R_ALLOC * 16u;
+  const int kg0 = c.kc * c8n;
+  for (int c8 = 0; c8 < c8n; ++c8)
+    bulk_g2s(stage + (uint32_t)c8 * col + (uint32_t)r0 * 16u, base + group_off(p.x, kg0 + c8), bytes, bar);
+}
+__device__ __forceinline__ void zero_fill_edges(const TcParams& p, const ChunkRef& c, uint8_t* stage, int tid) {
+  int r0, r1;
+  valid_rows(p, c, r0, r1);
+  if (r0 == 0 && r1 == p.R) return;
+  const size_t col = (size_t)p.R_ALLOC * 16;
+  for_units(p, tid, [&](int row, int c8) {
+    if (row < r0 || row >= r1)
+      *reinterpret_cast<uint4*>(stage + (size_t)c8 * col + (size_t)row * 16) = make_uint4(0u, 0u, 0u, 0u);
+  });
 }
 
 // LeakyReLU(0.2) on two packed bf16: max(x, 0.2 x).  0.2 is not a bf16, so the product is
@@ -173,26 +223,29 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
   const int gpr = (NT + 31) >> 5;                       // 32-column groups per row
   const int G = MTn * gpr;
   const bool has_res = p.res.p != nullptr;
-  auto res_ptr = [&](int g, bool& ok, int& ncol) -> const __nv_bfloat16* {
+  const uint4* res_base = reinterpret_cast<const uint4*>(p.res.p) + (long long)wk.b * p.res.sb +
+                          (long long)(p.res.hist - p.res_delay) * p.res.sT;
+  uint4* y_base = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) + (long long)wk.b * p.y.sb +
+                  (long long)p.y.hist * p.y.sT;
+  // 16-byte unit of channel group q (0..3) of 32-column group g of this thread's row
+  auto res_ptr = [&](int g, bool& ok, int& ncol, int& t, int& cg) {
     const int mt = g / gpr, c0 = (g - mt * gpr) * 32;
-    const int t = wk.t0 + mt * 128 + rit;
+    t = wk.t0 + mt * 128 + rit;
     ncol = NT - c0 < 32 ? NT - c0 : 32;
     ok = t < p.y.n;
-    return p.res.p + ((size_t)wk.b * p.res.ld + p.res.hist + (t - p.res_delay)) * p.res.C + ch0 + c0;
+    cg = (ch0 + c0) >> 3;
+  };
+  auto load_rr = [&](int g, uint4* rr) {
+    bool ok; int ncol, t, cg;
+    res_ptr(g, ok, ncol, t, cg);
+    if (!ok) return;
+    const uint4* rp = res_base + (long long)t * p.res.sT;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (q * 8 < ncol) rr[q] = __ldg(rp + group_off(p.res, cg + q));
   };
   uint4 rr[4];
-  if (has_res && half < G) {
-    bool ok; int ncol;
-    const __nv_bfloat16* rp = res_ptr(half, ok, ncol);
-    if (ok) {
-      rr[0] = __ldg(reinterpret_cast<const uint4*>(rp));
-      rr[1] = __ldg(reinterpret_cast<const uint4*>(rp + 8));
-      if (ncol > 16) {
-        rr[2] = __ldg(reinterpret_cast<const uint4*>(rp + 16));
-        rr[3] = __ldg(reinterpret_cast<const uint4*>(rp + 24));
-      }
-    }
-  }
+  if (has_res && half < G) load_rr(half, rr);
   mbar_wait(bar_full, parity);
   tc_fence_after();
   for (int g = half; g < G; g += 2) {
@@ -213,28 +266,17 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
         }
       }
     }
-    if (has_res && g + 2 < G) {                          // prefetch the next group's residual
-      bool ok; int n2;
-      const __nv_bfloat16* rp = res_ptr(g + 2, ok, n2);
-      if (ok) {
-        rr[0] = __ldg(reinterpret_cast<const uint4*>(rp));
-        rr[1] = __ldg(reinterpret_cast<const uint4*>(rp + 8));
-        if (n2 > 16) {
-          rr[2] = __ldg(reinterpret_cast<const uint4*>(rp + 16));
-          rr[3] = __ldg(reinterpret_cast<const uint4*>(rp + 24));
-        }
-      }
-    }
+    if (has_res && g + 2 < G) load_rr(g + 2, rr);       // prefetch the next group's residual
     if (valid) {
       if (p.out_mask && !(t & 1)) {
 #pragma unroll
         for (int e = 1; e < 32; e += 2) v[e] = -v[e];
       }
-      __nv_bfloat16* yp =
-          const_cast<__nv_bfloat16*>(p.y.p) + ((size_t)wk.b * p.y.ld + p.y.hist + t) * p.y.C + ch0 + c0;
+      uint4* yp = y_base + (long long)t * p.y.sT;
+      const int cg = (ch0 + c0) >> 3;
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        if (q * 8 < ncol) *reinterpret_cast<uint4*>(yp + q * 8) = pack8(v + q * 8);
+        if (q * 8 < ncol) yp[group_off(p.y, cg + q)] = pack8(v + q * 8);
     }
   }
   tc_fence_before();
@@ -269,6 +311,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       mbar_init(BAR(BAR_A_EMPTY + i), 1);
       mbar_init(BAR(BAR_W_FULL + i), 1);
       mbar_init(BAR(BAR_W_EMPTY + i), 1);
+      mbar_init(BAR(BAR_RAW_FULL + i), 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(BAR(BAR_D_FULL + i), 1);
@@ -315,8 +358,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       const ChunkRef c = pend[0];
       pend[0] = pend[1]; pend[1] = pend[2]; pend[2] = pend[3];
       --n_pend;
-      cp_async_wait(n_pend);
-      finish_a_chunk<PRE>(p, c, a_smem + (size_t)c.sa * p.a_stage_bytes, ltid);
+      uint8_t* stage = a_smem + (size_t)c.sa * p.a_stage_bytes;
+      if (p.bulk_a) {
+        mbar_wait(BAR(BAR_RAW_FULL + c.sa), c.ph);
+        zero_fill_edges(p, c, stage, ltid);
+      } else {
+        cp_async_wait(n_pend);
+      }
+      finish_a_chunk<PRE>(p, c, stage, ltid);
       fence_proxy_async();
       mbar_arrive(BAR(BAR_A_FULL + c.sa));
     };
@@ -325,9 +374,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       for (int kc = 0; kc < p.n_kchunks; ++kc) {
         if (__ldg(p.masks + wk.nt * p.n_kchunks + kc) == 0) continue;
         const uint32_t sa = it % p.SA, ph = (it / p.SA) & 1;
-        mbar_wait(BAR(BAR_A_EMPTY + sa), ph ^ 1);
-        ChunkRef c{wk.b, wk.t0 - p.off, kc, sa};
-        issue_a_chunk(p, c, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes), ltid);
+        ChunkRef c{wk.b, wk.t0 - p.off, kc, sa, ph};
+        const uint32_t stage = smem_u32(a_smem + (size_t)sa * p.a_stage_bytes);
+        if (p.bulk_a) {
+          if (ltid == 0) {
+            mbar_wait(BAR(BAR_A_EMPTY + sa), ph ^ 1);
+            issue_a_bulk(p, c, stage, BAR(BAR_RAW_FULL + sa));
+          }
+        } else {
+          mbar_wait(BAR(BAR_A_EMPTY + sa), ph ^ 1);
+          issue_a_chunk(p, c, stage, ltid);
+        }
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           if (k == n_pend) pend[k] = c;

@@ -21,10 +21,19 @@ namespace tc {
 constexpr int TC_MAX_NT = 8;        // output-channel tiles per layer
 constexpr int TC_THREADS = 448;     // warps 0-7 epilogue, 8-11 A loaders, 12 MMA issuer, 13 W producer
 
-// [stream][ld rows][C] bf16; element (b, t, c) at p[((size_t)b*ld + hist + t)*C + c], t in [lo, n)
+// A row view of an activation tensor, addressed in 16-byte units (8 bf16 = one channel group):
+//   unit(b, t, g) = b*sb + (hist + t)*sT + (g % G1)*sA + (g / G1)*sB        t in [lo, n)
+// g = view channel / 8.  The engine's internal layout is group-major [stream][C/8][row][8]
+// (sA = rows per stream, sB = 1, sT = view factor): a 128-row tile of one channel group is one
+// contiguous run, so loads are bulk copies and epilogue stores are fully coalesced.  Audio
+// ([stream][T], read / written as rows of 16 samples) uses sA = 1, sT = 2.
 struct TcView {
   const __nv_bfloat16* p;
-  int C, ld, hist, n, lo;
+  long long sb;
+  int sA, sB, sT, G1;
+  int g1_shift;             // log2(G1) when G1 is a power of two, else -1
+  int C;                    // view channels (8 * number of groups)
+  int hist, n, lo;
 };
 
 struct TcParams {
@@ -48,6 +57,7 @@ struct TcParams {
   int MT;                   // 128-row sub-tiles per work item (1 or 2)
   int R, R_ALLOC;           // A rows per stage (MT*128 + max shift), allocated (odd)
   int w_resident;           // all blocks live in smem for the whole kernel
+  int bulk_a;               // A rows are contiguous per channel group: load with cp.async.bulk
   int SA, SW, SD;           // A stages, W stages (streamed), accumulator stages
   int out_mask;             // 1: negate odd channels at even rows (pqmf.py:13-17 reverse_half)
   int tiles_per_stream, n_work;

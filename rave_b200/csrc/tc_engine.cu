@@ -248,7 +248,9 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
 }
 
 // ------------------------------------------------------------------ buffers and launches
-// One activation tensor of the bf16 engine, in un-reshaped row units.
+// One activation tensor of the bf16 engine, in un-reshaped row units.  Layout: group-major
+// [stream][cp/8][ld rows][8 channels] (cp = channels rounded up to 16); audio (cp == 1) is the
+// caller's dense [stream][ld samples].
 struct Buf {
   __nv_bfloat16* p = nullptr;
   int cp = 0, ld = 0, hist = 0, n = 0, lo = 0;
@@ -257,8 +259,17 @@ struct Buf {
 static int make_view(const Buf& b, int f, TcView* v) {
   RB_CHECK(b.ld % f == 0 && b.hist % f == 0 && b.n % f == 0, RB_ERR_INVALID,
            "tensor rows (%d,%d,%d) not divisible by the view factor %d", b.ld, b.hist, b.n, f);
-  v->p = b.p; v->C = b.cp * f; v->ld = b.ld / f; v->hist = b.hist / f; v->n = b.n / f;
-  v->lo = floordiv(b.lo, f);
+  v->p = b.p; v->hist = b.hist / f; v->n = b.n / f; v->lo = floordiv(b.lo, f);
+  if (b.cp == 1) {                              // audio: rows of f samples, f/8 groups per row
+    RB_CHECK(f % 8 == 0 && b.ld % 8 == 0, RB_ERR_INVALID, "audio view needs a factor that is a multiple of 8");
+    v->C = f; v->G1 = f / 8; v->sA = 1; v->sB = 0; v->sT = f / 8; v->sb = b.ld / 8;
+  } else {
+    const int G = b.cp / 8;
+    v->C = b.cp * f; v->G1 = G; v->sA = b.ld; v->sB = 1; v->sT = f; v->sb = (long long)G * b.ld;
+  }
+  v->g1_shift = -1;
+  for (int sh = 0; sh < 20; ++sh)
+    if ((1 << sh) == v->G1) v->g1_shift = sh;
   return RB_OK;
 }
 
@@ -287,14 +298,15 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   p.N_TILE = L.N_TILE; p.n_ntiles = L.n_ntiles;
   for (int i = 0; i <= L.n_ntiles; ++i) p.nt_base[i] = L.nt_base[i];
   p.out_mask = L.out_mask;
+  p.bulk_a = (p.x.sT == 1 && p.x.sB == 1) ? 1 : 0;
   p.fused = L.fused ? 1 : 0;
   p.act2 = L.act2; p.bias2 = L.bias2; p.alpha2 = L.alpha2; p.n_blk1 = L.total_blocks;
   const int halo = (L.n_taps - 1) * L.dil;
   const uint32_t budget = 224u * 1024u;
   const uint32_t w_total = (uint32_t)(L.total_blocks + (L.fused ? L.N_TILE / L.KC : 0)) * L.blk_bytes;
   p.w_blk_bytes = L.blk_bytes;
-  p.off_bias = 256;
-  const uint32_t fixed = align_up(256 + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
+  p.off_bias = 320;           // after 32 mbarriers (256 B) and the TMEM address slot
+  const uint32_t fixed = align_up(320 + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
   p.SH = L.fused ? 2 : 0;
   p.h_stage_bytes = L.fused ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
   const uint32_t h_total = p.SH * p.h_stage_bytes;
@@ -336,106 +348,110 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   return launch_tc_conv(p, s);
 }
 
-// ------------------------------------------------------- channels-last elementwise kernels
-// All of these are bandwidth-bound single passes; one thread per (row, 8-channel group) or
-// per element, rows of all streams flattened.
-__device__ __forceinline__ size_t row_index(const Buf& b, int bi, int t) {
-  return ((size_t)bi * b.ld + b.hist + t) * b.cp;
+// ------------------------------------------------------------------- elementwise kernels
+// Bandwidth-bound single passes over group-major tensors; the flat index runs in the memory
+// order of the output (stream, channel group, row, channel-in-group).
+__device__ __forceinline__ size_t eidx(const Buf& b, int bi, int t, int c) {
+  if (b.cp == 1) return (size_t)bi * b.ld + b.hist + t;
+  return (((size_t)bi * (b.cp >> 3) + (c >> 3)) * b.ld + b.hist + t) * 8 + (c & 7);
+}
+__device__ __forceinline__ void decode_gm(size_t i, const Buf& y, int& b, int& t, int& c) {
+  const int e = (int)(i & 7);
+  size_t r = i >> 3;
+  t = (int)(r % y.n);
+  r /= y.n;
+  const int G = y.cp >> 3;
+  c = (int)(r % G) * 8 + e;
+  b = (int)(r / G);
 }
 
-// [B][C][n] (caller layout, dense) -> [B][n][Cp]
-__global__ void cf_to_cl_kernel(const __nv_bfloat16* __restrict__ src, Buf dst, int C, int B) {
+// [B][C][n] (caller layout, dense) -> engine layout
+__global__ void cf_to_gm_kernel(const __nv_bfloat16* __restrict__ src, Buf dst, int C, int B) {
   const size_t total = (size_t)B * dst.n * dst.cp;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % dst.cp);
-    const size_t r = i / dst.cp;
-    const int t = (int)(r % dst.n), b = (int)(r / dst.n);
-    dst.p[row_index(dst, b, t) + c] = c < C ? src[((size_t)b * C + c) * dst.n + t] : __float2bfloat16_rn(0.f);
+    int b, t, c;
+    decode_gm(i, dst, b, t, c);
+    dst.p[eidx(dst, b, t, c)] = c < C ? src[((size_t)b * C + c) * dst.n + t] : __float2bfloat16_rn(0.f);
   }
 }
-// [B][n][Cp] -> [B][C][n]
-__global__ void cl_to_cf_kernel(Buf src, __nv_bfloat16* __restrict__ dst, int C, int B) {
+// engine layout -> [B][C][n]
+__global__ void gm_to_cf_kernel(Buf src, __nv_bfloat16* __restrict__ dst, int C, int B) {
   const size_t total = (size_t)B * C * src.n;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int t = (int)(i % src.n);
     const size_t r = i / src.n;
     const int c = (int)(r % C), b = (int)(r / C);
-    dst[i] = src.p[row_index(src, b, t) + c];
+    dst[i] = src.p[eidx(src, b, t, c)];
   }
 }
 // model.py:618-620: z = cat(z, speaker.repeat(B, 1, F)) (+ zero pad channels)
-__global__ void concat_cl_kernel(Buf z, Buf y, const float* __restrict__ cond, int c_z, int c_cond, int B) {
+__global__ void concat_gm_kernel(Buf z, Buf y, const float* __restrict__ cond, int c_z, int c_cond, int B) {
   const size_t total = (size_t)B * y.n * y.cp;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % y.cp);
-    const size_t r = i / y.cp;
-    const int t = (int)(r % y.n), b = (int)(r / y.n);
+    int b, t, c;
+    decode_gm(i, y, b, t, c);
     __nv_bfloat16 v = __float2bfloat16_rn(0.f);
-    if (c < c_z) v = z.p[row_index(z, b, t) + c];
+    if (c < c_z) v = z.p[eidx(z, b, t, c)];
     else if (c < c_z + c_cond) v = __float2bfloat16_rn(cond[c - c_z]);
-    y.p[row_index(y, b, t) + c] = v;
+    y.p[eidx(y, b, t, c)] = v;
   }
 }
 // AdaIN transfer (blocks.py:885-891) as x = a[b][c]*x + b[b][c], in place
-__global__ void affine_cl_kernel(Buf x, const float* __restrict__ a, const float* __restrict__ bb, int C, int B) {
-  const size_t total = (size_t)B * x.n * C;
+__global__ void affine_gm_kernel(Buf x, const float* __restrict__ a, const float* __restrict__ bb, int C, int B) {
+  const size_t total = (size_t)B * x.n * x.cp;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % C);
-    const size_t r = i / C;
-    const int t = (int)(r % x.n), b = (int)(r / x.n);
-    __nv_bfloat16* q = x.p + row_index(x, b, t) + c;
+    int b, t, c;
+    decode_gm(i, x, b, t, c);
+    if (c >= C) continue;
+    __nv_bfloat16* q = x.p + eidx(x, b, t, c);
     *q = __float2bfloat16_rn(fmaf(__bfloat162float(*q), a[(size_t)b * C + c], bb[(size_t)b * C + c]));
   }
 }
 // GeneratorV2.forward tail (blocks.py:699-707) + reverse_half of the synthesis bank input
-__global__ void head_v2_cl_kernel(Buf w, Buf nz, Buf y, int data, int am, int B) {
+__global__ void head_v2_gm_kernel(Buf w, Buf nz, Buf y, int data, int am, int B) {
   const size_t total = (size_t)B * y.n * y.cp;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % y.cp);
-    const size_t r = i / y.cp;
-    const int t = (int)(r % y.n), b = (int)(r / y.n);
+    int b, t, c;
+    decode_gm(i, y, b, t, c);
     float v = 0.f;
     if (c < data) {
-      const __nv_bfloat16* wp = w.p + row_index(w, b, t);
-      v = __bfloat162float(wp[c]);
-      if (am) v *= 1.f / (1.f + expf(-__bfloat162float(wp[data + c])));
-      if (nz.p) v += __bfloat162float(nz.p[row_index(nz, b, t) + c]);
+      v = __bfloat162float(w.p[eidx(w, b, t, c)]);
+      if (am) v *= 1.f / (1.f + __expf(-__bfloat162float(w.p[eidx(w, b, t, data + c)])));
+      if (nz.p) v += __bfloat162float(nz.p[eidx(nz, b, t, c)]);
       v = tanhf(v);
       if ((c & 1) && !(t & 1)) v = -v;
     }
-    y.p[row_index(y, b, t) + c] = __float2bfloat16_rn(v);
+    y.p[eidx(y, b, t, c)] = __float2bfloat16_rn(v);
   }
 }
 // Generator.forward tail (blocks.py:412): tanh(waveform) * mod_sigmoid(loudness)
-__global__ void head_v1_cl_kernel(Buf wv, Buf ld, Buf y, int data, int B) {
+__global__ void head_v1_gm_kernel(Buf wv, Buf ld, Buf y, int data, int B) {
   const size_t total = (size_t)B * y.n * y.cp;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % y.cp);
-    const size_t r = i / y.cp;
-    const int t = (int)(r % y.n), b = (int)(r / y.n);
+    int b, t, c;
+    decode_gm(i, y, b, t, c);
     float v = 0.f;
     if (c < data) {
-      const float sg = 1.f / (1.f + expf(-__bfloat162float(ld.p[row_index(ld, b, t)])));
-      v = tanhf(__bfloat162float(wv.p[row_index(wv, b, t) + c])) * (2.f * powf(sg, 2.3f) + 1e-7f);
+      const float sg = 1.f / (1.f + expf(-__bfloat162float(ld.p[eidx(ld, b, t, 0)])));
+      v = tanhf(__bfloat162float(wv.p[eidx(wv, b, t, c)])) * (2.f * powf(sg, 2.3f) + 1e-7f);
       if ((c & 1) && !(t & 1)) v = -v;
     }
-    y.p[row_index(y, b, t) + c] = __float2bfloat16_rn(v);
+    y.p[eidx(y, b, t, c)] = __float2bfloat16_rn(v);
   }
 }
 // NoiseGeneratorV2.forward tail (blocks.py:281-291, core.py:66,95-129) in closed form; one
 // thread per (stream, block q, band d) -- see kernels_f32.cu for the derivation.
-__global__ void noise_v2_cl_kernel(Buf amp, const float* __restrict__ noise, long long nbs, Buf y, int data,
+__global__ void noise_v2_gm_kernel(Buf amp, const float* __restrict__ noise, long long nbs, Buf y, int data,
                                    int nblk, unsigned long long seed, int B) {
   const size_t total = (size_t)B * nblk * data;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int d = (int)(i % data);
-    const size_t r = i / data;
-    const int q = (int)(r % nblk), b = (int)(r / nblk);
+    const int q = (int)(i % nblk);
+    const size_t r = i / nblk;
+    const int d = (int)(r % data), b = (int)(r / data);
     float a[5];
-    const __nv_bfloat16* ap = amp.p + row_index(amp, b, q) + d * 5;
 #pragma unroll
     for (int n = 0; n < 5; ++n) {
-      const float hh = __bfloat162float(ap[n]) - 5.f;
+      const float hh = __bfloat162float(amp.p[eidx(amp, b, q, d * 5 + n)]) - 5.f;
       const float sg = 1.f / (1.f + expf(-hh));
       a[n] = 2.f * powf(sg, 2.3f) + 1e-7f;
     }
@@ -466,17 +482,16 @@ __global__ void noise_v2_cl_kernel(Buf amp, const float* __restrict__ noise, lon
       float sacc = 0.f;
 #pragma unroll
       for (int j = 0; j <= t; ++j) sacc = fmaf(nzv[j], ir[t - j], sacc);
-      y.p[row_index(y, b, q * 8 + t) + d] = __float2bfloat16_rn(sacc);
+      y.p[eidx(y, b, q * 8 + t, d)] = __float2bfloat16_rn(sacc);
     }
   }
 }
 __global__ void zero_pad_channels_kernel(Buf y, int C, int B) {
-  const int padc = y.cp - C;
-  const size_t total = (size_t)B * y.n * padc;
+  const size_t total = (size_t)B * y.n * y.cp;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c = C + (int)(i % padc);
-    const size_t r = i / padc;
-    y.p[row_index(y, (int)(r / y.n), (int)(r % y.n)) + c] = __float2bfloat16_rn(0.f);
+    int b, t, c;
+    decode_gm(i, y, b, t, c);
+    if (c >= C) y.p[eidx(y, b, t, c)] = __float2bfloat16_rn(0.f);
   }
 }
 
@@ -571,25 +586,25 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
       RB_CHECK(B <= w.aff_rows, RB_ERR_INVALID,
                "batch %d exceeds the %d rows of AdaIN statistics (cc.MAX_BATCH_SIZE)", B, w.aff_rows);
       const Buf& x = bufs[op.src];
-      RB_LAUNCH_EW(affine_cl_kernel, (size_t)B * x.n * op.c_in, s, x, w.aff_a, w.aff_b, op.c_in, B);
+      RB_LAUNCH_EW(affine_gm_kernel, (size_t)B * x.n * x.cp, s, x, w.aff_a, w.aff_b, op.c_in, B);
       return RB_OK;
     }
     case RB_OP_HEAD_V2: {
       const Buf& y = bufs[op.dst];
-      RB_LAUNCH_EW(head_v2_cl_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src],
+      RB_LAUNCH_EW(head_v2_gm_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src],
                    op.src2 >= 0 ? bufs[op.src2] : Buf(), y, op.c_out, op.k, B);
       return RB_OK;
     }
     case RB_OP_HEAD_V1: {
       const Buf& y = bufs[op.dst];
-      RB_LAUNCH_EW(head_v1_cl_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src], bufs[op.src2], y, op.c_out, B);
+      RB_LAUNCH_EW(head_v1_gm_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src], bufs[op.src2], y, op.c_out, B);
       return RB_OK;
     }
     case RB_OP_NOISE_V2: {
       const Buf& amp = bufs[op.src];
       const Buf& y = bufs[op.dst];
-      if (y.cp > op.c_out) RB_LAUNCH_EW(zero_pad_channels_kernel, (size_t)B * y.n * (y.cp - op.c_out), s, y, op.c_out, B);
-      RB_LAUNCH_EW(noise_v2_cl_kernel, (size_t)B * amp.n * op.c_out, s, amp, noise, (long long)noise_bstride, y,
+      if (y.cp > op.c_out) RB_LAUNCH_EW(zero_pad_channels_kernel, (size_t)B * y.n * y.cp, s, y, op.c_out, B);
+      RB_LAUNCH_EW(noise_v2_gm_kernel, (size_t)B * amp.n * op.c_out, s, amp, noise, (long long)noise_bstride, y,
                    op.c_out, amp.n, h->noise_seed++, B);
       return RB_OK;
     }
@@ -597,7 +612,7 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
       const OpWeights& w = h->w[i];
       RB_CHECK(w.cond, RB_ERR_STATE, "conditioning vector (speaker embedding) not loaded");
       const Buf& y = bufs[op.dst];
-      RB_LAUNCH_EW(concat_cl_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src], y, w.cond, op.c_in,
+      RB_LAUNCH_EW(concat_gm_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src], y, w.cond, op.c_in,
                    op.c_out - op.c_in, B);
       return RB_OK;
     }
@@ -665,7 +680,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
       int rc = alloc_slot(in_slot);
       if (rc) return rc;
       const Buf& b = bufs[in_slot];
-      RB_LAUNCH_EW(cf_to_cl_kernel, (size_t)nb * b.n * b.cp, s,
+      RB_LAUNCH_EW(cf_to_gm_kernel, (size_t)nb * b.n * b.cp, s,
                    (const __nv_bfloat16*)in + (size_t)b0 * in_ch * b.n, b, in_ch, nb);
     }
     if (pl->cp[out_slot] == 1) {
@@ -714,7 +729,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
     if (pl->cp[out_slot] != 1) {
       const Buf& b = bufs[out_slot];
       RB_CHECK(b.p, RB_ERR_STATE, "program output was never written");
-      RB_LAUNCH_EW(cl_to_cf_kernel, (size_t)nb * out_ch * b.n, s, b,
+      RB_LAUNCH_EW(gm_to_cf_kernel, (size_t)nb * out_ch * b.n, s, b,
                    (__nv_bfloat16*)out + (size_t)b0 * out_ch * b.n, out_ch, nb);
     }
   }
@@ -786,7 +801,7 @@ extern "C" int rb_debug_conv_bf16(const rb_debug_conv* d) {
       for (int bi = 0; bi < B; ++bi)
         for (int c = 0; c < C; ++c)
           for (int t = 0; t < b.n; ++t)
-            tmp[((size_t)bi * b.n + t) * b.cp + c] = __float2bfloat16_rn(host[((size_t)bi * C + c) * b.n + t]);
+            tmp[(((size_t)bi * (b.cp >> 3) + (c >> 3)) * b.n + t) * 8 + (c & 7)] = __float2bfloat16_rn(host[((size_t)bi * C + c) * b.n + t]);
       RB_CUDA(cudaMemcpy(b.p, tmp.data(), elems * 2, cudaMemcpyHostToDevice));
     }
     return RB_OK;
@@ -812,7 +827,7 @@ extern "C" int rb_debug_conv_bf16(const rb_debug_conv* d) {
     for (int bi = 0; bi < B; ++bi)
       for (int c = 0; c < C; ++c)
         for (int t = 0; t < b.n; ++t)
-          d->y[((size_t)bi * C + c) * b.n + t] = __bfloat162float(tmp[((size_t)bi * b.n + t) * b.cp + c]);
+          d->y[((size_t)bi * C + c) * b.n + t] = __bfloat162float(tmp[(((size_t)bi * (b.cp >> 3) + (c >> 3)) * b.n + t) * 8 + (c & 7)]);
     if (d->fused_out) *d->fused_out = pl->layers[0].fused ? 1 : 0;
   }
   for (void* p : to_free) cudaFree(p);
