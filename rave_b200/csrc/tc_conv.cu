@@ -1,26 +1,31 @@
 // tc_conv.cu -- the tcgen05 implicit-GEMM convolution kernel of the bf16 engine.
 //
-// One persistent CTA per SM, warp-specialised (14 warps):
-//   warps 0-7   epilogue    TMEM -> registers (tcgen05.ld) -> bias / residual / sign mask -> HBM.
-//                           Warp w owns TMEM lanes 32*(w%4).. (hardware rule) and the 32-column
-//                           groups of parity w/4.  Fused DilatedUnit: also writes act(conv3 + b)
-//                           back to smem as the A operand of the 1x1 conv -- the intermediate
-//                           never leaves the SM.
-//   warps 8-11  A loaders   channels-last rows HBM -> smem by 16-byte cp.async (several chunks in
-//                           flight), zero padding / stream edges by zero-fill, then the
-//                           pre-activation (LeakyReLU / Snake) in place in smem, stored in the
-//                           UMMA K-major no-swizzle core-matrix layout
-//   warp  12    MMA issuer  one thread: tcgen05.mma (M=128, N=N_TILE, K=16) per tap and K step;
-//                           a dilated / shifted tap is only a different start row of the same
-//                           smem tile (descriptor start address + 16 B per row), fp32
+// One persistent CTA per SM, warp-specialised (15 warps):
+//   warps 0-7   epilogue    TMEM -> registers (tcgen05.ld) -> bias / residual / sign mask /
+//                           output activation -> HBM.  Warp w owns TMEM lanes 32*(w%4).. (hardware
+//                           rule) and the 32-column groups of parity w/4.  Fused DilatedUnit: also
+//                           writes act(conv3 + b) back to smem as the A operand of the 1x1 conv --
+//                           the intermediate never leaves the SM.
+//   warps 8-11  act pass    only when the input tensor is stored un-activated (Snake nets, raw
+//                           program inputs): pre-activation in place in smem between the TMA
+//                           landing and the MMA.  LeakyReLU nets store every tensor already
+//                           activated (the producer's epilogue applies it; a residual read inverts
+//                           it with min(z, 5z)), so these warps idle and TMA feeds the MMA directly.
+//   warp  12    MMA issuer  one elected thread: tcgen05.mma (M=128, N=N_TILE, K=16) per tap and K
+//                           step; a dilated / shifted tap is only a different start row of the
+//                           same smem tile (descriptor start address + 16 B per row), fp32
 //                           accumulators in TMEM, double-buffered against the epilogue
 //   warp  13    W producer  weight blocks L2 -> smem with cp.async.bulk on an mbarrier ring,
 //                           or once for the whole kernel when the layer's weights fit
+//   warp  14    A producer  one thread: TMA tensor-map boxes (rows x channel groups) of the input
+//                           view -> smem; strided / phase views, zero padding and stream edges
+//                           are all the tensor map's job (out-of-range rows are zero-filled)
 // Stages hand over through mbarriers only; tcgen05.commit releases smem stages and publishes
 // accumulators.  smem A tile:  addr(row, c8) = c8*(R_ALLOC*16) + row*16   (c8 = 8-channel group)
 //        weight block [N][KC]: addr(n,   c8) = c8*(N*16)       + n*16
-// The activation kinds are template parameters so that each instantiation stays small
-// (the first version branched per element and thrashed the instruction cache).
+// The activation kinds are template parameters so that each instantiation stays small.
+#include <cuda.h>
+
 #include "common.cuh"
 #include "tc_conv.cuh"
 #include "tc_ptx.cuh"
@@ -35,7 +40,7 @@ enum { BAR_A_FULL = 0, BAR_A_EMPTY = 4, BAR_W_FULL = 8, BAR_W_EMPTY = 12, BAR_D_
        BAR_RAW_FULL = 28, BAR_COUNT = 32 };
 constexpr int N_EPI = 256;       // epilogue threads
 constexpr int N_LOAD = 128;      // loader threads
-constexpr int W_LOAD0 = 8, W_MMA = 12, W_WPROD = 13;
+constexpr int W_LOAD0 = 8, W_MMA = 12, W_WPROD = 13, W_APROD = 14;
 
 template <int ACT>
 __device__ __forceinline__ float act_f(float v, float alpha) {
@@ -67,24 +72,38 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 struct Work {
   int nt, b, t0;
 };
-__device__ __forceinline__ Work decode(const TcParams& p, int w) {
-  const int n_rt = p.B * p.tiles_per_stream;
-  Work k;
-  k.nt = w / n_rt;
-  const int rt = w - k.nt * n_rt;
-  k.b = rt / p.tiles_per_stream;
-  k.t0 = (rt - k.b * p.tiles_per_stream) * p.MT * 128;
-  return k;
-}
+// The work items of one persistent CTA: w = blockIdx.x + i * gridDim.x, decoded once with
+// divisions and then advanced by the pre-decomposed grid stride (adds and compares only).
+struct WorkIter {
+  int nt, b, tile, left;
+  __device__ __forceinline__ void init(const TcParams& p) {
+    const int w = blockIdx.x;
+    const int n_rt = p.B * p.tiles_per_stream;
+    nt = w / n_rt;
+    const int rt = w - nt * n_rt;
+    b = rt / p.tiles_per_stream;
+    tile = rt - b * p.tiles_per_stream;
+    left = w < p.n_work ? (p.n_work - w + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  }
+  __device__ __forceinline__ void next(const TcParams& p) {
+    tile += p.step_tile;
+    if (tile >= p.tiles_per_stream) { tile -= p.tiles_per_stream; ++b; }
+    b += p.step_b;
+    if (b >= p.B) { b -= p.B; ++nt; }
+    nt += p.step_nt;
+    --left;
+  }
+  __device__ __forceinline__ Work work(const TcParams& p) const { return Work{nt, b, tile * p.MT * 128}; }
+};
 
-// ------------------------------------------------------------------------------ A loader
+// ------------------------------------------------------------------------------ A tile
 struct ChunkRef {
-  int b, row0, kc;
+  int kc;
   uint32_t sa, ph;
 };
 
-// (row, 8-channel group) units of one chunk, strided over the loader threads: consecutive
-// threads take consecutive rows of one channel group (contiguous in the group-major layout).
+// (row, 8-channel group) units of one chunk, strided over the act-pass threads: consecutive
+// threads take consecutive rows of one channel group (consecutive 16-byte units: no conflicts).
 template <typename F>
 __device__ __forceinline__ void for_units(const TcParams& p, int tid, F&& f) {
   const int c8n = p.KC >> 3;
@@ -114,52 +133,24 @@ __device__ __forceinline__ long long group_off(const TcView& v, int g) {
   return (long long)lo * v.sA + (long long)hi * v.sB;
 }
 
-__device__ __forceinline__ void issue_a_chunk(const TcParams& p, const ChunkRef& c, uint32_t stage, int tid) {
-  const uint4* base = reinterpret_cast<const uint4*>(p.x.p) + (long long)c.b * p.x.sb + (long long)p.x.hist * p.x.sT;
-  const uint32_t col = (uint32_t)p.R_ALLOC * 16u;
-  const int kg0 = c.kc * (p.KC >> 3);
-  for_units(p, tid, [&](int row, int c8) {
-    const int t = c.row0 + row;
-    const bool ok = t >= p.x.lo && t < p.x.n;
-    const void* src = ok ? (const void*)(base + group_off(p.x, kg0 + c8) + (long long)t * p.x.sT) : (const void*)p.x.p;
-    cp_async16(stage + (uint32_t)c8 * col + (uint32_t)row * 16u, src, ok ? 16u : 0u);
-  });
-  cp_async_commit();
-}
-
-// Bulk path (views whose rows are contiguous per channel group, sT == 1): ONE thread issues a
-// cp.async.bulk per channel group for the valid row range; rows outside [lo, n) are zeroed by
-// the loader threads in the finish pass.
-__device__ __forceinline__ void valid_rows(const TcParams& p, const ChunkRef& c, int& r0, int& r1) {
-  r0 = p.x.lo - c.row0;
-  if (r0 < 0) r0 = 0;
-  r1 = p.x.n - c.row0;
-  if (r1 > p.R) r1 = p.R;
-  if (r1 < r0) r1 = r0;
-}
-__device__ __forceinline__ void issue_a_bulk(const TcParams& p, const ChunkRef& c, uint32_t stage, uint32_t bar) {
-  int r0, r1;
-  valid_rows(p, c, r0, r1);
+// One chunk (KC/8 channel groups x R_ALLOC rows starting at view row `row0`) as TMA boxes.
+// Tensor-map coordinates: {0, phase, row - lo, channel group, stream}; rows outside [lo, n)
+// arrive as zeros (conv zero padding, stream edges), so no thread touches the tile.
+__device__ __forceinline__ void issue_a_tma(const TcParams& p, const void* tmap, int b, int row0, int kc,
+                                            uint32_t stage, uint32_t bar) {
+  mbar_expect_tx(bar, p.a_tx_bytes);
   const int c8n = p.KC >> 3;
-  const uint32_t bytes = (uint32_t)(r1 - r0) * 16u;
-  mbar_expect_tx(bar, bytes * (uint32_t)c8n);
-  if (bytes == 0) return;
-  const uint4* base = reinterpret_cast<const uint4*>(p.x.p) + (long long)c.b * p.x.sb +
-                      (long long)(p.x.hist + c.row0 + r0);
-  const uint32_t col = (uint32_t)p.R_ALLOC * 16u;
-  const int kg0 = c.kc * c8n;
-  for (int c8 = 0; c8 < c8n; ++c8)
-    bulk_g2s(stage + (uint32_t)c8 * col + (uint32_t)r0 * 16u, base + group_off(p.x, kg0 + c8), bytes, bar);
-}
-__device__ __forceinline__ void zero_fill_edges(const TcParams& p, const ChunkRef& c, uint8_t* stage, int tid) {
-  int r0, r1;
-  valid_rows(p, c, r0, r1);
-  if (r0 == 0 && r1 == p.R) return;
-  const size_t col = (size_t)p.R_ALLOC * 16;
-  for_units(p, tid, [&](int row, int c8) {
-    if (row < r0 || row >= r1)
-      *reinterpret_cast<uint4*>(stage + (size_t)c8 * col + (size_t)row * 16) = make_uint4(0u, 0u, 0u, 0u);
-  });
+  const int kg0 = kc * c8n;
+  const int row = row0 - p.x.lo;
+  for (int g = 0; g < c8n; g += p.a_gb) {
+    const int vg = kg0 + g;
+    int ph, cg;
+    if (p.x.g1_shift >= 0) { ph = vg >> p.x.g1_shift; cg = vg & (p.x.G1 - 1); }
+    else { ph = vg / p.x.G1; cg = vg - ph * p.x.G1; }
+    for (int rs = 0; rs < p.a_rsplit; ++rs)
+      tma_load_5d(stage + (uint32_t)(g * p.R_ALLOC + rs * p.a_box_rows) * 16u, tmap, 0, ph,
+                  row + rs * p.a_box_rows, cg, b, bar);
+  }
 }
 
 // LeakyReLU(0.2) on two packed bf16: max(x, 0.2 x).  0.2 is not a bf16, so the product is
@@ -172,9 +163,15 @@ __device__ __forceinline__ uint32_t leaky2(uint32_t w) {
   const __nv_bfloat162 y = __hmax2(x, __hfma2(x, c1, __hmul2(x, c2)));
   return *reinterpret_cast<const uint32_t*>(&y);
 }
+// Inverse of LeakyReLU(0.2) on two packed bf16: x = min(z, 5 z)  (5 z is exact to one rounding).
+__device__ __forceinline__ uint32_t unleaky2(uint32_t w) {
+  const __nv_bfloat162 z = *reinterpret_cast<const __nv_bfloat162*>(&w);
+  const __nv_bfloat162 y = __hmin2(z, __hmul2(z, __floats2bfloat162_rn(5.f, 5.f)));
+  return *reinterpret_cast<const uint32_t*>(&y);
+}
 
 template <int PRE>
-__device__ __forceinline__ void finish_a_chunk(const TcParams& p, const ChunkRef& c, uint8_t* stage, int tid) {
+__device__ __forceinline__ void finish_a_chunk(const TcParams& p, int kc, uint8_t* stage, int tid) {
   if (PRE == RB_ACT_NONE) return;
   const size_t col = (size_t)p.R_ALLOC * 16;
   for_units(p, tid, [&](int row, int c8) {
@@ -186,7 +183,7 @@ __device__ __forceinline__ void finish_a_chunk(const TcParams& p, const ChunkRef
     } else {
       float f[8];
       unpack8(*q, f);
-      const float4* al = reinterpret_cast<const float4*>(p.alpha + c.kc * p.KC + c8 * 8);
+      const float4* al = reinterpret_cast<const float4*>(p.alpha + kc * p.KC + c8 * 8);
       const float4 a0 = __ldg(al), a1 = __ldg(al + 1);
       const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
@@ -260,7 +257,9 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
       for (int q = 0; q < 4; ++q) {
         if (q * 8 < ncol) {
           float f[8];
-          unpack8(rr[q], f);
+          uint4 r4 = rr[q];
+          if (p.res_act) { r4.x = unleaky2(r4.x); r4.y = unleaky2(r4.y); r4.z = unleaky2(r4.z); r4.w = unleaky2(r4.w); }
+          unpack8(r4, f);
 #pragma unroll
           for (int e = 0; e < 8; ++e) v[q * 8 + e] += f[e];
         }
@@ -271,6 +270,10 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
       if (p.out_mask && !(t & 1)) {
 #pragma unroll
         for (int e = 1; e < 32; e += 2) v[e] = -v[e];
+      }
+      if (p.out_act) {                                  // stored activated: LeakyReLU(0.2)
+#pragma unroll
+        for (int e = 0; e < 32; ++e) v[e] = fmaxf(v[e], 0.2f * v[e]);
       }
       uint4* yp = y_base + (long long)t * p.y.sT;
       const int cg = (ch0 + c0) >> 3;
@@ -289,7 +292,8 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
 #define COMMIT(bar) do { if (leader) mma_commit(bar); } while (0)
 
 template <int PRE, int ACT2, bool FUSED>
-__global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_constant__ TcParams p) {
+__global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_constant__ TcParams p,
+                                                                const __grid_constant__ TcTmap tmx) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_COUNT * 8);
@@ -307,7 +311,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
 
   if (tid == 0) {
     for (int i = 0; i < 4; ++i) {
-      mbar_init(BAR(BAR_A_FULL + i), N_LOAD);
+      mbar_init(BAR(BAR_A_FULL + i), PRE == RB_ACT_NONE ? 1 : N_LOAD);
       mbar_init(BAR(BAR_A_EMPTY + i), 1);
       mbar_init(BAR(BAR_W_FULL + i), 1);
       mbar_init(BAR(BAR_W_EMPTY + i), 1);
@@ -345,55 +349,42 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
   const int C2 = p.N_TILE;                        // fused: channels of the unit
   const uint32_t d_stage_cols = FUSED ? 2u * C2 : (uint32_t)(p.MT * p.N_TILE);
 
-  if (warp >= W_LOAD0 && warp < W_MMA) {
-    // ============================================================== A loaders (128 threads)
-    // Software-pipelined: up to LA chunks are in flight (cp.async groups) before the oldest is
-    // finished (activation pass, proxy fence) and handed to the MMA warp.
-    const int ltid = tid - W_LOAD0 * 32;
-    const int LA = p.SA - 1 < 3 ? p.SA - 1 : 3;
-    ChunkRef pend[4] = {};
-    int n_pend = 0;
-    uint32_t it = 0;
-    auto retire = [&]() {
-      const ChunkRef c = pend[0];
-      pend[0] = pend[1]; pend[1] = pend[2]; pend[2] = pend[3];
-      --n_pend;
-      uint8_t* stage = a_smem + (size_t)c.sa * p.a_stage_bytes;
-      if (p.bulk_a) {
-        mbar_wait(BAR(BAR_RAW_FULL + c.sa), c.ph);
-        zero_fill_edges(p, c, stage, ltid);
-      } else {
-        cp_async_wait(n_pend);
-      }
-      finish_a_chunk<PRE>(p, c, stage, ltid);
-      fence_proxy_async();
-      mbar_arrive(BAR(BAR_A_FULL + c.sa));
-    };
-    for (int w = blockIdx.x; w < p.n_work; w += gridDim.x) {
-      const Work wk = decode(p, w);
-      for (int kc = 0; kc < p.n_kchunks; ++kc) {
-        if (__ldg(p.masks + wk.nt * p.n_kchunks + kc) == 0) continue;
-        const uint32_t sa = it % p.SA, ph = (it / p.SA) & 1;
-        ChunkRef c{wk.b, wk.t0 - p.off, kc, sa, ph};
-        const uint32_t stage = smem_u32(a_smem + (size_t)sa * p.a_stage_bytes);
-        if (p.bulk_a) {
-          if (ltid == 0) {
-            mbar_wait(BAR(BAR_A_EMPTY + sa), ph ^ 1);
-            issue_a_bulk(p, c, stage, BAR(BAR_RAW_FULL + sa));
-          }
-        } else {
+  if (warp == W_APROD) {
+    // ============================================================ A producer (one thread, TMA)
+    if (lane == 0) {
+      prefetch_tmap(&tmx);
+      uint32_t it = 0;
+      WorkIter wi;
+      for (wi.init(p); wi.left > 0; wi.next(p)) {
+        const Work wk = wi.work(p);
+        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+          if (__ldg(p.masks + wk.nt * p.n_kchunks + kc) == 0) continue;
+          const uint32_t sa = it % p.SA, ph = (it / p.SA) & 1;
           mbar_wait(BAR(BAR_A_EMPTY + sa), ph ^ 1);
-          issue_a_chunk(p, c, stage, ltid);
+          issue_a_tma(p, &tmx, wk.b, wk.t0 - p.off, kc, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes),
+                      BAR((PRE == RB_ACT_NONE ? BAR_A_FULL : BAR_RAW_FULL) + sa));
+          ++it;
         }
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (k == n_pend) pend[k] = c;
-        ++n_pend;
-        ++it;
-        if (n_pend > LA) retire();
       }
     }
-    while (n_pend > 0) retire();
+  } else if (warp >= W_LOAD0 && warp < W_MMA) {
+    // =============================== pre-activation pass in smem (un-activated inputs only)
+    if (PRE != RB_ACT_NONE) {
+      const int ltid = tid - W_LOAD0 * 32;
+      uint32_t it = 0;
+      WorkIter wi;
+      for (wi.init(p); wi.left > 0; wi.next(p)) {
+        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+          if (__ldg(p.masks + wi.nt * p.n_kchunks + kc) == 0) continue;
+          const uint32_t sa = it % p.SA, ph = (it / p.SA) & 1;
+          mbar_wait(BAR(BAR_RAW_FULL + sa), ph);
+          finish_a_chunk<PRE>(p, kc, a_smem + (size_t)sa * p.a_stage_bytes, ltid);
+          fence_proxy_async();
+          mbar_arrive(BAR(BAR_A_FULL + sa));
+          ++it;
+        }
+      }
+    }
   } else if (warp == W_WPROD) {
     // =========================================================== W producer (one thread)
     if (lane == 0) {
@@ -407,8 +398,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         }
       } else {
         uint32_t it = 0;
-        for (int w = blockIdx.x; w < p.n_work; w += gridDim.x) {
-          const Work wk = decode(p, w);
+        WorkIter wi;
+        for (wi.init(p); wi.left > 0; wi.next(p)) {
+          const Work wk = wi.work(p);
           int gblk = p.nt_base[wk.nt];
           for (int kc = 0; kc < p.n_kchunks; ++kc) {
             const uint64_t mask = __ldg(p.masks + wk.nt * p.n_kchunks + kc);
@@ -562,8 +554,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         COMMIT(BAR(BAR_D2_FULL + sd));
       };
       uint32_t i = 0;
-      for (int w = blockIdx.x; w < p.n_work; w += gridDim.x, ++i) {
-        gemm1(i, decode(p, w));
+      WorkIter wi;
+      for (wi.init(p); wi.left > 0; wi.next(p), ++i) {
+        gemm1(i, wi.work(p));
         if (FUSED && i >= 1) gemm2(i - 1);
       }
       if (FUSED && i >= 1) gemm2(i - 1);
@@ -615,8 +608,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
     };
     uint32_t i = 0;
     Work prev{0, 0, 0};
-    for (int w = blockIdx.x; w < p.n_work; w += gridDim.x, ++i) {
-      const Work wk = decode(p, w);
+    WorkIter wi;
+    for (wi.init(p); wi.left > 0; wi.next(p), ++i) {
+      const Work wk = wi.work(p);
       if (!FUSED) {
         epi_plain(i, wk);
       } else {
@@ -637,18 +631,56 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
 }
 
 template <int PRE, int ACT2, bool FUSED>
-static int launch_variant(const TcParams& p, int grid, cudaStream_t s) {
+static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
     RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024));
     attr_set = true;
   }
-  tc_conv_kernel<PRE, ACT2, FUSED><<<grid, TC_THREADS, p.smem_bytes, s>>>(p);
+  tc_conv_kernel<PRE, ACT2, FUSED><<<grid, TC_THREADS, p.smem_bytes, s>>>(p, tm);
   return RB_OK;
 }
 
-int launch_tc_conv(const TcParams& p, cudaStream_t s) {
+// 5-D tensor map over the input view (16-byte unit u(b,t,g) of tc_conv.cuh):
+//   dim0 8 bf16 | dim1 phase g/G1 (stride sB) | dim2 row t - lo (stride sT) | dim3 g%G1 (stride sA)
+//   | dim4 stream (stride sb);   box = {8, 1, a_box_rows, a_gb, 1}, zero fill out of range.
+static int make_tmap(const TcParams& p, TcTmap* tm) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                               const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                               CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = nullptr;
+  if (!encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    RB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+    RB_CHECK(fn && qr == cudaDriverEntryPointSuccess, RB_ERR_CUDA, "cuTensorMapEncodeTiled is not available");
+    encode = (EncodeFn)fn;
+  }
+  static_assert(sizeof(TcTmap) == sizeof(CUtensorMap), "tensor map size");
+  const TcView& x = p.x;
+  const int groups = x.C / 8;
+  const int phases = (groups + x.G1 - 1) / x.G1;
+  RB_CHECK(groups % x.G1 == 0 || phases == 1, RB_ERR_INVALID, "view groups %d not a multiple of G1 %d", groups, x.G1);
+  const int g1 = phases == 1 ? groups : x.G1;
+  const long long base_units = (long long)(x.hist + x.lo) * x.sT;
+  void* base = (void*)(reinterpret_cast<const uint4*>(x.p) + base_units);
+  auto stride = [](long long units) { return (cuuint64_t)(units > 0 ? units : 1) * 16ull; };
+  const cuuint64_t dims[5] = {8, (cuuint64_t)phases, (cuuint64_t)(x.n - x.lo), (cuuint64_t)g1, (cuuint64_t)p.B};
+  const cuuint64_t strides[4] = {stride(x.sB), stride(x.sT), stride(x.sA), stride(x.sb)};
+  const cuuint32_t box[5] = {8, 1, (cuuint32_t)p.a_box_rows, (cuuint32_t)p.a_gb, 1};
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  const CUresult r = encode(reinterpret_cast<CUtensorMap*>(tm), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, base, dims,
+                            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RB_CHECK(r == CUDA_SUCCESS, RB_ERR_CUDA,
+           "cuTensorMapEncodeTiled failed (%d): dims {8,%d,%d,%d,%d} strides {%lld,%lld,%lld,%lld} box {%d,%d}", (int)r,
+           phases, x.n - x.lo, g1, p.B, (long long)strides[0], (long long)strides[1], (long long)strides[2],
+           (long long)strides[3], p.a_box_rows, p.a_gb);
+  return RB_OK;
+}
+
+int launch_tc_conv(TcParams& p, cudaStream_t s) {
   if (p.n_work <= 0) return RB_OK;
   static int n_sm = 0;
   if (!n_sm) {
@@ -658,16 +690,29 @@ int launch_tc_conv(const TcParams& p, cudaStream_t s) {
   }
   RB_CHECK(p.smem_bytes <= 227u * 1024u, RB_ERR_UNSUPPORTED, "tc conv needs %u B of shared memory",
            p.smem_bytes);
+  RB_CHECK(p.out_act == RB_ACT_NONE || p.out_act == RB_ACT_LEAKY, RB_ERR_UNSUPPORTED,
+           "only LeakyReLU can be stored activated");
   const int grid = p.n_work < n_sm ? p.n_work : n_sm;
-  int rc = RB_ERR_UNSUPPORTED;
+  {
+    const int n_rt = p.B * p.tiles_per_stream;
+    p.step_nt = grid / n_rt;
+    const int r1 = grid - p.step_nt * n_rt;
+    p.step_b = r1 / p.tiles_per_stream;
+    p.step_tile = r1 - p.step_b * p.tiles_per_stream;
+  }
+  TcTmap tm;
+  int rc = make_tmap(p, &tm);
+  if (rc) return rc;
+  rc = RB_ERR_UNSUPPORTED;
   if (!p.fused) {
-    if (p.pre_act == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false>(p, grid, s);
-    else if (p.pre_act == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_NONE, false>(p, grid, s);
-    else if (p.pre_act == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_NONE, false>(p, grid, s);
+    if (p.pre_act == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false>(p, tm, grid, s);
+    else if (p.pre_act == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_NONE, false>(p, tm, grid, s);
+    else if (p.pre_act == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_NONE, false>(p, tm, grid, s);
   } else {
-    if (p.pre_act == RB_ACT_LEAKY && p.act2 == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_LEAKY, true>(p, grid, s);
-    else if (p.pre_act == RB_ACT_SNAKE && p.act2 == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_SNAKE, true>(p, grid, s);
-    else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, true>(p, grid, s);
+    if (p.pre_act == RB_ACT_LEAKY && p.act2 == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_LEAKY, true>(p, tm, grid, s);
+    else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true>(p, tm, grid, s);
+    else if (p.pre_act == RB_ACT_SNAKE && p.act2 == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_SNAKE, true>(p, tm, grid, s);
+    else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, true>(p, tm, grid, s);
   }
   if (rc == RB_ERR_UNSUPPORTED) {
     set_error("tc conv: activation combination (%d, %d, fused=%d) has no kernel variant", p.pre_act, p.act2, p.fused);

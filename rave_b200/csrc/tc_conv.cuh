@@ -2,7 +2,7 @@
 //
 // Every convolution of the path (cc.Conv1d, strided cc.Conv1d, cc.ConvTranspose1d as r
 // phase-convs, both PQMF banks) is expressed in the bf16 engine as a ROW-SHIFT GEMM over
-// channels-last activations [stream][row][channel]:
+// row views of the activations:
 //
 //     D[t, n] = sum_taps j  sum_c  A[t + j*dil - off, c] * W_j[n, c]
 //
@@ -19,7 +19,7 @@ namespace rb {
 namespace tc {
 
 constexpr int TC_MAX_NT = 8;        // output-channel tiles per layer
-constexpr int TC_THREADS = 448;     // warps 0-7 epilogue, 8-11 A loaders, 12 MMA issuer, 13 W producer
+constexpr int TC_THREADS = 480;     // warps 0-7 epilogue, 8-11 activation pass, 12 MMA, 13 W, 14 A producer
 
 // A row view of an activation tensor, addressed in 16-byte units (8 bf16 = one channel group):
 //   unit(b, t, g) = b*sb + (hist + t)*sT + (g % G1)*sA + (g / G1)*sB        t in [lo, n)
@@ -48,7 +48,9 @@ struct TcParams {
   const float* aff_a;       // AdaIN scale  [rows][c_in] applied before the pre-activation, or nullptr
   const float* aff_b;       // AdaIN shift
   int aff_C;                // channels of the affine tables (un-reshaped tensor)
-  int pre_act;              // rb_act on the input
+  int pre_act;              // rb_act applied to the input tile in smem (NONE: TMA feeds the MMA directly)
+  int out_act;              // rb_act applied to the stored output (consumers then skip their pre_act)
+  int res_act;              // the residual tensor is stored LeakyReLU-activated: invert it on read
   int B;
   int n_taps, dil, off;     // row taps: shift_j = j*dil - off
   int KC, n_kchunks;        // input channels per K chunk (multiple of 16), chunks per row
@@ -57,7 +59,11 @@ struct TcParams {
   int MT;                   // 128-row sub-tiles per work item (1 or 2)
   int R, R_ALLOC;           // A rows per stage (MT*128 + max shift), allocated (odd)
   int w_resident;           // all blocks live in smem for the whole kernel
-  int bulk_a;               // A rows are contiguous per channel group: load with cp.async.bulk
+  // A tile TMA boxes (tensor map over the input view, see launch_tc_conv): a chunk of KC/8
+  // channel groups x R_ALLOC rows is fetched as boxes of a_gb groups x a_box_rows rows
+  int a_gb, a_box_rows, a_rsplit;
+  uint32_t a_tx_bytes;      // bytes one chunk adds to its mbarrier
+  int step_nt, step_b, step_tile;   // work-item increment of a persistent CTA (grid stride, decomposed)
   int SA, SW, SD;           // A stages, W stages (streamed), accumulator stages
   int out_mask;             // 1: negate odd channels at even rows (pqmf.py:13-17 reverse_half)
   int tiles_per_stream, n_work;
@@ -74,7 +80,13 @@ struct TcParams {
   uint32_t tmem_cols;       // power of two >= 32
 };
 
-int launch_tc_conv(const TcParams& p, cudaStream_t s);
+// Opaque CUtensorMap (128 bytes, 64-byte aligned) passed to the kernel by value.
+struct alignas(64) TcTmap {
+  unsigned long long opaque[16];
+};
+
+// Fills the step_* fields and the tensor map from p.x, then launches.
+int launch_tc_conv(TcParams& p, cudaStream_t s);
 
 }  // namespace tc
 }  // namespace rb

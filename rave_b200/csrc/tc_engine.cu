@@ -47,6 +47,9 @@ struct Plan {
   std::vector<Layer> layers;      // per op
   std::vector<int> skip;          // op is the tail of a fused pair
   std::vector<int> cp;            // per slot channel pitch
+  // per slot: tensor is stored LeakyReLU-activated (every consumer wants act(x) as conv input, or
+  // x as a residual, which min(z, 5z) recovers) -- consumers then load it straight into the MMA
+  std::vector<int> sact;
 };
 
 static int slot_cp(const rb_handle* h, int sl) {
@@ -262,7 +265,7 @@ static int make_view(const Buf& b, int f, TcView* v) {
   v->p = b.p; v->hist = b.hist / f; v->n = b.n / f; v->lo = floordiv(b.lo, f);
   if (b.cp == 1) {                              // audio: rows of f samples, f/8 groups per row
     RB_CHECK(f % 8 == 0 && b.ld % 8 == 0, RB_ERR_INVALID, "audio view needs a factor that is a multiple of 8");
-    v->C = f; v->G1 = f / 8; v->sA = 1; v->sB = 0; v->sT = f / 8; v->sb = b.ld / 8;
+    v->C = f; v->G1 = 1; v->sA = 0; v->sB = 1; v->sT = f / 8; v->sb = b.ld / 8;   // group g of a row = unit g
   } else {
     const int G = b.cp / 8;
     v->C = b.cp * f; v->G1 = G; v->sA = b.ld; v->sB = 1; v->sT = f; v->sb = (long long)G * b.ld;
@@ -275,8 +278,9 @@ static int make_view(const Buf& b, int f, TcView* v) {
 
 static uint32_t align_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
 
+// x_act / res_act / out_act: the tensor is (to be) stored LeakyReLU-activated (Plan::sact).
 static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Buf& src, const Buf& dst,
-                     const Buf* res, int B, cudaStream_t s) {
+                     const Buf* res, int B, cudaStream_t s, int x_act = 0, int res_act = 0, int out_act = 0) {
   TcParams p;
   memset(&p, 0, sizeof(p));
   int rc = make_view(src, L.fin, &p.x);
@@ -291,14 +295,15 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     p.res_delay = rop.res_delay;
   }
   p.w = L.w; p.masks = L.masks; p.bias = L.bias; p.alpha = L.alpha;
-  p.pre_act = op.pre_act;
+  p.pre_act = x_act ? RB_ACT_NONE : op.pre_act;
+  p.out_act = out_act ? RB_ACT_LEAKY : RB_ACT_NONE;
+  p.res_act = (res && res_act) ? 1 : 0;
   p.B = B;
   p.n_taps = L.n_taps; p.dil = L.dil; p.off = L.off;
   p.KC = L.KC; p.n_kchunks = L.n_kchunks;
   p.N_TILE = L.N_TILE; p.n_ntiles = L.n_ntiles;
   for (int i = 0; i <= L.n_ntiles; ++i) p.nt_base[i] = L.nt_base[i];
   p.out_mask = L.out_mask;
-  p.bulk_a = (p.x.sT == 1 && p.x.sB == 1) ? 1 : 0;
   p.fused = L.fused ? 1 : 0;
   p.act2 = L.act2; p.bias2 = L.bias2; p.alpha2 = L.alpha2; p.n_blk1 = L.total_blocks;
   const int halo = (L.n_taps - 1) * L.dil;
@@ -318,8 +323,26 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     p.w_resident = resident ? 1 : 0;
     p.MT = (!resident && p.y.n >= 256) ? 2 : 1;
     p.R = p.MT * 128 + halo;
-    p.R_ALLOC = p.R | 1;
-    p.a_stage_bytes = align_up((uint32_t)(L.KC / 8) * p.R_ALLOC * 16u, 128);
+    {
+      // TMA boxes of the A tile: whole chunk in one box when the rows fit a box (<= 256), else
+      // one box per channel group and row half
+      const int c8n = L.KC / 8;
+      const int groups = p.x.C / 8;
+      const int g1 = groups <= p.x.G1 ? groups : p.x.G1;
+      const int r8 = (p.R + 7) & ~7;
+      if (r8 <= 256) {
+        p.R_ALLOC = r8; p.a_rsplit = 1; p.a_box_rows = r8;
+        int gb = c8n;
+        while (g1 % gb) --gb;
+        while (c8n % gb) --gb;
+        p.a_gb = gb;
+      } else {
+        p.R_ALLOC = (p.R + 15) & ~15; p.a_rsplit = 2; p.a_box_rows = p.R_ALLOC / 2; p.a_gb = 1;
+      }
+      RB_CHECK(p.a_box_rows <= 256, RB_ERR_UNSUPPORTED, "A tile of %d rows exceeds two TMA boxes", p.R);
+      p.a_tx_bytes = (uint32_t)c8n * p.R_ALLOC * 16u;
+    }
+    p.a_stage_bytes = (uint32_t)(L.KC / 8) * p.R_ALLOC * 16u;
     p.SW = resident ? 0 : 4;
     uint32_t w_bytes = resident ? align_up(w_total, 128) : p.SW * L.blk_bytes;
     if (!resident && fixed + w_bytes + 2 * p.a_stage_bytes > budget) { p.SW = 2; w_bytes = p.SW * L.blk_bytes; }
@@ -529,6 +552,27 @@ int tc_pack_weights(rb_handle* h) {
   pl->skip.assign(nops, 0);
   pl->cp.resize(h->slots.size());
   for (size_t s = 0; s < h->slots.size(); ++s) pl->cp[s] = slot_cp(h, (int)s);
+  // Activated storage: a slot written by a conv and read only by convs that pre-activate it
+  // with LeakyReLU (or add it as a residual) is stored as leaky(x) by its producer.
+  {
+    const int ns = (int)h->slots.size();
+    std::vector<int> ok(ns, 1), conv_reads(ns, 0), conv_writes(ns, 0);
+    auto bad = [&](int sl) { if (sl >= 0 && sl < ns) ok[sl] = 0; };
+    for (int i = 0; i < nops; ++i) {
+      const rb_op& op = h->ops[i];
+      if (op.kind == RB_OP_CONV) {
+        if (op.pre_act == RB_ACT_LEAKY && op.src_ch_off == 0) ++conv_reads[op.src]; else bad(op.src);
+        ++conv_writes[op.dst];
+      } else {
+        bad(op.src); bad(op.dst); bad(op.res);
+      }
+      bad(op.src2);
+    }
+    bad(h->spec.enc_in_slot); bad(h->spec.enc_out_slot); bad(h->spec.dec_in_slot); bad(h->spec.dec_out_slot);
+    bad(h->spec.noise_slot);
+    pl->sact.assign(ns, 0);
+    for (int sl = 0; sl < ns; ++sl) pl->sact[sl] = ok[sl] && conv_reads[sl] > 0 && conv_writes[sl] > 0;
+  }
   for (int i = 0; i < nops; ++i) {
     const rb_op& op = h->ops[i];
     if (pl->skip[i]) continue;
@@ -574,11 +618,14 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
     case RB_OP_PQMF_FWD:
     case RB_OP_PQMF_INV: {
       RB_CHECK(L.valid, RB_ERR_STATE, "op %d has no bf16 plan", i);
+      const std::vector<int>& sa = pl->sact;
       if (L.fused) {
         const rb_op& o2 = h->ops[L.fused_with];
-        return run_layer(L, op, &o2, bufs[op.src], bufs[o2.dst], &bufs[o2.res], B, s);
+        return run_layer(L, op, &o2, bufs[op.src], bufs[o2.dst], &bufs[o2.res], B, s, sa[op.src], sa[o2.res],
+                         sa[o2.dst]);
       }
-      return run_layer(L, op, nullptr, bufs[op.src], bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s);
+      return run_layer(L, op, nullptr, bufs[op.src], bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,
+                       sa[op.src], op.res >= 0 ? sa[op.res] : 0, sa[op.dst]);
     }
     case RB_OP_AFFINE: {
       const OpWeights& w = h->w[i];
@@ -652,7 +699,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
   if (mb <= 0) {
     size_t per_stream = 0;
     for (int sl = 0; sl < ns; ++sl) per_stream = std::max(per_stream, slot_bytes(sl, 1));
-    const size_t budget = (size_t)128 << 20;
+    const size_t budget = (size_t)2 << 30;   // persistent kernels want >= several waves of tiles per launch
     mb = (int)std::max<size_t>(1, std::min<size_t>(B, budget / std::max<size_t>(per_stream, 1)));
   }
   const int in_ch = h->slots[in_slot].channels, out_ch = h->slots[out_slot].channels;
@@ -806,6 +853,13 @@ extern "C" int rb_debug_conv_bf16(const rb_debug_conv* d) {
     }
     return RB_OK;
   };
+  {
+    const int osl = d->n_ops == 2 ? 2 : 1;
+    pl->sact.assign(h->slots.size(), 0);
+    pl->sact[0] = (d->flags & 1) ? 1 : 0;         // x is given (and stored) LeakyReLU-activated
+    pl->sact[osl] = (d->flags & 2) ? 1 : 0;       // y is returned LeakyReLU-activated
+    pl->sact[3] = (d->flags & 4) ? 1 : 0;         // the explicit residual is given activated
+  }
   rc = mk(0, d->x);
   if (!rc) rc = mk(1, nullptr);
   if (!rc && d->n_ops == 2) rc = mk(2, nullptr);

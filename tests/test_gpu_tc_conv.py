@@ -46,7 +46,7 @@ def _ptr(a):
     return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
 
 
-def _run(ops, ws, bs, als, x, res=None):
+def _run(ops, ws, bs, als, x, res=None, flags=0):
     lib = capi.load_library()
     d = capi.RbDebugConv()
     keep = []
@@ -70,6 +70,7 @@ def _run(ops, ws, bs, als, x, res=None):
     d.y = _ptr(y)
     fused = C.c_int32(-1)
     d.fused_out = C.pointer(fused)
+    d.flags = flags
     capi.check(lib.rb_debug_conv_bf16(C.byref(d)))
     return y, fused.value
 
@@ -141,5 +142,63 @@ def test_dilated_unit_pair(C_, dil, act, n):
     y, fused = _run(ops, [w3.numpy(), w1.numpy()], [b3.numpy(), b1.numpy()],
                     [None if a3 is None else a3.numpy(), None if a1 is None else a1.numpy()], x.numpy())
     assert fused == (1 if C_ <= 64 else 0)
+    assert np.isfinite(y).all()
+    assert _rel(y, ref.numpy()) < TOL
+
+
+def _unleaky(z):
+    """What the kernel recovers from a tensor stored as z = bf16(leaky(x)): min(z, bf16(5 z))."""
+    return torch.minimum(z, (z * 5.0).bfloat16().float())
+
+
+ACT_CASES = [
+    # activated input (TMA feeds the MMA directly), activated output, activated residual
+    dict(c_in=64, c_out=64, k=3, stride=1, dil=3, off=3, ileave=1, res=1, B=2, n=333, flags=7),
+    dict(c_in=512, c_out=512, k=1, stride=1, dil=1, off=0, ileave=1, res=1, B=2, n=640, flags=5),
+    dict(c_in=64, c_out=128, k=8, stride=4, dil=1, off=3, ileave=1, res=0, B=2, n=1024, flags=3),
+    dict(c_in=256, c_out=512, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=2, n=160, flags=3),
+    dict(c_in=512, c_out=512, k=3, stride=1, dil=9, off=9, ileave=1, res=0, B=2, n=700, flags=1),
+    dict(c_in=64, c_out=32, k=7, stride=1, dil=1, off=3, ileave=1, res=0, B=2, n=1000, flags=1),
+]
+
+
+@pytest.mark.parametrize("c", ACT_CASES, ids=lambda c: "ci{c_in}_co{c_out}_k{k}_s{stride}_il{ileave}_f{flags}".format(**c))
+def test_single_conv_activated_storage(c):
+    """LeakyReLU nets keep tensors as leaky(x): the conv input needs no pass, a residual is
+    inverted with min(z, 5z), the output is activated in the epilogue before the bf16 store."""
+    g = torch.Generator().manual_seed(c["c_in"] * 17 + c["k"])
+    z = _bf(F.leaky_relu(torch.randn(c["B"], c["c_in"], c["n"], generator=g), 0.2).numpy())   # stored input
+    w = _bf((torch.randn(c["c_out"], c["c_in"], c["k"], generator=g) / np.sqrt(c["c_in"] * c["k"])).numpy())
+    r = c["ileave"]
+    b = torch.randn(c["c_out"] // r, generator=g) * 0.1
+    ref = _ref_conv(z, w, b, c["k"], c["stride"], c["dil"], c["off"], r, 0, None)
+    res = None
+    if c["res"]:
+        res = _bf(F.leaky_relu(torch.randn(ref.shape, generator=g), 0.2).numpy())
+        ref = ref + (_unleaky(res) if c["flags"] & 4 else res)
+    if c["flags"] & 2:
+        ref = F.leaky_relu(ref, 0.2)
+    op = dict(c_in=c["c_in"], c_out=c["c_out"], k=c["k"], stride=c["stride"], dilation=c["dil"], off=c["off"],
+              ileave=r, pre_act=1, has_bias=1, res_delay=0)
+    y, _ = _run([op], [w.numpy()], [b.numpy()], [None], z.numpy(), None if res is None else res.numpy(),
+                flags=c["flags"])
+    assert np.isfinite(y).all()
+    assert _rel(y, ref.numpy()) < TOL
+
+
+@pytest.mark.parametrize("C_,dil,n", [(64, 9, 777), (32, 1, 256), (128, 3, 300)])
+def test_dilated_unit_pair_activated_storage(C_, dil, n):
+    g = torch.Generator().manual_seed(C_ * 3 + dil)
+    B = 2
+    z = _bf(F.leaky_relu(torch.randn(B, C_, n, generator=g), 0.2).numpy())
+    w3 = _bf((torch.randn(C_, C_, 3, generator=g) / np.sqrt(3 * C_)).numpy())
+    w1 = _bf((torch.randn(C_, C_, 1, generator=g) / np.sqrt(C_)).numpy())
+    b3, b1 = torch.randn(C_, generator=g) * 0.1, torch.randn(C_, generator=g) * 0.1
+    h = _ref_conv(z, w3, b3, 3, 1, dil, dil, 1, 0, None)
+    hb = F.leaky_relu(h.bfloat16().float() if C_ > 64 else h, 0.2)   # unfused path stores h in bf16
+    ref = F.leaky_relu(_unleaky(z) + _ref_conv(hb, w1, b1, 1, 1, 1, 0, 1, 0, None), 0.2)
+    ops = [dict(c_in=C_, c_out=C_, k=3, stride=1, dilation=dil, off=dil, ileave=1, pre_act=1, has_bias=1, res_delay=0),
+           dict(c_in=C_, c_out=C_, k=1, stride=1, dilation=1, off=0, ileave=1, pre_act=1, has_bias=1, res_delay=0)]
+    y, fused = _run(ops, [w3.numpy(), w1.numpy()], [b3.numpy(), b1.numpy()], [None, None], z.numpy(), flags=3)
     assert np.isfinite(y).all()
     assert _rel(y, ref.numpy()) < TOL
