@@ -35,9 +35,12 @@ namespace tc {
 
 namespace {
 
-enum { BAR_A_FULL = 0, BAR_A_EMPTY = 4, BAR_W_FULL = 8, BAR_W_EMPTY = 12, BAR_D_FULL = 16,
-       BAR_D_EMPTY = 18, BAR_H_FULL = 20, BAR_H_EMPTY = 22, BAR_D2_FULL = 24, BAR_D2_EMPTY = 26,
-       BAR_RAW_FULL = 28, BAR_COUNT = 32 };
+constexpr int MAX_SA = 12;       // A stages: enough bytes in flight per SM to cover HBM latency
+enum { BAR_A_FULL = 0, BAR_A_EMPTY = MAX_SA, BAR_RAW_FULL = 2 * MAX_SA, BAR_W_FULL = 3 * MAX_SA,
+       BAR_W_EMPTY = BAR_W_FULL + 4, BAR_D_FULL = BAR_W_EMPTY + 4, BAR_D_EMPTY = BAR_D_FULL + 2,
+       BAR_H_FULL = BAR_D_EMPTY + 2, BAR_H_EMPTY = BAR_H_FULL + 2, BAR_D2_FULL = BAR_H_EMPTY + 2,
+       BAR_D2_EMPTY = BAR_D2_FULL + 2, BAR_COUNT = BAR_D2_EMPTY + 2 };
+static_assert(BAR_COUNT * 8 + 8 <= 512, "barriers + TMEM slot must fit below off_bias");
 constexpr int N_EPI = 256;       // epilogue threads
 constexpr int N_LOAD = 128;      // loader threads
 constexpr int W_LOAD0 = 8, W_MMA = 12, W_WPROD = 13, W_APROD = 14;
@@ -94,6 +97,14 @@ struct WorkIter {
     --left;
   }
   __device__ __forceinline__ Work work(const TcParams& p) const { return Work{nt, b, tile * p.MT * 128}; }
+};
+
+// Stage index + phase bit of an mbarrier ring, advanced without divisions.
+struct Ring {
+  uint32_t idx = 0, ph = 0;
+  __device__ __forceinline__ void next(int n) {
+    if (++idx == (uint32_t)n) { idx = 0; ph ^= 1; }
+  }
 };
 
 // ------------------------------------------------------------------------------ A tile
@@ -194,95 +205,141 @@ __device__ __forceinline__ void finish_a_chunk(const TcParams& p, int kc, uint8_
 }
 
 // ----------------------------------------------------------------------------- epilogues
-// 32 accumulator columns (16 when ncol == 16) of one row from TMEM, + bias (smem, float4 reads).
-__device__ __forceinline__ void load_acc32(uint32_t taddr, int ncol, const float* bias_s, float* v) {
-  uint32_t r[32];
-  tmem_ld16(taddr, r);
-  if (ncol > 16) tmem_ld16(taddr + 16u, r + 16);
+// NC (16 or 32) accumulator columns of one row from TMEM, + bias (smem, float4 reads issued
+// before the TMEM wait), packed fp32 adds.
+template <int NC>
+__device__ __forceinline__ void load_acc(uint32_t taddr, const float* bias_s, float* v) {
+  uint32_t r[NC];
+  if (NC == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+  float4 b[NC / 4];
+#pragma unroll
+  for (int g = 0; g < NC / 4; ++g) b[g] = *reinterpret_cast<const float4*>(bias_s + g * 4);
   tmem_ld_wait();
 #pragma unroll
-  for (int g = 0; g < 8; ++g) {
-    const float4 b = *reinterpret_cast<const float4*>(bias_s + g * 4);
-    v[g * 4 + 0] = __uint_as_float(r[g * 4 + 0]) + b.x;
-    v[g * 4 + 1] = __uint_as_float(r[g * 4 + 1]) + b.y;
-    v[g * 4 + 2] = __uint_as_float(r[g * 4 + 2]) + b.z;
-    v[g * 4 + 3] = __uint_as_float(r[g * 4 + 3]) + b.w;
+  for (int g = 0; g < NC / 4; ++g) {
+    v[g * 4 + 0] = __uint_as_float(r[g * 4 + 0]); v[g * 4 + 1] = __uint_as_float(r[g * 4 + 1]);
+    v[g * 4 + 2] = __uint_as_float(r[g * 4 + 2]); v[g * 4 + 3] = __uint_as_float(r[g * 4 + 3]);
+    add2(v[g * 4 + 0], v[g * 4 + 1], b[g].x, b[g].y);
+    add2(v[g * 4 + 2], v[g * 4 + 3], b[g].z, b[g].w);
+  }
+}
+// LeakyReLU(0.2) on NC fp32 values: packed multiply + max.
+template <int NC>
+__device__ __forceinline__ void leaky_n(float* v) {
+#pragma unroll
+  for (int e = 0; e < NC; e += 2) {
+    float u0, u1;
+    mul2(u0, u1, v[e], v[e + 1], 0.2f, 0.2f);
+    v[e] = fmaxf(v[e], u0);
+    v[e + 1] = fmaxf(v[e + 1], u1);
   }
 }
 
-// Drains the 32-column groups of parity `half` of `MTn` sub-tiles x `NT` accumulator columns
-// (TMEM address `tbase`, lane base included) into y at channel offset ch0: + bias, + residual,
-// optional sign mask, bf16, 16-byte stores.  The residual of a group is loaded before the
-// accumulator barrier / the previous group's stores so that its latency overlaps.
-__device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
-                                      const float* bs, const Work& wk, int rit, int half, int ch0, int MTn,
-                                      int NT) {
-  const int gpr = (NT + 31) >> 5;                       // 32-column groups per row
-  const int G = MTn * gpr;
-  const bool has_res = p.res.p != nullptr;
-  const uint4* res_base = reinterpret_cast<const uint4*>(p.res.p) + (long long)wk.b * p.res.sb +
-                          (long long)(p.res.hist - p.res_delay) * p.res.sT;
-  uint4* y_base = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) + (long long)wk.b * p.y.sb +
-                  (long long)p.y.hist * p.y.sT;
-  // 16-byte unit of channel group q (0..3) of 32-column group g of this thread's row
-  auto res_ptr = [&](int g, bool& ok, int& ncol, int& t, int& cg) {
-    const int mt = g / gpr, c0 = (g - mt * gpr) * 32;
-    t = wk.t0 + mt * 128 + rit;
-    ncol = NT - c0 < 32 ? NT - c0 : 32;
-    ok = t < p.y.n;
-    cg = (ch0 + c0) >> 3;
-  };
-  auto load_rr = [&](int g, uint4* rr) {
-    bool ok; int ncol, t, cg;
-    res_ptr(g, ok, ncol, t, cg);
-    if (!ok) return;
-    const uint4* rp = res_base + (long long)t * p.res.sT;
+// 16-byte-unit offset of channel group g inside one stream of a view (32-bit: a stream's
+// tensor is far below 2^31 units).
+__device__ __forceinline__ int goff32(const TcView& v, int g) {
+  int hi, lo;
+  if (v.g1_shift >= 0) {
+    hi = g >> v.g1_shift;
+    lo = g & (v.G1 - 1);
+  } else {
+    hi = g / v.G1;
+    lo = g - hi * v.G1;
+  }
+  return lo * v.sA + hi * v.sB;
+}
+
+// One chunk of NC columns of one output row: accumulator + bias (+ residual) -> sign mask /
+// output activation -> bf16 -> NC/8 16-byte stores at yp[q * ystep] (ystep < 0: per-group offsets).
+template <int NC>
+__device__ __forceinline__ void drain_chunk(const TcParams& p, uint32_t taddr, const float* bs, const uint4* rr,
+                                            bool has_res, bool valid, bool negate_odd, uint4* yp, int ystep,
+                                            int cg) {
+  float v[NC];
+  load_acc<NC>(taddr, bs, v);
+  if (!valid) return;
+  if (has_res) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
-      if (q * 8 < ncol) rr[q] = __ldg(rp + group_off(p.res, cg + q));
-  };
-  uint4 rr[4];
-  if (has_res && half < G) load_rr(half, rr);
-  mbar_wait(bar_full, parity);
-  tc_fence_after();
-  for (int g = half; g < G; g += 2) {
-    const int mt = g / gpr, c0 = (g - mt * gpr) * 32;
-    const int t = wk.t0 + mt * 128 + rit;
-    const int ncol = NT - c0 < 32 ? NT - c0 : 32;
-    const bool valid = t < p.y.n;
-    float v[32];
-    load_acc32(tbase + (uint32_t)(mt * NT + c0), ncol, bs + ch0 + c0, v);
-    if (has_res && valid) {
+    for (int q = 0; q < NC / 8; ++q) {
+      uint4 r4 = rr[q];
+      if (p.res_act) { r4.x = unleaky2(r4.x); r4.y = unleaky2(r4.y); r4.z = unleaky2(r4.z); r4.w = unleaky2(r4.w); }
+      const uint32_t w[4] = {r4.x, r4.y, r4.z, r4.w};
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        if (q * 8 < ncol) {
-          float f[8];
-          uint4 r4 = rr[q];
-          if (p.res_act) { r4.x = unleaky2(r4.x); r4.y = unleaky2(r4.y); r4.z = unleaky2(r4.z); r4.w = unleaky2(r4.w); }
-          unpack8(r4, f);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) v[q * 8 + e] += f[e];
-        }
-      }
-    }
-    if (has_res && g + 2 < G) load_rr(g + 2, rr);       // prefetch the next group's residual
-    if (valid) {
-      if (p.out_mask && !(t & 1)) {
-#pragma unroll
-        for (int e = 1; e < 32; e += 2) v[e] = -v[e];
-      }
-      if (p.out_act) {                                  // stored activated: LeakyReLU(0.2)
-#pragma unroll
-        for (int e = 0; e < 32; ++e) v[e] = fmaxf(v[e], 0.2f * v[e]);
-      }
-      uint4* yp = y_base + (long long)t * p.y.sT;
-      const int cg = (ch0 + c0) >> 3;
-#pragma unroll
-      for (int q = 0; q < 4; ++q)
-        if (q * 8 < ncol) yp[group_off(p.y, cg + q)] = pack8(v + q * 8);
+      for (int e = 0; e < 4; ++e)
+        add2(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1], __uint_as_float(w[e] << 16), __uint_as_float(w[e] & 0xffff0000u));
     }
   }
+  if (negate_odd) {
+#pragma unroll
+    for (int e = 1; e < NC; e += 2) v[e] = -v[e];
+  }
+  if (p.out_act) leaky_n<NC>(v);                        // stored activated: LeakyReLU(0.2)
+#pragma unroll
+  for (int q = 0; q < NC / 8; ++q) yp[ystep >= 0 ? q * ystep : goff32(p.y, cg + q)] = pack8(v + q * 8);
+}
+
+// Drains part `part` of `nparts` of the 32-column chunks of `MTn` sub-tiles x `NT` accumulator
+// columns (TMEM address `tbase`, lane base included) into y at channel offset ch0.  The
+// residual of a chunk is loaded before the accumulator barrier / the previous chunk's stores
+// so that its latency overlaps.
+__device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
+                                      const float* bs, const Work& wk, int rit, int part, int nparts, int ch0,
+                                      int MTn, int NT) {
+  const bool has_res = p.res.p != nullptr;
+  const uint4* rs = reinterpret_cast<const uint4*>(p.res.p) + (long long)wk.b * p.res.sb;
+  uint4* ys = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) + (long long)wk.b * p.y.sb;
+  // four consecutive channel groups of a chunk sit sA apart when they share a phase
+  const bool quad_y = (p.y.G1 & 3) == 0, quad_r = (p.res.G1 & 3) == 0;
+  const int cstep = nparts * 32;
+  const int row = wk.t0 + rit;
+  uint4 rr[4];
+  auto load_rr = [&](int mt, int c0) {
+    const int t = row + mt * 128;
+    if (t >= p.y.n) return;
+    const int cg = (ch0 + c0) >> 3;
+    const uint4* rp = rs + ((p.res.hist - p.res_delay + t) * p.res.sT + (quad_r ? goff32(p.res, cg) : 0));
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+      if (q * 8 < NT - c0) rr[q] = __ldg(rp + (quad_r ? q * p.res.sA : goff32(p.res, cg + q)));
+  };
+  int mt = 0, c0 = part * 32;
+  if (c0 >= NT) mt = MTn;
+  if (has_res && mt < MTn) load_rr(mt, c0);
+  mbar_wait(bar_full, parity);
+  tc_fence_after();
+  while (mt < MTn) {
+    int mtn = mt, c0n = c0 + cstep;
+    if (c0n >= NT) { c0n = part * 32; ++mtn; }
+    const int t = row + mt * 128;
+    const bool valid = t < p.y.n;
+    const int cg = (ch0 + c0) >> 3;
+    uint4* yp = ys + ((p.y.hist + t) * p.y.sT + (quad_y ? goff32(p.y, cg) : 0));
+    const uint32_t taddr = tbase + (uint32_t)(mt * NT + c0);
+    const bool neg = p.out_mask && !(t & 1);
+    uint4 rc[4] = {rr[0], rr[1], rr[2], rr[3]};
+    if (has_res && mtn < MTn) load_rr(mtn, c0n);          // prefetch the next chunk's residual
+    if (NT - c0 >= 32) drain_chunk<32>(p, taddr, bs + ch0 + c0, rc, has_res, valid, neg, yp, quad_y ? p.y.sA : -1, cg);
+    else drain_chunk<16>(p, taddr, bs + ch0 + c0, rc, has_res, valid, neg, yp, quad_y ? p.y.sA : -1, cg);
+    mt = mtn;
+    c0 = c0n;
+  }
   tc_fence_before();
+}
+
+// Fused E1 chunk: h = act2(D1 + bias) as bf16 into the h tile (core-matrix layout, 2048 B per
+// channel group).
+template <int ACT2, int NC>
+__device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const float* alpha2, uint8_t* hdst) {
+  float v[NC];
+  load_acc<NC>(taddr, bs, v);
+  if (ACT2 == RB_ACT_LEAKY) {
+    leaky_n<NC>(v);
+  } else if (ACT2 == RB_ACT_SNAKE) {
+#pragma unroll
+    for (int e = 0; e < NC; ++e) v[e] = act_f<ACT2>(v[e], alpha2[e]);
+  }
+#pragma unroll
+  for (int q = 0; q < NC / 8; ++q) *reinterpret_cast<uint4*>(hdst + (size_t)q * 2048) = pack8(v + q * 8);
 }
 
 }  // namespace
@@ -308,22 +365,31 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // Output warps: when no activation pass is needed, warps 8-11 drain accumulators too.
+  //   plain:  warps [0, W_OUT_END) share the 32-column chunks round-robin
+  //   fused:  warps 0-3 run E1 (h tile), warps [4, W_OUT_END) run E2 (output)
+  constexpr int W_OUT_END = PRE == RB_ACT_NONE ? 12 : 8;
+  constexpr int W_OUT0 = FUSED ? 4 : 0;
+  constexpr int N_OUT = (W_OUT_END - W_OUT0) * 32;
+  constexpr int OUT_PARTS = (W_OUT_END - W_OUT0) / 4;
 
   if (tid == 0) {
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < MAX_SA; ++i) {
       mbar_init(BAR(BAR_A_FULL + i), PRE == RB_ACT_NONE ? 1 : N_LOAD);
       mbar_init(BAR(BAR_A_EMPTY + i), 1);
+      mbar_init(BAR(BAR_RAW_FULL + i), 1);
+    }
+    for (int i = 0; i < 4; ++i) {
       mbar_init(BAR(BAR_W_FULL + i), 1);
       mbar_init(BAR(BAR_W_EMPTY + i), 1);
-      mbar_init(BAR(BAR_RAW_FULL + i), 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(BAR(BAR_D_FULL + i), 1);
-      mbar_init(BAR(BAR_D_EMPTY + i), N_EPI);
-      mbar_init(BAR(BAR_H_FULL + i), N_EPI);
+      mbar_init(BAR(BAR_D_EMPTY + i), FUSED ? 128 : N_OUT);
+      mbar_init(BAR(BAR_H_FULL + i), 128);
       mbar_init(BAR(BAR_H_EMPTY + i), 1);
       mbar_init(BAR(BAR_D2_FULL + i), 1);
-      mbar_init(BAR(BAR_D2_EMPTY + i), N_EPI);
+      mbar_init(BAR(BAR_D2_EMPTY + i), N_OUT);
     }
     fence_mbar_init();
   }
@@ -353,35 +419,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
     // ============================================================ A producer (one thread, TMA)
     if (lane == 0) {
       prefetch_tmap(&tmx);
-      uint32_t it = 0;
+      Ring ra;
       WorkIter wi;
       for (wi.init(p); wi.left > 0; wi.next(p)) {
         const Work wk = wi.work(p);
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           if (__ldg(p.masks + wk.nt * p.n_kchunks + kc) == 0) continue;
-          const uint32_t sa = it % p.SA, ph = (it / p.SA) & 1;
-          mbar_wait(BAR(BAR_A_EMPTY + sa), ph ^ 1);
+          const uint32_t sa = ra.idx;
+          mbar_wait(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1);
           issue_a_tma(p, &tmx, wk.b, wk.t0 - p.off, kc, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes),
                       BAR((PRE == RB_ACT_NONE ? BAR_A_FULL : BAR_RAW_FULL) + sa));
-          ++it;
+          ra.next(p.SA);
         }
       }
     }
-  } else if (warp >= W_LOAD0 && warp < W_MMA) {
+  } else if (PRE != RB_ACT_NONE && warp >= W_LOAD0 && warp < W_MMA) {
     // =============================== pre-activation pass in smem (un-activated inputs only)
-    if (PRE != RB_ACT_NONE) {
+    {
       const int ltid = tid - W_LOAD0 * 32;
-      uint32_t it = 0;
+      Ring ra;
       WorkIter wi;
       for (wi.init(p); wi.left > 0; wi.next(p)) {
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           if (__ldg(p.masks + wi.nt * p.n_kchunks + kc) == 0) continue;
-          const uint32_t sa = it % p.SA, ph = (it / p.SA) & 1;
-          mbar_wait(BAR(BAR_RAW_FULL + sa), ph);
+          const uint32_t sa = ra.idx;
+          mbar_wait(BAR(BAR_RAW_FULL + sa), ra.ph);
           finish_a_chunk<PRE>(p, kc, a_smem + (size_t)sa * p.a_stage_bytes, ltid);
           fence_proxy_async();
           mbar_arrive(BAR(BAR_A_FULL + sa));
-          ++it;
+          ra.next(p.SA);
         }
       }
     }
@@ -397,7 +463,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
           bulk_g2s(smem_u32(w_smem + o), reinterpret_cast<const uint8_t*>(p.w) + o, n, BAR(BAR_W_FULL));
         }
       } else {
-        uint32_t it = 0;
+        Ring rw;
         WorkIter wi;
         for (wi.init(p); wi.left > 0; wi.next(p)) {
           const Work wk = wi.work(p);
@@ -406,14 +472,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
             const uint64_t mask = __ldg(p.masks + wk.nt * p.n_kchunks + kc);
             const int nb = __popcll(mask);
             for (int j = 0; j < nb; ++j) {
-              const uint32_t sw = it % p.SW, ph = (it / p.SW) & 1;
-              mbar_wait(BAR(BAR_W_EMPTY + sw), ph ^ 1);
+              const uint32_t sw = rw.idx;
+              mbar_wait(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
               mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
               bulk_g2s(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes),
                        reinterpret_cast<const uint8_t*>(p.w) + (size_t)gblk * p.w_blk_bytes, p.w_blk_bytes,
                        BAR(BAR_W_FULL + sw));
               ++gblk;
-              ++it;
+              rw.next(p.SW);
             }
           }
         }
@@ -431,15 +497,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       const uint32_t a_kadd = (2u * lbo_a) >> 4, w_kadd = (2u * lbo_w) >> 4;   // one K=16 step
       const uint32_t tap_add = (uint32_t)p.dil;                                // rows -> 16 B units
       const uint32_t blk_units = p.w_blk_bytes >> 4;
-      uint32_t it_a = 0, it_w = 0;
+      Ring ra, rw, rd1, rd2, rh;
       if (p.w_resident) {
         mbar_wait(BAR(BAR_W_FULL), 0);
         tc_fence_after();
       }
       // GEMM1 of local work item i (accumulator stage i % SD)
-      auto gemm1 = [&](uint32_t i, const Work& wk) {
-        const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
-        mbar_wait(BAR(BAR_D_EMPTY + sd), phd ^ 1);
+      auto gemm1 = [&](const Work& wk) {
+        const uint32_t sd = rd1.idx;
+        mbar_wait(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1);
+        rd1.next(p.SD);
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols;
         uint32_t acc = 0;
@@ -448,8 +515,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           uint64_t mask = __ldg(mrow + kc);
           if (mask == 0) continue;
-          const uint32_t sa = it_a % p.SA, pha = (it_a / p.SA) & 1;
-          mbar_wait(BAR(BAR_A_FULL + sa), pha);
+          const uint32_t sa = ra.idx;
+          mbar_wait(BAR(BAR_A_FULL + sa), ra.ph);
+          ra.next(p.SA);
           tc_fence_after();
           const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
           const int j0 = __ffsll((long long)mask) - 1, n_act = __popcll(mask);
@@ -499,8 +567,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
               blo = wres;
               wres += blk_units;
             } else {
-              sw = it_w % p.SW;
-              mbar_wait(BAR(BAR_W_FULL + sw), (it_w / p.SW) & 1);
+              sw = rw.idx;
+              mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
+              rw.next(p.SW);
               tc_fence_after();
               blo = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
             }
@@ -520,21 +589,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
             acc = 1;
             if (!p.w_resident) {
               COMMIT(BAR(BAR_W_EMPTY + sw));
-              ++it_w;
             }
           }
           COMMIT(BAR(BAR_A_EMPTY + sa));
-          ++it_a;
         }
         COMMIT(BAR(BAR_D_FULL + sd));
       };
       // GEMM2 (fused): D2 = h * W1^T  (h: [128][C2] core-matrix layout, LBO = 2048)
       const uint32_t h_lbo_bits = ((2048u >> 4) & 0x3FFFu) << 16, h_kadd = (2u * 2048u) >> 4;
-      auto gemm2 = [&](uint32_t i) {
-        const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
-        const uint32_t sh = i % p.SH, phh = (i / p.SH) & 1;
-        mbar_wait(BAR(BAR_H_FULL + sh), phh);
-        mbar_wait(BAR(BAR_D2_EMPTY + sd), phd ^ 1);
+      auto gemm2 = [&]() {
+        const uint32_t sd = rd2.idx, sh = rh.idx;
+        mbar_wait(BAR(BAR_H_FULL + sh), rh.ph);
+        mbar_wait(BAR(BAR_D2_EMPTY + sd), rd2.ph ^ 1);
+        rd2.next(p.SD);
+        rh.next(p.SH);
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols + (uint32_t)C2;
         uint32_t al = (((h0 + sh * p.h_stage_bytes) >> 4) & 0x3FFFu) | h_lbo_bits;
@@ -556,70 +624,56 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       uint32_t i = 0;
       WorkIter wi;
       for (wi.init(p); wi.left > 0; wi.next(p), ++i) {
-        gemm1(i, wi.work(p));
-        if (FUSED && i >= 1) gemm2(i - 1);
+        gemm1(wi.work(p));
+        if (FUSED && i >= 1) gemm2();
       }
-      if (FUSED && i >= 1) gemm2(i - 1);
+      if (FUSED && i >= 1) gemm2();
     }
   } else {
-    // ============================================================ epilogue (warps 0-7)
+    // ==================================================== epilogue (warps 0-7, or 0-11)
     const int rit = (warp & 3) * 32 + lane;                 // row within a 128-row sub-tile
-    const int half = warp >> 2;                             // parity of the 32-column groups owned
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
-    auto epi_plain = [&](uint32_t i, const Work& wk) {
-      const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
-      drain(p, BAR(BAR_D_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols, bias_s, wk, rit, half,
-            wk.nt * p.N_TILE, p.MT, p.N_TILE);
-      mbar_arrive(BAR(BAR_D_EMPTY + sd));
-    };
-    // fused E1: h = act2(D1 + bias) -> smem (A operand of the 1x1 conv)
-    auto epi_h = [&](uint32_t i) {
-      const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
-      const uint32_t sh = i % p.SH, phh = (i / p.SH) & 1;
-      mbar_wait(BAR(BAR_D_FULL + sd), phd);
-      mbar_wait(BAR(BAR_H_EMPTY + sh), phh ^ 1);
-      tc_fence_after();
-      uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
-      for (int c0 = half * 32; c0 < C2; c0 += 64) {
-        const int ncol = C2 - c0 < 32 ? C2 - c0 : 32;
-        float v[32];
-        load_acc32(tmem + lane_base + sd * d_stage_cols + (uint32_t)c0, ncol, bias_s + c0, v);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if (q * 8 < ncol) {
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-              v[q * 8 + e] = act_f<ACT2>(v[q * 8 + e], ACT2 == RB_ACT_SNAKE ? alpha2_s[c0 + q * 8 + e] : 1.f);
-            *reinterpret_cast<uint4*>(hb + (size_t)((c0 >> 3) + q) * 2048) = pack8(v + q * 8);
-          }
-        }
-      }
-      fence_proxy_async();
-      tc_fence_before();
-      mbar_arrive(BAR(BAR_H_FULL + sh));
-      mbar_arrive(BAR(BAR_D_EMPTY + sd));
-    };
-    // fused E2: y = D2 + bias2 + x
-    auto epi_out = [&](uint32_t i, const Work& wk) {
-      const uint32_t sd = i % p.SD, phd = (i / p.SD) & 1;
-      drain(p, BAR(BAR_D2_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols + (uint32_t)C2, bias2_s, wk, rit,
-            half, 0, 1, C2);
-      mbar_arrive(BAR(BAR_D2_EMPTY + sd));
-    };
-    uint32_t i = 0;
-    Work prev{0, 0, 0};
+    Ring rd, rh;
     WorkIter wi;
-    for (wi.init(p); wi.left > 0; wi.next(p), ++i) {
-      const Work wk = wi.work(p);
-      if (!FUSED) {
-        epi_plain(i, wk);
-      } else {
-        epi_h(i);
-        if (i >= 1) epi_out(i - 1, prev);
-        prev = wk;
+    if (!FUSED) {
+      const int part = warp >> 2;
+      for (wi.init(p); wi.left > 0; wi.next(p), rd.next(p.SD)) {
+        const Work wk = wi.work(p);
+        const uint32_t sd = rd.idx, phd = rd.ph;
+        drain(p, BAR(BAR_D_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols, bias_s, wk, rit, part,
+              OUT_PARTS, wk.nt * p.N_TILE, p.MT, p.N_TILE);
+        mbar_arrive(BAR(BAR_D_EMPTY + sd));
+      }
+    } else if (warp < 4) {
+      // fused E1: h = act2(D1 + bias) -> smem (A operand of the 1x1 conv)
+      for (wi.init(p); wi.left > 0; wi.next(p), rd.next(p.SD), rh.next(p.SH)) {
+        const uint32_t sd = rd.idx, phd = rd.ph;
+        const uint32_t sh = rh.idx, phh = rh.ph;
+        mbar_wait(BAR(BAR_D_FULL + sd), phd);
+        mbar_wait(BAR(BAR_H_EMPTY + sh), phh ^ 1);
+        tc_fence_after();
+        uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
+        for (int c0 = 0; c0 < C2; c0 += 32) {
+          const uint32_t taddr = tmem + lane_base + sd * d_stage_cols + (uint32_t)c0;
+          if (C2 - c0 >= 32) h_chunk<ACT2, 32>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
+          else h_chunk<ACT2, 16>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        mbar_arrive(BAR(BAR_H_FULL + sh));
+        mbar_arrive(BAR(BAR_D_EMPTY + sd));
+      }
+    } else {
+      // fused E2: y = D2 + bias2 + x
+      const int part = (warp - 4) >> 2;
+      for (wi.init(p); wi.left > 0; wi.next(p), rd.next(p.SD)) {
+        const Work wk = wi.work(p);
+        const uint32_t sd = rd.idx, phd = rd.ph;
+        drain(p, BAR(BAR_D2_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols + (uint32_t)C2, bias2_s, wk, rit,
+              part, OUT_PARTS, 0, 1, C2);
+        mbar_arrive(BAR(BAR_D2_EMPTY + sd));
       }
     }
-    if (FUSED && i >= 1) epi_out(i - 1, prev);
   }
 
   tc_fence_before();

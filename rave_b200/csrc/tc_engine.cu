@@ -310,8 +310,8 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   const uint32_t budget = 224u * 1024u;
   const uint32_t w_total = (uint32_t)(L.total_blocks + (L.fused ? L.N_TILE / L.KC : 0)) * L.blk_bytes;
   p.w_blk_bytes = L.blk_bytes;
-  p.off_bias = 320;           // after 32 mbarriers (256 B) and the TMEM address slot
-  const uint32_t fixed = align_up(320 + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
+  p.off_bias = 512;           // after the mbarriers and the TMEM address slot
+  const uint32_t fixed = align_up(512 + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
   p.SH = L.fused ? 2 : 0;
   p.h_stage_bytes = L.fused ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
   const uint32_t h_total = p.SH * p.h_stage_bytes;
@@ -351,7 +351,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       continue;
     }
     const uint32_t room = budget - fixed - w_bytes - h_total;
-    p.SA = (int)std::min<uint32_t>(4, room / p.a_stage_bytes);
+    p.SA = (int)std::min<uint32_t>(12, room / p.a_stage_bytes);
     if (resident && p.SA < 2) continue;
     p.off_a = fixed;
     p.off_w = p.off_a + p.SA * p.a_stage_bytes;
