@@ -177,6 +177,7 @@ typedef struct rb_debug_conv {
   float* y;               /* [B][c_out / ileave][n_out]                                     */
   int32_t* fused_out;     /* optional: set to 1 when the pair ran as one fused kernel       */
   int32_t flags;          /* activated storage: 1 x is leaky(x), 2 return leaky(y), 4 res   */
+  uint64_t* trace;        /* optional [64][16]: clock stamps of CTA 0's pipeline events     */
 } rb_debug_conv;
 int rb_debug_conv_bf16(const rb_debug_conv* d);
 int rb_abi_version(void);

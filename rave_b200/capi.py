@@ -47,7 +47,8 @@ class RbDebugConv(C.Structure):
                 ("w", C.POINTER(C.c_float) * 2), ("bias", C.POINTER(C.c_float) * 2),
                 ("alpha", C.POINTER(C.c_float) * 2), ("x", C.POINTER(C.c_float)),
                 ("res", C.POINTER(C.c_float)), ("y", C.POINTER(C.c_float)),
-                ("fused_out", C.POINTER(C.c_int32)), ("flags", C.c_int32)]
+                ("fused_out", C.POINTER(C.c_int32)), ("flags", C.c_int32),
+                ("trace", C.POINTER(C.c_uint64))]
 
 
 EXPORTS = {

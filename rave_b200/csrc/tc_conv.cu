@@ -26,6 +26,8 @@
 // The activation kinds are template parameters so that each instantiation stays small.
 #include <cuda.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "tc_conv.cuh"
 #include "tc_ptx.cuh"
@@ -36,14 +38,16 @@ namespace tc {
 namespace {
 
 constexpr int MAX_SA = 12;       // A stages: enough bytes in flight per SM to cover HBM latency
+constexpr int MAX_SD = 4;        // accumulator / h stages
 enum { BAR_A_FULL = 0, BAR_A_EMPTY = MAX_SA, BAR_RAW_FULL = 2 * MAX_SA, BAR_W_FULL = 3 * MAX_SA,
-       BAR_W_EMPTY = BAR_W_FULL + 4, BAR_D_FULL = BAR_W_EMPTY + 4, BAR_D_EMPTY = BAR_D_FULL + 2,
-       BAR_H_FULL = BAR_D_EMPTY + 2, BAR_H_EMPTY = BAR_H_FULL + 2, BAR_D2_FULL = BAR_H_EMPTY + 2,
-       BAR_D2_EMPTY = BAR_D2_FULL + 2, BAR_COUNT = BAR_D2_EMPTY + 2 };
-static_assert(BAR_COUNT * 8 + 8 <= 512, "barriers + TMEM slot must fit below off_bias");
+       BAR_W_EMPTY = BAR_W_FULL + 4, BAR_D_FULL = BAR_W_EMPTY + 4, BAR_D_EMPTY = BAR_D_FULL + MAX_SD,
+       BAR_H_FULL = BAR_D_EMPTY + MAX_SD, BAR_H_EMPTY = BAR_H_FULL + MAX_SD, BAR_D2_FULL = BAR_H_EMPTY + MAX_SD,
+       BAR_D2_EMPTY = BAR_D2_FULL + MAX_SD, BAR_COUNT = BAR_D2_EMPTY + MAX_SD };
+static_assert(BAR_COUNT * 8 + 8 <= 640, "barriers + TMEM slot must fit below off_bias");
 constexpr int N_EPI = 256;       // epilogue threads
 constexpr int N_LOAD = 128;      // loader threads
-constexpr int W_LOAD0 = 8, W_MMA = 12, W_WPROD = 13, W_APROD = 14;
+constexpr int W_LOAD0 = 12, W_MMA = 16, W_WPROD = 17, W_APROD = 18, W_MMA2 = 19;   // W_MMA2: GEMM2 issuer (fused)
+constexpr int E1_WARPS = 8;      // fused: warps [0, 8) build the h tile, the other output warps store y
 
 template <int ACT>
 __device__ __forceinline__ float act_f(float v, float alpha) {
@@ -71,6 +75,10 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
 __device__ __forceinline__ uint4 pack8(const float* f) {
   return make_uint4(pack2(f[0], f[1]), pack2(f[2], f[3]), pack2(f[4], f[5]), pack2(f[6], f[7]));
 }
+
+// debug event trace (CTA 0, first 64 work items): see tools_trace.py
+#define TRACE(tile, ev) do { if (p.trace && blockIdx.x == 0 && (tile) < 64u && (threadIdx.x & 31) == 0) \
+    p.trace[(tile) * 16u + (ev)] = (unsigned long long)clock64(); } while (0)
 
 struct Work {
   int nt, b, t0;
@@ -211,16 +219,24 @@ template <int NC>
 __device__ __forceinline__ void load_acc(uint32_t taddr, const float* bias_s, float* v) {
   uint32_t r[NC];
   if (NC == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
-  float4 b[NC / 4];
+  float4 b[4];
 #pragma unroll
-  for (int g = 0; g < NC / 4; ++g) b[g] = *reinterpret_cast<const float4*>(bias_s + g * 4);
+  for (int g = 0; g < 4; ++g) b[g] = *reinterpret_cast<const float4*>(bias_s + g * 4);
   tmem_ld_wait();
 #pragma unroll
-  for (int g = 0; g < NC / 4; ++g) {
-    v[g * 4 + 0] = __uint_as_float(r[g * 4 + 0]); v[g * 4 + 1] = __uint_as_float(r[g * 4 + 1]);
-    v[g * 4 + 2] = __uint_as_float(r[g * 4 + 2]); v[g * 4 + 3] = __uint_as_float(r[g * 4 + 3]);
-    add2(v[g * 4 + 0], v[g * 4 + 1], b[g].x, b[g].y);
-    add2(v[g * 4 + 2], v[g * 4 + 3], b[g].z, b[g].w);
+  for (int h = 0; h < NC / 16; ++h) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int e = h * 16 + g * 4;
+      v[e + 0] = __uint_as_float(r[e + 0]); v[e + 1] = __uint_as_float(r[e + 1]);
+      v[e + 2] = __uint_as_float(r[e + 2]); v[e + 3] = __uint_as_float(r[e + 3]);
+      add2(v[e + 0], v[e + 1], b[g].x, b[g].y);
+      add2(v[e + 2], v[e + 3], b[g].z, b[g].w);
+    }
+    if (h + 1 < NC / 16) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) b[g] = *reinterpret_cast<const float4*>(bias_s + 16 + g * 4);
+    }
   }
 }
 // LeakyReLU(0.2) on NC fp32 values: packed multiply + max.
@@ -249,42 +265,14 @@ __device__ __forceinline__ int goff32(const TcView& v, int g) {
   return lo * v.sA + hi * v.sB;
 }
 
-// One chunk of NC columns of one output row: accumulator + bias (+ residual) -> sign mask /
-// output activation -> bf16 -> NC/8 16-byte stores at yp[q * ystep] (ystep < 0: per-group offsets).
-template <int NC>
-__device__ __forceinline__ void drain_chunk(const TcParams& p, uint32_t taddr, const float* bs, const uint4* rr,
-                                            bool has_res, bool valid, bool negate_odd, uint4* yp, int ystep,
-                                            int cg) {
-  float v[NC];
-  load_acc<NC>(taddr, bs, v);
-  if (!valid) return;
-  if (has_res) {
-#pragma unroll
-    for (int q = 0; q < NC / 8; ++q) {
-      uint4 r4 = rr[q];
-      if (p.res_act) { r4.x = unleaky2(r4.x); r4.y = unleaky2(r4.y); r4.z = unleaky2(r4.z); r4.w = unleaky2(r4.w); }
-      const uint32_t w[4] = {r4.x, r4.y, r4.z, r4.w};
-#pragma unroll
-      for (int e = 0; e < 4; ++e)
-        add2(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1], __uint_as_float(w[e] << 16), __uint_as_float(w[e] & 0xffff0000u));
-    }
-  }
-  if (negate_odd) {
-#pragma unroll
-    for (int e = 1; e < NC; e += 2) v[e] = -v[e];
-  }
-  if (p.out_act) leaky_n<NC>(v);                        // stored activated: LeakyReLU(0.2)
-#pragma unroll
-  for (int q = 0; q < NC / 8; ++q) yp[ystep >= 0 ? q * ystep : goff32(p.y, cg + q)] = pack8(v + q * 8);
-}
-
 // Drains part `part` of `nparts` of the 32-column chunks of `MTn` sub-tiles x `NT` accumulator
-// columns (TMEM address `tbase`, lane base included) into y at channel offset ch0.  The
-// residual of a chunk is loaded before the accumulator barrier / the previous chunk's stores
-// so that its latency overlaps.
+// columns (TMEM address `tbase`, lane base included) into y at channel offset ch0: accumulator
+// + bias (+ residual) -> sign mask / output activation -> bf16 -> 16-byte stores.  The residual
+// of a chunk is requested as soon as the previous chunk has consumed its own (before the
+// accumulator barrier for the first chunk), so its latency overlaps the math and the stores.
 __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                       const float* bs, const Work& wk, int rit, int part, int nparts, int ch0,
-                                      int MTn, int NT) {
+                                      int MTn, int NT, const uint8_t* res_s = nullptr, uint32_t tr = 0xffffffffu) {
   const bool has_res = p.res.p != nullptr;
   const uint4* rs = reinterpret_cast<const uint4*>(p.res.p) + (long long)wk.b * p.res.sb;
   uint4* ys = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) + (long long)wk.b * p.y.sb;
@@ -297,6 +285,13 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
     const int t = row + mt * 128;
     if (t >= p.y.n) return;
     const int cg = (ch0 + c0) >> 3;
+    if (res_s) {                                          // fused unit: rows off.. of the A tile in smem
+      const uint4* sp = reinterpret_cast<const uint4*>(res_s) + (cg * p.R_ALLOC + rit + p.off);
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (q * 8 < NT - c0) rr[q] = sp[q * p.R_ALLOC];
+      return;
+    }
     const uint4* rp = rs + ((p.res.hist - p.res_delay + t) * p.res.sT + (quad_r ? goff32(p.res, cg) : 0));
 #pragma unroll
     for (int q = 0; q < 4; ++q)
@@ -304,25 +299,53 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
   };
   int mt = 0, c0 = part * 32;
   if (c0 >= NT) mt = MTn;
-  if (has_res && mt < MTn) load_rr(mt, c0);
+  if (has_res && !res_s && mt < MTn) load_rr(mt, c0);
   mbar_wait(bar_full, parity);
   tc_fence_after();
+  TRACE(tr, 12);
+  if (res_s && mt < MTn) load_rr(mt, c0);                 // the stage is certainly full by now
   while (mt < MTn) {
     int mtn = mt, c0n = c0 + cstep;
     if (c0n >= NT) { c0n = part * 32; ++mtn; }
     const int t = row + mt * 128;
     const bool valid = t < p.y.n;
     const int cg = (ch0 + c0) >> 3;
-    uint4* yp = ys + ((p.y.hist + t) * p.y.sT + (quad_y ? goff32(p.y, cg) : 0));
     const uint32_t taddr = tbase + (uint32_t)(mt * NT + c0);
-    const bool neg = p.out_mask && !(t & 1);
-    uint4 rc[4] = {rr[0], rr[1], rr[2], rr[3]};
-    if (has_res && mtn < MTn) load_rr(mtn, c0n);          // prefetch the next chunk's residual
-    if (NT - c0 >= 32) drain_chunk<32>(p, taddr, bs + ch0 + c0, rc, has_res, valid, neg, yp, quad_y ? p.y.sA : -1, cg);
-    else drain_chunk<16>(p, taddr, bs + ch0 + c0, rc, has_res, valid, neg, yp, quad_y ? p.y.sA : -1, cg);
+    auto body = [&](auto nc_tag) {
+      constexpr int NC = decltype(nc_tag)::value;
+      float v[NC];
+      load_acc<NC>(taddr, bs + ch0 + c0, v);
+      TRACE(tr, 13);
+      if (has_res && valid) {
+#pragma unroll
+        for (int q = 0; q < NC / 8; ++q) {
+          uint4 r4 = rr[q];
+          if (p.res_act) { r4.x = unleaky2(r4.x); r4.y = unleaky2(r4.y); r4.z = unleaky2(r4.z); r4.w = unleaky2(r4.w); }
+          const uint32_t w[4] = {r4.x, r4.y, r4.z, r4.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            add2(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1], __uint_as_float(w[e] << 16),
+                 __uint_as_float(w[e] & 0xffff0000u));
+        }
+      }
+      if (has_res && mtn < MTn) load_rr(mtn, c0n);        // next chunk's residual, in flight during the stores
+      if (!valid) return;
+      if (p.out_mask && !(t & 1)) {
+#pragma unroll
+        for (int e = 1; e < NC; e += 2) v[e] = -v[e];
+      }
+      if (p.out_act) leaky_n<NC>(v);                      // stored activated: LeakyReLU(0.2)
+      TRACE(tr, 14);
+      uint4* yp = ys + ((p.y.hist + t) * p.y.sT + (quad_y ? goff32(p.y, cg) : 0));
+#pragma unroll
+      for (int q = 0; q < NC / 8; ++q) yp[quad_y ? q * p.y.sA : goff32(p.y, cg + q)] = pack8(v + q * 8);
+    };
+    if (NT - c0 >= 32) body(std::integral_constant<int, 32>{});
+    else body(std::integral_constant<int, 16>{});
     mt = mtn;
     c0 = c0n;
   }
+  TRACE(tr, 15);
   tc_fence_before();
 }
 
@@ -348,12 +371,14 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
 #define MMA(...) do { if (leader) mma_bf16_lohi(__VA_ARGS__); } while (0)
 #define COMMIT(bar) do { if (leader) mma_commit(bar); } while (0)
 
+
 template <int PRE, int ACT2, bool FUSED>
-__global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_constant__ TcParams p,
+__global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams p,
                                                                 const __grid_constant__ TcTmap tmx) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_COUNT * 8);
+  uint64_t* mask_s = reinterpret_cast<uint64_t*>(smem + 640);   // [n_ntiles][n_kchunks] <= 128 entries
   float* bias_s = reinterpret_cast<float*>(smem + p.off_bias);
   const int N_total = p.N_TILE * p.n_ntiles;
   float* bias2_s = bias_s + N_total;              // fused only: [C]
@@ -365,34 +390,36 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  // Output warps: when no activation pass is needed, warps 8-11 drain accumulators too.
+  // Output warps: when no activation pass is needed, warps 12-15 drain accumulators too.
   //   plain:  warps [0, W_OUT_END) share the 32-column chunks round-robin
-  //   fused:  warps 0-3 run E1 (h tile), warps [4, W_OUT_END) run E2 (output)
-  constexpr int W_OUT_END = PRE == RB_ACT_NONE ? 12 : 8;
-  constexpr int W_OUT0 = FUSED ? 4 : 0;
+  //   fused:  warps [0, E1_WARPS) run E1 (h tile), warps [E1_WARPS, W_OUT_END) run E2 (output)
+  constexpr int W_OUT_END = PRE == RB_ACT_NONE ? 16 : 12;
+  constexpr int W_OUT0 = FUSED ? E1_WARPS : 0;
   constexpr int N_OUT = (W_OUT_END - W_OUT0) * 32;
   constexpr int OUT_PARTS = (W_OUT_END - W_OUT0) / 4;
+  constexpr int E1_PARTS = E1_WARPS / 4;
 
   if (tid == 0) {
     for (int i = 0; i < MAX_SA; ++i) {
       mbar_init(BAR(BAR_A_FULL + i), PRE == RB_ACT_NONE ? 1 : N_LOAD);
-      mbar_init(BAR(BAR_A_EMPTY + i), 1);
+      mbar_init(BAR(BAR_A_EMPTY + i), 1 + (p.res_smem ? W_OUT_END - W_OUT0 : 0));
       mbar_init(BAR(BAR_RAW_FULL + i), 1);
     }
     for (int i = 0; i < 4; ++i) {
       mbar_init(BAR(BAR_W_FULL + i), 1);
       mbar_init(BAR(BAR_W_EMPTY + i), 1);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < MAX_SD; ++i) {
       mbar_init(BAR(BAR_D_FULL + i), 1);
-      mbar_init(BAR(BAR_D_EMPTY + i), FUSED ? 128 : N_OUT);
-      mbar_init(BAR(BAR_H_FULL + i), 128);
+      mbar_init(BAR(BAR_D_EMPTY + i), FUSED ? E1_WARPS * 32 : N_OUT);
+      mbar_init(BAR(BAR_H_FULL + i), E1_WARPS * 32);
       mbar_init(BAR(BAR_H_EMPTY + i), 1);
       mbar_init(BAR(BAR_D2_FULL + i), 1);
       mbar_init(BAR(BAR_D2_EMPTY + i), N_OUT);
     }
     fence_mbar_init();
   }
+  for (int i = tid; i < p.n_ntiles * p.n_kchunks; i += TC_THREADS) mask_s[i] = p.masks[i];
   for (int i = tid; i < N_total; i += TC_THREADS) bias_s[i] = p.bias ? p.bias[i] : 0.f;
   if (FUSED) {
     for (int i = tid; i < p.N_TILE; i += TC_THREADS) {
@@ -421,14 +448,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       prefetch_tmap(&tmx);
       Ring ra;
       WorkIter wi;
-      for (wi.init(p); wi.left > 0; wi.next(p)) {
+      uint32_t ti = 0;
+      for (wi.init(p); wi.left > 0; wi.next(p), ++ti) {
         const Work wk = wi.work(p);
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
-          if (__ldg(p.masks + wk.nt * p.n_kchunks + kc) == 0) continue;
+          if (mask_s[wk.nt * p.n_kchunks + kc] == 0) continue;
           const uint32_t sa = ra.idx;
           mbar_wait(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1);
+          TRACE(ti, 10);
           issue_a_tma(p, &tmx, wk.b, wk.t0 - p.off, kc, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes),
                       BAR((PRE == RB_ACT_NONE ? BAR_A_FULL : BAR_RAW_FULL) + sa));
+          TRACE(ti, 11);
           ra.next(p.SA);
         }
       }
@@ -441,7 +471,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
       WorkIter wi;
       for (wi.init(p); wi.left > 0; wi.next(p)) {
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
-          if (__ldg(p.masks + wi.nt * p.n_kchunks + kc) == 0) continue;
+          if (mask_s[wi.nt * p.n_kchunks + kc] == 0) continue;
           const uint32_t sa = ra.idx;
           mbar_wait(BAR(BAR_RAW_FULL + sa), ra.ph);
           finish_a_chunk<PRE>(p, kc, a_smem + (size_t)sa * p.a_stage_bytes, ltid);
@@ -469,7 +499,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
           const Work wk = wi.work(p);
           int gblk = p.nt_base[wk.nt];
           for (int kc = 0; kc < p.n_kchunks; ++kc) {
-            const uint64_t mask = __ldg(p.masks + wk.nt * p.n_kchunks + kc);
+            const uint64_t mask = mask_s[wk.nt * p.n_kchunks + kc];
             const int nb = __popcll(mask);
             for (int j = 0; j < nb; ++j) {
               const uint32_t sw = rw.idx;
@@ -485,7 +515,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         }
       }
     }
-  } else if (warp == W_MMA) {
+  } else if (warp == W_MMA || warp == W_MMA2) {
     // ====================================== MMA issuer (warp-uniform control, elected lane issues)
     {
       const bool leader = elect_one();
@@ -503,20 +533,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         tc_fence_after();
       }
       // GEMM1 of local work item i (accumulator stage i % SD)
+      uint32_t t1 = 0, t2 = 0;                  // trace: tile counters of GEMM1 / GEMM2
       auto gemm1 = [&](const Work& wk) {
         const uint32_t sd = rd1.idx;
         mbar_wait(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1);
+        TRACE(t1, 0);
         rd1.next(p.SD);
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols;
         uint32_t acc = 0;
         uint32_t wres = ((w0 >> 4) & 0x3FFFu) | w_lbo_bits;      // resident: next block's desc.lo
-        const uint64_t* mrow = p.masks + wk.nt * p.n_kchunks;
+        const uint64_t* mrow = mask_s + wk.nt * p.n_kchunks;
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
-          uint64_t mask = __ldg(mrow + kc);
+          uint64_t mask = mrow[kc];
           if (mask == 0) continue;
           const uint32_t sa = ra.idx;
           mbar_wait(BAR(BAR_A_FULL + sa), ra.ph);
+          TRACE(t1, 1);
           ra.next(p.SA);
           tc_fence_after();
           const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
@@ -594,13 +627,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
           COMMIT(BAR(BAR_A_EMPTY + sa));
         }
         COMMIT(BAR(BAR_D_FULL + sd));
+        TRACE(t1, 2);
+        ++t1;
       };
       // GEMM2 (fused): D2 = h * W1^T  (h: [128][C2] core-matrix layout, LBO = 2048)
       const uint32_t h_lbo_bits = ((2048u >> 4) & 0x3FFFu) << 16, h_kadd = (2u * 2048u) >> 4;
       auto gemm2 = [&]() {
         const uint32_t sd = rd2.idx, sh = rh.idx;
         mbar_wait(BAR(BAR_H_FULL + sh), rh.ph);
+        TRACE(t2, 3);
         mbar_wait(BAR(BAR_D2_EMPTY + sd), rd2.ph ^ 1);
+        TRACE(t2, 4);
         rd2.next(p.SD);
         rh.next(p.SH);
         tc_fence_after();
@@ -620,14 +657,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
         }
         COMMIT(BAR(BAR_H_EMPTY + sh));
         COMMIT(BAR(BAR_D2_FULL + sd));
+        TRACE(t2, 5);
+        ++t2;
       };
-      uint32_t i = 0;
+      // GEMM1 and GEMM2 are issued by two different warps: each is a serial instruction stream
+      // (waits, descriptor set-up, commits), and for narrow units that stream is the bottleneck.
       WorkIter wi;
-      for (wi.init(p); wi.left > 0; wi.next(p), ++i) {
-        gemm1(wi.work(p));
-        if (FUSED && i >= 1) gemm2();
+      if (warp == W_MMA) {
+        for (wi.init(p); wi.left > 0; wi.next(p)) gemm1(wi.work(p));
+      } else if (FUSED) {
+        for (wi.init(p); wi.left > 0; wi.next(p)) gemm2();
       }
-      if (FUSED && i >= 1) gemm2();
     }
   } else {
     // ==================================================== epilogue (warps 0-7, or 0-11)
@@ -637,41 +677,83 @@ __global__ void __launch_bounds__(TC_THREADS, 1) tc_conv_kernel(const __grid_con
     WorkIter wi;
     if (!FUSED) {
       const int part = warp >> 2;
-      for (wi.init(p); wi.left > 0; wi.next(p), rd.next(p.SD)) {
+      uint32_t ti = 0;
+      for (wi.init(p); wi.left > 0; wi.next(p), rd.next(p.SD), ++ti) {
         const Work wk = wi.work(p);
         const uint32_t sd = rd.idx, phd = rd.ph;
+        if (warp == 0) TRACE(ti, 8);
         drain(p, BAR(BAR_D_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols, bias_s, wk, rit, part,
-              OUT_PARTS, wk.nt * p.N_TILE, p.MT, p.N_TILE);
+              OUT_PARTS, wk.nt * p.N_TILE, p.MT, p.N_TILE, nullptr, warp == 0 ? ti : 0xffffffffu);
         mbar_arrive(BAR(BAR_D_EMPTY + sd));
-      }
-    } else if (warp < 4) {
-      // fused E1: h = act2(D1 + bias) -> smem (A operand of the 1x1 conv)
-      for (wi.init(p); wi.left > 0; wi.next(p), rd.next(p.SD), rh.next(p.SH)) {
-        const uint32_t sd = rd.idx, phd = rd.ph;
-        const uint32_t sh = rh.idx, phh = rh.ph;
-        mbar_wait(BAR(BAR_D_FULL + sd), phd);
-        mbar_wait(BAR(BAR_H_EMPTY + sh), phh ^ 1);
-        tc_fence_after();
-        uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
-        for (int c0 = 0; c0 < C2; c0 += 32) {
-          const uint32_t taddr = tmem + lane_base + sd * d_stage_cols + (uint32_t)c0;
-          if (C2 - c0 >= 32) h_chunk<ACT2, 32>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
-          else h_chunk<ACT2, 16>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
-        }
-        fence_proxy_async();
-        tc_fence_before();
-        mbar_arrive(BAR(BAR_H_FULL + sh));
-        mbar_arrive(BAR(BAR_D_EMPTY + sd));
+        if (warp == 0) TRACE(ti, 9);
       }
     } else {
-      // fused E2: y = D2 + bias2 + x
-      const int part = (warp - 4) >> 2;
-      for (wi.init(p); wi.left > 0; wi.next(p), rd.next(p.SD)) {
-        const Work wk = wi.work(p);
-        const uint32_t sd = rd.idx, phd = rd.ph;
-        drain(p, BAR(BAR_D2_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols + (uint32_t)C2, bias2_s, wk, rit,
-              part, OUT_PARTS, 0, 1, C2);
-        mbar_arrive(BAR(BAR_D2_EMPTY + sd));
+      // Fused unit.  E1(i): h = act2(D1 + bias) -> smem (A operand of the 1x1 conv);
+      // E2(i): y = D2 + bias2 + x.  Without an activation pass the 16 output warps form two
+      // sets that alternate: set s runs E1 on tiles = s (mod 2) and E2 on the other tiles, so
+      // both sets carry the same load; otherwise warps 0-7 run E1 and warps 8-11 run E2.
+      constexpr bool ALT = PRE == RB_ACT_NONE;
+      const int set = ALT ? (warp >> 3) : 0;
+      const int step = ALT ? 2 : 1;
+      const int part = ALT ? ((warp >> 2) & 1) : (warp < E1_WARPS ? (warp >> 2) : 0);
+      const bool tr_warp = (warp & 7) == 0;
+      struct TileIt {
+        WorkIter wi;
+        Ring rd, rh, ra;
+        uint32_t ti;
+      } e1, e2;
+      auto start = [&](TileIt& it, int first, bool active) {
+        it.wi.init(p);
+        it.ti = 0;
+        if (!active) it.wi.left = 0;
+        for (int k = 0; k < first && it.wi.left > 0; ++k) {
+          it.wi.next(p); it.rd.next(p.SD); it.rh.next(p.SH); it.ra.next(p.SA); ++it.ti;
+        }
+      };
+      auto advance = [&](TileIt& it) {
+        for (int k = 0; k < step; ++k) {
+          it.wi.next(p); it.rd.next(p.SD); it.rh.next(p.SH); it.ra.next(p.SA); ++it.ti;
+        }
+      };
+      start(e1, ALT ? set : 0, ALT || warp < E1_WARPS);
+      start(e2, ALT ? 1 - set : 0, ALT || warp >= E1_WARPS);
+      bool first = true;
+      while (e1.wi.left > 0 || e2.wi.left > 0) {
+        if (e1.wi.left > 0) {
+          const uint32_t sd = e1.rd.idx, sh = e1.rh.idx;
+          mbar_wait(BAR(BAR_D_FULL + sd), e1.rd.ph);
+          if (tr_warp) TRACE(e1.ti, 6);
+          mbar_wait(BAR(BAR_H_EMPTY + sh), e1.rh.ph ^ 1);
+          tc_fence_after();
+          uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
+          for (int c0 = part * 32; c0 < C2; c0 += E1_PARTS * 32) {
+            const uint32_t taddr = tmem + lane_base + sd * d_stage_cols + (uint32_t)c0;
+            if (C2 - c0 >= 32) h_chunk<ACT2, 32>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
+            else h_chunk<ACT2, 16>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
+          }
+          fence_proxy_async();
+          tc_fence_before();
+          mbar_arrive(BAR(BAR_H_FULL + sh));
+          mbar_arrive(BAR(BAR_D_EMPTY + sd));
+          if (tr_warp) TRACE(e1.ti, 7);
+          advance(e1);
+        }
+        if (e2.wi.left > 0 && !(ALT && set == 0 && first)) {
+          const Work wk = e2.wi.work(p);
+          const uint32_t sd = e2.rd.idx, sa = e2.ra.idx;
+          if (tr_warp) TRACE(e2.ti, 8);
+          drain(p, BAR(BAR_D2_FULL + sd), e2.rd.ph, tmem + lane_base + sd * d_stage_cols + (uint32_t)C2, bias2_s,
+                wk, rit, part, OUT_PARTS, 0, 1, C2, p.res_smem ? a_smem + (size_t)sa * p.a_stage_bytes : nullptr,
+                tr_warp ? e2.ti : 0xffffffffu);
+          mbar_arrive(BAR(BAR_D2_EMPTY + sd));
+          if (p.res_smem) {                                 // this warp no longer needs the A stage
+            __syncwarp();
+            if (lane == 0) mbar_arrive(BAR(BAR_A_EMPTY + sa));
+          }
+          if (tr_warp) TRACE(e2.ti, 9);
+          advance(e2);
+        }
+        first = false;
       }
     }
   }

@@ -19,7 +19,7 @@ namespace rb {
 namespace tc {
 
 constexpr int TC_MAX_NT = 8;        // output-channel tiles per layer
-constexpr int TC_THREADS = 480;     // warps 0-7 epilogue, 8-11 activation pass, 12 MMA, 13 W, 14 A producer
+constexpr int TC_THREADS = 640;     // warps 0-15 output (12-15: activation pass if needed), 16 MMA, 17 W, 18 A producer, 19 MMA (fused GEMM2)
 
 // A row view of an activation tensor, addressed in 16-byte units (8 bf16 = one channel group):
 //   unit(b, t, g) = b*sb + (hist + t)*sT + (g % G1)*sA + (g / G1)*sB        t in [lo, n)
@@ -51,6 +51,7 @@ struct TcParams {
   int pre_act;              // rb_act applied to the input tile in smem (NONE: TMA feeds the MMA directly)
   int out_act;              // rb_act applied to the stored output (consumers then skip their pre_act)
   int res_act;              // the residual tensor is stored LeakyReLU-activated: invert it on read
+  int res_smem;             // fused unit: the residual is the A tile itself, read from smem (no reload)
   int B;
   int n_taps, dil, off;     // row taps: shift_j = j*dil - off
   int KC, n_kchunks;        // input channels per K chunk (multiple of 16), chunks per row
@@ -78,6 +79,7 @@ struct TcParams {
   uint32_t off_bias, off_a, off_w, off_h, smem_bytes;
   uint32_t a_stage_bytes, w_blk_bytes, h_stage_bytes;
   uint32_t tmem_cols;       // power of two >= 32
+  unsigned long long* trace;  // debug: CTA 0 writes clock stamps [tile < 64][event < 16] (nullptr: off)
 };
 
 // Opaque CUtensorMap (128 bytes, 64-byte aligned) passed to the kernel by value.

@@ -206,6 +206,7 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
             if (v.w[((size_t)n * v.cin_v + c) * v.n_taps + j] != 0.f) { nz = true; break; }
         if (nz) m |= (uint64_t)1 << j;
       }
+      if (extra && m == 0) m = 1;                      // fused unit: every chunk is loaded (E2 tracks the A ring)
       masks[(size_t)nt * L.n_kchunks + kc] = m;
       any |= m != 0;
     }
@@ -278,6 +279,8 @@ static int make_view(const Buf& b, int f, TcView* v) {
 
 static uint32_t align_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
 
+static unsigned long long* g_trace = nullptr;   // debug hook only: device buffer [64][16] of clock stamps
+
 // x_act / res_act / out_act: the tensor is (to be) stored LeakyReLU-activated (Plan::sact).
 static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Buf& src, const Buf& dst,
                      const Buf* res, int B, cudaStream_t s, int x_act = 0, int res_act = 0, int out_act = 0) {
@@ -298,21 +301,29 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   p.pre_act = x_act ? RB_ACT_NONE : op.pre_act;
   p.out_act = out_act ? RB_ACT_LEAKY : RB_ACT_NONE;
   p.res_act = (res && res_act) ? 1 : 0;
+  // fused unit whose residual is its own input: E2 reads it back from the A tile in smem
+  p.res_smem = (L.fused && res && res->p == src.p && rop.res_delay == 0 && L.n_kchunks == 1 &&
+                p.pre_act == RB_ACT_NONE) ? 1 : 0;   // (an activation pass would overwrite the tile)
   p.B = B;
   p.n_taps = L.n_taps; p.dil = L.dil; p.off = L.off;
   p.KC = L.KC; p.n_kchunks = L.n_kchunks;
   p.N_TILE = L.N_TILE; p.n_ntiles = L.n_ntiles;
   for (int i = 0; i <= L.n_ntiles; ++i) p.nt_base[i] = L.nt_base[i];
   p.out_mask = L.out_mask;
+  p.trace = g_trace;
   p.fused = L.fused ? 1 : 0;
   p.act2 = L.act2; p.bias2 = L.bias2; p.alpha2 = L.alpha2; p.n_blk1 = L.total_blocks;
   const int halo = (L.n_taps - 1) * L.dil;
   const uint32_t budget = 224u * 1024u;
   const uint32_t w_total = (uint32_t)(L.total_blocks + (L.fused ? L.N_TILE / L.KC : 0)) * L.blk_bytes;
   p.w_blk_bytes = L.blk_bytes;
-  p.off_bias = 512;           // after the mbarriers and the TMEM address slot
-  const uint32_t fixed = align_up(512 + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
-  p.SH = L.fused ? 2 : 0;
+  p.off_bias = 640 + 1024;    // after the mbarriers, the TMEM address slot and the tap masks
+  RB_CHECK(L.n_ntiles * L.n_kchunks <= 128, RB_ERR_UNSUPPORTED, "too many (n-tile, K-chunk) pairs");
+  const uint32_t fixed = align_up(p.off_bias + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
+  // accumulator stages: as many as TMEM holds (<= 4); the fused unit keeps one h tile per stage
+  const int acc_cols1 = L.fused ? 2 * L.N_TILE : L.N_TILE;
+  const int sd_max = std::max(1, std::min(4, 512 / acc_cols1));
+  p.SH = L.fused ? std::min(sd_max, p.res_smem ? 3 : 4) : 0;
   p.h_stage_bytes = L.fused ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
   const uint32_t h_total = p.SH * p.h_stage_bytes;
   // resident weights when the whole layer fits beside >= 2 A stages, else a streamed ring
@@ -361,8 +372,10 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   }
   RB_CHECK(p.SA >= 1, RB_ERR_UNSUPPORTED, "conv tile does not fit in shared memory");
   const int acc_cols = L.fused ? 2 * L.N_TILE : p.MT * L.N_TILE;
-  p.SD = (2 * acc_cols <= 512) ? 2 : 1;
-  RB_CHECK(!L.fused || p.SD == 2, RB_ERR_UNSUPPORTED, "fused unit needs two accumulator stages");
+  p.SD = std::max(1, std::min(4, 512 / acc_cols));
+  if (L.fused) p.SD = std::min(sd_max, 4);
+  if (p.res_smem && p.SA < 5) p.res_smem = 0;           // too few A stages to hold tiles until E2
+  RB_CHECK(!L.fused || p.SD >= 2, RB_ERR_UNSUPPORTED, "fused unit needs two accumulator stages");
   uint32_t cols = 32;
   while (cols < (uint32_t)(p.SD * acc_cols)) cols <<= 1;
   p.tmem_cols = cols;
@@ -864,9 +877,19 @@ extern "C" int rb_debug_conv_bf16(const rb_debug_conv* d) {
   if (!rc) rc = mk(1, nullptr);
   if (!rc && d->n_ops == 2) rc = mk(2, nullptr);
   if (!rc && d->res) rc = mk(3, d->res);
+  if (!rc && d->trace) {
+    RB_CUDA(cudaMalloc((void**)&tc::g_trace, 64 * 16 * 8));
+    RB_CUDA(cudaMemset(tc::g_trace, 0, 64 * 16 * 8));
+  }
   for (int i = 0; i < d->n_ops && !rc; ++i) {
     if (pl->skip[i]) continue;
     rc = tc_exec_op(h, pl, i, bufs, B, nullptr, 0, 0);
+  }
+  if (tc::g_trace) {
+    cudaDeviceSynchronize();
+    cudaMemcpy(d->trace, tc::g_trace, 64 * 16 * 8, cudaMemcpyDeviceToHost);
+    cudaFree(tc::g_trace);
+    tc::g_trace = nullptr;
   }
   if (!rc) {
     cudaError_t e = cudaDeviceSynchronize();

@@ -41,3 +41,15 @@ if len(sys.argv) > 2:
         for m in ('UTCHMMA', 'LDTM', 'LDGSTS', 'UBLKCP', 'UTCBAR', 'STG', 'BAR.SYNC', 'EXIT', 'TRYWAIT', 'ARRIVE', 'R2UR'):
             if m in r[idx['Source']]: cur['marks'].add(m)
     print(cur['start'], cur['samples'], cur['exec'], sorted(cur['marks']), sorted(cur['st'].items(), key=lambda x: -x[1])[:3])
+
+# every mbarrier wait site (first TRYWAIT of each mbar_wait) with the samples of its poll loop
+if len(sys.argv) > 2:
+    print("wait sites (instr index, samples in [site, site+32), executions of first try_wait):")
+    i = 0
+    while i < len(data):
+        if 'TRYWAIT' in data[i][idx['Source']]:
+            smp = sum(int(r[idx['# Samples']] or 0) for r in data[i:i + 32])
+            print("  %5d  samples %6d  exec %s" % (i, smp, data[i][idx['Instructions Executed']]))
+            i += 32
+        else:
+            i += 1
