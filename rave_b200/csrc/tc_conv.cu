@@ -319,13 +319,20 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
       if (has_res && valid) {
 #pragma unroll
         for (int q = 0; q < NC / 8; ++q) {
-          uint4 r4 = rr[q];
-          if (p.res_act) { r4.x = unleaky2(r4.x); r4.y = unleaky2(r4.y); r4.z = unleaky2(r4.z); r4.w = unleaky2(r4.w); }
+          const uint4 r4 = rr[q];
           const uint32_t w[4] = {r4.x, r4.y, r4.z, r4.w};
 #pragma unroll
-          for (int e = 0; e < 4; ++e)
-            add2(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1], __uint_as_float(w[e] << 16),
-                 __uint_as_float(w[e] & 0xffff0000u));
+          for (int e = 0; e < 4; ++e) {
+            float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
+            if (p.res_act) {
+              // stored as z = leaky(x): x = min(z, 5 z), exact in fp32 (no second bf16 rounding)
+              float l5, h5;
+              mul2(l5, h5, lo, hi, 5.f, 5.f);
+              lo = fminf(lo, l5);
+              hi = fminf(hi, h5);
+            }
+            add2(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1], lo, hi);
+          }
         }
       }
       if (has_res && mtn < MTn) load_rr(mtn, c0n);        // next chunk's residual, in flight during the stores

@@ -170,6 +170,57 @@ static int build_view_weight(const rb_handle* h, int oi, const Plan& pl, ViewWei
   return RB_ERR_INVALID;
 }
 
+// Row batching: F consecutive rows become ONE row of F x the channels on both sides,
+//   D'[t', s*N + n] = sum_j sum_c A[F t' + s + j*dil - off, c] W[n, c, j],   s < F,
+// i.e. a conv over rows of F*cin channels with ceil((F + halo) / F) taps.  Same bytes in memory
+// (view factors fin*F / fout*F); narrow layers (PQMF banks, first / last convs) get an MMA N
+// that is F times wider, F times fewer tiles and output chunks for every epilogue warp.  The
+// zero (tap, sub-row) blocks this creates are skipped by the packer's tap masks.
+static void batch_rows(ViewWeight& v, int F) {
+  ViewWeight o;
+  o.fin = v.fin * F; o.fout = v.fout * F; o.cin_v = v.cin_v * F; o.N_total = v.N_total * F;
+  const int amin = floordiv(-v.off, F), amax = floordiv(F - 1 + (v.n_taps - 1) * v.dil - v.off, F);
+  o.n_taps = amax - amin + 1; o.dil = 1; o.off = -amin; o.out_mask = 0;
+  o.w.assign((size_t)o.N_total * o.cin_v * o.n_taps, 0.f);
+  for (int s = 0; s < F; ++s)
+    for (int n = 0; n < v.N_total; ++n) {
+      // reverse_half (out_mask): odd channels of even rows change sign; F is even, so row parity = s parity
+      const float sign = (v.out_mask && !(s & 1) && (n & 1)) ? -1.f : 1.f;
+      for (int j = 0; j < v.n_taps; ++j) {
+        const int m = s + j * v.dil - v.off, a = floordiv(m, F), b = m - a * F;
+        for (int c = 0; c < v.cin_v; ++c)
+          o.at(s * v.N_total + n, b * v.cin_v + c, a - amin) = sign * v.at(n, c, j);
+      }
+    }
+  if (!v.bias.empty()) {
+    o.bias.resize(o.N_total);
+    for (int s = 0; s < F; ++s)
+      for (int n = 0; n < v.N_total; ++n)
+        o.bias[s * v.N_total + n] = ((v.out_mask && !(s & 1) && (n & 1)) ? -1.f : 1.f) * v.bias[n];
+  }
+  if (!v.alpha.empty()) {
+    o.alpha.resize(o.cin_v);
+    for (int b = 0; b < F; ++b)
+      for (int c = 0; c < v.cin_v; ++c) o.alpha[b * v.cin_v + c] = v.alpha[c];
+  }
+  v = std::move(o);
+}
+
+// Batching factor for a narrow layer: widest N <= 128 whose weights stay resident in smem.
+static int choose_row_batch(const ViewWeight& v, int rows_per_frame) {
+  if (v.N_total > 64) return 1;
+  for (int F = 4; F >= 2; F >>= 1) {
+    if (rows_per_frame % F) continue;
+    if (v.N_total * F > 128) continue;
+    const int taps = floordiv(F - 1 + (v.n_taps - 1) * v.dil - v.off, F) - floordiv(-v.off, F) + 1;
+    // non-zero (tap, sub-row) blocks: one per distinct row offset s + j*dil - off
+    const size_t bytes = (size_t)(v.N_total * F) * v.cin_v * (size_t)(F + (v.n_taps - 1) * v.dil) * 2;
+    if (taps > 64 || bytes > (size_t)112 * 1024) continue;
+    return F;
+  }
+  return 1;
+}
+
 static int largest_div16(int v, int cap) {
   int best = 16;
   for (int d = 16; d <= cap && d <= v; d += 16)
@@ -605,6 +656,10 @@ int tc_pack_weights(rb_handle* h) {
         rc = build_view_weight(h, i + 1, *pl, v2);
         if (rc) return rc;
       }
+    }
+    if (!fuse && op.res < 0) {
+      const int F = choose_row_batch(v, h->slots[op.dst].per_frame / v.fout);
+      if (F > 1) batch_rows(v, F);
     }
     Layer& L = pl->layers[i];
     rc = pack_layer(v, fuse ? 128 : 64, fuse ? &v2 : nullptr, L);
