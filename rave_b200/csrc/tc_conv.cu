@@ -337,6 +337,24 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
       }
       if (has_res && mtn < MTn) load_rr(mtn, c0n);        // next chunk's residual, in flight during the stores
       if (!valid) return;
+      if (NC == 32 && p.head) {
+        // waveform head (blocks.py:700-707, amplitude_modulation): tanh(wave * sigmoid(amp)), then the
+        // reverse_half sign of the PQMF synthesis input (pqmf.py:13-17): odd bands of even real rows
+        const int sub = (ch0 + c0) >> 5;                  // real row = t * head + sub
+        const bool even_row = (((t * p.head) + sub) & 1) == 0;
+        float o[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float g = __fdividef(1.f, 1.f + __expf(-v[16 + e]));
+          const float x = v[e] * g;
+          const float th = 1.f - __fdividef(2.f, 1.f + __expf(2.f * x));
+          o[e] = ((e & 1) && even_row) ? -th : th;
+        }
+        uint4* hp = ys + (p.y.hist + t) * p.y.sT;
+        hp[goff32(p.y, 2 * sub)] = pack8(o);
+        hp[goff32(p.y, 2 * sub + 1)] = pack8(o + 8);
+        return;
+      }
       if (p.out_mask && !(t & 1)) {
 #pragma unroll
         for (int e = 1; e < NC; e += 2) v[e] = -v[e];

@@ -67,6 +67,9 @@ struct TcParams {
   int step_nt, step_b, step_tile;   // work-item increment of a persistent CTA (grid stride, decomposed)
   int SA, SW, SD;           // A stages, W stages (streamed), accumulator stages
   int out_mask;             // 1: negate odd channels at even rows (pqmf.py:13-17 reverse_half)
+  // > 0: every 32-column chunk is [16 wave | 16 amplitude] of one real row (head = chunks per view
+  // row); the epilogue stores tanh(wave * sigmoid(amp)), reverse_half applied, as 16 channels
+  int head;
   int tiles_per_stream, n_work;
   // fused DilatedUnit (blocks.py:84-113 + Residual :32-46): second GEMM k=1 on act(D1 + bias)
   int fused;

@@ -38,6 +38,9 @@ struct Layer {
   // fused DilatedUnit: this layer also carries the 1x1 conv that follows it
   bool fused = false;
   int fused_with = -1;            // op index of the 1x1 conv
+  // op whose dst this launch writes: the fused 1x1 conv, or a HEAD_V2 op folded into the epilogue
+  int tail = -1;
+  int head = 0;                   // epilogue computes tanh(wave * sigmoid(amp)) (blocks.py amplitude_modulation)
   float* bias2 = nullptr;
   float* alpha2 = nullptr;
   int act2 = 0;
@@ -340,8 +343,9 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   int rc = make_view(src, L.fin, &p.x);
   if (rc) return rc;
   if ((rc = make_view(dst, L.fout, &p.y))) return rc;
-  RB_CHECK(p.x.C == L.cin_v && p.y.C == L.N_total, RB_ERR_INVALID, "layer/view channel mismatch (%d vs %d, %d vs %d)",
-           p.x.C, L.cin_v, p.y.C, L.N_total);
+  RB_CHECK(p.x.C == L.cin_v && p.y.C == (L.head ? L.N_total / 2 : L.N_total), RB_ERR_INVALID,
+           "layer/view channel mismatch (%d vs %d, %d vs %d)", p.x.C, L.cin_v, p.y.C, L.N_total);
+  p.head = L.head;
   const rb_op& rop = op2 ? *op2 : op;
   if (res) {
     if ((rc = make_view(*res, 1, &p.res))) return rc;
@@ -664,9 +668,24 @@ int tc_pack_weights(rb_handle* h) {
     Layer& L = pl->layers[i];
     rc = pack_layer(v, fuse ? 128 : 64, fuse ? &v2 : nullptr, L);
     if (rc) return rc;
+    // conv -> HEAD_V2 (no noise branch, amplitude modulation, 16 bands): the head runs in the epilogue
+    if (!fuse && op.kind == RB_OP_CONV && op.res < 0 && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {
+      const rb_op& o2 = h->ops[i + 1];
+      bool only_reader = true;
+      for (int j = 0; j < nops; ++j)
+        if (j != i + 1 && (h->ops[j].src == op.dst || h->ops[j].src2 == op.dst || h->ops[j].res == op.dst)) only_reader = false;
+      if (o2.kind == RB_OP_HEAD_V2 && o2.src == op.dst && o2.src2 < 0 && o2.k == 1 && o2.c_out == 16 &&
+          op.c_out == 32 && std::max(op.ileave, 1) == 1 && only_reader && pl->cp[o2.dst] == 16 &&
+          op.dst != h->spec.dec_out_slot && L.N_total % 32 == 0) {
+        L.head = L.N_total / 32;
+        L.tail = i + 1;
+        pl->skip[i + 1] = 1;
+      }
+    }
     if (fuse) {
       L.fused = true;
       L.fused_with = i + 1;
+      L.tail = i + 1;
       L.act2 = h->ops[i + 1].pre_act;
       if (!v2.bias.empty() && (rc = dev_upload(v2.bias, &L.bias2))) return rc;
       if (!v2.alpha.empty() && (rc = dev_upload(v2.alpha, &L.alpha2))) return rc;
@@ -692,6 +711,8 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
         return run_layer(L, op, &o2, bufs[op.src], bufs[o2.dst], &bufs[o2.res], B, s, sa[op.src], sa[o2.res],
                          sa[o2.dst]);
       }
+      if (L.head)
+        return run_layer(L, op, nullptr, bufs[op.src], bufs[h->ops[L.tail].dst], nullptr, B, s, sa[op.src], 0, 0);
       return run_layer(L, op, nullptr, bufs[op.src], bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,
                        sa[op.src], op.res >= 0 ? sa[op.res] : 0, sa[op.dst]);
     }
@@ -754,9 +775,9 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
   for (int i = ob; i < oe; ++i) {
     if (pl->skip[i]) continue;
     const rb_op& op = h->ops[i];
-    const rb_op& ol = pl->layers[i].fused ? h->ops[pl->layers[i].fused_with] : op;
+    const rb_op& ol = pl->layers[i].tail >= 0 ? h->ops[pl->layers[i].tail] : op;
     last_use[op.src] = i;
-    if (ol.res >= 0) last_use[ol.res] = i;
+    if (ol.res >= 0 && !pl->layers[i].head) last_use[ol.res] = i;
     if (op.src2 >= 0) last_use[op.src2] = i;
     last_use[ol.dst] = std::max(last_use[ol.dst], i);
   }
@@ -820,7 +841,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
       }
       if (pl->skip[i]) continue;
       const rb_op& op = h->ops[i];
-      const rb_op& ol = pl->layers[i].fused ? h->ops[pl->layers[i].fused_with] : op;
+      const rb_op& ol = pl->layers[i].tail >= 0 ? h->ops[pl->layers[i].tail] : op;
       if (!bufs[ol.dst].p) {
         int rc = alloc_slot(ol.dst);
         if (rc) return rc;
@@ -834,7 +855,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
         rc = tc_exec_op(h, pl, i, bufs, nb, noise, noise_bstride, s);
       }
       if (rc) return rc;
-      const int used[3] = {op.src, ol.res, op.src2};
+      const int used[3] = {op.src, pl->layers[i].head ? -1 : ol.res, op.src2};
       for (int u : used)
         if (u >= 0 && last_use[u] == i && buf_of[u] >= 0) {
           h->pool[buf_of[u]].busy = false;
