@@ -380,7 +380,6 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   const int sd_max = std::max(1, std::min(4, 512 / acc_cols1));
   p.SH = L.fused ? std::min(sd_max, p.res_smem ? 3 : 4) : 0;
   p.h_stage_bytes = L.fused ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
-  const uint32_t h_total = p.SH * p.h_stage_bytes;
   // resident weights when the whole layer fits beside >= 2 A stages, else a streamed ring
   for (int attempt = 0; attempt < 2; ++attempt) {
     const bool resident = attempt == 0 && (L.n_ntiles == 1) && w_total <= 160u * 1024u;
@@ -412,6 +411,11 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     p.SW = resident ? 0 : 4;
     uint32_t w_bytes = resident ? align_up(w_total, 128) : p.SW * L.blk_bytes;
     if (!resident && fixed + w_bytes + 2 * p.a_stage_bytes > budget) { p.SW = 2; w_bytes = p.SW * L.blk_bytes; }
+    if (L.fused) {
+      // fewer h stages when smem is tight (wide units): keep at least 3 A stages if possible
+      while (p.SH > 1 && fixed + w_bytes + p.SH * p.h_stage_bytes + 3 * p.a_stage_bytes > budget) --p.SH;
+    }
+    const uint32_t h_total = p.SH * p.h_stage_bytes;
     if (fixed + w_bytes + h_total + p.a_stage_bytes > budget) {
       RB_CHECK(resident, RB_ERR_UNSUPPORTED, "conv tile does not fit in shared memory");
       continue;
@@ -655,7 +659,8 @@ int tc_pack_weights(rb_handle* h) {
       const rb_op& o2 = h->ops[i + 1];
       fuse = o2.kind == RB_OP_CONV && o2.k == 1 && o2.stride == 1 && o2.ileave <= 1 && op.stride == 1 &&
              op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 && o2.pre_act == op.pre_act &&
-             v.N_total == v.cin_v && v.N_total <= 64 && pl->cp[o2.dst] == v.N_total;
+             v.N_total == v.cin_v && v.N_total <= 128 && pl->cp[o2.dst] == v.N_total &&
+             (size_t)v.N_total * v.cin_v * (v.n_taps + 1) * 2 <= (size_t)128 * 1024;
       if (fuse) {
         rc = build_view_weight(h, i + 1, *pl, v2);
         if (rc) return rc;
@@ -666,7 +671,7 @@ int tc_pack_weights(rb_handle* h) {
       if (F > 1) batch_rows(v, F);
     }
     Layer& L = pl->layers[i];
-    rc = pack_layer(v, fuse ? 128 : 64, fuse ? &v2 : nullptr, L);
+    rc = pack_layer(v, 64, fuse ? &v2 : nullptr, L);
     if (rc) return rc;
     // conv -> HEAD_V2 (no noise branch, amplitude modulation, 16 bands): the head runs in the epilogue
     if (!fuse && op.kind == RB_OP_CONV && op.res < 0 && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {

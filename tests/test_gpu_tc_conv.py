@@ -123,7 +123,8 @@ def test_single_conv(c):
 
 
 @pytest.mark.parametrize("C_,dil,act,n", [(64, 1, 1, 512), (64, 9, 1, 333), (64, 3, 2, 1000), (16, 3, 1, 130),
-                                          (32, 9, 1, 4096), (128, 3, 1, 300)])
+                                          (32, 9, 1, 4096), (128, 3, 1, 300), (128, 9, 1, 1000), (128, 1, 2, 700),
+                                          (256, 3, 1, 300)])
 def test_dilated_unit_pair(C_, dil, act, n):
     """Residual(DilatedUnit): x + W1 act(W3 *_d act(x) + b3) + b1 (blocks.py:32-46,84-113)."""
     g = torch.Generator().manual_seed(C_ + dil)
@@ -135,13 +136,13 @@ def test_dilated_unit_pair(C_, dil, act, n):
     a3 = 1.0 + 0.1 * torch.randn(C_, generator=g) if act == 2 else None
     a1 = 1.0 + 0.1 * torch.randn(C_, generator=g) if act == 2 else None
     h = _ref_conv(x, w3, b3, 3, 1, dil, dil, 1, act, a3)
-    hb = h.bfloat16().float() if C_ > 64 else h          # unfused path stores h in bf16
+    hb = h.bfloat16().float() if C_ > 128 else h         # unfused path stores h in bf16
     ref = x + _ref_conv(hb, w1, b1, 1, 1, 1, 0, 1, act, a1)
     ops = [dict(c_in=C_, c_out=C_, k=3, stride=1, dilation=dil, off=dil, ileave=1, pre_act=act, has_bias=1, res_delay=0),
            dict(c_in=C_, c_out=C_, k=1, stride=1, dilation=1, off=0, ileave=1, pre_act=act, has_bias=1, res_delay=0)]
     y, fused = _run(ops, [w3.numpy(), w1.numpy()], [b3.numpy(), b1.numpy()],
                     [None if a3 is None else a3.numpy(), None if a1 is None else a1.numpy()], x.numpy())
-    assert fused == (1 if C_ <= 64 else 0)
+    assert fused == (1 if C_ <= 128 else 0)
     assert np.isfinite(y).all()
     assert _rel(y, ref.numpy()) < TOL
 
@@ -186,7 +187,7 @@ def test_single_conv_activated_storage(c):
     assert _rel(y, ref.numpy()) < TOL
 
 
-@pytest.mark.parametrize("C_,dil,n", [(64, 9, 777), (32, 1, 256), (128, 3, 300)])
+@pytest.mark.parametrize("C_,dil,n", [(64, 9, 777), (32, 1, 256), (128, 3, 300), (128, 9, 2000)])
 def test_dilated_unit_pair_activated_storage(C_, dil, n):
     g = torch.Generator().manual_seed(C_ * 3 + dil)
     B = 2
@@ -195,7 +196,7 @@ def test_dilated_unit_pair_activated_storage(C_, dil, n):
     w1 = _bf((torch.randn(C_, C_, 1, generator=g) / np.sqrt(C_)).numpy())
     b3, b1 = torch.randn(C_, generator=g) * 0.1, torch.randn(C_, generator=g) * 0.1
     h = _ref_conv(z, w3, b3, 3, 1, dil, dil, 1, 0, None)
-    hb = F.leaky_relu(h.bfloat16().float() if C_ > 64 else h, 0.2)   # unfused path stores h in bf16
+    hb = F.leaky_relu(h.bfloat16().float() if C_ > 128 else h, 0.2)  # unfused path stores h in bf16
     ref = F.leaky_relu(_unleaky(z) + _ref_conv(hb, w1, b1, 1, 1, 1, 0, 1, 0, None), 0.2)
     ops = [dict(c_in=C_, c_out=C_, k=3, stride=1, dilation=dil, off=dil, ileave=1, pre_act=1, has_bias=1, res_delay=0),
            dict(c_in=C_, c_out=C_, k=1, stride=1, dilation=1, off=0, ileave=1, pre_act=1, has_bias=1, res_delay=0)]

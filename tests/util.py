@@ -30,3 +30,54 @@ def rel_l2(a, b):
     a = np.asarray(a, dtype=np.float64).ravel()
     b = np.asarray(b, dtype=np.float64).ravel()
     return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+def bf16_floor(name):
+    """Error of the REFERENCE ALGORITHM ITSELF when it is run in bf16: the CPU oracle with its
+    folded conv weights, its conv / AdaIN outputs and its inputs rounded to bf16 (everything
+    else fp32).  Returns rel-L2 against the fp32 golden for (encoded latent, decode, forward).  Nets whose
+    floor is far above the 1e-2 bar (v3: Snake + AdaIN at random init is chaotic in bf16 -- weight
+    rounding alone moves the output by > 10 %) cannot be held to that bar by any bf16 engine; the
+    bf16 parity test holds the CUDA path to a multiple of this floor instead."""
+    import torch
+    from oracle import rave_oracle as O
+    from oracle.model import OracleRAVE
+
+    def bf(t):
+        return t.bfloat16().float()
+
+    meta, a = load_golden(name)
+    sd = golden_state_dict(meta)
+    saved = (O._conv, O._conv_transpose, O._adain, O._folded)
+
+    def conv(*args, **kw):
+        y, d = saved[0](*args, **kw)
+        return bf(y), d
+
+    def convt(*args, **kw):
+        y, d = saved[1](*args, **kw)
+        return bf(y), d
+
+    def adain(*args, **kw):
+        return bf(saved[2](*args, **kw))
+
+    def folded(sd_, prefix):
+        r = saved[3](sd_, prefix)
+        return (bf(r[0]),) + tuple(r[1:])
+
+    O._conv, O._conv_transpose, O._adain, O._folded = conv, convt, adain, folded
+    try:
+        o = OracleRAVE(meta["cfg"], sd)
+        x = bf(torch.from_numpy(golden_input(a)))
+        noise = None
+        if meta["cfg"].get("noise"):
+            from oracle.weights_recipe import recipe_input
+            B, _, T = x.shape
+            noise = torch.from_numpy(recipe_input((B, T // 16 // 8, 16, 8), int(a["noise_seed"].item()), uniform=True))
+        z = bf(o.encode(x))
+        y = bf(o.decode(bf(torch.from_numpy(a["z"])), noise))
+        y2 = bf(o.decode(z, noise))
+    finally:
+        O._conv, O._conv_transpose, O._adain, O._folded = saved
+    nl = meta["cfg"]["latent_size"]       # the speaker-embedding channels of z are exact: score the latent alone
+    return rel_l2(z[:, :nl].numpy(), a["z"][:, :nl]), rel_l2(y.numpy(), a["y"]), rel_l2(y2.numpy(), a["y"])
