@@ -4,10 +4,11 @@
     python bench.py --gpus N --steps K --warmup W [--impl reference] [--dtype bf16|f32]
 
 A step = one pass of RAVE.forward (encode -> decode) over the synthetic batch of
-BASELINE.json configs[1]: 512 streams x 2^18 samples @44.1 kHz, random-init v2 weights
-(name-keyed recipe, oracle/weights_recipe.py), streams sharded over the N ranks with no
-exchange; the only collective is the final NCCL all-gather of the outputs (inside the
-timed region).  Prints ONE JSON line on rank 0.
+BASELINE.json configs[1]: 512 streams x 2^18 samples @44.1 kHz per GPU, random-init v2 weights
+(name-keyed recipe, oracle/weights_recipe.py).  Streams are independent (tests: bitwise), so
+N GPUs run N shards of 512 streams each with no data-path collective (weak scaling); the only
+collectives are the barrier and the max-over-ranks of the device time.  Prints ONE JSON line
+on rank 0.
 
 --impl reference: the reference's own CPU path (the oracle port of its PyTorch modules --
 the reference itself is not importable) on the host cores, each step a
@@ -118,7 +119,7 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "audio-sec/sec", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": {"workload": f"v2 encode+decode, {STREAMS} streams x 2^18 samples", "sample": sample},
         "cpu_baseline": {"value": val, "unit": "audio-sec/sec", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -139,9 +140,9 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     esz = 2 if args.dtype == "bf16" else 4
-    streams, T = args.streams, args.samples
-    assert streams % world == 0
-    B = streams // world
+    T = args.samples
+    B = args.streams                       # per GPU (weak scaling: every rank runs the full configuration)
+    streams = B * world
     meta, sd = _state_dict()
     m = RAVE.from_gin(["v2.gin"], device=f"cuda:{local}", dtype=dtype)
     m.load_state_dict(sd)
@@ -151,13 +152,9 @@ def run_ours(args):
     base = torch.from_numpy(recipe_input((64, 1, T), 1234 + rank)).cuda()
     x = base.repeat((B + 63) // 64, 1, 1)[:B].contiguous().to(dtype)
     x += (0.001 * torch.arange(B, device="cuda").view(B, 1, 1)).to(dtype)
-    gathered = torch.empty(world * B, 1, T, dtype=dtype, device="cuda") if world > 1 else None
 
     def step():
-        y = m(x)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, y)
-        return y
+        return m(x)
 
     def barrier():
         if world > 1:
@@ -195,34 +192,55 @@ def run_ours(args):
     torch.cuda.synchronize()
     op_ms = m.op_times_ms()
     m.profile_ops(False)
-    conv_ms = conv_flops = 0.0
+    # every conv / PQMF op is one launch of tc_conv_kernel (a fused DilatedUnit: one launch for two
+    # ops -- the second op then reports 0 ms): algorithmic flops and HBM bytes of those launches
     frames = B * T // m.spec.samples_per_frame
-    for op, t_ms in zip(m.spec.ops, op_ms):
+    slots = m.spec.slots
+
+    def slot_bytes(sl):
+        return slots[sl].per_frame * frames * slots[sl].channels * esz
+
+    conv_ms = conv_flops = conv_bytes = 0.0
+    n_launch = 0
+    rows = []
+    ops = list(m.spec.ops)
+    for i, (op, t_ms) in enumerate(zip(ops, op_ms)):
+        mac = 0
         if op.kind == 1:
-            conv_ms += t_ms
-            pf = m.spec.slots[op.dst].per_frame
+            pf = slots[op.dst].per_frame
             mac = pf * (2 * op.c_in * (op.c_out // op.ileave) if op.ileave > 1 else op.c_in * op.c_out * op.k)
+        elif op.kind in (2, 3):
+            mac = slots[op.dst if op.kind == 2 else op.src].per_frame * op.k * op.c_out * (1 if op.kind == 2 else op.c_in)
+        if op.kind in (1, 2, 3):
+            conv_ms += t_ms
             conv_flops += 2.0 * mac * frames
+            if t_ms > 0:
+                n_launch += 1
+                fused_next = i + 1 < len(ops) and ops[i + 1].kind in (1, 5) and op_ms[i + 1] == 0.0
+                dst = ops[i + 1].dst if fused_next else op.dst
+                conv_bytes += slot_bytes(op.src) + slot_bytes(dst)
+                if op.res >= 0 and not fused_next:
+                    conv_bytes += slot_bytes(op.res)
+        rows.append({"name": op.name, "kind": op.kind, "c_in": op.c_in, "c_out": op.c_out, "k": op.k,
+                     "stride": op.stride, "dil": op.dilation, "ileave": op.ileave, "ms": t_ms,
+                     "gflop": 2e-9 * mac * frames, "out_mb": slot_bytes(op.dst) / 1e6})
     if args.dump_ops and rank == 0:
-        rows = []
-        for op, t_ms in zip(m.spec.ops, op_ms):
-            pf = m.spec.slots[op.dst].per_frame
-            mac = 0
-            if op.kind == 1:
-                mac = pf * (2 * op.c_in * (op.c_out // op.ileave) if op.ileave > 1 else op.c_in * op.c_out * op.k)
-            rows.append({"name": op.name, "kind": op.kind, "c_in": op.c_in, "c_out": op.c_out, "k": op.k,
-                         "stride": op.stride, "dil": op.dilation, "ileave": op.ileave, "ms": t_ms,
-                         "gflop": 2e-9 * mac * frames,
-                         "out_mb": pf * frames * m.spec.slots[op.dst].channels * esz / 1e6})
         os.makedirs(os.path.dirname(os.path.abspath(args.dump_ops)), exist_ok=True)
         json.dump(rows, open(args.dump_ops, "w"), indent=1)
-    n_conv = sum(1 for op in m.spec.ops if op.kind == 1)
     pk = _peaks()
     achieved = conv_flops / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "r01_tc_conv_traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get("dram_bytes_per_step")
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["tf_sus"], "unit": "TFLOP/s",
-                "frac": achieved / pk["tf_sus"], "traffic": None,
-                "kernel": "conv (all %d conv launches of one step: %.1f of %.1f ms)" % (n_conv, conv_ms, sum(op_ms)),
+                "frac": achieved / pk["tf_sus"], "traffic": traffic,
+                "kernel": "tc_conv_kernel (the %d launches of one step, %.2f of %.2f ms; achieved = their "
+                          "algorithmic flops / their summed CUDA-event time)" % (n_launch, conv_ms, sum(op_ms)),
                 "peak_source": pk["src"] + ", sustained bf16",
+                "algorithmic_bytes": conv_bytes,
+                "hbm": {"achieved": conv_bytes / (conv_ms / 1e3) / 1e9 if conv_ms > 0 else 0.0, "peak": pk["hbm"],
+                        "unit": "GB/s", "frac": (conv_bytes / (conv_ms / 1e3) / 1e9) / pk["hbm"] if conv_ms > 0 else 0.0},
                 "whole_path_frac": (flops_step * world / (ms / args.steps / 1e3) / 1e12) / (pk["tf_sus"] * world)}
 
     # ---- end to end through the public API with HOST buffers (pinned), H2D + D2H inside
@@ -252,9 +270,9 @@ def run_ours(args):
         out = {
             "metric": METRIC, "value": value, "unit": "audio-sec/sec", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": f"v2 encode+decode, {streams} streams x {T} samples @44.1 kHz, "
-                                   f"{B} streams per GPU, final NCCL all-gather of outputs",
+            "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": f"v2 encode+decode (BASELINE configs[1]), {B} streams x {T} samples @44.1 kHz "
+                                   f"per GPU, {streams} streams in all, no data-path collective",
                        "l2": f"inputs {B * T * esz >> 20} MiB per GPU > 126 MB L2, no flush needed",
                        "weights": "random-init (name-keyed recipe), CAPACITY=64"},
             "clocks": sampler.summary(),
@@ -273,7 +291,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--dtype", default=os.environ.get("RAVE_BENCH_DTYPE", "bf16"), choices=["bf16", "f32"])

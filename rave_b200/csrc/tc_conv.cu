@@ -87,21 +87,22 @@ struct Work {
 // divisions and then advanced by the pre-decomposed grid stride (adds and compares only).
 struct WorkIter {
   int nt, b, tile, left;
+  // w = (b * tiles_per_stream + tile) * n_ntiles + nt: the n-tiles of one row tile run at the same
+  // time on neighbouring CTAs, so the A tile is read from HBM once and from L2 afterwards
   __device__ __forceinline__ void init(const TcParams& p) {
     const int w = blockIdx.x;
-    const int n_rt = p.B * p.tiles_per_stream;
-    nt = w / n_rt;
-    const int rt = w - nt * n_rt;
+    const int rt = w / p.n_ntiles;
+    nt = w - rt * p.n_ntiles;
     b = rt / p.tiles_per_stream;
     tile = rt - b * p.tiles_per_stream;
     left = w < p.n_work ? (p.n_work - w + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   }
   __device__ __forceinline__ void next(const TcParams& p) {
+    nt += p.step_nt;
+    if (nt >= p.n_ntiles) { nt -= p.n_ntiles; ++tile; }
     tile += p.step_tile;
     if (tile >= p.tiles_per_stream) { tile -= p.tiles_per_stream; ++b; }
     b += p.step_b;
-    if (b >= p.B) { b -= p.B; ++nt; }
-    nt += p.step_nt;
     --left;
   }
   __device__ __forceinline__ Work work(const TcParams& p) const { return Work{nt, b, tile * p.MT * 128}; }
@@ -855,11 +856,10 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
            "only LeakyReLU can be stored activated");
   const int grid = p.n_work < n_sm ? p.n_work : n_sm;
   {
-    const int n_rt = p.B * p.tiles_per_stream;
-    p.step_nt = grid / n_rt;
-    const int r1 = grid - p.step_nt * n_rt;
-    p.step_b = r1 / p.tiles_per_stream;
-    p.step_tile = r1 - p.step_b * p.tiles_per_stream;
+    const int rt = grid / p.n_ntiles;                      // grid stride, decomposed (WorkIter::next)
+    p.step_nt = grid - rt * p.n_ntiles;
+    p.step_b = rt / p.tiles_per_stream;
+    p.step_tile = rt - p.step_b * p.tiles_per_stream;
   }
   TcTmap tm;
   int rc = make_tmap(p, &tm);
