@@ -119,7 +119,7 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "audio-sec/sec", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": {"workload": f"v2 encode+decode, {STREAMS} streams x 2^18 samples", "sample": sample},
         "cpu_baseline": {"value": val, "unit": "audio-sec/sec", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -141,7 +141,10 @@ def run_ours(args):
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     esz = 2 if args.dtype == "bf16" else 4
     T = args.samples
-    B = args.streams                       # per GPU (weak scaling: every rank runs the full configuration)
+    from rave_b200.shard import OverlappedGather, max_over_ranks, stream_shard
+    # weak (default): every rank runs the full configuration, no collective;
+    # strong: SURVEY 8(e) variant, 512 / N streams per GPU + final all-gather of the outputs
+    _, B = stream_shard(args.streams, world, rank, args.scaling)
     streams = B * world
     meta, sd = _state_dict()
     m = RAVE.from_gin(["v2.gin"], device=f"cuda:{local}", dtype=dtype)
@@ -152,9 +155,12 @@ def run_ours(args):
     base = torch.from_numpy(recipe_input((64, 1, T), 1234 + rank)).cuda()
     x = base.repeat((B + 63) // 64, 1, 1)[:B].contiguous().to(dtype)
     x += (0.001 * torch.arange(B, device="cuda").view(B, 1, 1)).to(dtype)
+    gathered = world > 1 and args.scaling == "strong"
+    gather = OverlappedGather(world) if gathered else None
 
     def step():
-        return m(x)
+        y = m(x)
+        return gather(y) if gathered else y
 
     def barrier():
         if world > 1:
@@ -172,15 +178,14 @@ def run_ours(args):
     ev0.record()
     for _ in range(args.steps):
         step()
+    if gathered:
+        gather.finish()                    # the last step's gather is inside the timed region
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
     launches = m.kernel_launches() - l0
     sampler.stop = True
-    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    ms = max_over_ranks(ms, "cuda")
     audio_s = streams * T / SR
     value = args.steps * audio_s / (ms / 1e3)
 
@@ -260,19 +265,17 @@ def run_ours(args):
         e2e_step()
     ev1.record()
     barrier()
-    t = torch.tensor([ev0.elapsed_time(ev1)], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_val = e2e_steps * audio_s / (float(t.item()) / 1e3)
+    e2e_val = e2e_steps * audio_s / (max_over_ranks(ev0.elapsed_time(ev1), "cuda") / 1e3)
 
     if rank == 0:
         sampler.join(timeout=2)
         out = {
             "metric": METRIC, "value": value, "unit": "audio-sec/sec", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": f"v2 encode+decode (BASELINE configs[1]), {B} streams x {T} samples @44.1 kHz "
-                                   f"per GPU, {streams} streams in all, no data-path collective",
+                                   f"per GPU, {streams} streams in all, " +
+                                   ("NCCL all-gather of every step's outputs, overlapped with the next step" if gathered else "no data-path collective"),
                        "l2": f"inputs {B * T * esz >> 20} MiB per GPU > 126 MB L2, no flush needed",
                        "weights": "random-init (name-keyed recipe), CAPACITY=64"},
             "clocks": sampler.summary(),
@@ -298,6 +301,8 @@ def main():
     ap.add_argument("--streams", type=int, default=STREAMS)
     ap.add_argument("--samples", type=int, default=SAMPLES)
     ap.add_argument("--microbatch", type=int, default=0)
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="strong (default, BASELINE configs[1]): --streams in all, sharded over the ranks, final all-gather; weak: --streams per GPU, no collective")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--dump-ops", default="", help="write per-op device times (JSON) to this file")
     args = ap.parse_args()

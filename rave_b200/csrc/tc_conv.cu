@@ -26,6 +26,7 @@
 // The activation kinds are template parameters so that each instantiation stays small.
 #include <cuda.h>
 
+#include <cstring>
 #include <type_traits>
 
 #include "common.cuh"
@@ -416,6 +417,9 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // Programmatic dependent launch: let the next kernel of the stream start its prologue on SMs
+  // this grid has already left; everything that touches activations waits below.
+  asm volatile("griddepcontrol.launch_dependents;");
   // Output warps: when no activation pass is needed, warps 12-15 drain accumulators too.
   //   plain:  warps [0, W_OUT_END) share the 32-column chunks round-robin
   //   fused:  warps [0, E1_WARPS) run E1 (h tile), warps [E1_WARPS, W_OUT_END) run E2 (output)
@@ -461,6 +465,9 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // the prologue above (barriers, TMEM, bias / masks) and the weight loads of the W producer do not
+  // depend on the previous kernel; activations do
+  if (warp != W_WPROD) asm volatile("griddepcontrol.wait;" ::: "memory");
 
   const uint32_t lbo_a = (uint32_t)p.R_ALLOC * 16u;
   const uint32_t lbo_w = (uint32_t)p.N_TILE * 16u;
@@ -800,7 +807,18 @@ static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStr
                                  227 * 1024));
     attr_set = true;
   }
-  tc_conv_kernel<PRE, ACT2, FUSED><<<grid, TC_THREADS, p.smem_bytes, s>>>(p, tm);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = p.smem_bytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED>, p, tm));
   return RB_OK;
 }
 
