@@ -1,11 +1,12 @@
 // tc_engine.cu -- bf16 tensor-core engine: layer planning / weight packing for the tcgen05
-// implicit-GEMM kernel (tc_conv.cu), the small channels-last elementwise kernels, and the
+// implicit-GEMM kernel (tc_conv.cu), the small group-major elementwise kernels, and the
 // op interpreter for dtype == RB_BF16.
 //
-// Activation layout: channels-last  [stream][row][Cp]  bf16, Cp = channels rounded up to 16
-// (audio slots: Cp = 1).  A stride-s conv reads its input through the view [rows/s][s*Cp],
-// a transposed conv writes its output through [rows][r*Cp'] -- same bytes, no copies -- so
-// every conv of the path becomes a stride-1 row-shift GEMM (tc_conv.cuh).
+// Activation layout: group-major  [stream][Cp/8][row][8 channels]  bf16, Cp = channels rounded
+// up to 16 (audio slots: Cp = 1, the caller's dense [stream][T]).  A stride-s conv reads its
+// input through the view [rows/s][s*Cp], a transposed conv writes its output through
+// [rows][r*Cp'] -- same bytes, no copies -- so every conv of the path becomes a stride-1
+// row-shift GEMM (tc_conv.cuh).  LeakyReLU nets store tensors already activated (Plan::sact).
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -764,7 +765,7 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
 
 // Runs ops [ob, oe) on bf16 buffers.  `in` / `out` are in the CALLER's layout ([B,1,T] audio
 // or [B,C,F] latents, dense); a range that spans both programs keeps the latent on the
-// device in channels-last form (rb_forward).
+// device in group-major form (rb_forward).
 int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int B, int F, cudaStream_t s) {
   Plan* pl = (Plan*)h->tc;
   RB_CHECK(pl, RB_ERR_STATE, "bf16 engine: weights are not packed");
@@ -839,7 +840,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
       noise = h->noise + (size_t)b0 * noise_bstride;
     }
     for (int i = ob; i < oe; ++i) {
-      if (i == n_enc && has_enc && has_dec) {      // latent stays on the device, channels-last
+      if (i == n_enc && has_enc && has_dec) {      // latent stays on the device, group-major
         bufs[h->spec.dec_in_slot] = bufs[h->spec.enc_out_slot];
         buf_of[h->spec.dec_in_slot] = buf_of[h->spec.enc_out_slot];
         buf_of[h->spec.enc_out_slot] = -1;
