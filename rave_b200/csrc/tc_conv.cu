@@ -301,6 +301,23 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
   };
   int mt = 0, c0 = part * 32;
   if (c0 >= NT) mt = MTn;
+  if (has_res && !res_s && (rit & 7) == 0) {
+    // The residual tensor was written two kernels ago and has usually left L2: pull this warp's
+    // rows of every chunk into L2 now (one prefetch per 128-byte line, no registers), while the
+    // MMAs of this work item run; the loads below then see L2 latency instead of HBM latency.
+    for (int pm = 0; pm < MTn; ++pm) {
+      const int t = row + pm * 128;
+      if (t >= p.y.n) break;
+      for (int pc = part * 32; pc < NT; pc += cstep) {
+        const int cg = (ch0 + pc) >> 3;
+        const uint4* rp = rs + ((p.res.hist - p.res_delay + t) * p.res.sT + (quad_r ? goff32(p.res, cg) : 0));
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (q * 8 < NT - pc)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + (quad_r ? q * p.res.sA : goff32(p.res, cg + q))));
+      }
+    }
+  }
   if (has_res && !res_s && mt < MTn) load_rr(mt, c0);
   mbar_wait(bar_full, parity);
   tc_fence_after();

@@ -9,6 +9,7 @@
 // row-shift GEMM (tc_conv.cuh).  LeakyReLU nets store tensors already activated (Plan::sact).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "engine.h"
@@ -243,7 +244,9 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
   L.fin = v.fin; L.fout = v.fout; L.cin_v = v.cin_v; L.n_taps = v.n_taps; L.dil = v.dil; L.off = v.off;
   L.N_total = v.N_total; L.out_mask = v.out_mask;
   RB_CHECK(v.n_taps <= 64, RB_ERR_UNSUPPORTED, "conv with %d row taps (max 64)", v.n_taps);
-  L.N_TILE = largest_div16(v.N_total, 256);
+  int ncap = 256;
+  if (const char* e = getenv("RB_TC_NTILE_CAP")) ncap = std::max(16, atoi(e));   // experiments only
+  L.N_TILE = largest_div16(v.N_total, ncap);
   L.n_ntiles = v.N_total / L.N_TILE;
   RB_CHECK(L.n_ntiles <= TC_MAX_NT, RB_ERR_UNSUPPORTED, "too many output-channel tiles");
   L.KC = largest_div16(v.cin_v, kc_cap);
@@ -409,7 +412,9 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       p.a_tx_bytes = (uint32_t)c8n * p.R_ALLOC * 16u;
     }
     p.a_stage_bytes = (uint32_t)(L.KC / 8) * p.R_ALLOC * 16u;
-    p.SW = resident ? 0 : 4;
+    // W ring depth: a single-tap layer consumes one A chunk per W block, so it needs A stages in
+    // flight (HBM latency) more than W stages (L2 latency); multi-tap layers the other way round
+    p.SW = resident ? 0 : (L.n_taps == 1 ? 2 : 4);
     uint32_t w_bytes = resident ? align_up(w_total, 128) : p.SW * L.blk_bytes;
     if (!resident && fixed + w_bytes + 2 * p.a_stage_bytes > budget) { p.SW = 2; w_bytes = p.SW * L.blk_bytes; }
     if (L.fused) {
