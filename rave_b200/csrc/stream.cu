@@ -12,6 +12,14 @@
 
 using namespace rb;
 
+namespace rb {
+// bf16 streaming on the tensor-core engine (tc_engine.cu)
+int tc_stream_alloc(rb_handle* h);
+int tc_stream_reset(rb_handle* h, const int32_t* ids, int n);
+int tc_stream_run(rb_handle* h, int ob, int oe, int B, int F, const void* in, void* out, cudaStream_t s);
+int tc_stream_handoff(rb_handle* h, int B, int F, cudaStream_t s);
+}  // namespace rb
+
 namespace {
 
 int slot_view(rb_handle* h, int sl, int F, View* v) {
@@ -92,7 +100,7 @@ extern "C" {
 int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype) {
   RB_CHECK(h && max_streams > 0 && max_chunk > 0, RB_ERR_INVALID, "rb_stream_alloc: bad arguments");
   RB_CHECK(h->spec.streaming, RB_ERR_STATE, "model was not built with streaming=True");
-  RB_CHECK(dtype == RB_F32, RB_ERR_UNSUPPORTED, "streaming runs on the fp32 engine in this version");
+  RB_CHECK(dtype == RB_F32 || dtype == RB_BF16, RB_ERR_INVALID, "rb_stream_alloc: bad dtype");
   RB_CHECK(max_chunk % h->spec.samples_per_frame == 0, RB_ERR_INVALID,
            "chunk %d is not a multiple of the model ratio %d", max_chunk, h->spec.samples_per_frame);
   RB_CUDA(cudaSetDevice(h->device));
@@ -104,6 +112,12 @@ int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype) {
   h->max_streams = max_streams;
   h->max_frames = max_chunk / h->spec.samples_per_frame;
   h->stream_dtype = dtype;
+  if (dtype == RB_BF16) {
+    int rc = tc_stream_alloc(h);
+    if (rc) return rc;
+    h->stream_ready = true;
+    return RB_OK;
+  }
   for (int sl = 0; sl < ns; ++sl) {
     const rb_slot& s = h->slots[sl];
     if (sl == h->spec.noise_slot) continue;
@@ -120,6 +134,7 @@ int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype) {
 int rb_stream_reset(rb_handle* h, const int32_t* ids, int n) {
   RB_CHECK(h && h->stream_ready, RB_ERR_STATE, "streams are not allocated");
   RB_CUDA(cudaSetDevice(h->device));
+  if (h->stream_dtype == RB_BF16) return tc_stream_reset(h, ids, n);
   for (size_t sl = 0; sl < h->slots.size(); ++sl) {
     if (!h->sbuf[sl]) continue;
     const size_t row = (size_t)h->slots[sl].channels * h->s_ld[sl] * sizeof(float);
@@ -146,8 +161,12 @@ int rb_stream_encode(rb_handle* h, const void* x, int B, int n, void* z, void* s
   RB_CHECK(g.ok, RB_ERR_STATE, "rb_stream_* calls on one handle must be serialised");
   const long long before = g_launches;
   cudaStream_t s = (cudaStream_t)stream;
-  rc = copy_in(h, h->spec.enc_in_slot, (const float*)x, B, F, s);
-  if (!rc) rc = run_stream_ops(h, 0, h->spec.n_enc_ops, B, F, h->spec.enc_out_slot, (float*)z, s);
+  if (h->stream_dtype == RB_BF16) {
+    rc = tc_stream_run(h, 0, h->spec.n_enc_ops, B, F, x, z, s);
+  } else {
+    rc = copy_in(h, h->spec.enc_in_slot, (const float*)x, B, F, s);
+    if (!rc) rc = run_stream_ops(h, 0, h->spec.n_enc_ops, B, F, h->spec.enc_out_slot, (float*)z, s);
+  }
   h->launches += g_launches - before;
   return rc;
 }
@@ -160,8 +179,12 @@ int rb_stream_decode(rb_handle* h, const void* z, int B, int frames, void* y, vo
   RB_CHECK(g.ok, RB_ERR_STATE, "rb_stream_* calls on one handle must be serialised");
   const long long before = g_launches;
   cudaStream_t s = (cudaStream_t)stream;
-  rc = copy_in(h, h->spec.dec_in_slot, (const float*)z, B, frames, s);
-  if (!rc) rc = run_stream_ops(h, h->spec.n_enc_ops, h->spec.n_ops, B, frames, h->spec.dec_out_slot, (float*)y, s);
+  if (h->stream_dtype == RB_BF16) {
+    rc = tc_stream_run(h, h->spec.n_enc_ops, h->spec.n_ops, B, frames, z, y, s);
+  } else {
+    rc = copy_in(h, h->spec.dec_in_slot, (const float*)z, B, frames, s);
+    if (!rc) rc = run_stream_ops(h, h->spec.n_enc_ops, h->spec.n_ops, B, frames, h->spec.dec_out_slot, (float*)y, s);
+  }
   h->launches += g_launches - before;
   return rc;
 }
@@ -181,6 +204,13 @@ int rb_stream_step(rb_handle* h, const void* x, int B, int n, void* y, void* str
   RB_CHECK(g.ok, RB_ERR_STATE, "rb_stream_* calls on one handle must be serialised");
   const long long before = g_launches;
   cudaStream_t s = (cudaStream_t)stream;
+  if (h->stream_dtype == RB_BF16) {
+    rc = tc_stream_run(h, 0, h->spec.n_enc_ops, B, F, x, nullptr, s);
+    if (!rc) rc = tc_stream_handoff(h, B, F, s);
+    if (!rc) rc = tc_stream_run(h, h->spec.n_enc_ops, h->spec.n_ops, B, F, nullptr, y, s);
+    h->launches += g_launches - before;
+    return rc;
+  }
   rc = copy_in(h, h->spec.enc_in_slot, (const float*)x, B, F, s);
   if (!rc) rc = run_stream_ops(h, 0, h->spec.n_enc_ops, B, F, -1, nullptr, s);
   if (!rc) {

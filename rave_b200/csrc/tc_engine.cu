@@ -672,7 +672,7 @@ int tc_pack_weights(rb_handle* h) {
         if (rc) return rc;
       }
     }
-    if (!fuse && op.res < 0) {
+    if (!fuse && op.res < 0 && !h->spec.streaming) {   // (streaming keeps plain row views: history alignment)
       const int F = choose_row_batch(v, h->slots[op.dst].per_frame / v.fout);
       if (F > 1) batch_rows(v, F);
     }
@@ -880,6 +880,177 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
                    (__nv_bfloat16*)out + (size_t)b0 * out_ch * b.n, out_ch, nb);
     }
   }
+  return RB_OK;
+}
+
+}  // namespace rb
+
+// ------------------------------------------------------------------------- bf16 streaming
+// cached_conv semantics (scripts/export.py:542-594) on the tensor-core engine.  Same scheme as
+// the fp32 engine (stream.cu): every slot owns one persistent group-major buffer
+// [max_streams][Cp/8][hist + max rows][8] whose first `hist` rows are the left context its
+// consumers need (CachedPadding1d state of each conv, AlignBranches delay line, transposed-conv
+// overlap).  A step writes the new rows behind the context, runs the same kernels as the offline
+// path with lo = -hist (the TMA tensor map starts at the history rows), then rolls the tail of
+// each row window to the front.  hist is rounded up to 16 rows so that every strided / phase /
+// audio view of the slot stays aligned.
+namespace rb {
+namespace tc {
+
+__global__ void roll_gm_kernel(Buf b, int rows_per_stream_group, int n) {
+  // one CTA per (stream, channel group): rows [n, n + hist) -> [0, hist), 16-byte units
+  uint4* base = reinterpret_cast<uint4*>(b.p) + (size_t)blockIdx.x * rows_per_stream_group;
+  for (int r0 = 0; r0 < b.hist; r0 += blockDim.x) {
+    const int r = r0 + threadIdx.x;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (r < b.hist) v = base[r + n];
+    __syncthreads();
+    if (r < b.hist) base[r] = v;
+    __syncthreads();
+  }
+}
+__global__ void roll_audio_kernel(__nv_bfloat16* p, int ld, int hist, int n) {
+  __nv_bfloat16* base = p + (size_t)blockIdx.x * ld;
+  for (int r0 = 0; r0 < hist; r0 += blockDim.x) {
+    const int r = r0 + threadIdx.x;
+    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+    if (r < hist) v = base[r + n];
+    __syncthreads();
+    if (r < hist) base[r] = v;
+    __syncthreads();
+  }
+}
+__global__ void copy_gm_kernel(Buf src, Buf dst, int B) {
+  const size_t total = (size_t)B * dst.n * dst.cp;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    int b, t, c;
+    decode_gm(i, dst, b, t, c);
+    dst.p[eidx(dst, b, t, c)] = src.p[eidx(src, b, t, c)];
+  }
+}
+
+static Buf stream_buf(rb_handle* h, Plan* pl, int sl, int F) {
+  Buf b;
+  b.p = (__nv_bfloat16*)h->sbuf[sl];
+  b.cp = pl->cp[sl]; b.ld = h->s_ld[sl]; b.hist = h->s_hist[sl];
+  b.n = h->slots[sl].per_frame * F; b.lo = -b.hist;
+  return b;
+}
+
+}  // namespace tc
+
+int tc_stream_alloc(rb_handle* h) {
+  Plan* pl = (Plan*)h->tc;
+  RB_CHECK(pl, RB_ERR_STATE, "bf16 engine: weights are not packed");
+  const int ns = (int)h->slots.size();
+  for (int sl = 0; sl < ns; ++sl) {
+    const rb_slot& sd = h->slots[sl];
+    if (sl == h->spec.noise_slot) continue;
+    h->s_hist[sl] = (sd.hist + 15) & ~15;
+    h->s_ld[sl] = h->s_hist[sl] + ((sd.per_frame * h->max_frames + 15) & ~15);
+    const size_t bytes = (size_t)h->max_streams * pl->cp[sl] * h->s_ld[sl] * sizeof(__nv_bfloat16);
+    RB_CUDA(cudaMalloc(&h->sbuf[sl], bytes));
+    RB_CUDA(cudaMemset(h->sbuf[sl], 0, bytes));
+  }
+  return RB_OK;
+}
+
+int tc_stream_reset(rb_handle* h, const int32_t* ids, int n) {
+  Plan* pl = (Plan*)h->tc;
+  RB_CHECK(pl, RB_ERR_STATE, "bf16 engine: weights are not packed");
+  for (size_t sl = 0; sl < h->slots.size(); ++sl) {
+    if (!h->sbuf[sl]) continue;
+    const size_t row = (size_t)pl->cp[sl] * h->s_ld[sl] * sizeof(__nv_bfloat16);
+    if (!ids) {
+      RB_CUDA(cudaMemset(h->sbuf[sl], 0, row * h->max_streams));
+    } else {
+      for (int i = 0; i < n; ++i) {
+        RB_CHECK(ids[i] >= 0 && ids[i] < h->max_streams, RB_ERR_INVALID, "stream id %d out of range", ids[i]);
+        RB_CUDA(cudaMemset((char*)h->sbuf[sl] + row * ids[i], 0, row));
+      }
+    }
+  }
+  return RB_OK;
+}
+
+// Runs ops [ob, oe) of one program on the persistent buffers.  `in` (caller layout) is copied
+// behind the history of the program's input slot when given; `out` receives the program output.
+int tc_stream_run(rb_handle* h, int ob, int oe, int B, int F, const void* in, void* out, cudaStream_t s) {
+  Plan* pl = (Plan*)h->tc;
+  RB_CHECK(pl, RB_ERR_STATE, "bf16 engine: weights are not packed");
+  const int ns = (int)h->slots.size();
+  const bool is_enc = ob < h->spec.n_enc_ops;
+  const int in_slot = is_enc ? h->spec.enc_in_slot : h->spec.dec_in_slot;
+  const int out_slot = is_enc ? h->spec.enc_out_slot : h->spec.dec_out_slot;
+  std::vector<Buf> bufs(ns);
+  for (int sl = 0; sl < ns; ++sl)
+    if (h->sbuf[sl]) bufs[sl] = stream_buf(h, pl, sl, F);
+  if (in) {
+    const Buf& b = bufs[in_slot];
+    if (b.cp == 1) {
+      RB_CUDA(cudaMemcpy2DAsync(b.p + b.hist, (size_t)b.ld * 2, in, (size_t)b.n * 2, (size_t)b.n * 2, B,
+                                cudaMemcpyDeviceToDevice, s));
+    } else {
+      const int in_ch = h->slots[in_slot].channels;
+      RB_LAUNCH_EW(cf_to_gm_kernel, (size_t)B * b.n * b.cp, s, (const __nv_bfloat16*)in, b, in_ch, B);
+    }
+  }
+  const bool direct_out = out && pl->cp[out_slot] == 1 && h->s_hist[out_slot] == 0;
+  if (direct_out) {
+    Buf& b = bufs[out_slot];
+    b.p = (__nv_bfloat16*)out; b.ld = b.n; b.hist = 0; b.lo = 0;
+  }
+  const float* noise = nullptr;
+  int64_t noise_bstride = 0;
+  if (h->spec.noise_slot >= 0 && h->noise) {
+    const rb_slot& nsl = h->slots[h->spec.noise_slot];
+    noise_bstride = (int64_t)nsl.channels * nsl.per_frame * F;
+    RB_CHECK(h->noise_numel >= (int64_t)B * noise_bstride, RB_ERR_INVALID, "noise tensor too small");
+    noise = h->noise;
+  }
+  for (int i = ob; i < oe; ++i) {
+    if (pl->skip[i]) continue;
+    int rc = tc_exec_op(h, pl, i, bufs, B, noise, noise_bstride, s);
+    if (rc) return rc;
+  }
+  if (out && !direct_out) {
+    const Buf& b = bufs[out_slot];
+    if (b.cp == 1) {
+      RB_CUDA(cudaMemcpy2DAsync(out, (size_t)b.n * 2, b.p + b.hist, (size_t)b.ld * 2, (size_t)b.n * 2, B,
+                                cudaMemcpyDeviceToDevice, s));
+    } else {
+      const int out_ch = h->slots[out_slot].channels;
+      RB_LAUNCH_EW(gm_to_cf_kernel, (size_t)B * out_ch * b.n, s, b, (__nv_bfloat16*)out, out_ch, B);
+    }
+  }
+  // state update: every slot this program reads with history
+  std::vector<char> seen(ns, 0);
+  for (int i = ob; i < oe; ++i) {
+    const rb_op& op = h->ops[i];
+    const int used[3] = {op.src, op.res, op.src2};
+    for (int u : used) {
+      if (u < 0 || seen[u] || !h->sbuf[u] || h->s_hist[u] == 0 || u == h->spec.noise_slot) continue;
+      seen[u] = 1;
+      const Buf& b = bufs[u];
+      if (b.cp == 1) {
+        roll_audio_kernel<<<B, 256, 0, s>>>(b.p, b.ld, b.hist, b.n);
+      } else {
+        // streams [0, B) x groups are contiguous blocks of ld rows
+        roll_gm_kernel<<<B * (b.cp / 8), 128, 0, s>>>(b, b.ld, b.n);
+      }
+      RB_CUDA(cudaGetLastError());
+      ++g_launches;
+    }
+  }
+  return RB_OK;
+}
+
+// latent hand-over of rb_stream_step: encoder output slot -> decoder input slot (behind its history)
+int tc_stream_handoff(rb_handle* h, int B, int F, cudaStream_t s) {
+  Plan* pl = (Plan*)h->tc;
+  const Buf src = stream_buf(h, pl, h->spec.enc_out_slot, F), dst = stream_buf(h, pl, h->spec.dec_in_slot, F);
+  RB_CHECK(src.cp == dst.cp, RB_ERR_INVALID, "encoder output and decoder input widths differ");
+  RB_LAUNCH_EW(copy_gm_kernel, (size_t)B * dst.n * dst.cp, s, src, dst, B);
   return RB_OK;
 }
 

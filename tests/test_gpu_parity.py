@@ -198,3 +198,25 @@ def test_offline_bf16_matches_golden(name):
     assert rel_l2(y.float().cpu().numpy(), a["y"]) < tol_y
     y2 = m(x)
     assert rel_l2(y2.float().cpu().numpy(), a["y"]) < (tol_f if name in BF16_CHAOTIC else 2 * BF16_TOL)
+
+
+@pytest.mark.parametrize("name", [n for n in GIN if n not in ("v2noise_c8", "v2_c64") + BF16_CHAOTIC])
+def test_streaming_bf16_matches_golden_chunk_by_chunk(name):
+    """cached_conv streaming on the bf16 tensor-core engine: chunk-by-chunk outputs against the
+    oracle's fp32 streaming run (same bar as the offline bf16 path)."""
+    m, meta, a = _model(name, streaming=True, dtype=torch.bfloat16)
+    x = torch.from_numpy(golden_input(a)).cuda().bfloat16()
+    n = int(a["chunk"].item())
+    zs, ys, ys2 = [], [], []
+    zg = torch.from_numpy(a["z_stream"]).cuda().bfloat16()
+    fpc = zg.shape[-1] // (x.shape[-1] // n)
+    for c in range(x.shape[-1] // n):
+        zs.append(m.encode(x[..., c * n:(c + 1) * n].contiguous()))
+        ys.append(m.decode(zg[..., c * fpc:(c + 1) * fpc].contiguous()))   # decoder fed the oracle's latents
+    assert rel_l2(torch.cat(zs, -1).float().cpu().numpy(), a["z_stream"]) < BF16_TOL
+    assert rel_l2(torch.cat(ys, -1).float().cpu().numpy(), a["y_stream"]) < 1.2 * BF16_TOL
+    # whole-step entry (rb_stream_step) on fresh state: encode -> decode with the latent kept on device
+    m.reset_streams()
+    for c in range(x.shape[-1] // n):
+        ys2.append(m(x[..., c * n:(c + 1) * n].contiguous()))
+    assert rel_l2(torch.cat(ys2, -1).float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
