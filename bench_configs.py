@@ -1,0 +1,122 @@
+#!/usr/bin/env python
+"""Secondary measurements for BASELINE.json configs[2..4] (bench.py carries the headline line):
+
+  C3  v2 causal streaming, 2048-sample chunks, 1024 concurrent streams, state resident across chunks
+  C4  discrete config: RVQ encode (bit-exact indices are a test) + decode-from-indices throughput
+  C5  v3 (Snake + AdaIN) batched decode-only from latents
+
+One JSON line per leg on stdout.  Synthetic weights (name-keyed recipe), CUDA-event timing.
+C4 / C5 use the CAPACITY=8 fixtures' parameter lists (the only discrete / v3 name lists committed),
+C3 the CAPACITY=64 v2 list.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+SR = 44100
+
+
+def _sd(name):
+    from tests.util import golden_state_dict, load_golden
+    meta, _ = load_golden(name)
+    return meta, golden_state_dict(meta)
+
+
+def _time(fn, warmup, steps):
+    import torch
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps
+
+
+def c3(args):
+    import torch
+    from rave_b200 import RAVE
+    from oracle.weights_recipe import recipe_input
+    _, sd = _sd("v2_c64")
+    out = []
+    for dtype, tag in ((torch.bfloat16, "bf16"), (torch.float32, "f32")):
+        m = RAVE.from_gin(["v2.gin", "causal.gin"], streaming=True, dtype=dtype)
+        m.load_state_dict(sd)
+        B, n = args.streams, 2048
+        m.alloc_streams(B, n)
+        x = torch.from_numpy(recipe_input((64, 1, n), 99)).cuda().repeat(B // 64, 1, 1).contiguous().to(dtype)
+        l0 = m.kernel_launches()
+        ms = _time(lambda: m(x), 8, args.steps)
+        out.append({"config": "C3 v2 causal streaming, %d streams x 2048-sample chunks, CAPACITY=64" % B,
+                    "dtype": tag, "ms_per_step": ms, "value": B * n / SR / (ms / 1e3), "unit": "audio-sec/sec",
+                    "real_time_factor_per_stream": (n / SR) / (ms / 1e3),
+                    "state_elements_per_stream": m.stream_state_elements(),
+                    "launches_per_step": (m.kernel_launches() - l0) // (8 + args.steps)})
+        del m
+    return out
+
+
+def c4(args):
+    import torch
+    from rave_b200 import RAVE
+    from oracle.weights_recipe import recipe_input
+    meta, sd = _sd("discrete_c8")
+    m = RAVE.from_gin(["discrete.gin"], ["CAPACITY=8"], dtype=torch.bfloat16)
+    m.load_state_dict(sd)
+    B, T = args.batch, 2 ** 18
+    x = torch.from_numpy(recipe_input((64, 1, T), 7)).cuda().repeat(B // 64, 1, 1).contiguous().bfloat16()
+    z = m.encode(x)
+    nl = m.latent_size
+    zl = z[:, :nl].float().contiguous()
+    idx = m.encoder.rvq.encode(zl)
+    ms_enc = _time(lambda: m.encoder.rvq.encode(zl), 3, args.steps)
+
+    def dec():
+        zq = m.encoder.rvq.decode(idx)
+        zz = z.clone()
+        zz[:, :nl] = zq.to(z.dtype)
+        return m.decode(zz)
+
+    ms_dec = _time(dec, 3, args.steps)
+    return [{"config": "C4 discrete (RVQ %dx%d, dim %d), CAPACITY=8, %d streams x 2^18" %
+                       (idx.shape[1], m.spec.rvq["codebook_size"], nl, B),
+             "dtype": "bf16 net / fp32 RVQ", "rvq_encode_ms": ms_enc, "vectors": int(B * idx.shape[2]),
+             "rvq_encode_Mvec_per_s": B * idx.shape[2] / ms_enc / 1e3,
+             "decode_from_indices_ms": ms_dec, "value": B * T / SR / (ms_dec / 1e3), "unit": "audio-sec/sec (decode)"}]
+
+
+def c5(args):
+    import torch
+    from rave_b200 import RAVE
+    meta, sd = _sd("v3_c8")
+    m = RAVE.from_gin(["v3.gin"], ["CAPACITY=8"], dtype=torch.bfloat16)
+    m.load_state_dict(sd)
+    B, F = min(args.batch, 64), 256       # AdaIN statistics rows: cc.MAX_BATCH_SIZE = 64 streams
+    g = torch.Generator(device="cuda").manual_seed(5)
+    z = torch.randn(B, m.spec.dec_latent_size, F, generator=g, device="cuda").bfloat16()
+    ms = _time(lambda: m.decode(z), 3, args.steps)
+    T = F * m.spec.samples_per_frame
+    return [{"config": "C5 v3 (Snake + AdaIN) decode-only, CAPACITY=8, %d streams x %d frames" % (B, F),
+             "dtype": "bf16", "ms_per_step": ms, "value": B * T / SR / (ms / 1e3), "unit": "audio-sec/sec (decode)"}]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--legs", default="c3,c4,c5")
+    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--streams", type=int, default=1024)
+    ap.add_argument("--batch", type=int, default=512)
+    args = ap.parse_args()
+    for leg in args.legs.split(","):
+        for row in {"c3": c3, "c4": c4, "c5": c5}[leg](args):
+            print(json.dumps(row), flush=True)
+
+
+if __name__ == "__main__":
+    main()
