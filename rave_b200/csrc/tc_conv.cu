@@ -78,7 +78,9 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 }
 
 // debug event trace (CTA 0, first 64 work items): see tools_trace.py
-#define TRACE(tile, ev) do { if (p.trace && blockIdx.x == 0 && (tile) < 64u && (threadIdx.x & 31) == 0) \
+// `tmask` (in scope at every use) is 0 for lane 0 of CTA 0 when tracing is on, else all ones: one
+// compare per site in production runs
+#define TRACE(tile, ev) do { if (((tile) | tmask) < 64u) \
     p.trace[(tile) * 16u + (ev)] = (unsigned long long)clock64(); } while (0)
 
 struct Work {
@@ -267,6 +269,94 @@ __device__ __forceinline__ int goff32(const TcView& v, int g) {
   return lo * v.sA + hi * v.sB;
 }
 
+// The common case of drain() below, with the address arithmetic hoisted out of the chunk loop:
+// NT a multiple of 32, channel groups of a chunk sA apart in y (and in the residual), no waveform
+// head, no sign mask.  RES: 0 none, 1 global (L2-prefetched), 2 the A tile in smem (fused unit).
+template <int RES>
+__device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
+                                           const float* bs, const Work& wk, int rit, int part, int nparts, int ch0,
+                                           int MTn, int NT, const uint8_t* res_s, uint32_t tr) {
+  constexpr uint32_t tmask = 0;
+  const int row = wk.t0 + rit;
+  const int cstep = nparts * 32;
+  // per-thread offsets in 16-byte units from the (warp-uniform) tensor bases: 32 bits cover 64 GB
+  const uint32_t yoff = (uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT);
+  const uint32_t roff = RES == 1 ? (uint32_t)((long long)wk.b * p.res.sb) +
+                                       (uint32_t)((p.res.hist - p.res_delay + row) * p.res.sT)
+                                 : 0u;
+  uint4* const ybase = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p));
+  const uint4* const rbase = reinterpret_cast<const uint4*>(p.res.p);
+  const uint4* const srow = RES == 2 ? reinterpret_cast<const uint4*>(res_s) + (rit + p.off) : nullptr;
+  uint4 rr[4];
+  auto load_rr = [&](int mt, int c0) {
+    if (RES == 1) {
+      if (row + mt * 128 >= p.y.n) return;
+      const uint32_t o = roff + (uint32_t)(mt * 128 * p.res.sT + goff32(p.res, (ch0 + c0) >> 3));
+#pragma unroll
+      for (int q = 0; q < 4; ++q) rr[q] = __ldg(rbase + (o + (uint32_t)(q * p.res.sA)));
+    }
+  };
+  int mt = 0, c0 = part * 32;
+  if (c0 >= NT) mt = MTn;
+  if (RES == 1 && (rit & 7) == 0) {
+    // pull this warp's residual rows into L2 while the MMAs of this work item run (see drain())
+    for (int pm = 0; pm < MTn && row + pm * 128 < p.y.n; ++pm)
+      for (int pc = part * 32; pc < NT; pc += cstep) {
+        const uint32_t o = roff + (uint32_t)(pm * 128 * p.res.sT + goff32(p.res, (ch0 + pc) >> 3));
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(rbase + (o + (uint32_t)(q * p.res.sA))));
+      }
+  }
+  if (RES == 1 && mt < MTn) load_rr(mt, c0);
+  mbar_wait(bar_full, parity);
+  tc_fence_after();
+  TRACE(tr, 12);
+  while (mt < MTn) {
+    int mtn = mt, c0n = c0 + cstep;
+    if (c0n >= NT) { c0n = part * 32; ++mtn; }
+    if (RES == 2) {                                         // the stage is certainly full by now
+      const uint4* sp = srow + ((ch0 + c0) >> 3) * p.R_ALLOC;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) rr[q] = sp[q * p.R_ALLOC];
+    }
+    float v[32];
+    load_acc<32>(tbase + (uint32_t)(mt * NT + c0), bs + ch0 + c0, v);
+    TRACE(tr, 13);
+    const bool valid = row + mt * 128 < p.y.n;
+    if (RES != 0 && valid) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint4 r4 = rr[q];
+        const uint32_t w[4] = {r4.x, r4.y, r4.z, r4.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
+          if (p.res_act) {                                  // stored as leaky(x): x = min(z, 5 z), exact in fp32
+            float l5, h5;
+            mul2(l5, h5, lo, hi, 5.f, 5.f);
+            lo = fminf(lo, l5);
+            hi = fminf(hi, h5);
+          }
+          add2(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1], lo, hi);
+        }
+      }
+    }
+    if (RES == 1 && mtn < MTn) load_rr(mtn, c0n);           // next chunk's residual, in flight during the stores
+    if (valid) {
+      if (p.out_act) leaky_n<32>(v);
+      TRACE(tr, 14);
+      const uint32_t o = yoff + (uint32_t)(mt * 128 * p.y.sT + goff32(p.y, (ch0 + c0) >> 3));
+#pragma unroll
+      for (int q = 0; q < 4; ++q) ybase[o + (uint32_t)(q * p.y.sA)] = pack8(v + q * 8);
+    }
+    mt = mtn;
+    c0 = c0n;
+  }
+  TRACE(tr, 15);
+  tc_fence_before();
+}
+
 // Drains part `part` of `nparts` of the 32-column chunks of `MTn` sub-tiles x `NT` accumulator
 // columns (TMEM address `tbase`, lane base included) into y at channel offset ch0: accumulator
 // + bias (+ residual) -> sign mask / output activation -> bf16 -> 16-byte stores.  The residual
@@ -275,6 +365,7 @@ __device__ __forceinline__ int goff32(const TcView& v, int g) {
 __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                       const float* bs, const Work& wk, int rit, int part, int nparts, int ch0,
                                       int MTn, int NT, const uint8_t* res_s = nullptr, uint32_t tr = 0xffffffffu) {
+  constexpr uint32_t tmask = 0;                             // `tr` already carries the trace mask
   const bool has_res = p.res.p != nullptr;
   const uint4* rs = reinterpret_cast<const uint4*>(p.res.p) + (long long)wk.b * p.res.sb;
   uint4* ys = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) + (long long)wk.b * p.y.sb;
@@ -416,7 +507,10 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
 #define COMMIT(bar) do { if (leader) mma_commit(bar); } while (0)
 
 
-template <int PRE, int ACT2, bool FUSED>
+// DR: how accumulators are drained -- 0 generic drain(), 1 drain_fast (global or no residual),
+// 2 drain_fast with the residual read from the A tile in smem (fused only).  One drain per
+// instantiation keeps every variant inside the 96-register budget without spills.
+template <int PRE, int ACT2, bool FUSED, int DR>
 __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams p,
                                                                 const __grid_constant__ TcTmap tmx) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -434,6 +528,7 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t tmask = (p.trace && blockIdx.x == 0 && lane == 0) ? 0u : 0xffffffffu;
   // Programmatic dependent launch: let the next kernel of the stream start its prologue on SMs
   // this grid has already left; everything that touches activations waits below.
   asm volatile("griddepcontrol.launch_dependents;");
@@ -732,78 +827,100 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
         const Work wk = wi.work(p);
         const uint32_t sd = rd.idx, phd = rd.ph;
         if (warp == 0) TRACE(ti, 8);
-        drain(p, BAR(BAR_D_FULL + sd), phd, tmem + lane_base + sd * d_stage_cols, bias_s, wk, rit, part,
-              OUT_PARTS, wk.nt * p.N_TILE, p.MT, p.N_TILE, nullptr, warp == 0 ? ti : 0xffffffffu);
+        const uint32_t trc = (warp == 0 ? ti : 0xffffffffu) | tmask;
+        const uint32_t tb = tmem + lane_base + sd * d_stage_cols;
+        if (DR == 0)
+          drain(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
+                p.N_TILE, nullptr, trc);
+        else if (p.res.p)
+          drain_fast<1>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
+                        p.N_TILE, nullptr, trc);
+        else
+          drain_fast<0>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
+                        p.N_TILE, nullptr, trc);
         mbar_arrive(BAR(BAR_D_EMPTY + sd));
         if (warp == 0) TRACE(ti, 9);
       }
     } else {
       // Fused unit.  E1(i): h = act2(D1 + bias) -> smem (A operand of the 1x1 conv);
       // E2(i): y = D2 + bias2 + x.  Without an activation pass the 16 output warps form two
-      // sets that alternate: set s runs E1 on tiles = s (mod 2) and E2 on the other tiles, so
-      // both sets carry the same load; otherwise warps 0-7 run E1 and warps 8-11 run E2.
+      // sets that alternate: set s runs E1 on tiles = s (mod 2) and, after each, E2 on the tile
+      // before it, so both sets carry the same load; otherwise warps 0-7 run E1 and 8-11 run E2.
       constexpr bool ALT = PRE == RB_ACT_NONE;
-      const int set = ALT ? (warp >> 3) : 0;
-      const int step = ALT ? 2 : 1;
       const int part = ALT ? ((warp >> 2) & 1) : (warp < E1_WARPS ? (warp >> 2) : 0);
       const bool tr_warp = (warp & 7) == 0;
-      struct TileIt {
-        WorkIter wi;
-        Ring rd, rh, ra;
-        uint32_t ti;
-      } e1, e2;
-      auto start = [&](TileIt& it, int first, bool active) {
-        it.wi.init(p);
-        it.ti = 0;
-        if (!active) it.wi.left = 0;
-        for (int k = 0; k < first && it.wi.left > 0; ++k) {
-          it.wi.next(p); it.rd.next(p.SD); it.rh.next(p.SH); it.ra.next(p.SA); ++it.ti;
+      // E1 of local tile `ti` (ring positions rd / rh of that tile)
+      auto run_e1 = [&](const Ring& rd_, const Ring& rh_, uint32_t ti) {
+        const uint32_t sd = rd_.idx, sh = rh_.idx;
+        mbar_wait(BAR(BAR_D_FULL + sd), rd_.ph);
+        if (tr_warp) TRACE(ti, 6);
+        mbar_wait(BAR(BAR_H_EMPTY + sh), rh_.ph ^ 1);
+        tc_fence_after();
+        uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
+        for (int c0 = part * 32; c0 < C2; c0 += E1_PARTS * 32) {
+          const uint32_t taddr = tmem + lane_base + sd * d_stage_cols + (uint32_t)c0;
+          if (C2 - c0 >= 32) h_chunk<ACT2, 32>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
+          else h_chunk<ACT2, 16>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
         }
+        fence_proxy_async();
+        tc_fence_before();
+        mbar_arrive(BAR(BAR_H_FULL + sh));
+        mbar_arrive(BAR(BAR_D_EMPTY + sd));
+        if (tr_warp) TRACE(ti, 7);
       };
-      auto advance = [&](TileIt& it) {
-        for (int k = 0; k < step; ++k) {
-          it.wi.next(p); it.rd.next(p.SD); it.rh.next(p.SH); it.ra.next(p.SA); ++it.ti;
+      // E2 of the tile at work position wk (ring positions rd_ / ra_ of that tile)
+      auto run_e2 = [&](const Work& wk, const Ring& rd_, const Ring& ra_, uint32_t ti) {
+        const uint32_t sd = rd_.idx, sa = ra_.idx;
+        if (tr_warp) TRACE(ti, 8);
+        const uint32_t trc = (tr_warp ? ti : 0xffffffffu) | tmask;
+        const uint32_t tb = tmem + lane_base + sd * d_stage_cols + (uint32_t)C2;
+        const uint8_t* rs = p.res_smem ? a_smem + (size_t)sa * p.a_stage_bytes : nullptr;
+        if (DR == 0)
+          drain(p, BAR(BAR_D2_FULL + sd), rd_.ph, tb, bias2_s, wk, rit, part, OUT_PARTS, 0, 1, C2, rs, trc);
+        else if (DR == 2)
+          drain_fast<2>(p, BAR(BAR_D2_FULL + sd), rd_.ph, tb, bias2_s, wk, rit, part, OUT_PARTS, 0, 1, C2, rs, trc);
+        else
+          drain_fast<1>(p, BAR(BAR_D2_FULL + sd), rd_.ph, tb, bias2_s, wk, rit, part, OUT_PARTS, 0, 1, C2, rs, trc);
+        mbar_arrive(BAR(BAR_D2_EMPTY + sd));
+        if (p.res_smem) {                                   // this warp no longer needs the A stage
+          __syncwarp();
+          if (lane == 0) mbar_arrive(BAR(BAR_A_EMPTY + sa));
         }
+        if (tr_warp) TRACE(ti, 9);
       };
-      start(e1, ALT ? set : 0, ALT || warp < E1_WARPS);
-      start(e2, ALT ? 1 - set : 0, ALT || warp >= E1_WARPS);
-      bool first = true;
-      while (e1.wi.left > 0 || e2.wi.left > 0) {
-        if (e1.wi.left > 0) {
-          const uint32_t sd = e1.rd.idx, sh = e1.rh.idx;
-          mbar_wait(BAR(BAR_D_FULL + sd), e1.rd.ph);
-          if (tr_warp) TRACE(e1.ti, 6);
-          mbar_wait(BAR(BAR_H_EMPTY + sh), e1.rh.ph ^ 1);
-          tc_fence_after();
-          uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
-          for (int c0 = part * 32; c0 < C2; c0 += E1_PARTS * 32) {
-            const uint32_t taddr = tmem + lane_base + sd * d_stage_cols + (uint32_t)c0;
-            if (C2 - c0 >= 32) h_chunk<ACT2, 32>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
-            else h_chunk<ACT2, 16>(taddr, bias_s + c0, alpha2_s + c0, hb + (size_t)(c0 >> 3) * 2048);
-          }
-          fence_proxy_async();
-          tc_fence_before();
-          mbar_arrive(BAR(BAR_H_FULL + sh));
-          mbar_arrive(BAR(BAR_D_EMPTY + sd));
-          if (tr_warp) TRACE(e1.ti, 7);
-          advance(e1);
+      Ring ra;                                              // A stage of a tile (one chunk per tile when res_smem)
+      wi.init(p);
+      if (ALT) {
+        // one iterator: the E2 tile of an iteration is the tile passed over while stepping from
+        // one E1 tile to the next
+        const int set = warp >> 3;
+        const int n = wi.left;
+        Ring rd2, ra2;
+        Work mid{0, 0, 0};
+        bool have_e2 = false;
+        int ti = 0;
+        auto step = [&]() { wi.next(p); rd.next(p.SD); rh.next(p.SH); ra.next(p.SA); };
+        if (set == 1 && n > 0) {
+          mid = wi.work(p); rd2 = rd; ra2 = ra; have_e2 = true;
+          step();
+          ti = 1;
         }
-        if (e2.wi.left > 0 && !(ALT && set == 0 && first)) {
-          const Work wk = e2.wi.work(p);
-          const uint32_t sd = e2.rd.idx, sa = e2.ra.idx;
-          if (tr_warp) TRACE(e2.ti, 8);
-          drain(p, BAR(BAR_D2_FULL + sd), e2.rd.ph, tmem + lane_base + sd * d_stage_cols + (uint32_t)C2, bias2_s,
-                wk, rit, part, OUT_PARTS, 0, 1, C2, p.res_smem ? a_smem + (size_t)sa * p.a_stage_bytes : nullptr,
-                tr_warp ? e2.ti : 0xffffffffu);
-          mbar_arrive(BAR(BAR_D2_EMPTY + sd));
-          if (p.res_smem) {                                 // this warp no longer needs the A stage
-            __syncwarp();
-            if (lane == 0) mbar_arrive(BAR(BAR_A_EMPTY + sa));
+        while (ti < n || have_e2) {
+          if (ti < n) run_e1(rd, rh, (uint32_t)ti);
+          if (have_e2) run_e2(mid, rd2, ra2, (uint32_t)(ti - 1));
+          have_e2 = false;
+          if (ti + 1 < n) {
+            step();
+            mid = wi.work(p); rd2 = rd; ra2 = ra; have_e2 = true;
+            step();
           }
-          if (tr_warp) TRACE(e2.ti, 9);
-          advance(e2);
+          ti += 2;
         }
-        first = false;
+      } else if (warp < E1_WARPS) {
+        for (uint32_t ti = 0; wi.left > 0; wi.next(p), rd.next(p.SD), rh.next(p.SH), ++ti) run_e1(rd, rh, ti);
+      } else {
+        for (uint32_t ti = 0; wi.left > 0; wi.next(p), rd.next(p.SD), ra.next(p.SA), ++ti)
+          run_e2(wi.work(p), rd, ra, ti);
       }
     }
   }
@@ -816,11 +933,11 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
   }
 }
 
-template <int PRE, int ACT2, bool FUSED>
+template <int PRE, int ACT2, bool FUSED, int DR>
 static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED, DR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024));
     attr_set = true;
   }
@@ -835,7 +952,7 @@ static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStr
   attr.val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
-  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED>, p, tm));
+  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR>, p, tm));
   return RB_OK;
 }
 
@@ -900,15 +1017,30 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
   int rc = make_tmap(p, &tm);
   if (rc) return rc;
   rc = RB_ERR_UNSUPPORTED;
+  // drain_fast: whole 32-column chunks whose four channel groups sit sA apart, plain stores
+  const bool fast = !p.head && !p.out_mask && (p.N_TILE & 31) == 0 && (p.y.G1 & 3) == 0 &&
+                    (p.res.p == nullptr || p.res_smem || (p.res.G1 & 3) == 0);
   if (!p.fused) {
-    if (p.pre_act == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false>(p, tm, grid, s);
-    else if (p.pre_act == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_NONE, false>(p, tm, grid, s);
-    else if (p.pre_act == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_NONE, false>(p, tm, grid, s);
+    if (p.pre_act == RB_ACT_NONE) {
+      rc = fast ? launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 1>(p, tm, grid, s)
+                : launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 0>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_LEAKY) {
+      rc = launch_variant<RB_ACT_LEAKY, RB_ACT_NONE, false, 0>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_SNAKE) {
+      rc = launch_variant<RB_ACT_SNAKE, RB_ACT_NONE, false, 0>(p, tm, grid, s);
+    }
   } else {
-    if (p.pre_act == RB_ACT_LEAKY && p.act2 == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_LEAKY, RB_ACT_LEAKY, true>(p, tm, grid, s);
-    else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_LEAKY) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true>(p, tm, grid, s);
-    else if (p.pre_act == RB_ACT_SNAKE && p.act2 == RB_ACT_SNAKE) rc = launch_variant<RB_ACT_SNAKE, RB_ACT_SNAKE, true>(p, tm, grid, s);
-    else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_NONE) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, true>(p, tm, grid, s);
+    if (p.pre_act == RB_ACT_LEAKY && p.act2 == RB_ACT_LEAKY) {
+      rc = launch_variant<RB_ACT_LEAKY, RB_ACT_LEAKY, true, 0>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_LEAKY) {
+      if (fast && p.res.p && p.res_smem) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 2>(p, tm, grid, s);
+      else if (fast && p.res.p) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 1>(p, tm, grid, s);
+      else rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 0>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_SNAKE && p.act2 == RB_ACT_SNAKE) {
+      rc = launch_variant<RB_ACT_SNAKE, RB_ACT_SNAKE, true, 0>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_NONE) {
+      rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, true, 0>(p, tm, grid, s);
+    }
   }
   if (rc == RB_ERR_UNSUPPORTED) {
     set_error("tc conv: activation combination (%d, %d, fused=%d) has no kernel variant", p.pre_act, p.act2, p.fused);

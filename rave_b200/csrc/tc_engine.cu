@@ -391,6 +391,11 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     RB_CHECK(resident || !L.fused, RB_ERR_UNSUPPORTED, "fused unit does not fit in shared memory");
     p.w_resident = resident ? 1 : 0;
     p.MT = (!resident && p.y.n >= 256) ? 2 : 1;
+    if (const char* e = getenv("RB_TC_MT1")) {           // experiments only
+      const int m = atoi(e);
+      if (m == 1 && L.N_TILE == 256) p.MT = 1;
+      if (m == 2 && L.N_TILE == 256 && L.n_taps * L.n_kchunks <= 8) p.MT = 1;
+    }
     p.R = p.MT * 128 + halo;
     {
       // TMA boxes of the A tile: whole chunk in one box when the rows fit a box (<= 256), else
