@@ -164,6 +164,16 @@ __device__ __forceinline__ void issue_a_tma(const TcParams& p, const void* tmap,
   mbar_expect_tx(bar, p.a_tx_bytes);
   const int c8n = p.KC >> 3;
   const int kg0 = kc * c8n;
+  if (p.a_flat && row0 >= p.x.lo && row0 + p.R_ALLOC <= p.x.n) {
+    // interior tile of a unit-stride view: the rows of one channel group are one contiguous run
+    // in HBM and in the smem tile, so a linear bulk copy per group replaces the tensor box (whose
+    // 16-byte inner dimension caps the TMA unit at ~32 B/clk); edge tiles keep the zero-filling box
+    const uint4* src = reinterpret_cast<const uint4*>(p.x.p) + ((long long)b * p.x.sb + (p.x.hist + row0));
+    const uint32_t gbytes = (uint32_t)p.R_ALLOC * 16u;
+    for (int g = 0; g < c8n; ++g)
+      bulk_g2s(stage + (uint32_t)g * gbytes, src + group_off(p.x, kg0 + g), gbytes, bar);
+    return;
+  }
   const int row = row0 - p.x.lo;
   for (int g = 0; g < c8n; g += p.a_gb) {
     const int vg = kg0 + g;
@@ -626,18 +636,10 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
         }
       }
     }
-  } else if (warp == W_WPROD) {
-    // =========================================================== W producer (one thread)
+  } else if (warp == W_WPROD && !p.w_resident) {
+    // ============================================== W producer (one thread, streamed weights)
     if (lane == 0) {
-      if (p.w_resident) {
-        const uint32_t total = (uint32_t)p.nt_base[p.n_ntiles] * p.w_blk_bytes +
-                               (FUSED ? (uint32_t)(C2 / p.KC) * p.w_blk_bytes : 0u);
-        mbar_expect_tx(BAR(BAR_W_FULL), total);
-        for (uint32_t o = 0; o < total; o += 32768u) {
-          const uint32_t n = total - o < 32768u ? total - o : 32768u;
-          bulk_g2s(smem_u32(w_smem + o), reinterpret_cast<const uint8_t*>(p.w) + o, n, BAR(BAR_W_FULL));
-        }
-      } else {
+      {
         Ring rw;
         WorkIter wi;
         for (wi.init(p); wi.left > 0; wi.next(p)) {
@@ -660,8 +662,21 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
         }
       }
     }
-  } else if (warp == W_MMA || warp == W_MMA2) {
+  } else if (warp == W_MMA || warp == W_MMA2 || warp == W_WPROD) {
     // ====================================== MMA issuer (warp-uniform control, elected lane issues)
+    // Resident weights: the W producer warp loads them once; for narrow layers (dual_g1) it then
+    // issues GEMM1 of the odd local tiles (W_MMA takes the even ones): there the serial issue
+    // stream of one warp, sharing its scheduler with four output warps, bounds the tile rate.
+    if (warp == W_WPROD && lane == 0) {
+      const uint32_t total = (uint32_t)p.nt_base[p.n_ntiles] * p.w_blk_bytes +
+                             (FUSED ? (uint32_t)(C2 / p.KC) * p.w_blk_bytes : 0u);
+      mbar_expect_tx(BAR(BAR_W_FULL), total);
+      for (uint32_t o = 0; o < total; o += 32768u) {
+        const uint32_t n = total - o < 32768u ? total - o : 32768u;
+        bulk_g2s(smem_u32(w_smem + o), reinterpret_cast<const uint8_t*>(p.w) + o, n, BAR(BAR_W_FULL));
+      }
+    }
+    __syncwarp();
     {
       const bool leader = elect_one();
       const uint32_t idesc = make_idesc_bf16(128, p.N_TILE);
@@ -807,11 +822,26 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
       };
       // GEMM1 and GEMM2 are issued by two different warps: each is a serial instruction stream
       // (waits, descriptor set-up, commits), and for narrow units that stream is the bottleneck.
+      // the rings of a GEMM1 tile issued by the other warp: same advances, no instructions
+      auto skip1 = [&](const Work& wk) {
+        rd1.next(p.SD);
+        const uint64_t* mrow = mask_s + wk.nt * p.n_kchunks;
+        for (int kc = 0; kc < p.n_kchunks; ++kc)
+          if (mrow[kc] != 0) ra.next(p.SA);
+        ++t1;
+      };
       WorkIter wi;
-      if (warp == W_MMA) {
-        for (wi.init(p); wi.left > 0; wi.next(p)) gemm1(wi.work(p));
-      } else if (FUSED) {
-        for (wi.init(p); wi.left > 0; wi.next(p)) gemm2();
+      if (warp == W_MMA2) {
+        if (FUSED)
+          for (wi.init(p); wi.left > 0; wi.next(p)) gemm2();
+      } else if (!p.dual_g1) {
+        if (warp == W_MMA)
+          for (wi.init(p); wi.left > 0; wi.next(p)) gemm1(wi.work(p));
+      } else {
+        bool mine = warp == W_MMA;
+        for (wi.init(p); wi.left > 0; wi.next(p), mine = !mine) {
+          if (mine) gemm1(wi.work(p)); else skip1(wi.work(p));
+        }
       }
     }
   } else {

@@ -60,9 +60,11 @@ struct TcParams {
   int MT;                   // 128-row sub-tiles per work item (1 or 2)
   int R, R_ALLOC;           // A rows per stage (MT*128 + max shift), allocated (odd)
   int w_resident;           // all blocks live in smem for the whole kernel
+  int dual_g1;              // resident + narrow: two warps issue GEMM1 of alternate work items
   // A tile TMA boxes (tensor map over the input view, see launch_tc_conv): a chunk of KC/8
   // channel groups x R_ALLOC rows is fetched as boxes of a_gb groups x a_box_rows rows
   int a_gb, a_box_rows, a_rsplit;
+  int a_flat;               // unit-stride view: interior tiles are fetched as linear bulk copies per group
   uint32_t a_tx_bytes;      // bytes one chunk adds to its mbarrier
   int step_nt, step_b, step_tile;   // work-item increment of a persistent CTA (grid stride, decomposed)
   int SA, SW, SD;           // A stages, W stages (streamed), accumulator stages

@@ -390,6 +390,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     if (attempt == 0 && !resident) continue;
     RB_CHECK(resident || !L.fused, RB_ERR_UNSUPPORTED, "fused unit does not fit in shared memory");
     p.w_resident = resident ? 1 : 0;
+    p.dual_g1 = (resident && L.N_TILE <= 64 && !getenv("RB_TC_NODUAL")) ? 1 : 0;
     p.MT = (!resident && p.y.n >= 256) ? 2 : 1;
     if (const char* e = getenv("RB_TC_MT1")) {           // experiments only
       const int m = atoi(e);
@@ -415,6 +416,11 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       }
       RB_CHECK(p.a_box_rows <= 256, RB_ERR_UNSUPPORTED, "A tile of %d rows exceeds two TMA boxes", p.R);
       p.a_tx_bytes = (uint32_t)c8n * p.R_ALLOC * 16u;
+      {
+        int flat_min = 0;
+        if (const char* e = getenv("RB_TC_FLATMIN")) flat_min = atoi(e);   // experiments only
+        p.a_flat = (p.x.sT == 1 && p.R_ALLOC >= flat_min) ? 1 : 0;
+      }
     }
     p.a_stage_bytes = (uint32_t)(L.KC / 8) * p.R_ALLOC * 16u;
     // W ring depth: a single-tap layer consumes one A chunk per W block, so it needs A stages in
