@@ -168,10 +168,16 @@ __device__ __forceinline__ void issue_a_tma(const TcParams& p, const void* tmap,
     // interior tile of a unit-stride view: the rows of one channel group are one contiguous run
     // in HBM and in the smem tile, so a linear bulk copy per group replaces the tensor box (whose
     // 16-byte inner dimension caps the TMA unit at ~32 B/clk); edge tiles keep the zero-filling box
-    const uint4* src = reinterpret_cast<const uint4*>(p.x.p) + ((long long)b * p.x.sb + (p.x.hist + row0));
+    // (a unit-stride view has a single phase: group g sits g * sA units into the stream)
+    const uint4* src = reinterpret_cast<const uint4*>(p.x.p) +
+                       ((long long)b * p.x.sb + (p.x.hist + row0) + (long long)kg0 * p.x.sA);
     const uint32_t gbytes = (uint32_t)p.R_ALLOC * 16u;
-    for (int g = 0; g < c8n; ++g)
-      bulk_g2s(stage + (uint32_t)g * gbytes, src + group_off(p.x, kg0 + g), gbytes, bar);
+#pragma unroll 4
+    for (int g = 0; g < c8n; ++g) {
+      bulk_g2s(stage, src, gbytes, bar);
+      stage += gbytes;
+      src += p.x.sA;
+    }
     return;
   }
   const int row = row0 - p.x.lo;
@@ -520,7 +526,8 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
 // DR: how accumulators are drained -- 0 generic drain(), 1 drain_fast (global or no residual),
 // 2 drain_fast with the residual read from the A tile in smem (fused only).  One drain per
 // instantiation keeps every variant inside the 96-register budget without spills.
-template <int PRE, int ACT2, bool FUSED, int DR>
+// TR: event trace compiled in (tools_trace.py); production launches use TR = false.
+template <int PRE, int ACT2, bool FUSED, int DR, bool TR>
 __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams p,
                                                                 const __grid_constant__ TcTmap tmx) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -538,7 +545,7 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t tmask = (p.trace && blockIdx.x == 0 && lane == 0) ? 0u : 0xffffffffu;
+  const uint32_t tmask = (TR && p.trace && blockIdx.x == 0 && lane == 0) ? 0u : 0xffffffffu;
   // Programmatic dependent launch: let the next kernel of the stream start its prologue on SMs
   // this grid has already left; everything that touches activations waits below.
   asm volatile("griddepcontrol.launch_dependents;");
@@ -963,11 +970,11 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
   }
 }
 
-template <int PRE, int ACT2, bool FUSED, int DR>
+template <int PRE, int ACT2, bool FUSED, int DR, bool TR = false>
 static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED, DR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED, DR, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  227 * 1024));
     attr_set = true;
   }
@@ -982,7 +989,7 @@ static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStr
   attr.val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
-  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR>, p, tm));
+  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR, TR>, p, tm));
   return RB_OK;
 }
 
@@ -1050,7 +1057,12 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
   // drain_fast: whole 32-column chunks whose four channel groups sit sA apart, plain stores
   const bool fast = !p.head && !p.out_mask && (p.N_TILE & 31) == 0 && (p.y.G1 & 3) == 0 &&
                     (p.res.p == nullptr || p.res_smem || (p.res.G1 & 3) == 0);
-  if (!p.fused) {
+  if (p.trace && p.pre_act == RB_ACT_NONE && fast && (!p.fused || (p.act2 == RB_ACT_LEAKY && p.res.p))) {
+    // traced variants (debug hook): the headline kernels only
+    if (!p.fused) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 1, true>(p, tm, grid, s);
+    else if (p.res_smem) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 2, true>(p, tm, grid, s);
+    else rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 1, true>(p, tm, grid, s);
+  } else if (!p.fused) {
     if (p.pre_act == RB_ACT_NONE) {
       rc = fast ? launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 1>(p, tm, grid, s)
                 : launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 0>(p, tm, grid, s);

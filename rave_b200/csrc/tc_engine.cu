@@ -419,7 +419,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       {
         int flat_min = 0;
         if (const char* e = getenv("RB_TC_FLATMIN")) flat_min = atoi(e);   // experiments only
-        p.a_flat = (p.x.sT == 1 && p.R_ALLOC >= flat_min) ? 1 : 0;
+        p.a_flat = (p.x.sT == 1 && p.x.C / 8 <= p.x.G1 && p.R_ALLOC >= flat_min) ? 1 : 0;
       }
     }
     p.a_stage_bytes = (uint32_t)(L.KC / 8) * p.R_ALLOC * 16u;

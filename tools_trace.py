@@ -7,6 +7,7 @@ Prints, per work item, the clock stamps (relative, in cycles) of:
   12 out: acc barrier ok   13 out: first acc in registers   14 out: math done   15 out: stores issued
 """
 import ctypes as C
+import os
 import sys
 
 import numpy as np
@@ -25,7 +26,7 @@ def main():
     d = capi.RbDebugConv()
     if mode == "du":
         Cc, dil = int(sys.argv[2]), int(sys.argv[3])
-        B, n = 48, 16384 * 64 // Cc
+        B, n = int(os.environ.get("RB_TRACE_B", 48)), 16384 * 64 // Cc
         ops = [dict(c_in=Cc, c_out=Cc, k=3, stride=1, dilation=dil, off=dil, ileave=1, pre_act=1, has_bias=1),
                dict(c_in=Cc, c_out=Cc, k=1, stride=1, dilation=1, off=0, ileave=1, pre_act=1, has_bias=1)]
         ws = [rng.standard_normal((Cc, Cc, 3), dtype=np.float32) / np.sqrt(3 * Cc),
@@ -35,7 +36,7 @@ def main():
         flags = 3
     else:
         ci, co, k = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
-        B, n = 48, 16384 * 64 // ci
+        B, n = int(os.environ.get("RB_TRACE_B", 48)), 16384 * 64 // ci
         ops = [dict(c_in=ci, c_out=co, k=k, stride=1, dilation=1, off=k // 2, ileave=1, pre_act=1, has_bias=1)]
         ws = [rng.standard_normal((co, ci, k), dtype=np.float32) / np.sqrt(k * ci)]
         res = rng.standard_normal((B, co, n), dtype=np.float32) if len(sys.argv) > 5 else None
