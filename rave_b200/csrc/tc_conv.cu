@@ -92,13 +92,16 @@ struct WorkIter {
   int nt, b, tile, left;
   // w = (b * tiles_per_stream + tile) * n_ntiles + nt: the n-tiles of one row tile run at the same
   // time on neighbouring CTAs, so the A tile is read from HBM once and from L2 afterwards
+  // Pair mode (p.pair = 1): the two CTAs of a cluster walk the same work sequence -- same n-tile,
+  // hence the same weight blocks in the same order, which lets each load half of every block and
+  // multicast it to both -- and take the even / odd 128*MT-row tile of each slot.
   __device__ __forceinline__ void init(const TcParams& p) {
-    const int w = blockIdx.x;
+    const int w = (int)blockIdx.x >> p.pair, stride = (int)gridDim.x >> p.pair;
     const int rt = w / p.n_ntiles;
     nt = w - rt * p.n_ntiles;
     b = rt / p.tiles_per_stream;
     tile = rt - b * p.tiles_per_stream;
-    left = w < p.n_work ? (p.n_work - w + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    left = w < p.n_work ? (p.n_work - w + stride - 1) / stride : 0;
   }
   __device__ __forceinline__ void next(const TcParams& p) {
     nt += p.step_nt;
@@ -108,7 +111,9 @@ struct WorkIter {
     b += p.step_b;
     --left;
   }
-  __device__ __forceinline__ Work work(const TcParams& p) const { return Work{nt, b, tile * p.MT * 128}; }
+  __device__ __forceinline__ Work work(const TcParams& p) const {
+    return Work{nt, b, ((tile << p.pair) + ((int)blockIdx.x & p.pair)) * p.MT * 128};
+  }
 };
 
 // Stage index + phase bit of an mbarrier ring, advanced without divisions.
@@ -566,7 +571,7 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
     }
     for (int i = 0; i < 4; ++i) {
       mbar_init(BAR(BAR_W_FULL + i), 1);
-      mbar_init(BAR(BAR_W_EMPTY + i), 1);
+      mbar_init(BAR(BAR_W_EMPTY + i), 1 + p.pair);        // pair: released by both CTAs' MMAs
     }
     for (int i = 0; i < MAX_SD; ++i) {
       mbar_init(BAR(BAR_D_FULL + i), 1);
@@ -594,6 +599,7 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  if (p.pair) cluster_sync();                     // the peer's barriers exist before anything targets them
   // the prologue above (barriers, TMEM, bias / masks) and the weight loads of the W producer do not
   // depend on the previous kernel; activations do
   if (warp != W_WPROD) asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -659,9 +665,17 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
               const uint32_t sw = rw.idx;
               mbar_wait(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
               mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
-              bulk_g2s(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes),
-                       reinterpret_cast<const uint8_t*>(p.w) + (size_t)gblk * p.w_blk_bytes, p.w_blk_bytes,
-                       BAR(BAR_W_FULL + sw));
+              if (p.pair) {
+                // this CTA's half of the block, written into both CTAs' rings (the peer sends the other half)
+                const uint32_t half = p.w_blk_bytes >> 1, o = ((uint32_t)blockIdx.x & 1u) * half;
+                bulk_g2s_mc2(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes) + o,
+                             reinterpret_cast<const uint8_t*>(p.w) + (size_t)gblk * p.w_blk_bytes + o, half,
+                             BAR(BAR_W_FULL + sw));
+              } else {
+                bulk_g2s(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes),
+                         reinterpret_cast<const uint8_t*>(p.w) + (size_t)gblk * p.w_blk_bytes, p.w_blk_bytes,
+                         BAR(BAR_W_FULL + sw));
+              }
               ++gblk;
               rw.next(p.SW);
             }
@@ -788,7 +802,8 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
             }
             acc = 1;
             if (!p.w_resident) {
-              COMMIT(BAR(BAR_W_EMPTY + sw));
+              if (p.pair) { if (leader) mma_commit_mc2(BAR(BAR_W_EMPTY + sw)); }
+              else COMMIT(BAR(BAR_W_EMPTY + sw));
             }
           }
           COMMIT(BAR(BAR_A_EMPTY + sa));
@@ -964,6 +979,7 @@ __global__ void __maxnreg__(96) tc_conv_kernel(const __grid_constant__ TcParams 
 
   tc_fence_before();
   __syncthreads();
+  if (p.pair) cluster_sync();                     // no CTA leaves while its peer may still signal it
   if (warp == W_MMA) {
     tc_fence_after();
     tmem_dealloc(tmem, p.tmem_cols);
@@ -984,11 +1000,15 @@ static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStr
   cfg.blockDim = dim3(TC_THREADS);
   cfg.dynamicSmemBytes = p.smem_bytes;
   cfg.stream = s;
-  cudaLaunchAttribute attr;
-  attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr.val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = &attr;
-  cfg.numAttrs = 1;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = 2;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.pair ? 2 : 1;
   RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR, TR>, p, tm));
   return RB_OK;
 }
@@ -1043,10 +1063,15 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
            p.smem_bytes);
   RB_CHECK(p.out_act == RB_ACT_NONE || p.out_act == RB_ACT_LEAKY, RB_ERR_UNSUPPORTED,
            "only LeakyReLU can be stored activated");
-  const int grid = p.n_work < n_sm ? p.n_work : n_sm;
+  RB_CHECK(!p.pair || (!p.fused && !p.w_resident && p.pre_act == RB_ACT_NONE), RB_ERR_INVALID,
+           "pair mode is for plain streamed layers");
+  // pair mode: one cluster of two CTAs per work slot
+  const int slots = p.pair ? n_sm / 2 : n_sm;
+  const int stride = p.n_work < slots ? p.n_work : slots;
+  const int grid = p.pair ? 2 * stride : stride;
   {
-    const int rt = grid / p.n_ntiles;                      // grid stride, decomposed (WorkIter::next)
-    p.step_nt = grid - rt * p.n_ntiles;
+    const int rt = stride / p.n_ntiles;                    // grid stride, decomposed (WorkIter::next)
+    p.step_nt = stride - rt * p.n_ntiles;
     p.step_b = rt / p.tiles_per_stream;
     p.step_tile = rt - p.step_b * p.tiles_per_stream;
   }

@@ -60,6 +60,7 @@ struct TcParams {
   int MT;                   // 128-row sub-tiles per work item (1 or 2)
   int R, R_ALLOC;           // A rows per stage (MT*128 + max shift), allocated (odd)
   int w_resident;           // all blocks live in smem for the whole kernel
+  int pair;                 // 1: clusters of two CTAs share each streamed weight block (half each, multicast)
   int dual_g1;              // resident + narrow: two warps issue GEMM1 of alternate work items
   // A tile TMA boxes (tensor map over the input view, see launch_tc_conv): a chunk of KC/8
   // channel groups x R_ALLOC rows is fetched as boxes of a_gb groups x a_box_rows rows

@@ -246,6 +246,10 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
   RB_CHECK(v.n_taps <= 64, RB_ERR_UNSUPPORTED, "conv with %d row taps (max 64)", v.n_taps);
   int ncap = 256;
   if (const char* e = getenv("RB_TC_NTILE_CAP")) ncap = std::max(16, atoi(e));   // experiments only
+  if (const char* e = getenv("RB_TC_NTILE_CAP_IL")) {                             // experiments only
+    const int fo = atoi(e) / 1000, cap = atoi(e) % 1000;     // "4128": layers with fout >= 4 get cap 128
+    if (v.fout >= fo) ncap = cap;
+  }
   L.N_TILE = largest_div16(v.N_total, ncap);
   L.n_ntiles = v.N_total / L.N_TILE;
   RB_CHECK(L.n_ntiles <= TC_MAX_NT, RB_ERR_UNSUPPORTED, "too many output-channel tiles");
@@ -392,11 +396,17 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     p.w_resident = resident ? 1 : 0;
     p.dual_g1 = (resident && L.N_TILE <= 64 && !getenv("RB_TC_NODUAL")) ? 1 : 0;
     p.MT = (!resident && p.y.n >= 256) ? 2 : 1;
-    if (const char* e = getenv("RB_TC_MT1")) {           // experiments only
-      const int m = atoi(e);
-      if (m == 1 && L.N_TILE == 256) p.MT = 1;
-      if (m == 2 && L.N_TILE == 256 && L.n_taps * L.n_kchunks <= 8) p.MT = 1;
-    }
+    // streamed transposed convs run as cluster pairs: the two CTAs split every weight block (half
+    // the L2 -> SM weight traffic each), which pays for one sub-tile per accumulator stage and so
+    // for two stages at N_TILE = 256 -- the MMAs of the next work item overlap the epilogue, and
+    // these layers (r phases of output per input row) are epilogue-heavy.  Measured neutral or
+    // worse on the plain k = 1 / k = 3 layers (the 4-deep weight ring is then consumed in ~2000
+    // cycles, about its refill latency), so those keep two sub-tiles per weight block.
+    p.pair = (!resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256 && L.fout >= 2 &&
+              !getenv("RB_TC_NOPAIR")) ? 1 : 0;
+    if (const char* e = getenv("RB_TC_PAIRALL"))           // experiments only
+      p.pair = (atoi(e) && !resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256) ? 1 : 0;
+    if (p.pair) p.MT = (2 * L.N_TILE <= 256 && p.y.n >= 512) ? 2 : 1;
     p.R = p.MT * 128 + halo;
     {
       // TMA boxes of the A tile: whole chunk in one box when the rows fit a box (<= 256), else
@@ -456,6 +466,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   while (cols < (uint32_t)(p.SD * acc_cols)) cols <<= 1;
   p.tmem_cols = cols;
   p.tiles_per_stream = (p.y.n + p.MT * 128 - 1) / (p.MT * 128);
+  if (p.pair) p.tiles_per_stream = (p.tiles_per_stream + 1) / 2;   // work slots: two row tiles each
   p.n_work = L.n_ntiles * B * p.tiles_per_stream;
   return launch_tc_conv(p, s);
 }

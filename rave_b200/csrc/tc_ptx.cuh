@@ -65,6 +65,19 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
       : "memory");
 }
 
+// Same, delivered to the same offset of both CTAs of a cluster pair; each CTA's mbarrier (same
+// offset) receives the byte count.
+__device__ __forceinline__ void bulk_g2s_mc2(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1], %2, [%3], %4;" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "h"((unsigned short)3)
+      : "memory");
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // TMA tiled load of one 5-D box (tensor map in kernel parameter space) into shared memory;
 // out-of-range coordinates are zero-filled and the full box size is counted on the mbarrier.
 __device__ __forceinline__ void tma_load_5d(uint32_t dst, const void* tmap, int c0, int c1, int c2, int c3,
@@ -181,6 +194,13 @@ __device__ __forceinline__ uint32_t desc_hi(uint32_t sbo) { return ((sbo >> 4) &
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                : "memory");
+}
+// Same, arriving on the mbarrier at this offset in both CTAs of a cluster pair.
+__device__ __forceinline__ void mma_commit_mc2(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"((unsigned short)3)
+      : "memory");
 }
 // 32 lanes x 16 consecutive fp32 columns: thread l of the warp gets row (lane base + l).
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
