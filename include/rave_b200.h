@@ -136,6 +136,17 @@ int rb_forward(rb_handle* h, const void* x, int B, int T, int dtype, void* y, vo
  * synchronous.  This is what a non-torch caller binds. */
 int rb_forward_host(rb_handle* h, const float* x, int B, int T, int dtype, float* y);
 
+/* Pipelined host-buffer path (what a serving loop calls).  x / y are PINNED host buffers of
+ * `dtype` elements, [B,1,T].  The batch is cut into n_chunks blocks of streams (B % n_chunks == 0);
+ * each block's host->device copy, forward and device->host copy run on three internal streams,
+ * so the copies of one block overlap the compute of its neighbours -- and, because the call only
+ * enqueues, the copies of the next call overlap the tail of this one.  x must stay unchanged and
+ * y is undefined until rb_host_sync (host blocks) or until work ordered after rb_host_join
+ * (`stream` waits for everything enqueued so far; nothing blocks). */
+int rb_forward_host_async(rb_handle* h, const void* x, int B, int T, int dtype, void* y, int n_chunks);
+int rb_host_join(rb_handle* h, void* stream);
+int rb_host_sync(rb_handle* h);
+
 /* Uniform noise U(-1,1) for the noise branch, [B, L/8, n_band, 8] fp32 device pointer
  * (the reference draws it unseeded, blocks.py:287); NULL = engine-generated (Philox). */
 int rb_set_noise(rb_handle* h, const float* noise, int64_t numel);

@@ -60,6 +60,9 @@ EXPORTS = {
     "rb_decode": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_forward": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_forward_host": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p],
+    "rb_forward_host_async": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int],
+    "rb_host_join": [C.c_void_p, C.c_void_p],
+    "rb_host_sync": [C.c_void_p],
     "rb_set_noise": [C.c_void_p, C.c_void_p, C.c_int64],
     "rb_rvq_encode": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_rvq_decode": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],

@@ -258,6 +258,15 @@ int rb_destroy(rb_handle* h) {
   if (h->stage_in) cudaFreeHost(h->stage_in);
   if (h->stage_out) cudaFreeHost(h->stage_out);
   cudaFree(h->dev_in); cudaFree(h->dev_out);
+  if (h->pipe.ready) {
+    cudaStreamSynchronize(h->pipe.s_out); cudaStreamSynchronize(h->pipe.s_cmp); cudaStreamSynchronize(h->pipe.s_in);
+    for (int i = 0; i < rb_handle::HostPipe::NBUF; ++i) {
+      cudaFree(h->pipe.din[i]); cudaFree(h->pipe.dout[i]);
+      cudaEventDestroy(h->pipe.in_done[i]); cudaEventDestroy(h->pipe.cmp_done[i]); cudaEventDestroy(h->pipe.out_done[i]);
+    }
+    cudaEventDestroy(h->pipe.join_ev);
+    cudaStreamDestroy(h->pipe.s_in); cudaStreamDestroy(h->pipe.s_cmp); cudaStreamDestroy(h->pipe.s_out);
+  }
   delete h;
   return RB_OK;
 }
@@ -471,6 +480,78 @@ int rb_forward_host(rb_handle* h, const float* x, int B, int T, int dtype, float
   RB_CUDA(cudaMemcpyAsync(h->stage_out, h->dev_out, n * sizeof(float), cudaMemcpyDeviceToHost, 0));
   RB_CUDA(cudaStreamSynchronize(0));
   memcpy(y, h->stage_out, n * sizeof(float));
+  return RB_OK;
+}
+
+// Block k of a call: H2D on s_in -> forward on s_cmp -> D2H on s_out.  Ring slot i = seq % NBUF:
+// its input block may be overwritten once the forward that read it is done (cmp_done[i]), its
+// output block once the copy that drained it is done (out_done[i]).  Waiting on an event that
+// was never recorded is a no-op, which covers the first lap.
+int rb_forward_host_async(rb_handle* h, const void* x, int B, int T, int dtype, void* y, int n_chunks) {
+  int rc = check_ready(h);
+  if (rc) return rc;
+  RB_CHECK(x && y && B > 0 && T > 0 && n_chunks > 0, RB_ERR_INVALID, "rb_forward_host_async: bad arguments");
+  RB_CHECK(B % n_chunks == 0, RB_ERR_INVALID, "B=%d is not a multiple of n_chunks=%d", B, n_chunks);
+  RB_CHECK(dtype == RB_F32 || dtype == RB_BF16, RB_ERR_INVALID, "unknown dtype %d", dtype);
+  RB_CUDA(cudaSetDevice(h->device));
+  auto& pp = h->pipe;
+  constexpr int NBUF = rb_handle::HostPipe::NBUF;
+  if (!pp.ready) {
+    RB_CUDA(cudaStreamCreateWithFlags(&pp.s_in, cudaStreamNonBlocking));
+    RB_CUDA(cudaStreamCreateWithFlags(&pp.s_cmp, cudaStreamNonBlocking));
+    RB_CUDA(cudaStreamCreateWithFlags(&pp.s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < NBUF; ++i) {
+      RB_CUDA(cudaEventCreateWithFlags(&pp.in_done[i], cudaEventDisableTiming));
+      RB_CUDA(cudaEventCreateWithFlags(&pp.cmp_done[i], cudaEventDisableTiming));
+      RB_CUDA(cudaEventCreateWithFlags(&pp.out_done[i], cudaEventDisableTiming));
+    }
+    RB_CUDA(cudaEventCreateWithFlags(&pp.join_ev, cudaEventDisableTiming));
+    pp.ready = true;
+  }
+  const int Bc = B / n_chunks;
+  const size_t bytes = (size_t)Bc * T * (dtype == RB_BF16 ? 2 : 4);
+  if (pp.block_bytes < bytes) {
+    RB_CUDA(cudaStreamSynchronize(pp.s_out)); RB_CUDA(cudaStreamSynchronize(pp.s_cmp)); RB_CUDA(cudaStreamSynchronize(pp.s_in));
+    for (int i = 0; i < NBUF; ++i) {
+      cudaFree(pp.din[i]); cudaFree(pp.dout[i]);
+      pp.din[i] = pp.dout[i] = nullptr;
+    }
+    pp.block_bytes = 0;
+    for (int i = 0; i < NBUF; ++i) {
+      RB_CUDA(cudaMalloc(&pp.din[i], bytes));
+      RB_CUDA(cudaMalloc(&pp.dout[i], bytes));
+    }
+    pp.block_bytes = bytes;
+  }
+  for (int k = 0; k < n_chunks; ++k, ++pp.seq) {
+    const int i = (int)(pp.seq % NBUF);
+    RB_CUDA(cudaStreamWaitEvent(pp.s_in, pp.cmp_done[i], 0));
+    RB_CUDA(cudaMemcpyAsync(pp.din[i], (const char*)x + (size_t)k * bytes, bytes, cudaMemcpyHostToDevice, pp.s_in));
+    RB_CUDA(cudaEventRecord(pp.in_done[i], pp.s_in));
+    RB_CUDA(cudaStreamWaitEvent(pp.s_cmp, pp.in_done[i], 0));
+    RB_CUDA(cudaStreamWaitEvent(pp.s_cmp, pp.out_done[i], 0));
+    rc = rb_forward(h, pp.din[i], Bc, T, dtype, pp.dout[i], pp.s_cmp);
+    if (rc) return rc;
+    RB_CUDA(cudaEventRecord(pp.cmp_done[i], pp.s_cmp));
+    RB_CUDA(cudaStreamWaitEvent(pp.s_out, pp.cmp_done[i], 0));
+    RB_CUDA(cudaMemcpyAsync((char*)y + (size_t)k * bytes, pp.dout[i], bytes, cudaMemcpyDeviceToHost, pp.s_out));
+    RB_CUDA(cudaEventRecord(pp.out_done[i], pp.s_out));
+  }
+  return RB_OK;
+}
+
+int rb_host_join(rb_handle* h, void* stream) {
+  RB_CHECK(h, RB_ERR_INVALID, "null handle");
+  if (!h->pipe.ready) return RB_OK;
+  RB_CUDA(cudaEventRecord(h->pipe.join_ev, h->pipe.s_out));   // s_out is ordered after s_cmp after s_in
+  RB_CUDA(cudaStreamWaitEvent((cudaStream_t)stream, h->pipe.join_ev, 0));
+  return RB_OK;
+}
+
+int rb_host_sync(rb_handle* h) {
+  RB_CHECK(h, RB_ERR_INVALID, "null handle");
+  if (!h->pipe.ready) return RB_OK;
+  RB_CUDA(cudaStreamSynchronize(h->pipe.s_out));
   return RB_OK;
 }
 

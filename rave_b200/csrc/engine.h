@@ -87,6 +87,18 @@ struct rb_handle {
   void* dev_out = nullptr;
   size_t stage_elems = 0;
 
+  // rb_forward_host_async: three streams, rings of device in / out blocks guarded by events
+  struct HostPipe {
+    static constexpr int NBUF = 3;
+    cudaStream_t s_in = nullptr, s_cmp = nullptr, s_out = nullptr;
+    void* din[NBUF] = {nullptr, nullptr, nullptr};
+    void* dout[NBUF] = {nullptr, nullptr, nullptr};
+    cudaEvent_t in_done[NBUF], cmp_done[NBUF], out_done[NBUF], join_ev;
+    size_t block_bytes = 0;
+    unsigned long long seq = 0;
+    bool ready = false;
+  } pipe;
+
   // per-op profiling (rb_profile_ops)
   bool profile = false;
   struct Ev { int op; cudaEvent_t a, b; };

@@ -248,6 +248,33 @@ class RAVE:
                                              capi.RB_F32, y.ctypes.data_as(C.c_void_p)))
         return y
 
+    def forward_host_async(self, x_host: torch.Tensor, y_host: torch.Tensor, n_chunks: int = 4):
+        """Pipelined host-buffer forward (rb_forward_host_async): x_host / y_host are PINNED CPU tensors
+        [B, 1, T] of the model dtype.  Only enqueues: blocks of B / n_chunks streams are copied in,
+        run and copied out on three internal streams, so copies overlap compute within the call and
+        across consecutive calls.  y_host is valid after host_sync() (or, for GPU work, after
+        host_join())."""
+        for t, what in ((x_host, "x_host"), (y_host, "y_host")):
+            if t.device.type != "cpu" or not t.is_pinned() or not t.is_contiguous() or t.dtype != self.dtype:
+                raise ValueError(f"forward_host_async: {what} must be a pinned contiguous CPU tensor of {self.dtype}")
+        if x_host.dim() != 3 or x_host.shape[1] != 1 or y_host.shape != x_host.shape:
+            raise ValueError("forward_host_async expects x_host and y_host of shape [B, 1, T]")
+        B, _, T = x_host.shape
+        if T % self.spec.samples_per_frame:
+            raise ValueError(f"forward: T={T} must be a multiple of the model ratio {self.spec.samples_per_frame}")
+        if n_chunks < 1 or B % n_chunks:
+            raise ValueError(f"forward_host_async: B={B} is not a multiple of n_chunks={n_chunks}")
+        capi.check(self._lib.rb_forward_host_async(self._h, x_host.data_ptr(), B, T, self._rb_dtype,
+                                                   y_host.data_ptr(), n_chunks))
+
+    def host_join(self):
+        """The current torch stream waits for everything forward_host_async has enqueued."""
+        capi.check(self._lib.rb_host_join(self._h, _stream_ptr()))
+
+    def host_sync(self):
+        """Blocks until every forward_host_async result has landed in its host buffer."""
+        capi.check(self._lib.rb_host_sync(self._h))
+
     # ------------------------------------------------------------------ introspection
     def kernel_launches(self):
         n = C.c_int64()

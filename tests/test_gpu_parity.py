@@ -220,3 +220,28 @@ def test_streaming_bf16_matches_golden_chunk_by_chunk(name):
     for c in range(x.shape[-1] // n):
         ys2.append(m(x[..., c * n:(c + 1) * n].contiguous()))
     assert rel_l2(torch.cat(ys2, -1).float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_host_pipeline_equals_device_forward(dtype):
+    """rb_forward_host_async (blocks of streams on three streams, two calls back to back so the ring
+    of device blocks wraps) returns exactly what forward() returns for the same inputs."""
+    m, meta, a = _model("v2_c8", dtype=dtype)
+    x0 = torch.from_numpy(golden_input(a))
+    B0, _, T = x0.shape
+    reps = 8 // B0 if B0 < 8 else 1
+    xs = [torch.cat([x0 * (1.0 + 0.1 * (i + r)) for r in range(reps)]).to(dtype) for i in range(2)]
+    want = [m(x.cuda()).cpu() for x in xs]
+    xh = [x.contiguous().pin_memory() for x in xs]
+    yh = [torch.empty_like(x).pin_memory() for x in xh]
+    B = xh[0].shape[0]
+    for i in range(2):
+        m.forward_host_async(xh[i], yh[i], n_chunks=B if i == 0 else 2)
+    m.host_sync()
+    for i in range(2):
+        assert torch.equal(yh[i], want[i])
+    with pytest.raises(ValueError):
+        m.forward_host_async(xh[0], yh[0], n_chunks=3)
+    with pytest.raises(ValueError):
+        m.forward_host_async(xs[0], yh[0])            # not pinned
