@@ -366,7 +366,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   p.res_act = (res && res_act) ? 1 : 0;
   // fused unit whose residual is its own input: E2 reads it back from the A tile in smem
   p.res_smem = (L.fused && res && res->p == src.p && rop.res_delay == 0 && L.n_kchunks == 1 &&
-                p.pre_act == RB_ACT_NONE) ? 1 : 0;   // (an activation pass would overwrite the tile)
+                p.pre_act == RB_ACT_NONE && !getenv("RB_TC_NORESSMEM")) ? 1 : 0;   // (an activation pass would overwrite the tile)
   p.B = B;
   p.n_taps = L.n_taps; p.dil = L.dil; p.off = L.off;
   p.KC = L.KC; p.n_kchunks = L.n_kchunks;
@@ -508,15 +508,30 @@ __global__ void gm_to_cf_kernel(Buf src, __nv_bfloat16* __restrict__ dst, int C,
   }
 }
 // model.py:618-620: z = cat(z, speaker.repeat(B, 1, F)) (+ zero pad channels)
+// One thread per 16-byte unit (8 channels of one row): z groups are copied, conditioning groups are
+// the same 8 values for every row of every stream, pad groups are zero.
 __global__ void concat_gm_kernel(Buf z, Buf y, const float* __restrict__ cond, int c_z, int c_cond, int B) {
-  const size_t total = (size_t)B * y.n * y.cp;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    int b, t, c;
-    decode_gm(i, y, b, t, c);
-    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
-    if (c < c_z) v = z.p[eidx(z, b, t, c)];
-    else if (c < c_z + c_cond) v = __float2bfloat16_rn(cond[c - c_z]);
-    y.p[eidx(y, b, t, c)] = v;
+  const int G = y.cp >> 3, Gz = z.cp >> 3;
+  const long long units = (long long)B * G * y.n;
+  for (long long u = blockIdx.x * (long long)blockDim.x + threadIdx.x; u < units; u += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(u % y.n);
+    const int r = (int)(u / y.n);
+    const int g = r % G, b = r / G;
+    const int c0 = g * 8;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (c0 + 8 <= c_z) {
+      v = reinterpret_cast<const uint4*>(z.p)[((size_t)b * Gz + g) * z.ld + z.hist + t];
+    } else {
+      __align__(16) __nv_bfloat16 e[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int c = c0 + k;
+        e[k] = c < c_z ? z.p[eidx(z, b, t, c)]
+                       : (c < c_z + c_cond ? __float2bfloat16_rn(cond[c - c_z]) : __float2bfloat16_rn(0.f));
+      }
+      v = *reinterpret_cast<const uint4*>(e);
+    }
+    reinterpret_cast<uint4*>(y.p)[((size_t)b * G + g) * y.ld + y.hist + t] = v;
   }
 }
 // AdaIN transfer (blocks.py:885-891) as x = a[b][c]*x + b[b][c], in place
@@ -781,7 +796,7 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
       const OpWeights& w = h->w[i];
       RB_CHECK(w.cond, RB_ERR_STATE, "conditioning vector (speaker embedding) not loaded");
       const Buf& y = bufs[op.dst];
-      RB_LAUNCH_EW(concat_gm_kernel, (size_t)B * y.n * y.cp, s, bufs[op.src], y, w.cond, op.c_in,
+      RB_LAUNCH_EW(concat_gm_kernel, (size_t)B * y.n * (y.cp / 8), s, bufs[op.src], y, w.cond, op.c_in,
                    op.c_out - op.c_in, B);
       return RB_OK;
     }
