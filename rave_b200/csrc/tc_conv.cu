@@ -608,7 +608,11 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   const uint32_t bar0 = smem_u32(bars);
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // read %tid.x ONCE: ptxas otherwise rematerialises S2R SR_TID.X inside the epilogue loops to save a
+  // register (-1 % cycles over the step)
+  int tid;
+  asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));
+  const int warp = tid >> 5, lane = tid & 31;
   const uint32_t tmask = (TR && p.trace && blockIdx.x == 0 && lane == 0) ? 0u : 0xffffffffu;
   // Programmatic dependent launch: let the next kernel of the stream start its prologue on SMs
   // this grid has already left; everything that touches activations waits below.

@@ -203,6 +203,17 @@ __global__ void k_bulk(long long* out, const uint8_t* src, size_t cta_stride, in
   }
 }
 
+// HBM streams: mode 0 write-only (STG.128), 1 read-only (LDG.128), 2 copy; every thread strides the buffer
+__global__ void k_stream(uint4* dst, const uint4* src, size_t n, int mode, uint4* sink) {
+  uint4 acc = make_uint4(0, 0, 0, 0);
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    if (mode == 0) dst[i] = make_uint4((uint32_t)i, 1u, 2u, 3u);
+    else if (mode == 1) { const uint4 v = src[i]; acc.x ^= v.x; acc.y ^= v.y; acc.z ^= v.z; acc.w ^= v.w; }
+    else dst[i] = src[i];
+  }
+  if (mode == 1 && acc.x == 0x12345678u) *sink = acc;
+}
+
 // instruction-mix issue rates: every warp runs `iters` rounds of 32 independent ops of one kind
 template <int KIND>
 __global__ void k_alu(long long* out, float* sink, int iters) {
@@ -283,6 +294,26 @@ int main() {
   }
 
 
+
+  {
+    const size_t bytes = (size_t)2 << 30, n = bytes / 16;
+    uint4 *a, *b;
+    cudaMalloc(&a, bytes); cudaMalloc(&b, bytes);
+    cudaMemset(a, 1, bytes); cudaMemset(b, 2, bytes);
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const char* mn[3] = {"write-only", "read-only", "copy (r+w)"};
+    for (int mode = 0; mode < 3; ++mode) {
+      float best = 1e9f;
+      for (int it = 0; it < 5; ++it) {
+        cudaEventRecord(e0);
+        k_stream<<<148 * 8, 512>>>(a, b, n, mode, (uint4*)sink);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        float ms; cudaEventElapsedTime(&ms, e0, e1); if (ms < best) best = ms;
+      }
+      printf("hbm   %-10s 2 GiB: %.3f ms -> %.0f GB/s\n", mn[mode], best, (mode == 2 ? 2.0 : 1.0) * bytes / best / 1e6);
+    }
+    cudaFree(a); cudaFree(b);
+  }
   cudaFuncSetAttribute(k_mma_commit, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   for (int nc : {0, 1, 2}) {
     for (int g : {4, 12}) {
