@@ -18,7 +18,7 @@
 
 namespace rb {
 
-constexpr int RVQ_ROWS = 64;    // rows (latent vectors) per CTA
+constexpr int RVQ_ROWS = 128;   // rows (latent vectors) per CTA
 constexpr int RVQ_CODES = 64;   // codes per smem chunk
 constexpr int RVQ_MAXD = 256;
 
@@ -60,26 +60,31 @@ int launch_rvq_norms(const float* cb, int rows, int D, float* e2, cudaStream_t s
   return RB_OK;
 }
 
-// One CTA = 64 latent vectors through all Q stages.  Residuals stay in shared memory across
-// the stages ([k][row] so a thread's 4 rows are one float4); codebook chunks of 64 codes are
-// staged transposed ([k][code]).  Thread (ty, tx) owns rows 4ty..4ty+3 x codes 4tx..4tx+3 of
-// each chunk: 16 independent FMA chains, 2 LDS.128 per 16 FMA.
+// One CTA = 128 latent vectors through all Q stages.  Residuals stay in shared memory across
+// the stages ([k][row]: a thread's 8 rows are two float4); codebook chunks of 64 codes are staged
+// transposed ([k][code], the 4-code groups of row k XOR-swizzled by (k >> 2) & 7 so that the
+// coalesced global read -- a warp takes 128 contiguous bytes of four codes -- stores without
+// bank conflicts).  Thread (ty, tx) owns rows 8ty..8ty+7 x codes 4tx..4tx+3 of each chunk:
+// 32 independent FMA chains, 3 LDS.128 per 32 FMA.
+constexpr int RVQ_RPT = RVQ_ROWS / 16;      // rows per thread
+static_assert(RVQ_ROWS == 128 && RVQ_CODES == 64 && RVQ_RPT == 8, "index math below assumes 128 rows x 64 codes");
+
 __global__ void __launch_bounds__(256)
 rvq_encode_kernel(const float* __restrict__ z, int B, int D, int F, const float* __restrict__ cb,
                   const float* __restrict__ e2, int Q, int K, long long* __restrict__ idx) {
   extern __shared__ float smem[];
-  float* rs = smem;                         // [D][64] residuals, row-minor
-  float* es = rs + (size_t)D * RVQ_ROWS;    // [D][64] codebook chunk, code-minor
-  float* t1 = es + (size_t)D * RVQ_CODES;   // [64]
-  float* bestv = t1 + RVQ_ROWS;             // [64][16]
+  float* rs = smem;                         // [D][128] residuals, row-minor
+  float* es = rs + (size_t)D * RVQ_ROWS;    // [D][64] codebook chunk, code-minor (swizzled)
+  float* t1 = es + (size_t)D * RVQ_CODES;   // [128]
+  float* bestv = t1 + RVQ_ROWS;             // [128][16]
   int* besti = (int*)(bestv + RVQ_ROWS * 16);
-  int* win = besti + RVQ_ROWS * 16;         // [64]
+  int* win = besti + RVQ_ROWS * 16;         // [128]
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const long long N = (long long)B * F;
   const long long row0 = (long long)blockIdx.x * RVQ_ROWS;
   // load residual = z[b, :, f] for row n = b*F + f   (permute(0,2,1).reshape(-1, D))
   for (int i = tid; i < D * RVQ_ROWS; i += 256) {
-    const int k = i / RVQ_ROWS, r = i - k * RVQ_ROWS;
+    const int k = i >> 7, r = i & (RVQ_ROWS - 1);
     const long long n = row0 + r;
     float v = 0.f;
     if (n < N) {
@@ -91,32 +96,50 @@ rvq_encode_kernel(const float* __restrict__ z, int B, int D, int F, const float*
   __syncthreads();
   for (int q = 0; q < Q; ++q) {
     if (tid < RVQ_ROWS) t1[tid] = torch_row_sumsq(rs + tid, D, RVQ_ROWS);
-    float bv[4];
-    int bi[4];
+    float bv[RVQ_RPT];
+    int bi[RVQ_RPT];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) { bv[r] = INFINITY; bi[r] = 0x7fffffff; }
+    for (int r = 0; r < RVQ_RPT; ++r) { bv[r] = INFINITY; bi[r] = 0x7fffffff; }
     const float* cq = cb + (size_t)q * K * D;
     for (int c0 = 0; c0 < K; c0 += RVQ_CODES) {
       __syncthreads();                      // previous chunk consumed, t1 visible
-      for (int i = tid; i < D * RVQ_CODES; i += 256) {
-        const int c = i / D, k = i - c * D; // coalesced along k
-        es[k * RVQ_CODES + c] = (c0 + c < K) ? __ldg(cq + (size_t)(c0 + c) * D + k) : 0.f;
+      // stage the chunk: lane = (code-in-group, k4 within a run of 8) reads 16 bytes; the four words go
+      // to rows 4k4..4k4+3 at group (g ^ (k4 & 7)): 8 runs x 4 codes cover the 32 banks exactly once
+      for (int i = tid; i < (D >> 2) * RVQ_CODES; i += 256) {
+        const int cc = i & 3, kk = (i >> 2) & 7, w = i >> 5;
+        const int g = w & 15, k4 = ((w >> 4) << 3) + kk;
+        const int c = 4 * g + cc;
+        float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k4 < (D >> 2) && c0 + c < K) e = __ldg(reinterpret_cast<const float4*>(cq + (size_t)(c0 + c) * D) + k4);
+        if (k4 < (D >> 2)) {
+          float* d = es + (size_t)(4 * k4) * RVQ_CODES + 4 * (g ^ (k4 & 7)) + cc;
+          d[0] = e.x; d[RVQ_CODES] = e.y; d[2 * RVQ_CODES] = e.z; d[3 * RVQ_CODES] = e.w;
+        }
       }
       __syncthreads();
-      float acc[4][4];
+      // The reference's chain is acc <- fma(2 x_k, e_k, acc).  Doubling commutes with every rounding
+      // (no overflow / subnormals at these magnitudes), so the chain runs on x_k and the result is
+      // doubled once: bit-identical, and nothing but FMAs and three LDS.128 in the loop.
+      float acc[RVQ_RPT][4];
 #pragma unroll
-      for (int r = 0; r < 4; ++r)
+      for (int r = 0; r < RVQ_RPT; ++r)
 #pragma unroll
         for (int c = 0; c < 4; ++c) acc[r][c] = 0.f;
-      for (int k = 0; k < D; ++k) {
-        const float4 rv = *reinterpret_cast<const float4*>(rs + k * RVQ_ROWS + ty * 4);
-        const float4 ev = *reinterpret_cast<const float4*>(es + k * RVQ_CODES + tx * 4);
-        const float r2[4] = {2.f * rv.x, 2.f * rv.y, 2.f * rv.z, 2.f * rv.w};
-        const float e[4] = {ev.x, ev.y, ev.z, ev.w};
+      for (int k0 = 0; k0 < D; k0 += 4) {
+        const float* ep = es + (size_t)k0 * RVQ_CODES + 4 * (tx ^ ((k0 >> 2) & 7));
+        const float* rp = rs + (size_t)k0 * RVQ_ROWS + ty * RVQ_RPT;
 #pragma unroll
-        for (int r = 0; r < 4; ++r)
+        for (int kk = 0; kk < 4; ++kk) {
+          const float4 ra = *reinterpret_cast<const float4*>(rp + kk * RVQ_ROWS);
+          const float4 rb = *reinterpret_cast<const float4*>(rp + kk * RVQ_ROWS + 4);
+          const float4 ev = *reinterpret_cast<const float4*>(ep + kk * RVQ_CODES);
+          const float rr[8] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z, rb.w};
+          const float e[4] = {ev.x, ev.y, ev.z, ev.w};
 #pragma unroll
-          for (int c = 0; c < 4; ++c) acc[r][c] = __fmaf_rn(r2[r], e[c], acc[r][c]);
+          for (int r = 0; r < RVQ_RPT; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) acc[r][c] = __fmaf_rn(rr[r], e[c], acc[r][c]);
+        }
       }
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
@@ -124,18 +147,18 @@ rvq_encode_kernel(const float* __restrict__ z, int B, int D, int F, const float*
         if (code < K) {
           const float t3 = __ldg(e2 + (size_t)q * K + code);
 #pragma unroll
-          for (int r = 0; r < 4; ++r) {
+          for (int r = 0; r < RVQ_RPT; ++r) {
             // w = (|x|^2 - 2x.e) + |e|^2 ; dist = -w ; argmax dist = first argmin w
-            const float w = __fadd_rn(__fsub_rn(t1[ty * 4 + r], acc[r][c]), t3);
+            const float w = __fadd_rn(__fsub_rn(t1[ty * RVQ_RPT + r], __fmul_rn(2.f, acc[r][c])), t3);
             if (w < bv[r]) { bv[r] = w; bi[r] = code; }   // codes visited in increasing order
           }
         }
       }
     }
 #pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      bestv[(ty * 4 + r) * 16 + tx] = bv[r];
-      besti[(ty * 4 + r) * 16 + tx] = bi[r];
+    for (int r = 0; r < RVQ_RPT; ++r) {
+      bestv[(ty * RVQ_RPT + r) * 16 + tx] = bv[r];
+      besti[(ty * RVQ_RPT + r) * 16 + tx] = bi[r];
     }
     __syncthreads();
     if (tid < RVQ_ROWS) {
@@ -154,10 +177,15 @@ rvq_encode_kernel(const float* __restrict__ z, int B, int D, int F, const float*
       }
     }
     __syncthreads();
-    // residual -= E[q][win]   (quantization.py:307-308)
-    for (int i = tid; i < D * RVQ_ROWS; i += 256) {
-      const int r = i / D, k = i - r * D;   // coalesced codebook read along k
-      rs[k * RVQ_ROWS + r] = __fsub_rn(rs[k * RVQ_ROWS + r], __ldg(cq + (size_t)win[r] * D + k));
+    // residual -= E[q][win]   (quantization.py:307-308); lane -> row: conflict-free smem, 16-byte reads
+    for (int i = tid; i < (D >> 2) * RVQ_ROWS; i += 256) {
+      const int r = i & (RVQ_ROWS - 1), k4 = i >> 7;
+      const float4 e = __ldg(reinterpret_cast<const float4*>(cq + (size_t)win[r] * D) + k4);
+      float* d = rs + (size_t)(4 * k4) * RVQ_ROWS + r;
+      d[0] = __fsub_rn(d[0], e.x);
+      d[RVQ_ROWS] = __fsub_rn(d[RVQ_ROWS], e.y);
+      d[2 * RVQ_ROWS] = __fsub_rn(d[2 * RVQ_ROWS], e.z);
+      d[3 * RVQ_ROWS] = __fsub_rn(d[3 * RVQ_ROWS], e.w);
     }
     __syncthreads();
   }
@@ -171,7 +199,7 @@ int launch_rvq_encode(const float* z, int B, int D, int F, const float* cb, cons
                       (RVQ_ROWS * 16 + RVQ_ROWS) * sizeof(int);
   static bool attr_set = false;
   if (!attr_set) {
-    RB_CUDA(cudaFuncSetAttribute(rvq_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    RB_CUDA(cudaFuncSetAttribute(rvq_encode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     attr_set = true;
   }
   const int grid = (int)((N + RVQ_ROWS - 1) / RVQ_ROWS);
