@@ -109,7 +109,10 @@ typedef enum rb_role {
   RB_W_AFFINE_A = 3,  /* AFFINE scale  [max_streams][C]                                     */
   RB_W_AFFINE_B = 4,  /* AFFINE shift  [max_streams][C]                                     */
   RB_W_COND = 5,      /* conditioning vector [cond_channels] (op = CONCAT_COND)             */
-  RB_W_CODEBOOK = 6   /* RVQ codebooks [Q][codebook_size][dim] (op index ignored)           */
+  RB_W_CODEBOOK = 6,  /* RVQ codebooks [Q][codebook_size][dim] (op index ignored)           */
+  RB_W_ADAIN_STATS = 7 /* AdaIN buffers of an AFFINE op (blocks.py:860-868): [4][max_streams][C] =
+                          mean_x, std_x, mean_y, std_y, then num_update_x, num_update_y (2 floats);
+                          replaces AFFINE_A / _B and allows statistic learning (rb_adain_update) */
 } rb_role;
 
 typedef struct rb_tensor_desc {
@@ -166,6 +169,16 @@ int rb_stream_state_elements(rb_handle* h, int64_t* per_stream);
 int rb_workspace_bytes(rb_handle* h, int B, int T, int dtype, size_t* bytes);
 int rb_kernel_launches(rb_handle* h, int64_t* count);   /* launches issued so far */
 int rb_set_microbatch(rb_handle* h, int streams);       /* 0 = automatic */
+
+/* AdaIN statistic learning (rave/blocks.py:870-883,893-919), driven like ScriptedRAVE.update_adain
+ * (scripts/export.py:248-265): learn_source sets learn_x, learn_target sets learn_y on every AdaIN
+ * site; reset_source / reset_target zero the means, set the stds to one and clear the counters.
+ * While a flag is set every encode / decode / forward / stream step folds the per-(stream, channel)
+ * mean and unbiased std of the site's input into the running statistics of rows [0, B).  Needs
+ * the statistics loaded with RB_W_ADAIN_STATS. */
+int rb_adain_update(rb_handle* h, int learn_source, int learn_target, int reset_source, int reset_target);
+/* stats: host buffer of 4 * max_streams * C floats (mean_x, std_x, mean_y, std_y) or NULL. */
+int rb_adain_get_stats(rb_handle* h, int op, float* stats, int64_t numel, int* num_update_x, int* num_update_y);
 /* Per-op device timing (CUDA events on the launching stream around every op of the
  * program).  enable!=0 starts recording; rb_op_times synchronises, writes the accumulated
  * milliseconds per op (n = number of ops) and clears the record. */

@@ -46,6 +46,23 @@ class OracleRAVE:
     def _ctx(self):
         return O._Ctx(self.sd, self.causal, self.stream)
 
+    def update_adain(self, learn_source=False, learn_target=False, reset_source=False, reset_target=False):
+        """ScriptedRAVE.update_adain (scripts/export.py:248-265) on every AdaIN module's buffers:
+        learn_source -> learn_x, learn_target -> learn_y; resets as blocks.py:875-883."""
+        import torch
+        for key in [k for k in self.sd if k.endswith("num_update_x")]:
+            p = key[:-len("num_update_x")]
+            self.sd[p + "learn_x"] = torch.full((1,), 1.0 if learn_source else 0.0)
+            self.sd[p + "learn_y"] = torch.full((1,), 1.0 if learn_target else 0.0)
+            if reset_target:
+                self.sd[p + "mean_y"].zero_()
+                self.sd[p + "std_y"].zero_().add_(1)
+                self.sd[p + "num_update_y"].zero_()
+            if reset_source:
+                self.sd[p + "mean_x"].zero_()
+                self.sd[p + "std_x"].zero_().add_(1)
+                self.sd[p + "num_update_x"].zero_()
+
     # -- PQMF -------------------------------------------------------------------------
     def pqmf_forward(self, x):
         """CachedPQMF.forward, pqmf.py:269-273."""

@@ -184,11 +184,34 @@ def _act(ctx, prefix, x, kind):
     return F.leaky_relu(x, 0.2)
 
 
+def _adain_update(target, source, num_updates):
+    """AdaptiveInstanceNormalization.update (blocks.py:870-873): running mean over calls."""
+    bs = source.shape[0]
+    target[:bs] += (source - target[:bs]) / (num_updates + 1)
+
+
 def _adain(ctx, prefix, x):
-    """blocks.py:885-919 in eval mode with learn_x = learn_y = 0."""
+    """AdaptiveInstanceNormalization.forward in eval mode (blocks.py:893-919).  The statistics
+    buffers and the learn_x / learn_y flags live in the state dict and are updated IN PLACE,
+    like the module's registered buffers (driven by OracleRAVE.update_adain = export.py:248-265)."""
     sd = ctx.sd
+    learn_x = float(sd[prefix + "learn_x"]) if prefix + "learn_x" in sd else 0.0
+    learn_y = float(sd[prefix + "learn_y"]) if prefix + "learn_y" in sd else 0.0
+    if learn_y:
+        mean = x.mean(-1, keepdim=True)
+        std = x.std(-1, keepdim=True)
+        _adain_update(sd[prefix + "mean_y"], mean, sd[prefix + "num_update_y"])
+        _adain_update(sd[prefix + "std_y"], std, sd[prefix + "num_update_y"])
+        sd[prefix + "num_update_y"] += 1
+        return x
+    if learn_x:
+        mean = x.mean(-1, keepdim=True)
+        std = x.std(-1, keepdim=True)
+        _adain_update(sd[prefix + "mean_x"], mean, sd[prefix + "num_update_x"])
+        _adain_update(sd[prefix + "std_x"], std, sd[prefix + "num_update_x"])
+        sd[prefix + "num_update_x"] += 1
     if float(sd[prefix + "num_update_x"]) and float(sd[prefix + "num_update_y"]):
-        bs = x.shape[0]
+        bs = x.shape[0]                                        # transfer, blocks.py:885-891
         x = (x - sd[prefix + "mean_x"][:bs]) / (sd[prefix + "std_x"][:bs] + 1e-5)
         x = x * sd[prefix + "std_y"][:bs] + sd[prefix + "mean_y"][:bs]
     return x

@@ -11,7 +11,8 @@ LIB_PATH = os.path.join(_HERE, "librave_b200.so")
 
 RB_OK, RB_ERR_INVALID, RB_ERR_CUDA, RB_ERR_STATE, RB_ERR_UNSUPPORTED = 0, -1, -2, -3, -4
 RB_F32, RB_BF16 = 0, 1
-(RB_W_CONV, RB_W_BIAS, RB_W_ALPHA, RB_W_AFFINE_A, RB_W_AFFINE_B, RB_W_COND, RB_W_CODEBOOK) = range(7)
+(RB_W_CONV, RB_W_BIAS, RB_W_ALPHA, RB_W_AFFINE_A, RB_W_AFFINE_B, RB_W_COND, RB_W_CODEBOOK,
+ RB_W_ADAIN_STATS) = range(8)
 ABI_VERSION = 1
 
 
@@ -75,6 +76,9 @@ EXPORTS = {
     "rb_workspace_bytes": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)],
     "rb_kernel_launches": [C.c_void_p, C.POINTER(C.c_int64)],
     "rb_set_microbatch": [C.c_void_p, C.c_int],
+    "rb_adain_update": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int],
+    "rb_adain_get_stats": [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int64, C.POINTER(C.c_int),
+                           C.POINTER(C.c_int)],
     "rb_profile_ops": [C.c_void_p, C.c_int],
     "rb_op_times": [C.c_void_p, C.POINTER(C.c_float), C.c_int],
     "rb_last_error": [],

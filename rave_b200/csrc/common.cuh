@@ -58,6 +58,11 @@ int launch_pqmf_fwd_f32(const View& x, const View& y, const float* w /*[k][8]*/,
 int launch_pqmf_inv_f32(const View& x, const View& y, const float* w /*[c][k][m]*/, int B, int n_band,
                         int k, int off, int lo, cudaStream_t s);
 int launch_affine_f32(const View& x, const float* a, const float* b, int B, cudaStream_t s);
+// AdaIN running statistics (blocks.py:870-873,897-914): per (stream, channel) mean and unbiased std of
+// x over time, folded into rows [0, B) of the tables as target += (value - target) / (count + 1)
+int launch_adain_stats_f32(const View& x, int B, float* mean_t, float* std_t, int count, cudaStream_t s);
+// a = std_y / (std_x + 1e-5), b = mean_y - mean_x * a  (identity when the transfer is inactive)
+int launch_adain_ab(const float* stats, int rows, int C, int active, float* a, float* b, cudaStream_t s);
 int launch_head_v2_f32(const View& w, const View& noise, const View& y, int B, int data, int am,
                        cudaStream_t s);
 int launch_head_v1_f32(const View& wave, const View& loud, const View& y, int B, int data,

@@ -94,11 +94,20 @@ int exec_op_f32(RunCtx& c, int oi) {
       return launch_pqmf_fwd_f32(x, y, w.w, c.B, op.c_out, op.n_band, op.k, op.off, lo, c.s);
     case RB_OP_PQMF_INV:
       return launch_pqmf_inv_f32(x, y, w.w, c.B, op.n_band, op.k, op.off, lo, c.s);
-    case RB_OP_AFFINE:
+    case RB_OP_AFFINE: {
       RB_CHECK(w.aff_a && w.aff_b, RB_ERR_STATE, "op %d: AdaIN statistics not loaded", oi);
-      RB_CHECK(c.B <= w.aff_rows, RB_ERR_INVALID,
-               "batch %d exceeds the %d rows of AdaIN statistics (cc.MAX_BATCH_SIZE)", c.B, w.aff_rows);
-      return launch_affine_f32(x, w.aff_a, w.aff_b, c.B, c.s);
+      const int b0 = c.h->cur_b0;
+      RB_CHECK(b0 + c.B <= w.aff_rows, RB_ERR_INVALID,
+               "batch %d exceeds the %d rows of AdaIN statistics (cc.MAX_BATCH_SIZE)", b0 + c.B, w.aff_rows);
+      bool apply = true;
+      OpWeights& wm = c.h->w[oi];
+      const size_t ro = (size_t)b0 * op.c_in;
+      int rc = adain_step(c.h, wm, op.c_in, c.s, [&](float* mean_t, float* std_t, int count) -> int {
+        return launch_adain_stats_f32(x, c.B, mean_t + ro, std_t + ro, count, c.s);
+      }, &apply);
+      if (rc) return rc;
+      return apply ? launch_affine_f32(x, w.aff_a + ro, w.aff_b + ro, c.B, c.s) : RB_OK;
+    }
     case RB_OP_HEAD_V2:
       return launch_head_v2_f32(x, op.src2 >= 0 ? c.v[op.src2] : View(), y, c.B, op.c_out, op.k, c.s);
     case RB_OP_HEAD_V1:
@@ -149,6 +158,7 @@ static int run_offline_f32(rb_handle* h, int op_begin, int op_end, int in_slot, 
   for (int b0 = 0; b0 < B; b0 += mb) {
     const int nb = std::min(mb, B - b0);
     RunCtx c{h, nb, F, std::vector<View>(ns), s, false, nullptr, 0};
+    h->cur_b0 = b0;
     for (auto& pb : h->pool) pb.busy = false;
     std::fill(buf_of.begin(), buf_of.end(), -1);
     auto make_view = [&](int sl, float* p) {
@@ -196,7 +206,40 @@ static int run_offline_f32(rb_handle* h, int op_begin, int op_end, int in_slot, 
         }
     }
   }
+  h->cur_b0 = 0;
+  adain_finalize(h, op_begin, op_end);
   return RB_OK;
+}
+
+// ---------------------------------------------------------------------------- AdaIN learning
+int adain_step(rb_handle* h, OpWeights& w, int C, cudaStream_t s,
+               const std::function<int(float*, float*, int)>& stats_fn, bool* apply) {
+  *apply = true;
+  if (!w.stats) return RB_OK;                    // plain a / b tables (RB_W_AFFINE_A / _B): always applied
+  const size_t n = (size_t)w.aff_rows * C;
+  int rc = RB_OK;
+  if (h->adain_learn_y) {                        // blocks.py:897-905: learn the target, pass x through
+    if ((rc = stats_fn(w.stats + 2 * n, w.stats + 3 * n, w.ny))) return rc;
+    w.touch_y = true;
+    *apply = false;
+  } else if (h->adain_learn_x) {                 // :908-914, then the transfer with the new statistics
+    if ((rc = stats_fn(w.stats, w.stats + n, w.nx))) return rc;
+    w.touch_x = true;
+  }
+  const bool active = (w.nx + (w.touch_x ? 1 : 0)) > 0 && (w.ny + (w.touch_y ? 1 : 0)) > 0;
+  if (w.touch_x || w.touch_y)
+    if ((rc = launch_adain_ab(w.stats, w.aff_rows, C, active ? 1 : 0, w.aff_a, w.aff_b, s))) return rc;
+  if (!active) *apply = false;                   // :916: identity until both sides have statistics
+  return RB_OK;
+}
+
+void adain_finalize(rb_handle* h, int ob, int oe) {
+  for (int i = ob; i < oe && i < (int)h->w.size(); ++i) {
+    OpWeights& w = h->w[i];
+    if (w.touch_x) ++w.nx;
+    if (w.touch_y) ++w.ny;
+    w.touch_x = w.touch_y = false;
+  }
 }
 
 }  // namespace rb
@@ -249,7 +292,7 @@ int rb_destroy(rb_handle* h) {
   cudaSetDevice(h->device);
   tc_free(h);
   for (auto& w : h->w) {
-    cudaFree(w.w); cudaFree(w.bias); cudaFree(w.alpha); cudaFree(w.aff_a); cudaFree(w.aff_b);
+    cudaFree(w.w); cudaFree(w.bias); cudaFree(w.alpha); cudaFree(w.aff_a); cudaFree(w.aff_b); cudaFree(w.stats);
     cudaFree(w.cond);
   }
   cudaFree(h->codebooks); cudaFree(h->cb_norms); cudaFree(h->rvq_ws);
@@ -346,6 +389,23 @@ int rb_load_weights(rb_handle* h, const rb_tensor_desc* t, int n) {
         RB_CHECK(op.kind == RB_OP_AFFINE && d.numel % op.c_in == 0, RB_ERR_INVALID, "op %d: affine size", d.op);
         w.aff_rows = (int)(d.numel / op.c_in);
         rc = upload(d.data, d.numel, d.role == RB_W_AFFINE_A ? &w.aff_a : &w.aff_b);
+        break;
+      }
+      case RB_W_ADAIN_STATS: {
+        // [4][rows][C] (mean_x, std_x, mean_y, std_y) followed by num_update_x, num_update_y
+        RB_CHECK(op.kind == RB_OP_AFFINE && d.numel > 2 && (d.numel - 2) % (4 * op.c_in) == 0, RB_ERR_INVALID,
+                 "op %d: AdaIN statistics size", d.op);
+        w.aff_rows = (int)((d.numel - 2) / (4 * op.c_in));
+        const int64_t n = (int64_t)w.aff_rows * op.c_in;
+        if ((rc = upload(d.data, 4 * n, &w.stats))) break;
+        w.nx = (int)d.data[4 * n];
+        w.ny = (int)d.data[4 * n + 1];
+        w.touch_x = w.touch_y = false;
+        std::vector<float> zero((size_t)n, 0.f);
+        if ((rc = upload(zero.data(), n, &w.aff_a))) break;
+        if ((rc = upload(zero.data(), n, &w.aff_b))) break;
+        rc = launch_adain_ab(w.stats, w.aff_rows, op.c_in, (w.nx > 0 && w.ny > 0) ? 1 : 0, w.aff_a, w.aff_b, 0);
+        if (!rc) RB_CUDA(cudaStreamSynchronize(0));
         break;
       }
       case RB_W_COND:
@@ -580,6 +640,58 @@ int rb_op_times(rb_handle* h, float* ms, int n) {
     cudaEventDestroy(e.b);
   }
   h->events.clear();
+  return RB_OK;
+}
+
+// ScriptedRAVE.update_adain (scripts/export.py:248-265): learn_source -> learn_x, learn_target -> learn_y
+// of every AdaIN site; resets as AdaptiveInstanceNormalization.reset_x / reset_y (blocks.py:875-883).
+int rb_adain_update(rb_handle* h, int learn_source, int learn_target, int reset_source, int reset_target) {
+  RB_CHECK(h, RB_ERR_INVALID, "rb_adain_update: null handle");
+  RB_CUDA(cudaSetDevice(h->device));
+  h->adain_learn_x = learn_source != 0;
+  h->adain_learn_y = learn_target != 0;
+  for (size_t i = 0; i < h->w.size(); ++i) {
+    OpWeights& w = h->w[i];
+    if (h->ops[i].kind != RB_OP_AFFINE) continue;
+    RB_CHECK(w.stats || !(learn_source || learn_target || reset_source || reset_target), RB_ERR_STATE,
+             "op %d: AdaIN statistics were loaded as fixed a / b tables (RB_W_ADAIN_STATS is needed to learn)", (int)i);
+    if (!w.stats) continue;
+    const int C = h->ops[i].c_in;
+    const size_t n = (size_t)w.aff_rows * C;
+    std::vector<float> zeros(n, 0.f), ones(n, 1.f);
+    if (reset_source) {
+      RB_CUDA(cudaMemcpy(w.stats, zeros.data(), n * 4, cudaMemcpyHostToDevice));
+      RB_CUDA(cudaMemcpy(w.stats + n, ones.data(), n * 4, cudaMemcpyHostToDevice));
+      w.nx = 0;
+    }
+    if (reset_target) {
+      RB_CUDA(cudaMemcpy(w.stats + 2 * n, zeros.data(), n * 4, cudaMemcpyHostToDevice));
+      RB_CUDA(cudaMemcpy(w.stats + 3 * n, ones.data(), n * 4, cudaMemcpyHostToDevice));
+      w.ny = 0;
+    }
+    if (reset_source || reset_target) {
+      int rc = launch_adain_ab(w.stats, w.aff_rows, C, (w.nx > 0 && w.ny > 0) ? 1 : 0, w.aff_a, w.aff_b, 0);
+      if (rc) return rc;
+      RB_CUDA(cudaStreamSynchronize(0));
+    }
+  }
+  return RB_OK;
+}
+
+// Reads back the statistics of AdaIN op `op` (host buffer of 4 * rows * C floats) and its counters.
+int rb_adain_get_stats(rb_handle* h, int op, float* stats, int64_t numel, int* num_update_x, int* num_update_y) {
+  RB_CHECK(h && op >= 0 && op < (int)h->ops.size() && h->ops[op].kind == RB_OP_AFFINE, RB_ERR_INVALID,
+           "rb_adain_get_stats: op %d is not an AdaIN site", op);
+  const OpWeights& w = h->w[op];
+  RB_CHECK(w.stats, RB_ERR_STATE, "op %d: no AdaIN statistics loaded", op);
+  const int64_t n = 4ll * w.aff_rows * h->ops[op].c_in;
+  RB_CHECK(!stats || numel == n, RB_ERR_INVALID, "rb_adain_get_stats: buffer of %lld floats, need %lld",
+           (long long)numel, (long long)n);
+  RB_CUDA(cudaSetDevice(h->device));
+  RB_CUDA(cudaDeviceSynchronize());
+  if (stats) RB_CUDA(cudaMemcpy(stats, w.stats, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  if (num_update_x) *num_update_x = w.nx;
+  if (num_update_y) *num_update_y = w.ny;
   return RB_OK;
 }
 

@@ -2,6 +2,7 @@
 #pragma once
 #include <atomic>
 #include <map>
+#include <functional>
 #include <vector>
 
 #include "common.cuh"
@@ -23,6 +24,13 @@ struct RunCtx {
 };
 
 int exec_op_f32(RunCtx& c, int oi);
+struct OpWeights;
+// AdaIN.forward in eval mode around the transfer (blocks.py:893-919); `stats_fn(mean, std, count)`
+// updates the running statistics of rows [b0, b0 + B) from the op's input.  Sets *apply when the
+// transfer a*x + b has to run.  adain_finalize counts the updates of ops [ob, oe) once per call.
+int adain_step(rb_handle* h, OpWeights& w, int C, cudaStream_t s,
+               const std::function<int(float*, float*, int)>& stats_fn, bool* apply);
+void adain_finalize(rb_handle* h, int ob, int oe);
 int pool_get(rb_handle* h, size_t bytes, int* idx);   // offline workspace pool (engine.cu)
 
 // RAII: records a start/stop event pair for op `oi` when profiling is on
@@ -39,6 +47,11 @@ struct OpWeights {
   float* aff_a = nullptr;   // [rows][C]
   float* aff_b = nullptr;
   int aff_rows = 0;
+  // AdaIN statistics (blocks.py:860-868): [4][aff_rows][C] = mean_x, std_x, mean_y, std_y; the
+  // update counters live on the host (their increments never depend on data)
+  float* stats = nullptr;
+  int nx = 0, ny = 0;
+  bool touch_x = false, touch_y = false;   // learned during the running call: counted once at its end
   float* cond = nullptr;
   // host copies kept for the bf16 tensor-core packer (tc_engine.cu)
   std::vector<float> w_host;   // folded fp32 [c_out][c_in][k] (PQMF: as loaded)
@@ -72,6 +85,8 @@ struct rb_handle {
 
   std::vector<rb::PoolBuf> pool;  // offline activation workspace
   int microbatch = 0;
+  int cur_b0 = 0;               // first stream of the microbatch being executed (per-stream tables)
+  bool adain_learn_x = false, adain_learn_y = false;   // export.py:248-265 learn_source / learn_target
 
   // streaming state arena: one persistent buffer per slot
   bool stream_ready = false;

@@ -286,6 +286,67 @@ int launch_affine_f32(const View& x, const float* a, const float* b, int B, cuda
   return RB_OK;
 }
 
+// Block-wide sum (256 threads), result in every thread.
+__device__ __forceinline__ float block_sum_256(float v, float* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) t += sh[w];
+  return t;
+}
+// One CTA per (stream, channel) row: two passes (mean, then centred sum of squares).
+__global__ void __launch_bounds__(256)
+adain_stats_f32_kernel(View x, float* __restrict__ mean_t, float* __restrict__ std_t, int count) {
+  __shared__ float sh[8];
+  const int row = blockIdx.x;                            // b*C + c
+  const float* p = x.p + (size_t)row * x.ld + x.hist;
+  float s1 = 0.f;
+  for (int t = threadIdx.x; t < x.n; t += 256) s1 += p[t];
+  const float mean = block_sum_256(s1, sh) / (float)x.n;
+  float s2 = 0.f;
+  for (int t = threadIdx.x; t < x.n; t += 256) { const float d = p[t] - mean; s2 = fmaf(d, d, s2); }
+  const float var = block_sum_256(s2, sh) / (float)(x.n - 1);          // torch.std: unbiased
+  if (threadIdx.x == 0) {
+    const float inv = 1.f / (float)(count + 1);
+    mean_t[row] += (mean - mean_t[row]) * inv;
+    std_t[row] += (sqrtf(var) - std_t[row]) * inv;
+  }
+}
+
+int launch_adain_stats_f32(const View& x, int B, float* mean_t, float* std_t, int count, cudaStream_t s) {
+  if (x.n <= 0 || B <= 0) return RB_OK;
+  adain_stats_f32_kernel<<<B * x.C, 256, 0, s>>>(x, mean_t, std_t, count);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
+__global__ void adain_ab_kernel(const float* __restrict__ st, int n, int active, float* __restrict__ a,
+                                float* __restrict__ b) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float av = 1.f, bv = 0.f;
+  if (active) {
+    av = st[3 * n + i] / (st[n + i] + 1e-5f);            // std_y / (std_x + 1e-5)
+    bv = st[2 * n + i] - st[i] * av;                     // mean_y - mean_x * a
+  }
+  a[i] = av;
+  b[i] = bv;
+}
+
+int launch_adain_ab(const float* stats, int rows, int C, int active, float* a, float* b, cudaStream_t s) {
+  const int n = rows * C;
+  if (n <= 0) return RB_OK;
+  adain_ab_kernel<<<(n + 255) / 256, 256, 0, s>>>(stats, n, active, a, b);
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
+  return RB_OK;
+}
+
 // GeneratorV2.forward tail (blocks.py:699-707): x, amp = split; tanh(x*sigmoid(amp) + noise)
 __global__ void head_v2_f32_kernel(View w, View nz, View y, int data, int am) {
   const int b = blockIdx.z, c = blockIdx.y;

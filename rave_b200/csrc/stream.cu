@@ -64,6 +64,7 @@ int run_stream_ops(rb_handle* h, int ob, int oe, int B, int F, int out_slot, flo
       if (rc) return rc;
     }
   }
+  adain_finalize(h, ob, oe);
   return RB_OK;
 }
 

@@ -545,6 +545,36 @@ __global__ void affine_gm_kernel(Buf x, const float* __restrict__ a, const float
     *q = __float2bfloat16_rn(fmaf(__bfloat162float(*q), a[(size_t)b * C + c], bb[(size_t)b * C + c]));
   }
 }
+// AdaIN running statistics on a group-major tensor: one CTA per (stream, channel), two passes.
+__global__ void __launch_bounds__(256)
+adain_stats_gm_kernel(Buf x, int C, float* __restrict__ mean_t, float* __restrict__ std_t, int count) {
+  __shared__ float sh[8];
+  const int b = blockIdx.x / C, c = blockIdx.x - b * C;
+  const __nv_bfloat16* p = x.p + eidx(x, b, 0, c);        // element t sits 8 * t further on
+  auto bsum = [&](float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sh[w];
+    return t;
+  };
+  float s1 = 0.f;
+  for (int t = threadIdx.x; t < x.n; t += 256) s1 += __bfloat162float(p[(size_t)t * 8]);
+  const float mean = bsum(s1) / (float)x.n;
+  float s2 = 0.f;
+  for (int t = threadIdx.x; t < x.n; t += 256) { const float d = __bfloat162float(p[(size_t)t * 8]) - mean; s2 = fmaf(d, d, s2); }
+  const float var = bsum(s2) / (float)(x.n - 1);
+  if (threadIdx.x == 0) {
+    const float inv = 1.f / (float)(count + 1);
+    const int row = blockIdx.x;
+    mean_t[row] += (mean - mean_t[row]) * inv;
+    std_t[row] += (sqrtf(var) - std_t[row]) * inv;
+  }
+}
 // GeneratorV2.forward tail (blocks.py:699-707) + reverse_half of the synthesis bank input
 __global__ void head_v2_gm_kernel(Buf w, Buf nz, Buf y, int data, int am, int B) {
   const size_t total = (size_t)B * y.n * y.cp;
@@ -767,10 +797,23 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
     case RB_OP_AFFINE: {
       const OpWeights& w = h->w[i];
       RB_CHECK(w.aff_a && w.aff_b, RB_ERR_STATE, "op %d: AdaIN statistics not loaded", i);
-      RB_CHECK(B <= w.aff_rows, RB_ERR_INVALID,
-               "batch %d exceeds the %d rows of AdaIN statistics (cc.MAX_BATCH_SIZE)", B, w.aff_rows);
+      const int b0 = h->cur_b0;
+      RB_CHECK(b0 + B <= w.aff_rows, RB_ERR_INVALID,
+               "batch %d exceeds the %d rows of AdaIN statistics (cc.MAX_BATCH_SIZE)", b0 + B, w.aff_rows);
       const Buf& x = bufs[op.src];
-      RB_LAUNCH_EW(affine_gm_kernel, (size_t)B * x.n * x.cp, s, x, w.aff_a, w.aff_b, op.c_in, B);
+      RB_CHECK(x.cp != 1, RB_ERR_UNSUPPORTED, "AdaIN on an audio-layout tensor");
+      const size_t ro = (size_t)b0 * op.c_in;
+      bool apply = true;
+      int rc = adain_step(h, h->w[i], op.c_in, s, [&](float* mean_t, float* std_t, int count) -> int {
+        if (x.n > 0 && B > 0) {
+          adain_stats_gm_kernel<<<B * op.c_in, 256, 0, s>>>(x, op.c_in, mean_t + ro, std_t + ro, count);
+          ++g_launches;
+          RB_CUDA(cudaGetLastError());
+        }
+        return (int)RB_OK;
+      }, &apply);
+      if (rc) return rc;
+      if (apply) RB_LAUNCH_EW(affine_gm_kernel, (size_t)B * x.n * x.cp, s, x, w.aff_a + ro, w.aff_b + ro, op.c_in, B);
       return RB_OK;
     }
     case RB_OP_HEAD_V2: {
@@ -843,6 +886,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
   for (int b0 = 0; b0 < B; b0 += mb) {
     const int nb = std::min(mb, B - b0);
     std::vector<Buf> bufs(ns);
+    h->cur_b0 = b0;
     for (auto& pb : h->pool) pb.busy = false;
     std::fill(buf_of.begin(), buf_of.end(), -1);
     auto alloc_slot = [&](int sl) -> int {
@@ -917,6 +961,8 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
                    (__nv_bfloat16*)out + (size_t)b0 * out_ch * b.n, out_ch, nb);
     }
   }
+  h->cur_b0 = 0;
+  adain_finalize(h, ob, oe);
   return RB_OK;
 }
 
@@ -1079,6 +1125,7 @@ int tc_stream_run(rb_handle* h, int ob, int oe, int B, int F, const void* in, vo
       ++g_launches;
     }
   }
+  adain_finalize(h, ob, oe);
   return RB_OK;
 }
 

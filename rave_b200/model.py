@@ -72,6 +72,7 @@ class RAVE:
         self._lib = capi.load_library()
         self._h = C.c_void_p()
         self._keep = []
+        self._adain_rows = {}
         slots = (capi.RbSlot * len(spec.slots))(*[capi.RbSlot(s.channels, s.per_frame, s.hist, 0) for s in spec.slots])
         ops = (capi.RbOp * len(spec.ops))()
         for i, o in enumerate(spec.ops):
@@ -139,6 +140,8 @@ class RAVE:
             arr[j].op, arr[j].role = int(op), int(role)
             arr[j].data = a.ctypes.data_as(C.POINTER(C.c_float))
             arr[j].numel = a.size
+            if int(role) == capi.RB_W_ADAIN_STATS:           # rows of the statistics tables (cc.MAX_BATCH_SIZE)
+                self._adain_rows[int(op)] = (a.size - 2) // (4 * self.spec.ops[int(op)].c_in)
         capi.check(self._lib.rb_load_weights(self._h, arr, len(items)))
 
     def load_state_dict(self, state_dict, strict=True):
@@ -294,6 +297,36 @@ class RAVE:
         buf = (C.c_float * n)()
         capi.check(self._lib.rb_op_times(self._h, buf, n))
         return list(buf)
+
+    # ------------------------------------------------------------------ AdaIN statistics
+    def update_adain(self, learn_source=False, learn_target=False, reset_source=False, reset_target=False):
+        """ScriptedRAVE.update_adain (scripts/export.py:248-265): learn_source / learn_target set
+        learn_x / learn_y of every AdaptiveInstanceNormalization site (blocks.py:893-919), the
+        resets restore mean 0 / std 1 / zero updates.  While a flag is set every call folds the
+        statistics of its input into the running buffers, on the device."""
+        capi.check(self._lib.rb_adain_update(self._h, int(bool(learn_source)), int(bool(learn_target)),
+                                             int(bool(reset_source)), int(bool(reset_target))))
+
+    def adain_state(self):
+        """{reference buffer name: tensor} of every AdaIN site (mean_x, std_x, mean_y, std_y
+        [MAX_BATCH_SIZE, C, 1] and the two update counters), read back from the device."""
+        from .netspec import OP_AFFINE
+        out = {}
+        for i, op in enumerate(self.spec.ops):
+            if op.kind != OP_AFFINE:
+                continue
+            nx, ny = C.c_int(), C.c_int()
+            rows = self._adain_rows[i]
+            buf = np.empty(4 * rows * op.c_in, np.float32)
+            capi.check(self._lib.rb_adain_get_stats(self._h, i, buf.ctypes.data_as(C.POINTER(C.c_float)), buf.size,
+                                                    C.byref(nx), C.byref(ny)))
+            p = op.params["adain"]
+            for j, name in enumerate(("mean_x", "std_x", "mean_y", "std_y")):
+                out[p + name] = torch.from_numpy(buf[j * rows * op.c_in:(j + 1) * rows * op.c_in]
+                                                 .reshape(rows, op.c_in, 1).copy())
+            out[p + "num_update_x"] = torch.tensor([float(nx.value)])
+            out[p + "num_update_y"] = torch.tensor([float(ny.value)])
+        return out
 
     def set_microbatch(self, streams):
         capi.check(self._lib.rb_set_microbatch(self._h, int(streams)))

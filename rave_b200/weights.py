@@ -94,15 +94,13 @@ def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True):
                 p = P["adain"]
                 mx, sx = _np(sd[p + "mean_x"])[..., 0], _np(sd[p + "std_x"])[..., 0]
                 my, sy = _np(sd[p + "mean_y"])[..., 0], _np(sd[p + "std_y"])[..., 0]
-                active = float(_np(sd[p + "num_update_x"]).reshape(-1)[0]) and \
-                    float(_np(sd[p + "num_update_y"]).reshape(-1)[0])
-                if active:
-                    a = sy / (sx + np.float32(1e-5))
-                    bsh = my - mx * a
-                else:
-                    a, bsh = np.ones_like(mx), np.zeros_like(mx)
-                out.append((i, capi.RB_W_AFFINE_A, a))
-                out.append((i, capi.RB_W_AFFINE_B, bsh))
+                # the four buffers + the two counters travel as they are (blocks.py:860-868): the engine
+                # derives a = std_y / (std_x + 1e-5), b = mean_y - mean_x * a and can go on learning
+                nx = float(_np(sd[p + "num_update_x"]).reshape(-1)[0])
+                ny = float(_np(sd[p + "num_update_y"]).reshape(-1)[0])
+                stats = np.concatenate([np.ascontiguousarray(t, np.float32).reshape(-1) for t in (mx, sx, my, sy)] +
+                                       [np.array([nx, ny], np.float32)])
+                out.append((i, capi.RB_W_ADAIN_STATS, stats))
             elif op.kind == OP_CONCAT:
                 if "speaker" in sd:
                     out.append((i, capi.RB_W_COND, _np(sd["speaker"]).reshape(-1)))

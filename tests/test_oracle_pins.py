@@ -172,3 +172,42 @@ def test_oracle_matches_live_reference(name):
         y = m.decode(z)
     assert rel_l2(o.encode(x).numpy(), z.numpy()) < 2e-5
     assert rel_l2(o.decode(z).numpy(), y.numpy()) < 5e-5
+
+
+def _ref_update_adain(m, blocks, learn_source=False, learn_target=False, reset_source=False, reset_target=False):
+    """scripts/export.py:248-265 (ScriptedRAVE.update_adain) applied to the live reference modules."""
+    for mod in m.modules():
+        if isinstance(mod, blocks.AdaptiveInstanceNormalization):
+            mod.learn_x.zero_()
+            mod.learn_y.zero_()
+            if learn_target:
+                mod.learn_y.add_(1)
+            if learn_source:
+                mod.learn_x.add_(1)
+            if reset_target:
+                mod.reset_y()
+            if reset_source:
+                mod.reset_x()
+
+
+@needs_ref
+@pytest.mark.reference
+def test_oracle_adain_statistic_learning_matches_live_reference():
+    """AdaIN learn_y / learn_x running statistics and the transfer that follows (blocks.py:893-919)."""
+    cfg = C.NAMED["v3"](4)
+    m = R.build_reference(cfg)
+    R.fill_deterministic(m, 5)
+    blocks = R.load("blocks")
+    o = OracleRAVE(cfg, {k: v.detach().clone() for k, v in m.state_dict().items()})
+    xs = [torch.from_numpy(recipe_input((2, 1, 4096), 20 + i)) for i in range(5)]
+    plan = [dict(reset_source=True, reset_target=True, learn_target=True), dict(learn_target=True),
+            dict(learn_source=True), dict(learn_source=True), dict()]
+    for x, kw in zip(xs, plan):
+        _ref_update_adain(m, blocks, **kw)
+        o.update_adain(**kw)
+        with torch.no_grad():
+            y = m.decode(m.encode(x))
+        assert rel_l2(o.forward(x).numpy(), y.numpy()) < 3e-4      # random-init Snake net: fp32 noise grows
+    for k, v in m.state_dict().items():
+        if any(t in k for t in ("mean_x", "std_x", "mean_y", "std_y", "num_update")):
+            assert torch.allclose(o.sd[k], v, rtol=1e-3, atol=1e-3), k
