@@ -179,6 +179,38 @@ int rb_set_microbatch(rb_handle* h, int streams);       /* 0 = automatic */
 int rb_adain_update(rb_handle* h, int learn_source, int learn_target, int reset_source, int reset_target);
 /* stats: host buffer of 4 * max_streams * C floats (mean_x, std_x, mean_y, std_y) or NULL. */
 int rb_adain_get_stats(rb_handle* h, int op, float* stats, int64_t numel, int* num_update_x, int* num_update_y);
+/* Speaker encoder `SpeakerRAVE` (rave/CombinedRave.py:200-328; bound by v2.gin:98 / onnx.gin:20), the
+ * step before the path: model.py:246-247 computes speaker = speaker_encoder(pqmf(utterance)), the
+ * vector RB_W_COND carries.  Offline, fp32.  Layers in forward order; weights are the module's own
+ * tensors, [c_out][c_in][k] (fc6: [256][1536]). */
+typedef enum rb_speaker_layer {
+  RB_SPK_IN = 0,                                       /* in_layer        16 -> 128, k7           */
+  RB_SPK_L2_DIL = 1, RB_SPK_L2_PW = 2, RB_SPK_L2_DOWN = 3,   /* layer2: DilatedUnit d=1, 128 -> 256 /4 */
+  RB_SPK_L3_DIL = 4, RB_SPK_L3_PW = 5, RB_SPK_L3_DOWN = 6,   /* layer3: d=3, 256 -> 256 /4             */
+  RB_SPK_L4_DIL = 7, RB_SPK_L4_PW = 8, RB_SPK_L4_DOWN = 9,   /* layer4: d=5, 256 -> 256 /2             */
+  RB_SPK_CAT = 10,                                     /* cat_layer       256 -> 256, k1          */
+  RB_SPK_OUT = 11,                                     /* out_layer       768 -> 768, k3          */
+  RB_SPK_ATT1 = 12, RB_SPK_ATT2 = 13,                  /* attention.0 2304 -> 128, attention.3 128 -> 768 */
+  RB_SPK_FC6 = 14,                                     /* fc6 Linear(1536, 256)                   */
+  RB_SPK_N_LAYERS = 15
+} rb_speaker_layer;
+typedef struct rb_speaker rb_speaker;
+int rb_speaker_create(int device, rb_speaker** out);
+int rb_speaker_destroy(rb_speaker* s);
+int rb_speaker_load(rb_speaker* s, int layer, const float* weight, int64_t w_numel, const float* bias,
+                    int64_t b_numel);                  /* HOST pointers */
+/* which = 0: attention.2 BatchNorm1d(128); 1: bn5 BatchNorm1d(1536); eval mode (running statistics) */
+int rb_speaker_load_bn(rb_speaker* s, int which, const float* gamma, const float* beta, const float* mean,
+                       const float* var, int n, float eps);
+/* x: device fp32 [B,16,T] PQMF bands of the utterance (T % 32 == 0), emb: device fp32 [B,256];
+ * enqueued on `stream`, does not synchronise (except to grow its workspace). */
+int rb_speaker_embed(rb_speaker* s, const float* x, int B, int T, float* emb, void* stream);
+/* The utterance itself: w = CachedPQMF.forward_conv.weight [16][1][k] (host), then audio: device fp32
+ * [B,1,T], T % 512 == 0 -> pqmf (pqmf.py:269-273) -> rb_speaker_embed. */
+int rb_speaker_load_pqmf(rb_speaker* s, const float* w, int n_band, int k);
+int rb_speaker_embed_audio(rb_speaker* s, const float* audio, int B, int T, float* emb, void* stream);
+int rb_speaker_launches(rb_speaker* s, int64_t* count);
+
 /* Per-op device timing (CUDA events on the launching stream around every op of the
  * program).  enable!=0 starts recording; rb_op_times synchronises, writes the accumulated
  * milliseconds per op (n = number of ops) and clears the record. */

@@ -79,6 +79,15 @@ EXPORTS = {
     "rb_adain_update": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int],
     "rb_adain_get_stats": [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int64, C.POINTER(C.c_int),
                            C.POINTER(C.c_int)],
+    "rb_speaker_create": [C.c_int, C.POINTER(C.c_void_p)],
+    "rb_speaker_destroy": [C.c_void_p],
+    "rb_speaker_load": [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int64, C.POINTER(C.c_float), C.c_int64],
+    "rb_speaker_load_bn": [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float),
+                           C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_int, C.c_float],
+    "rb_speaker_load_pqmf": [C.c_void_p, C.POINTER(C.c_float), C.c_int, C.c_int],
+    "rb_speaker_embed": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
+    "rb_speaker_embed_audio": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
+    "rb_speaker_launches": [C.c_void_p, C.POINTER(C.c_int64)],
     "rb_profile_ops": [C.c_void_p, C.c_int],
     "rb_op_times": [C.c_void_p, C.POINTER(C.c_float), C.c_int],
     "rb_last_error": [],
