@@ -84,11 +84,30 @@ def pqmf_fixture():
     print("wrote pqmf_bank", tuple(pq.hk.shape))
 
 
+@torch.no_grad()
+def speaker_fixture():
+    """SpeakerRAVE (CombinedRave.py:200-328) on recipe weights: bands -> embedding, and the
+    model.py:246-247 chain utterance -> CachedPQMF -> embedding."""
+    cc = R.cc
+    cc.use_cached_conv(False)
+    cc.set_padding_mode("centered")
+    spk = R.load("CombinedRave").SpeakerRAVE().eval()
+    R.fill_deterministic(spk, SEED)
+    pq = R.load("pqmf").CachedPQMF(attenuation=100, n_band=16)
+    bands = torch.from_numpy(recipe_input((2, 16, 2048), 41, scale=1.0))
+    audio = torch.from_numpy(recipe_input((1, 1, 32768), 42, scale=0.3))
+    _save("speaker", dict(kind="speaker"), spk,
+          dict(bands_seed=np.int64(41), bands_shape=np.array([2, 16, 2048]), emb=spk(bands).numpy(),
+               audio_seed=np.int64(42), audio_shape=np.array([1, 1, 32768]),
+               emb_audio=spk(pq(audio)).numpy()))
+
+
 def main():
     if not R.available():
         sys.exit("reference tree not available; golden files can only be made in the build container")
     torch.manual_seed(0)
     pqmf_fixture()
+    speaker_fixture()
     offline_and_stream("v2_c8", C.v2(8), 2, 16384, 2048)
     offline_and_stream("v2causal_c8", C.v2(8, causal=True), 2, 16384, 2048)
     offline_and_stream("v3_c8", C.v3(8), 2, 16384, 2048)

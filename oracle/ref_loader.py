@@ -78,6 +78,14 @@ def _install_stubs():
             pl.Callback = object
             pl.LightningModule = torch.nn.Module
             sys.modules["pytorch_lightning"] = pl
+    if "torchaudio" not in sys.modules:            # CombinedRave.py:16 imports Spectrogram (unused by SpeakerRAVE)
+        try:
+            import torchaudio  # noqa: F401
+        except Exception:
+            ta, tt = types.ModuleType("torchaudio"), types.ModuleType("torchaudio.transforms")
+            tt.Spectrogram = object
+            ta.transforms = tt
+            sys.modules["torchaudio"], sys.modules["torchaudio.transforms"] = ta, tt
     sys.modules["cached_conv"] = cc
     # scipy shim: pqmf.py:10 imports scipy.signal.kaiser (moved to scipy.signal.windows) and
     # pqmf.py:69 calls firwin(..., nyq=pi) (keyword replaced by fs=2*nyq).
@@ -110,6 +118,8 @@ def load(name: str):
         sys.modules["rave"] = pkg
     if name == "blocks":
         load("core")
+    if name == "CombinedRave":
+        load("pqmf")
     path = os.path.join(REFERENCE_ROOT, "rave", name + ".py")
     spec = importlib.util.spec_from_file_location("rave." + name, path)
     mod = importlib.util.module_from_spec(spec)

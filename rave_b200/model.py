@@ -104,7 +104,7 @@ class RAVE:
         self.encoder = SimpleNamespace(noise_augmentation=0, enabled=int(spec.rvq is not None),
                                        rvq=_RVQ(self) if spec.rvq else None, kind=spec.encoder_type)
         self.decoder = SimpleNamespace(latent_size=spec.dec_latent_size)
-        self.speaker_encoder = None   # SpeakerRAVE is upstream of the path
+        self.speaker_encoder = None   # see load_speaker_encoder (rave_b200/speaker.py)
         self.latent_pca = np.eye(spec.latent_size, dtype=np.float32)
         self.latent_mean = np.zeros(spec.latent_size, dtype=np.float32)
         self.fidelity = np.zeros(spec.latent_size, dtype=np.float32)
@@ -153,6 +153,25 @@ class RAVE:
     def set_speaker(self, emb):
         """`self.speaker` of the reference (model.py:246-247): the fixed [1, S, 1] embedding."""
         self.load_state_dict({"speaker": emb}, strict=False)
+
+    def load_speaker_encoder(self, state_dict):
+        """model.py:164-174: build the speaker encoder (CombinedRave.SpeakerRAVE) from its state_dict."""
+        from .speaker import N_BANDS, SpeakerRAVE
+        wa = np.asarray(self.pqmf.forward_conv_weight, dtype=np.float32)
+        wa = wa.reshape(self.spec.n_band, 1, -1) if self.spec.n_band == N_BANDS else None
+        self.speaker_encoder = SpeakerRAVE(state_dict, pqmf_weight=wa, device=self.device)
+        return self.speaker_encoder
+
+    def set_speaker_from_audio(self, audio):
+        """model.py:246-247: speaker = speaker_encoder(pqmf(utterance)).unsqueeze(2), on the device.
+        audio: [1, 1, T].  Returns the [1, 256] embedding it installed."""
+        if self.speaker_encoder is None:
+            raise RuntimeError("no speaker encoder: call load_speaker_encoder(state_dict) first")
+        if audio.dim() != 3 or audio.shape[0] != 1:
+            raise ValueError("the reference keeps one speaker embedding: audio must be [1, 1, T]")
+        emb = self.speaker_encoder.embed_audio(audio)
+        self.set_speaker(emb.reshape(-1))
+        return emb
 
     def eval(self):
         return self

@@ -277,3 +277,63 @@ def test_adain_statistic_learning_vs_oracle(dtype):
             assert rel_l2(v[:3].numpy(), ref[:3].numpy()) < tol, k
         n_checked += 1
     assert n_checked >= 6
+
+
+# ----------------------------------------------------------------------------- speaker encoder
+def _speaker():
+    from oracle import rave_oracle as O
+    from oracle.weights_recipe import recipe_input
+    from rave_b200.speaker import SpeakerRAVE
+    meta, a = load_golden("speaker")
+    sd = golden_state_dict(meta)
+    _, hk = O.pqmf_bank(100, 16)
+    wf, _ = O.pqmf_conv_weights(hk)
+    enc = SpeakerRAVE(sd, pqmf_weight=wf)
+    bands = recipe_input(tuple(int(v) for v in a["bands_shape"]), int(a["bands_seed"].item()), scale=1.0)
+    audio = recipe_input(tuple(int(v) for v in a["audio_shape"]), int(a["audio_seed"].item()), scale=0.3)
+    return enc, {k: torch.from_numpy(v) for k, v in sd.items()}, wf, a, bands, audio
+
+
+def test_speaker_encoder_matches_golden_and_oracle():
+    """CombinedRave.py:297-328 on the device vs the reference's outputs (golden) and the oracle."""
+    from oracle import speaker_oracle as S
+    from oracle.weights_recipe import recipe_input
+    enc, sd, wf, a, bands, audio = _speaker()
+    emb = enc(torch.from_numpy(bands).cuda())
+    assert tuple(emb.shape) == (2, 256) and emb.dtype == torch.float32
+    assert rel_l2(emb.cpu().numpy(), a["emb"]) < F32_TOL
+    emb_a = enc.embed_audio(torch.from_numpy(audio).cuda())
+    assert rel_l2(emb_a.cpu().numpy(), a["emb_audio"]) < F32_TOL
+    # sizes the fixture does not hold: oracle on the same seeded input
+    for B, T in ((1, 64), (3, 4096), (2, 8192 + 32)):
+        x = torch.from_numpy(recipe_input((B, 16, T), 100 + T, scale=1.0))
+        assert rel_l2(enc(x.cuda()).cpu().numpy(), S.speaker_embed(sd, x).numpy()) < F32_TOL, (B, T)
+    x = torch.from_numpy(recipe_input((2, 1, 131072), 77, scale=0.3))     # model.py:30: 131072 samples
+    assert rel_l2(enc.embed_audio(x.cuda()).cpu().numpy(), S.speaker_from_audio(sd, wf, x).numpy()) < F32_TOL
+    assert enc.kernel_launches > 0
+
+
+def test_speaker_encoder_errors_and_rows_independent():
+    enc, sd, wf, a, bands, audio = _speaker()
+    with pytest.raises(ValueError):
+        enc(torch.zeros(1, 16, 100).cuda())           # not a multiple of the strides
+    with pytest.raises(ValueError):
+        enc(torch.zeros(1, 8, 1024).cuda())           # wrong band count
+    with pytest.raises(ValueError):
+        enc.embed_audio(torch.zeros(1, 1, 1000).cuda())
+    x = torch.from_numpy(bands).cuda()
+    both = enc(x)
+    assert torch.equal(enc(x[1:2]), both[1:2])        # rows do not interact (eval-mode batch norm)
+
+
+def test_set_speaker_from_audio_feeds_encode():
+    """model.py:246-247 then :618-620: the embedding of the utterance is what encode() appends."""
+    enc, sd, wf, a, bands, audio = _speaker()
+    m, meta, ga = _model("v2_c8")
+    assert m.cond_channels == 256
+    m.load_speaker_encoder(golden_state_dict(load_golden("speaker")[0]))
+    emb = m.set_speaker_from_audio(torch.from_numpy(audio).cuda())
+    assert rel_l2(emb.cpu().numpy(), a["emb_audio"]) < F32_TOL
+    z = m.encode(torch.from_numpy(golden_input(ga)).cuda())
+    tail = z[:, -256:, :].cpu().numpy()
+    assert np.array_equal(tail, np.broadcast_to(emb.cpu().numpy().reshape(1, 256, 1), tail.shape))

@@ -211,3 +211,37 @@ def test_oracle_adain_statistic_learning_matches_live_reference():
     for k, v in m.state_dict().items():
         if any(t in k for t in ("mean_x", "std_x", "mean_y", "std_y", "num_update")):
             assert torch.allclose(o.sd[k], v, rtol=1e-3, atol=1e-3), k
+
+
+# ----------------------------------------------------------------------------- speaker encoder
+def _speaker_golden():
+    meta, a = load_golden("speaker")
+    sd = {k: torch.from_numpy(v) for k, v in golden_state_dict(meta).items()}
+    bands = torch.from_numpy(recipe_input(tuple(int(v) for v in a["bands_shape"]), int(a["bands_seed"].item()), scale=1.0))
+    audio = torch.from_numpy(recipe_input(tuple(int(v) for v in a["audio_shape"]), int(a["audio_seed"].item()), scale=0.3))
+    return sd, a, bands, audio
+
+
+def test_speaker_oracle_matches_golden():
+    """oracle/speaker_oracle.py vs the outputs of the real SpeakerRAVE / CachedPQMF (make_golden)."""
+    from oracle import speaker_oracle as S
+    sd, a, bands, audio = _speaker_golden()
+    assert rel_l2(S.speaker_embed(sd, bands).numpy(), a["emb"]) < 1e-5
+    _, hk = O.pqmf_bank(100, 16)
+    wf, _ = O.pqmf_conv_weights(hk)
+    assert rel_l2(S.speaker_from_audio(sd, wf, audio).numpy(), a["emb_audio"]) < 1e-5
+
+
+@needs_ref
+@pytest.mark.reference
+def test_speaker_oracle_matches_live_reference():
+    from oracle import speaker_oracle as S
+    R.cc.use_cached_conv(False)
+    spk = R.load("CombinedRave").SpeakerRAVE().eval()
+    R.fill_deterministic(spk, 3)
+    x = torch.from_numpy(recipe_input((3, 16, 1024), 8, scale=1.0))
+    with torch.no_grad():
+        ref = spk(x)
+    got = S.speaker_embed(spk.state_dict(), x)
+    assert ref.shape == (3, 256)
+    assert rel_l2(got.numpy(), ref.numpy()) < 1e-5
