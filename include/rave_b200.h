@@ -211,6 +211,21 @@ int rb_speaker_load_pqmf(rb_speaker* s, const float* w, int n_band, int k);
 int rb_speaker_embed_audio(rb_speaker* s, const float* audio, int B, int T, float* emb, void* stream);
 int rb_speaker_launches(rb_speaker* s, int64_t* count);
 
+/* `rave.resampler.Resampler` (rave/resampler.py:9-66), wrapped around encode / decode by the exported
+ * model (scripts/export.py:377-378, :405-406).  down_w [k_down] = downsample.weight, up_w [ratio][k_up] =
+ * upsample.weight (host).  streaming = cc.USE_BUFFER_CONV at construction: per-stream history replaces the
+ * centred zero padding (cached_conv.CachedConv1d), rows [0, B) <-> streams, max_streams rows allocated.
+ * x / y: device, [B,1,n] of `dtype` (rb_dtype); to_model: n % ratio == 0 -> n / ratio samples;
+ * from_model: -> n * ratio samples.  Enqueued on `stream`; never synchronises. */
+typedef struct rb_resampler rb_resampler;
+int rb_resampler_create(int device, int ratio, const float* down_w, int k_down, const float* up_w, int k_up,
+                        int streaming, int max_streams, rb_resampler** out);
+int rb_resampler_destroy(rb_resampler* r);
+int rb_resampler_reset(rb_resampler* r, void* stream);
+int rb_resampler_to_model(rb_resampler* r, const void* x, int B, int n, int dtype, void* y, void* stream);
+int rb_resampler_from_model(rb_resampler* r, const void* x, int B, int n, int dtype, void* y, void* stream);
+int rb_resampler_launches(rb_resampler* r, int64_t* count);
+
 /* Per-op device timing (CUDA events on the launching stream around every op of the
  * program).  enable!=0 starts recording; rb_op_times synchronises, writes the accumulated
  * milliseconds per op (n = number of ops) and clears the record. */
