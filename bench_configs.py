@@ -106,15 +106,44 @@ def c5(args):
              "dtype": "bf16", "ms_per_step": ms, "value": B * T / SR / (ms / 1e3), "unit": "audio-sec/sec (decode)"}]
 
 
+def c6(args):
+    """Resampler pair (rave/resampler.py) and the speaker encoder (CombinedRave.py:200-328): the steps
+    either side of the path.  Resampler: 512 streams x 2^19 samples at 2x the model rate; algorithmic
+    bytes = input + output once."""
+    import torch
+    from rave_b200.resampler import Resampler
+    from rave_b200.speaker import SpeakerRAVE
+    rows = []
+    B, T = args.batch, 2 ** 19
+    for dtype, name, eb in ((torch.bfloat16, "bf16", 2), (torch.float32, "f32", 4)):
+        r = Resampler(88200, 44100)
+        x = (torch.rand(B, 1, T, device="cuda") - 0.5).to(dtype)
+        y = r.to_model_sampling_rate(x)
+        ms_d = _time(lambda: r.to_model_sampling_rate(x), 3, args.steps)
+        ms_u = _time(lambda: r.from_model_sampling_rate(y), 3, args.steps)
+        nbytes = B * (T + T // 2) * eb
+        rows.append({"config": "C6 resampler ratio 2 (k=39 / 2x21), %d streams x 2^19 samples" % B, "dtype": name,
+                     "to_model_ms": ms_d, "to_model_GBps": nbytes / ms_d / 1e6, "from_model_ms": ms_u,
+                     "from_model_GBps": nbytes / ms_u / 1e6, "note": "times include the output allocation of the shim"})
+        del x, y
+    meta, sd = _sd("speaker")
+    enc = SpeakerRAVE(sd)
+    xb = torch.randn(1, 16, 8192, device="cuda")          # model.py:30: 131072 samples = 8192 band samples
+    ms = _time(lambda: enc(xb), 3, args.steps)
+    rows.append({"config": "C6 speaker encoder, 1 utterance x 131072 samples (16 x 8192 band samples)", "dtype": "f32",
+                 "ms_per_step": ms, "launches_per_step": 20})
+    return rows
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--legs", default="c3,c4,c5")
+    ap.add_argument("--legs", default="c3,c4,c5,c6")
     ap.add_argument("--steps", type=int, default=32)
     ap.add_argument("--streams", type=int, default=1024)
     ap.add_argument("--batch", type=int, default=512)
     args = ap.parse_args()
     for leg in args.legs.split(","):
-        for row in {"c3": c3, "c4": c4, "c5": c5}[leg](args):
+        for row in {"c3": c3, "c4": c4, "c5": c5, "c6": c6}[leg](args):
             print(json.dumps(row), flush=True)
 
 

@@ -102,12 +102,46 @@ def speaker_fixture():
                emb_audio=spk(pq(audio)).numpy()))
 
 
+@torch.no_grad()
+def resampler_fixture():
+    """rave/resampler.py on the ratios of the reference's tests/test_resampler.py: offline for 2 and 3,
+    cached_conv streaming (chunk by chunk) for 2."""
+    res = R.load("resampler")
+    cc = R.cc
+    arrays = dict(x_seed=np.int64(51), x_shape=np.array([2, 1, 6144]), chunk=np.int64(1536))
+    x = torch.from_numpy(recipe_input((2, 1, 6144), 51, scale=0.5))
+    try:
+        for ratio, (tsr, msr) in ((2, (44100, 22050)), (3, (48000, 16000))):
+            cc.use_cached_conv(False)
+            r = res.Resampler(tsr, msr)
+            y = r.to_model_sampling_rate(x)
+            arrays[f"down{ratio}"] = y.numpy()
+            arrays[f"up{ratio}"] = r.from_model_sampling_rate(y).numpy()
+            arrays[f"w_down{ratio}"] = r.downsample.weight.detach().numpy()
+            arrays[f"w_up{ratio}"] = r.upsample.weight.detach().numpy()
+        cc.use_cached_conv(True)
+        r = res.Resampler(44100, 22050)
+        ys, zs = [], []
+        for c in range(4):
+            y = r.to_model_sampling_rate(x[..., c * 1536:(c + 1) * 1536])
+            ys.append(y)
+            zs.append(r.from_model_sampling_rate(y))
+        arrays["down2_stream"] = torch.cat(ys, -1).numpy()
+        arrays["up2_stream"] = torch.cat(zs, -1).numpy()
+    finally:
+        cc.use_cached_conv(False)
+    os.makedirs(OUT, exist_ok=True)
+    np.savez_compressed(os.path.join(OUT, "resampler.npz"), **arrays)
+    print("wrote resampler", {k: tuple(np.shape(v)) for k, v in arrays.items()})
+
+
 def main():
     if not R.available():
         sys.exit("reference tree not available; golden files can only be made in the build container")
     torch.manual_seed(0)
     pqmf_fixture()
     speaker_fixture()
+    resampler_fixture()
     offline_and_stream("v2_c8", C.v2(8), 2, 16384, 2048)
     offline_and_stream("v2causal_c8", C.v2(8, causal=True), 2, 16384, 2048)
     offline_and_stream("v3_c8", C.v3(8), 2, 16384, 2048)

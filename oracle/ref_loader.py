@@ -118,7 +118,7 @@ def load(name: str):
         sys.modules["rave"] = pkg
     if name == "blocks":
         load("core")
-    if name == "CombinedRave":
+    if name in ("CombinedRave", "resampler"):
         load("pqmf")
     path = os.path.join(REFERENCE_ROOT, "rave", name + ".py")
     spec = importlib.util.spec_from_file_location("rave." + name, path)

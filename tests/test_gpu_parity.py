@@ -337,3 +337,79 @@ def test_set_speaker_from_audio_feeds_encode():
     z = m.encode(torch.from_numpy(golden_input(ga)).cuda())
     tail = z[:, -256:, :].cpu().numpy()
     assert np.array_equal(tail, np.broadcast_to(emb.cpu().numpy().reshape(1, 256, 1), tail.shape))
+
+
+# ----------------------------------------------------------------------------- resampler
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("ratio", [2, 3])
+def test_resampler_offline_vs_golden_and_oracle(ratio, dtype):
+    """rave/resampler.py:58-66 on the device (ratios of the reference's tests/test_resampler.py)."""
+    import os
+    from oracle.resampler_oracle import ResamplerOracle
+    from oracle.weights_recipe import recipe_input
+    from rave_b200.resampler import Resampler
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "resampler.npz"))
+    tol = 1e-5 if dtype == torch.float32 else 6e-3
+    r = Resampler(ratio * 16000, 16000)
+    assert np.array_equal(r.down_weight, d[f"w_down{ratio}"].reshape(-1))
+    assert np.array_equal(r.up_weight, d[f"w_up{ratio}"].reshape(ratio, -1))
+    x = torch.from_numpy(recipe_input(tuple(int(v) for v in d["x_shape"]), int(d["x_seed"].item()), scale=0.5))
+    y = r.to_model_sampling_rate(x.to(dtype).cuda())
+    assert y.dtype == dtype and tuple(y.shape) == d[f"down{ratio}"].shape
+    assert rel_l2(y.float().cpu().numpy(), d[f"down{ratio}"]) < tol
+    z = r.from_model_sampling_rate(torch.from_numpy(d[f"down{ratio}"]).to(dtype).cuda())
+    assert tuple(z.shape) == tuple(x.shape)
+    assert rel_l2(z.float().cpu().numpy(), d[f"up{ratio}"]) < tol
+    # ragged lengths (not a multiple of the CTA tile), more streams: oracle on the same input
+    o = ResamplerOracle(ratio)
+    for B, T in ((1, 6 * ratio), (5, 1000 * ratio * 3 + 6 * ratio), (3, 2 ** 16 * ratio)):
+        x = torch.from_numpy(recipe_input((B, 1, T), T, scale=0.5)).to(dtype)
+        y = r.to_model_sampling_rate(x.cuda())
+        yo = o.to_model_sampling_rate(x.float())
+        assert rel_l2(y.float().cpu().numpy(), yo.numpy()) < tol, (B, T)
+        z = r.from_model_sampling_rate(y)
+        assert rel_l2(z.float().cpu().numpy(), o.from_model_sampling_rate(y.float().cpu()).numpy()) < tol, (B, T)
+    with pytest.raises(ValueError):
+        r.to_model_sampling_rate(torch.zeros(1, 1, ratio * 8 + 1).cuda())
+    assert r.kernel_launches > 0
+
+
+def test_resampler_streaming_chunk_by_chunk():
+    """cached_conv mode: chunk-by-chunk against the golden stream of the real module and, with ragged
+    chunk sizes (shorter than the history) and idle rows, against the oracle."""
+    import os
+    from oracle.resampler_oracle import ResamplerOracle
+    from oracle.weights_recipe import recipe_input
+    from rave_b200.resampler import Resampler
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "resampler.npz"))
+    x = torch.from_numpy(recipe_input(tuple(int(v) for v in d["x_shape"]), int(d["x_seed"].item()), scale=0.5)).cuda()
+    c = int(d["chunk"].item())
+    r = Resampler(44100, 22050, streaming=True, max_streams=4)
+    ys = [r.to_model_sampling_rate(x[..., i:i + c]) for i in range(0, x.shape[-1], c)]
+    zs = [r.from_model_sampling_rate(y) for y in ys]
+    assert rel_l2(torch.cat(ys, -1).cpu().numpy(), d["down2_stream"]) < 1e-5
+    assert rel_l2(torch.cat(zs, -1).cpu().numpy(), d["up2_stream"]) < 1e-5
+    r.reset()
+    o = ResamplerOracle(2, streaming=True)
+    xs = torch.from_numpy(recipe_input((4, 1, 8192), 3, scale=0.5))
+    pos = 0
+    for n in (2048, 16, 6, 30, 4096, 1996):
+        xc = xs[..., pos:pos + n]
+        pos += n
+        y = r.to_model_sampling_rate(xc.cuda())
+        yo = o.to_model_sampling_rate(xc)
+        assert rel_l2(y.cpu().numpy(), yo.numpy()) < 1e-5, n
+        z = r.from_model_sampling_rate(y)
+        assert rel_l2(z.cpu().numpy(), o.from_model_sampling_rate(yo).numpy()) < 1e-5, n
+    # a call with fewer rows must not disturb the idle rows' history
+    r.reset()
+    o = ResamplerOracle(2, streaming=True)
+    a, b = xs[..., :1024], xs[..., 1024:2048]
+    r.to_model_sampling_rate(a.cuda())
+    o.to_model_sampling_rate(a)
+    r.to_model_sampling_rate(xs[:2, :, 4096:4096 + 512].cuda())          # rows 0-1 only
+    y = r.to_model_sampling_rate(b.cuda())
+    yo_rows23 = o.to_model_sampling_rate(b)[2:]
+    assert rel_l2(y[2:].cpu().numpy(), yo_rows23.numpy()) < 1e-5
+    with pytest.raises(ValueError):
+        Resampler(48000, 16000, streaming=True)

@@ -245,3 +245,58 @@ def test_speaker_oracle_matches_live_reference():
     got = S.speaker_embed(spk.state_dict(), x)
     assert ref.shape == (3, 256)
     assert rel_l2(got.numpy(), ref.numpy()) < 1e-5
+
+
+# ----------------------------------------------------------------------------- resampler
+def _resampler_golden():
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "resampler.npz"))
+    x = torch.from_numpy(recipe_input(tuple(int(v) for v in d["x_shape"]), int(d["x_seed"].item()), scale=0.5))
+    return d, x
+
+
+def test_resampler_oracle_matches_golden():
+    """oracle/resampler_oracle.py vs outputs of the real rave.resampler.Resampler (make_golden)."""
+    from oracle.resampler_oracle import ResamplerOracle, design
+    d, x = _resampler_golden()
+    for ratio in (2, 3):
+        down, up = design(ratio)
+        assert np.array_equal(down.numpy(), d[f"w_down{ratio}"].reshape(-1))
+        assert np.array_equal(up.numpy(), d[f"w_up{ratio}"].reshape(ratio, -1))
+        o = ResamplerOracle(ratio)
+        y = o.to_model_sampling_rate(x)
+        assert rel_l2(y.numpy(), d[f"down{ratio}"]) < 1e-6
+        assert rel_l2(o.from_model_sampling_rate(y).numpy(), d[f"up{ratio}"]) < 1e-6
+    o = ResamplerOracle(2, streaming=True)
+    c = int(d["chunk"].item())
+    ys = [o.to_model_sampling_rate(x[..., i:i + c]) for i in range(0, x.shape[-1], c)]
+    zs = [o.from_model_sampling_rate(y) for y in ys]
+    assert rel_l2(torch.cat(ys, -1).numpy(), d["down2_stream"]) < 1e-6
+    assert rel_l2(torch.cat(zs, -1).numpy(), d["up2_stream"]) < 1e-6
+
+
+@needs_ref
+@pytest.mark.reference
+@pytest.mark.parametrize("target_sr,model_sr", [(44100, 22050), (48000, 16000)])   # tests/test_resampler.py:8
+def test_resampler_oracle_matches_live_reference(target_sr, model_sr):
+    from oracle.resampler_oracle import ResamplerOracle
+    R.load("pqmf")
+    res = R.load("resampler")
+    x = torch.from_numpy(recipe_input((1, 1, 2 ** 12 * 3), 9, scale=1.0))
+    for streaming in (False, True):
+        R.cc.use_cached_conv(streaming)
+        try:
+            try:
+                ref = res.Resampler(target_sr, model_sr)
+            except ValueError:
+                assert streaming and (target_sr // model_sr) % 2
+                continue
+            o = ResamplerOracle(target_sr // model_sr, streaming)
+            for _ in range(2):
+                with torch.no_grad():
+                    y = ref.to_model_sampling_rate(x)
+                    z = ref.from_model_sampling_rate(y)
+                yo = o.to_model_sampling_rate(x)
+                assert z.shape == x.shape
+                assert torch.equal(y, yo) and torch.equal(z, o.from_model_sampling_rate(yo))
+        finally:
+            R.cc.use_cached_conv(False)
