@@ -212,7 +212,7 @@ int rb_speaker_embed_audio(rb_speaker* s, const float* audio, int B, int T, floa
 int rb_speaker_launches(rb_speaker* s, int64_t* count);
 
 /* `rave.resampler.Resampler` (rave/resampler.py:9-66), wrapped around encode / decode by the exported
- * model (scripts/export.py:377-378, :405-406).  down_w [k_down] = downsample.weight, up_w [ratio][k_up] =
+ * model (scripts/export.py:377-378, :407-408).  down_w [k_down] = downsample.weight, up_w [ratio][k_up] =
  * upsample.weight (host).  streaming = cc.USE_BUFFER_CONV at construction: per-stream history replaces the
  * centred zero padding (cached_conv.CachedConv1d), rows [0, B) <-> streams, max_streams rows allocated.
  * x / y: device, [B,1,n] of `dtype` (rb_dtype); to_model: n % ratio == 0 -> n / ratio samples;

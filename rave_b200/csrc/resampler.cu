@@ -1,5 +1,5 @@
 // resampler.cu -- `rave.resampler.Resampler` (rave/resampler.py:9-66), the Kaiser FIR pair the exported
-// model wraps around encode / decode (scripts/export.py:377-378 to_model_sampling_rate, :405-406
+// model wraps around encode / decode (scripts/export.py:377-378 to_model_sampling_rate, :407-408
 // from_model_sampling_rate).  Both directions are one continuous FIR over [stream][time] audio:
 //
 //   to_model    y[t]              = sum_j down[j]   * x[t*ratio + j - off_d]          (resampler.py:31-41, :58-59)

@@ -1,5 +1,5 @@
 """Host-side mirror of `rave.resampler.Resampler` (rave/resampler.py:9-66): the Kaiser FIR pair the
-exported model wraps around encode / decode (scripts/export.py:377-378, :405-406).  Filter design on
+exported model wraps around encode / decode (scripts/export.py:377-378, :407-408).  Filter design on
 the host exactly as upstream; both directions run in librave_b200.so (csrc/resampler.cu).  No CPU
 or PyTorch fallback.
 """
