@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE ONLY -- CPU restatement of `rave.resampler.Resampler` (rave/resampler.py:9-66),
 the Kaiser FIR pair the exported model wraps around encode / decode (scripts/export.py:377-378,
-405-406).
+407-408).
 
   design        resampler.py:26-56   kaiser_filter(pi / ratio, 140) (pqmf.py:55-70); the up-sampler is
                                      the same filter split into `ratio` polyphase rows (left-padded
