@@ -86,6 +86,13 @@ def _install_stubs():
             tt.Spectrogram = object
             ta.transforms = tt
             sys.modules["torchaudio"], sys.modules["torchaudio.transforms"] = ta, tt
+    if "torchfcpe" not in sys.modules:             # pitch_utils.py:10-12 spawns the FCPE model on cuda:2 at import
+        try:
+            import torchfcpe  # noqa: F401
+        except Exception:
+            tf = types.ModuleType("torchfcpe")
+            tf.spawn_bundled_infer_model = lambda device=None: None
+            sys.modules["torchfcpe"] = tf
     sys.modules["cached_conv"] = cc
     # scipy shim: pqmf.py:10 imports scipy.signal.kaiser (moved to scipy.signal.windows) and
     # pqmf.py:69 calls firwin(..., nyq=pi) (keyword replaced by fs=2*nyq).
