@@ -226,6 +226,20 @@ int rb_resampler_to_model(rb_resampler* r, const void* x, int B, int n, int dtyp
 int rb_resampler_from_model(rb_resampler* r, const void* x, int B, int n, int dtype, void* y, void* stream);
 int rb_resampler_launches(rb_resampler* r, int64_t* count);
 
+/* Pitch front-end (rave/pitch_utils.py): the f0 channels the export wrapper concatenates to the latent
+ * (scripts/export.py:347-358, :395).  rb_yin_estimate = estimate() :15-42 (YIN: framing, difference
+ * function, cumulative-mean normalisation, threshold + first-minimum search); x: device fp32 [B][T],
+ * f0: device fp32 [B][n_frames] in Hz, 0 = not periodic; n_frames from rb_yin_frames.  get_pitch()
+ * :100-106 is this call with frame_stride_s = (T - 2*int(fs/pitch_min)) / (T/block - 1) / fs.
+ * rb_f0_one_hot = get_f0_norm() :116-135 ('abs' normalisation) for f0 from any estimator: one_hot device
+ * fp32 [B][F][bins+1] (channels_first: [B][bins+1][F], the layout the wrapper permutes to), class `bins`
+ * = unvoiced; log_f0_norm [B][F] (NaN where unvoiced) or NULL. */
+int rb_yin_frames(int T, int sample_rate, double pitch_min, double frame_stride_s, int* n_frames);
+int rb_yin_estimate(const float* x, int B, int T, int sample_rate, double pitch_min, double pitch_max,
+                    double frame_stride_s, double threshold, float* f0, int n_frames, void* stream);
+int rb_f0_one_hot(const float* f0, int B, int F, int num_bins, int channels_first, float* one_hot,
+                  float* log_f0_norm, void* stream);
+
 /* Per-op device timing (CUDA events on the launching stream around every op of the
  * program).  enable!=0 starts recording; rb_op_times synchronises, writes the accumulated
  * milliseconds per op (n = number of ops) and clears the record. */

@@ -135,6 +135,24 @@ def resampler_fixture():
     print("wrote resampler", {k: tuple(np.shape(v)) for k, v in arrays.items()})
 
 
+@torch.no_grad()
+def pitch_fixture():
+    """rave/pitch_utils.py get_pitch / estimate / get_f0_norm (FCPE replaced by the YIN output) on the
+    deterministic signals of tests/util.py:pitch_signals."""
+    sys.path.insert(0, os.path.dirname(OUT))
+    from tests.util import pitch_signals
+    pu = R.load("pitch_utils")
+    x = torch.from_numpy(pitch_signals())
+    f0 = pu.get_pitch(x, 1024)
+    f0_wide = pu.estimate(x, 44100, 50., 800., 0.01, 0.15)
+    pu.extract_utterance_fcpe = lambda y, sr, fl: f0.unsqueeze(-1).clone()
+    oh, ln = pu.get_f0_norm(x, torch.zeros(4, 1), torch.ones(4, 1), 44100, 1024)
+    os.makedirs(OUT, exist_ok=True)
+    np.savez_compressed(os.path.join(OUT, "pitch.npz"), f0=f0.numpy(), f0_wide=f0_wide.numpy(),
+                        one_hot_idx=oh.argmax(-1).numpy().astype(np.int16), log_f0_norm=ln.numpy())
+    print("wrote pitch", tuple(f0.shape), tuple(f0_wide.shape), tuple(oh.shape))
+
+
 def main():
     if not R.available():
         sys.exit("reference tree not available; golden files can only be made in the build container")
@@ -142,6 +160,7 @@ def main():
     pqmf_fixture()
     speaker_fixture()
     resampler_fixture()
+    pitch_fixture()
     offline_and_stream("v2_c8", C.v2(8), 2, 16384, 2048)
     offline_and_stream("v2causal_c8", C.v2(8, causal=True), 2, 16384, 2048)
     offline_and_stream("v3_c8", C.v3(8), 2, 16384, 2048)

@@ -80,4 +80,5 @@ def f0_norm_one_hot(f0, num_f0_bins=256):
     log_f0_norm = log_f0_norm + 0.5
     bins = torch.linspace(0, 1, num_f0_bins + 1).to(f0)
     idx = torch.bucketize(log_f0_norm, bins, right=True) - 1
-    return F.one_hot(idx, num_f0_bins + 1).to(f0), log_f0_norm
+    eye = torch.eye(num_f0_bins + 1).to(f0)                    # one_hot() :107-113: a row lookup, so -1 wraps
+    return eye[idx.reshape(-1)].reshape(idx.shape[0], idx.shape[1], num_f0_bins + 1), log_f0_norm

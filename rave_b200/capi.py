@@ -95,6 +95,10 @@ EXPORTS = {
     "rb_resampler_to_model": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_resampler_from_model": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_resampler_launches": [C.c_void_p, C.POINTER(C.c_int64)],
+    "rb_yin_frames": [C.c_int, C.c_int, C.c_double, C.c_double, C.POINTER(C.c_int)],
+    "rb_yin_estimate": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
+                        C.c_void_p, C.c_int, C.c_void_p],
+    "rb_f0_one_hot": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p],
     "rb_profile_ops": [C.c_void_p, C.c_int],
     "rb_op_times": [C.c_void_p, C.POINTER(C.c_float), C.c_int],
     "rb_last_error": [],

@@ -413,3 +413,70 @@ def test_resampler_streaming_chunk_by_chunk():
     assert rel_l2(y[2:].cpu().numpy(), yo_rows23.numpy()) < 1e-5
     with pytest.raises(ValueError):
         Resampler(48000, 16000, streaming=True)
+
+
+# ----------------------------------------------------------------------------- pitch front-end
+def _f0_agreement(got, want, sr=44100):
+    """Fraction of frames with the identical f0 value, and the worst period disagreement elsewhere."""
+    got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+    same = got == want
+    both = (got > 0) & (want > 0) & ~same
+    dtau = np.abs(sr / got[both] - sr / want[both]) if both.any() else np.zeros(1)
+    flips = int(((got > 0) != (want > 0)).sum())
+    return same.mean(), float(dtau.max()), flips
+
+
+def test_yin_matches_golden_and_oracle():
+    """pitch_utils.py:15-106 on the device.  The reference takes the autocorrelation from an fp32 FFT, the
+    kernel from direct fp32 sums: periods are integers, so frames either agree exactly or differ where the
+    reference's own rounding noise picks the lag; the test bounds how often and by how much."""
+    import os
+    from oracle import pitch_oracle as P
+    from rave_b200 import pitch
+    from .util import pitch_signals
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "pitch.npz"))
+    x = torch.from_numpy(pitch_signals()).cuda()
+    f0 = pitch.get_pitch(x, 1024)
+    assert tuple(f0.shape) == d["f0"].shape
+    same, dtau, flips = _f0_agreement(f0.cpu().numpy(), d["f0"])
+    assert same >= 0.97 and dtau <= 2.0 and flips <= 2, (same, dtau, flips)
+    assert (f0[1] == 0).all()                                              # white noise: no period
+    fw = pitch.estimate(x, 44100, 50., 800., 0.01, 0.15)
+    assert tuple(fw.shape) == d["f0_wide"].shape
+    same, dtau, flips = _f0_agreement(fw.cpu().numpy(), d["f0_wide"])
+    assert same >= 0.97 and dtau <= 2.0 and flips <= 4, (same, dtau, flips)
+    # other shapes: leading dims, a signal shorter than one frame, a low pitch floor (large tau_max)
+    xs = torch.from_numpy(pitch_signals(32768))
+    for args in ((44100, 30., 1000., 0.02, 0.2), (44100, 20., 2000., 0.05, 0.1), (22050, 70., 400., 0.01, 0.1)):
+        ref = P.estimate(xs.reshape(2, 2, -1), *args)
+        got = pitch.estimate(xs.reshape(2, 2, -1).cuda(), *args)
+        assert got.shape == ref.shape
+        same, dtau, flips = _f0_agreement(got.cpu().numpy(), ref.numpy(), args[0])
+        assert same >= 0.95 and dtau <= 2.0 and flips <= 3, (args, same, dtau, flips)
+    short = xs[:1, :700]
+    assert torch.equal(pitch.estimate(short.cuda(), 44100, 70., 400.).cpu() > 0, P.estimate(short, 44100, 70., 400.) > 0)
+    with pytest.raises(ValueError):
+        pitch.estimate(xs.cuda(), 44100, 70., 400., frame_stride=1e-6)
+
+
+def test_f0_one_hot_matches_golden_and_oracle():
+    """pitch_utils.py:116-135: f0 -> normalised log-f0 -> 257-class one-hot (class 256 = unvoiced)."""
+    import os
+    from oracle import pitch_oracle as P
+    from rave_b200 import pitch
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "pitch.npz"))
+    f0 = torch.from_numpy(d["f0"])
+    oh, ln = pitch.f0_norm_one_hot(f0.cuda())
+    assert tuple(oh.shape) == (4, f0.shape[1], 257) and torch.all(oh.sum(-1) == 1)
+    idx = oh.argmax(-1).cpu().numpy()
+    edge = np.abs(d["log_f0_norm"] * 256 - np.round(d["log_f0_norm"] * 256)) < 1e-3     # on a bin boundary
+    ok = (idx == d["one_hot_idx"]) | edge
+    assert ok.all()
+    assert np.allclose(np.nan_to_num(ln.cpu().numpy(), nan=-9.), np.nan_to_num(d["log_f0_norm"], nan=-9.), atol=2e-6)
+    cf, _ = pitch.f0_norm_one_hot(f0.cuda(), channels_first=True)
+    assert torch.equal(cf, oh.permute(0, 2, 1))                            # scripts/export.py:358
+    # out-of-range and unvoiced values: below 40 Hz wraps to the last class like upstream's eye() lookup
+    f = torch.tensor([[0., 20., 39.9, 40., 41., 399., 2000., 30000.]])
+    oh2, _ = pitch.f0_norm_one_hot(f.cuda())
+    want, _ = P.f0_norm_one_hot(f)
+    assert torch.equal(oh2.cpu(), want)

@@ -300,3 +300,35 @@ def test_resampler_oracle_matches_live_reference(target_sr, model_sr):
                 assert torch.equal(y, yo) and torch.equal(z, o.from_model_sampling_rate(yo))
         finally:
             R.cc.use_cached_conv(False)
+
+
+# ----------------------------------------------------------------------------- pitch front-end
+def test_pitch_oracle_matches_golden():
+    """oracle/pitch_oracle.py vs outputs of the real rave/pitch_utils.py functions (make_golden)."""
+    from oracle import pitch_oracle as P
+    from .util import pitch_signals
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "pitch.npz"))
+    x = torch.from_numpy(pitch_signals())
+    f0 = P.get_pitch(x, 1024)
+    assert np.array_equal(f0.numpy(), d["f0"])
+    assert np.array_equal(P.estimate(x, 44100, 50., 800., 0.01, 0.15).numpy(), d["f0_wide"])
+    oh, ln = P.f0_norm_one_hot(f0)
+    assert np.array_equal(oh.argmax(-1).numpy(), d["one_hot_idx"])
+    assert np.array_equal(np.nan_to_num(ln.numpy(), nan=-9.), np.nan_to_num(d["log_f0_norm"], nan=-9.))
+    assert (d["f0"][0] > 0).all() and (d["f0"][1] == 0).all()       # voiced tone / white noise
+
+
+@needs_ref
+@pytest.mark.reference
+def test_pitch_oracle_matches_live_reference():
+    from oracle import pitch_oracle as P
+    from .util import pitch_signals
+    pu = R.load("pitch_utils")
+    x = torch.from_numpy(pitch_signals(32768))
+    assert torch.equal(pu.get_pitch(x, 512), P.get_pitch(x, 512))
+    assert torch.equal(pu.estimate(x, 44100, 30., 1000., 0.02, 0.2), P.estimate(x, 44100, 30., 1000., 0.02, 0.2))
+    f0 = P.get_pitch(x, 1024)
+    pu.extract_utterance_fcpe = lambda y, sr, fl: f0.unsqueeze(-1).clone()
+    oh, ln = pu.get_f0_norm(x, torch.zeros(4, 1), torch.ones(4, 1), 44100, 1024)
+    oh2, ln2 = P.f0_norm_one_hot(f0)
+    assert torch.equal(oh, oh2) and torch.equal(torch.nan_to_num(ln, nan=-9.), torch.nan_to_num(ln2, nan=-9.))

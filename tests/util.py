@@ -81,3 +81,17 @@ def bf16_floor(name):
         O._conv, O._conv_transpose, O._adain, O._folded = saved
     nl = meta["cfg"]["latent_size"]       # the speaker-embedding channels of z are exact: score the latent alone
     return rel_l2(z[:, :nl].numpy(), a["z"][:, :nl]), rel_l2(y.numpy(), a["y"]), rel_l2(y2.numpy(), a["y"])
+
+
+def pitch_signals(n=65536, sr=44100):
+    """Deterministic test signals for the pitch front-end (numpy float64 -> float32): a vibrato voice-like
+    tone with a harmonic and a little noise, white noise, a gated 300 Hz tone, a two-note sequence."""
+    g = np.random.Generator(np.random.PCG64(17))
+    t = np.arange(n) / sr
+    f = 110 * (1 + 0.3 * np.sin(2 * np.pi * 0.7 * t))
+    ph = np.cumsum(2 * np.pi * f / sr)
+    a = np.sin(ph) + 0.3 * np.sin(2 * ph) + 0.01 * g.standard_normal(n)
+    b = 0.1 * g.standard_normal(n)
+    c = np.sin(2 * np.pi * 300 * t) * np.clip(np.sin(2 * np.pi * 1.5 * t), 0, None)
+    d = np.where(t < t[n // 2], np.sin(2 * np.pi * 196 * t), np.sin(2 * np.pi * 261.63 * t)) + 0.05 * g.standard_normal(n)
+    return np.ascontiguousarray(np.stack([a, b, c, d]), dtype=np.float32)
