@@ -135,15 +135,32 @@ def c6(args):
     return rows
 
 
+def c7(args):
+    """YIN pitch front-end (rave/pitch_utils.py get_pitch, 70-400 Hz, one frame per 1024-sample block) and the
+    f0 -> one-hot channels, on the streams of the headline workload."""
+    import torch
+    from rave_b200 import pitch
+    B, T = args.batch, 2 ** 18
+    x = torch.rand(B, T, device="cuda") - 0.5
+    f0 = pitch.get_pitch(x, 1024)
+    ms = _time(lambda: pitch.get_pitch(x, 1024), 2, max(2, args.steps // 4))
+    ms_oh = _time(lambda: pitch.f0_norm_one_hot(f0, channels_first=True), 3, args.steps)
+    frames = f0.numel()
+    return [{"config": "C7 YIN get_pitch (tau_max 630, frame 1260) + f0 one-hot, %d streams x 2^18 samples" % B,
+             "dtype": "f32", "yin_ms": ms, "frames": frames, "Mframes_per_s": frames / ms / 1e3,
+             "GFMA_per_s": frames * 630 * 1260 / ms / 1e6, "value": B * T / SR / (ms / 1e3), "unit": "audio-sec/sec (pitch)",
+             "one_hot_ms": ms_oh}]
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--legs", default="c3,c4,c5,c6")
+    ap.add_argument("--legs", default="c3,c4,c5,c6,c7")
     ap.add_argument("--steps", type=int, default=32)
     ap.add_argument("--streams", type=int, default=1024)
     ap.add_argument("--batch", type=int, default=512)
     args = ap.parse_args()
     for leg in args.legs.split(","):
-        for row in {"c3": c3, "c4": c4, "c5": c5, "c6": c6}[leg](args):
+        for row in {"c3": c3, "c4": c4, "c5": c5, "c6": c6, "c7": c7}[leg](args):
             print(json.dumps(row), flush=True)
 
 

@@ -130,7 +130,8 @@ yin_kernel(const float* __restrict__ x, float* __restrict__ f0, int T, int n_fra
   __syncthreads();
   if (threadIdx.x == 0) {
     const int tau = s_pick == 0x7fffffff ? 0 : s_pick;
-    f0[(size_t)b * n_frames + fr] = tau > 0 ? sample_rate / (float)(tau + tau_min + 1) : 0.f;
+    // `sample_rate / tensor` is torch's __rtruediv__: reciprocal(tensor) * sample_rate, two fp32 roundings
+    f0[(size_t)b * n_frames + fr] = tau > 0 ? __fmul_rn(__frcp_rn((float)(tau + tau_min + 1)), sample_rate) : 0.f;
   }
 }
 
@@ -180,7 +181,7 @@ extern "C" int rb_yin_frames(int T, int sample_rate, double pitch_min, double fr
 
 extern "C" int rb_yin_estimate(const float* x, int B, int T, int sample_rate, double pitch_min, double pitch_max,
                                double frame_stride_s, double threshold, float* f0, int n_frames, void* stream) {
-  RB_CHECK(x && f0 && B > 0 && T > 0, RB_ERR_INVALID, "rb_yin_estimate: bad argument");
+  RB_CHECK(x && f0 && B > 0 && B <= 65535 && T > 0, RB_ERR_INVALID, "rb_yin_estimate: bad argument (1 <= B <= 65535)");
   RB_CHECK(sample_rate > 0 && pitch_min > 0 && pitch_max > pitch_min, RB_ERR_INVALID, "rb_yin_estimate: pitch range");
   const int tau_min = (int)(sample_rate / pitch_max), tau_max = (int)(sample_rate / pitch_min);
   const int L = 2 * tau_max, stride = (int)(frame_stride_s * sample_rate);

@@ -44,7 +44,7 @@ def get_pitch(x, block_size: int, fs: int = 44100, pitch_min: float = 70.0, pitc
 
 def f0_norm_one_hot(f0, num_f0_bins: int = 256, channels_first: bool = False):
     """get_f0_norm (pitch_utils.py:116-135, norm_mode 'abs'): f0 [B, F] in Hz (0 = unvoiced) ->
-    (one_hot [B, F, bins + 1] -- or [B, bins + 1, F], what scripts/export.py:358 permutes to --,
+    (one_hot [B, F, bins + 1] -- or [B, bins + 1, F], what scripts/export.py:359 permutes to --,
     log_f0_norm [B, F] with NaN where unvoiced)."""
     if not f0.is_cuda or f0.dim() != 2:
         raise ValueError("f0 must be a CUDA tensor [B, F]")
