@@ -227,7 +227,7 @@ int rb_resampler_from_model(rb_resampler* r, const void* x, int B, int n, int dt
 int rb_resampler_launches(rb_resampler* r, int64_t* count);
 
 /* Pitch front-end (rave/pitch_utils.py): the f0 channels the export wrapper concatenates to the latent
- * (scripts/export.py:348-359, :396).  rb_yin_estimate = estimate() :15-42 (YIN: framing, difference
+ * (scripts/export.py:348-359, :397).  rb_yin_estimate = estimate() :15-42 (YIN: framing, difference
  * function, cumulative-mean normalisation, threshold + first-minimum search); x: device fp32 [B][T],
  * f0: device fp32 [B][n_frames] in Hz, 0 = not periodic; n_frames from rb_yin_frames.  get_pitch()
  * :100-106 is this call with frame_stride_s = (T - 2*int(fs/pitch_min)) / (T/block - 1) / fs.

@@ -150,6 +150,32 @@ class RAVE:
                                                    self.pqmf.inverse_conv_weight), strict=strict))
         return self
 
+    @classmethod
+    def from_run(cls, run, streaming=False, ema_weights=False, device="cuda:0", dtype=torch.float32,
+                 search_paths=None):
+        """scripts/export.py:541-568: `run/config.gin` + the newest `*last*.ckpt` under `run`."""
+        import os
+        from . import checkpoint as ck
+        m = cls.from_gin([os.path.join(run, "config.gin")], None, streaming=streaming, device=device, dtype=dtype,
+                         search_paths=search_paths)
+        path = ck.search_for_run(run)
+        if path is None:
+            print("No checkpoint found, RAVE will remain randomly initialized")      # export.py:570
+            return m
+        m.load_checkpoint(path, ema_weights=ema_weights)
+        return m
+
+    def load_checkpoint(self, path, ema_weights=False):
+        """scripts/export.py:557-568 (strict=False as upstream); also builds the speaker encoder when the
+        checkpoint carries `speaker_encoder.*` (model.py:164-174)."""
+        from . import checkpoint as ck
+        own, spk = ck.split_state_dict(ck.load_checkpoint(path, ema_weights=ema_weights))
+        self.load_state_dict(own, strict=False)
+        if spk and all(k + ".weight" in spk or k + ".weight_g" in spk for k in ("in_layer", "fc6")) \
+                and "bn5.running_var" in spk:
+            self.load_speaker_encoder(spk)
+        return self
+
     def set_speaker(self, emb):
         """`self.speaker` of the reference (model.py:246-247): the fixed [1, S, 1] embedding."""
         self.load_state_dict({"speaker": emb}, strict=False)

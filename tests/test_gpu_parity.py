@@ -480,3 +480,25 @@ def test_f0_one_hot_matches_golden_and_oracle():
     oh2, _ = pitch.f0_norm_one_hot(f.cuda())
     want, _ = P.f0_norm_one_hot(f)
     assert torch.equal(oh2.cpu(), want)
+
+
+def test_from_run_loads_config_checkpoint_and_speaker_encoder(tmp_path):
+    """scripts/export.py:541-568: run/config.gin + newest *last*.ckpt (state_dict or callbacks.EMA); the
+    `speaker_encoder.*` tensors of the checkpoint build the speaker encoder (model.py:164-174)."""
+    from rave_b200 import RAVE
+    meta, a = load_golden("v2_c8")
+    sd = {k: torch.from_numpy(v) for k, v in golden_state_dict(meta).items()}
+    spk = {"speaker_encoder." + k: torch.from_numpy(v) for k, v in golden_state_dict(load_golden("speaker")[0]).items()}
+    run = tmp_path / "myrun"
+    (run / "version_0" / "checkpoints").mkdir(parents=True)
+    (run / "config.gin").write_text('include "v2.gin"\nCAPACITY = 8\n')
+    ema = {k: v * 0 for k, v in sd.items() if k.endswith(("weight_g", "bias"))}
+    torch.save({"state_dict": {**sd, **spk}, "callbacks": {"EMA": ema}}, run / "version_0" / "checkpoints" / "epoch9-last.ckpt")
+    m = RAVE.from_run(str(run))
+    x = torch.from_numpy(golden_input(a)).cuda()
+    assert rel_l2(m.encode(x).cpu().numpy(), a["z"]) < F32_TOL
+    assert m.speaker_encoder is not None
+    emb = m.speaker_encoder(torch.zeros(1, 16, 256).cuda())
+    assert tuple(emb.shape) == (1, 256) and torch.isfinite(emb).all()
+    m2 = RAVE.from_run(str(run), ema_weights=True)          # zeroed gains / biases: a different model
+    assert rel_l2(m2.encode(x).cpu().numpy(), a["z"]) > 0.1

@@ -151,3 +151,42 @@ def test_no_cuda_device_fails_loudly():
     from rave_b200 import RAVE
     with pytest.raises(RuntimeError):
         RAVE.from_gin(["v2.gin"], ["CAPACITY=2"])
+
+
+def test_checkpoint_search_and_load(tmp_path):
+    """rave/core.py:132-139 + scripts/export.py:557-568 on a Lightning-shaped checkpoint file."""
+    import torch
+    from rave_b200 import checkpoint as ck
+    run = tmp_path / "run" / "version_0" / "checkpoints"
+    run.mkdir(parents=True)
+    sd = {"encoder.encoder.net.0.weight": torch.ones(2, 3, 7), "speaker_encoder.in_layer.weight": torch.zeros(128, 16, 7),
+          "speaker_encoder.bn5.running_var": torch.ones(1536), "decoder.net.1.weight_g": torch.ones(4, 1, 1)}
+    ema = {"encoder.encoder.net.0.weight": torch.full((2, 3, 7), 2.0)}
+    torch.save({"state_dict": sd, "callbacks": {"EMA": ema}, "epoch": 3}, run / "epoch3-last.ckpt")
+    torch.save({"state_dict": sd, "callbacks": {}}, run / "best.ckpt")
+    torch.save({"state_dict": {}, "callbacks": {}}, run / "epoch1-last.ckpt")
+    root = str(tmp_path / "run")
+    assert ck.search_for_run(None) is None
+    assert ck.search_for_run(str(run / "best.ckpt")) == str(run / "best.ckpt")
+    assert ck.search_for_run(root).endswith("epoch3-last.ckpt")          # sorted, last one wins
+    assert ck.search_for_run(root, mode="best").endswith("best.ckpt")
+    assert ck.search_for_run(str(tmp_path / "run" / "version_0"), mode="nothing") is None
+    got = ck.load_checkpoint(ck.search_for_run(root))
+    assert set(got) == set(sd) and torch.equal(got["encoder.encoder.net.0.weight"], sd["encoder.encoder.net.0.weight"])
+    got = ck.load_checkpoint(ck.search_for_run(root), ema_weights=True)
+    assert set(got) == set(ema) and float(got["encoder.encoder.net.0.weight"].mean()) == 2.0
+    got = ck.load_checkpoint(str(run / "best.ckpt"), ema_weights=True)   # no EMA callback: falls back to state_dict
+    assert set(got) == set(sd)
+    own, spk = ck.split_state_dict(sd)
+    assert set(spk) == {"in_layer.weight", "bn5.running_var"} and "decoder.net.1.weight_g" in own and len(own) == 2
+
+
+def test_resampler_design_matches_oracle_and_rejects_what_upstream_rejects():
+    from oracle.resampler_oracle import design as oracle_design
+    from rave_b200.resampler import design
+    for ratio in (2, 3):
+        d, u = design(ratio)
+        do, uo = oracle_design(ratio)
+        assert np.array_equal(d, do.numpy()) and np.array_equal(u, uo.numpy())
+    with pytest.raises(RuntimeError):
+        design(4)                        # upstream's reshape(-1, ratio) fails for this filter length too
