@@ -5,7 +5,7 @@
 
 A step = one pass of RAVE.forward (encode -> decode) over the synthetic batch of
 BASELINE.json configs[1]: 512 streams x 2^18 samples @44.1 kHz per GPU, random-init v2 weights
-(name-keyed recipe, oracle/weights_recipe.py).  Streams are independent (tests: bitwise), so
+(name-keyed recipe, rave_b200/synth.py).  Streams are independent (tests: bitwise), so
 N GPUs run N shards of 512 streams each with no data-path collective (weak scaling); the only
 collectives are the barrier and the max-over-ranks of the device time.  Prints ONE JSON line
 on rank 0.
@@ -46,9 +46,8 @@ def _peaks():
 
 
 def _state_dict():
-    from tests.util import golden_state_dict, load_golden
-    meta, _ = load_golden("v2_c64")            # only the (name, shape) list is read from the fixture
-    return meta, golden_state_dict(meta)
+    from rave_b200.synth import golden_state_dict
+    return golden_state_dict("v2_c64")         # only the (name, shape) list is read from the fixture
 
 
 class ClockSampler(threading.Thread):
@@ -136,7 +135,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from rave_b200 import RAVE
-    from oracle.weights_recipe import recipe_input
+    from rave_b200.synth import recipe_input
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))

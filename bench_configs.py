@@ -20,9 +20,8 @@ SR = 44100
 
 
 def _sd(name):
-    from tests.util import golden_state_dict, load_golden
-    meta, _ = load_golden(name)
-    return meta, golden_state_dict(meta)
+    from rave_b200.synth import golden_state_dict
+    return golden_state_dict(name)
 
 
 def _time(fn, warmup, steps):
@@ -42,7 +41,7 @@ def _time(fn, warmup, steps):
 def c3(args):
     import torch
     from rave_b200 import RAVE
-    from oracle.weights_recipe import recipe_input
+    from rave_b200.synth import recipe_input
     _, sd = _sd("v2_c64")
     out = []
     for dtype, tag in ((torch.bfloat16, "bf16"), (torch.float32, "f32")):
@@ -65,7 +64,7 @@ def c3(args):
 def c4(args):
     import torch
     from rave_b200 import RAVE
-    from oracle.weights_recipe import recipe_input
+    from rave_b200.synth import recipe_input
     meta, sd = _sd("discrete_c8")
     m = RAVE.from_gin(["discrete.gin"], ["CAPACITY=8"], dtype=torch.bfloat16)
     m.load_state_dict(sd)
