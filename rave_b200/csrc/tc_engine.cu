@@ -46,10 +46,17 @@ struct Layer {
   float* bias2 = nullptr;
   float* alpha2 = nullptr;
   int act2 = 0;
+  // stream-as-row twin (Plan::sr_layers): geometry of the conv it was unrolled from
+  int sr_taps = 0, sr_dil = 1, sr_off = 0;
 };
 
 struct Plan {
   std::vector<Layer> layers;      // per op
+  // Streaming, deep layers (<= 4 rows per stream and chunk): the same conv with its taps unrolled into
+  // the K dimension (im2col over taps, n_taps = 1), run with the STREAM index as the row axis of the
+  // views -- one launch per row of the chunk fills 128-row tiles with 128 streams instead of running
+  // one nearly empty tile (and one pass over the whole weight set) per stream.  See run_layer.
+  std::vector<Layer> sr_layers;
   std::vector<int> skip;          // op is the tail of a fused pair
   std::vector<int> cp;            // per slot channel pitch
   // per slot: tensor is stored LeakyReLU-activated (every consumer wants act(x) as conv input, or
@@ -344,13 +351,30 @@ static uint32_t align_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
 static unsigned long long* g_trace = nullptr;   // debug hook only: device buffer [64][16] of clock stamps
 
 // x_act / res_act / out_act: the tensor is (to be) stored LeakyReLU-activated (Plan::sact).
+// sr_t0 >= 0: L is a stream-as-row twin (Plan::sr_layers); computes row sr_t0 of the chunk for all streams.
 static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Buf& src, const Buf& dst,
-                     const Buf* res, int B, cudaStream_t s, int x_act = 0, int res_act = 0, int out_act = 0) {
+                     const Buf* res, int B, cudaStream_t s, int x_act = 0, int res_act = 0, int out_act = 0,
+                     int sr_t0 = -1) {
   TcParams p;
   memset(&p, 0, sizeof(p));
   int rc = make_view(src, L.fin, &p.x);
   if (rc) return rc;
   if ((rc = make_view(dst, L.fout, &p.y))) return rc;
+  const int n_streams = B;
+  if (sr_t0 >= 0) {
+    // rows = streams: row stride = the per-stream stride; tap j (and sub-row of a strided view) becomes
+    // the phase g / G1 of the view, `sB` units apart; the first tap's row is folded into the pointer
+    TcView& x = p.x;
+    RB_CHECK(src.cp != 1 && dst.cp != 1 && L.sr_taps > 0, RB_ERR_INVALID, "stream-as-row layer on an audio slot");
+    RB_CHECK(x.hist + sr_t0 - L.sr_off >= 0, RB_ERR_INVALID, "stream-as-row: history shorter than the filter");
+    x.p = src.p + (long long)(x.hist + sr_t0 - L.sr_off) * x.sT * 8;
+    x.sB = L.fin == 1 ? L.sr_dil : 1;
+    x.sT = (int)x.sb; x.sb = 0; x.hist = 0; x.lo = 0; x.n = n_streams; x.C = L.cin_v;
+    TcView& y = p.y;
+    y.p = dst.p + (long long)(y.hist + sr_t0) * y.sT * 8;
+    y.sT = (int)y.sb; y.sb = 0; y.hist = 0; y.lo = 0; y.n = n_streams;
+    B = 1;
+  }
   RB_CHECK(p.x.C == L.cin_v && p.y.C == (L.head ? L.N_total / 2 : L.N_total), RB_ERR_INVALID,
            "layer/view channel mismatch (%d vs %d, %d vs %d)", p.x.C, L.cin_v, p.y.C, L.N_total);
   p.head = L.head;
@@ -359,6 +383,13 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     if ((rc = make_view(*res, 1, &p.res))) return rc;
     RB_CHECK(L.fout == 1 && p.res.C == L.N_total, RB_ERR_INVALID, "residual shape mismatch");
     p.res_delay = rop.res_delay;
+    if (sr_t0 >= 0) {
+      TcView& r = p.res;
+      RB_CHECK(res->cp != 1 && r.hist + sr_t0 - rop.res_delay >= 0, RB_ERR_INVALID, "stream-as-row: residual history");
+      r.p = res->p + (long long)(r.hist + sr_t0 - rop.res_delay) * 8;
+      r.sT = (int)r.sb; r.sb = 0; r.hist = 0; r.lo = 0; r.n = n_streams;
+      p.res_delay = 0;
+    }
   }
   p.w = L.w; p.masks = L.masks; p.bias = L.bias; p.alpha = L.alpha;
   p.pre_act = x_act ? RB_ACT_NONE : op.pre_act;
@@ -402,7 +433,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     // these layers (r phases of output per input row) are epilogue-heavy.  Measured neutral or
     // worse on the plain k = 1 / k = 3 layers (the 4-deep weight ring is then consumed in ~2000
     // cycles, about its refill latency), so those keep two sub-tiles per weight block.
-    p.pair = (!resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256 && L.fout >= 2 &&
+    p.pair = (!resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256 && L.fout >= 2 && sr_t0 < 0 &&
               !getenv("RB_TC_NOPAIR")) ? 1 : 0;
     if (const char* e = getenv("RB_TC_PAIRALL"))           // experiments only
       p.pair = (atoi(e) && !resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256) ? 1 : 0;
@@ -683,6 +714,7 @@ void tc_free(rb_handle* h) {
   Plan* pl = (Plan*)h->tc;
   if (!pl) return;
   for (auto& L : pl->layers) free_layer(L);
+  for (auto& L : pl->sr_layers) free_layer(L);
   delete pl;
   h->tc = nullptr;
 }
@@ -694,6 +726,7 @@ int tc_pack_weights(rb_handle* h) {
   h->tc = pl;
   const int nops = (int)h->ops.size();
   pl->layers.resize(nops);
+  pl->sr_layers.resize(nops);
   pl->skip.assign(nops, 0);
   pl->cp.resize(h->slots.size());
   for (size_t s = 0; s < h->slots.size(); ++s) pl->cp[s] = slot_cp(h, (int)s);
@@ -746,6 +779,27 @@ int tc_pack_weights(rb_handle* h) {
     Layer& L = pl->layers[i];
     rc = pack_layer(v, 64, fuse ? &v2 : nullptr, L);
     if (rc) return rc;
+    if (h->spec.streaming && !fuse && op.kind == RB_OP_CONV && v.out_mask == 0 &&
+        pl->cp[op.src] != 1 && pl->cp[op.dst] != 1 && h->slots[op.dst].per_frame / v.fout <= 4 &&
+        (size_t)v.cin_v * v.n_taps <= 16384 && !getenv("RB_TC_NOSR")) {
+      ViewWeight u;                                    // taps unrolled into channels: c' = j * cin_v + c
+      u.N_total = v.N_total; u.cin_v = v.cin_v * v.n_taps; u.n_taps = 1; u.dil = 1; u.off = 0;
+      u.fin = v.fin; u.fout = v.fout; u.out_mask = 0;
+      u.w.assign((size_t)u.N_total * u.cin_v, 0.f);
+      for (int n = 0; n < v.N_total; ++n)
+        for (int c = 0; c < v.cin_v; ++c)
+          for (int j = 0; j < v.n_taps; ++j)
+            u.w[(size_t)n * u.cin_v + (size_t)j * v.cin_v + c] = v.w[((size_t)n * v.cin_v + c) * v.n_taps + j];
+      u.bias = v.bias;
+      if (!v.alpha.empty())
+        for (int j = 0; j < v.n_taps; ++j) u.alpha.insert(u.alpha.end(), v.alpha.begin(), v.alpha.end());
+      Layer& S = pl->sr_layers[i];
+      rc = pack_layer(u, largest_div16(pl->cp[op.src], 64), nullptr, S);
+      if (rc) return rc;
+      S.sr_taps = v.n_taps; S.sr_dil = v.dil; S.sr_off = v.off;
+      // a K chunk must stay inside one tap / sub-row phase; the kernel's mask table holds 128 (n-tile, chunk) pairs
+      if (pl->cp[op.src] % S.KC != 0 || S.n_ntiles * S.n_kchunks > 128) free_layer(S);
+    }
     // conv -> HEAD_V2 (no noise branch, amplitude modulation, 16 bands): the head runs in the epilogue
     if (!fuse && op.kind == RB_OP_CONV && op.res < 0 && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {
       const rb_op& o2 = h->ops[i + 1];
@@ -791,6 +845,20 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
       }
       if (L.head)
         return run_layer(L, op, nullptr, bufs[op.src], bufs[h->ops[L.tail].dst], nullptr, B, s, sa[op.src], 0, 0);
+      {
+        const Layer& S = pl->sr_layers[i];
+        const Buf& src = bufs[op.src];
+        const int rows = bufs[op.dst].n / L.fout;
+        const int sr_min_b = getenv("RB_TC_SR_MINB") ? atoi(getenv("RB_TC_SR_MINB")) : 128;   // tests lower it
+        if (S.valid && src.lo < 0 && B >= sr_min_b && rows >= 1 && rows <= 4) {
+          for (int t0 = 0; t0 < rows; ++t0) {
+            const int rc = run_layer(S, op, nullptr, src, bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,
+                                     sa[op.src], op.res >= 0 ? sa[op.res] : 0, sa[op.dst], t0);
+            if (rc) return rc;
+          }
+          return RB_OK;
+        }
+      }
       return run_layer(L, op, nullptr, bufs[op.src], bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,
                        sa[op.src], op.res >= 0 ? sa[op.res] : 0, sa[op.dst]);
     }

@@ -222,6 +222,30 @@ def test_streaming_bf16_matches_golden_chunk_by_chunk(name):
     assert rel_l2(torch.cat(ys2, -1).float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
 
 
+@pytest.mark.parametrize("name", ["v2_c8", "v2causal_c8", "raspberry_causal_c16"])
+def test_streaming_bf16_stream_as_row_layers(name, monkeypatch):
+    """Deep layers of a streaming step (<= 4 rows per stream and chunk) run with the stream index as the row
+    axis and the taps unrolled into K once there are >= 128 streams; RB_TC_SR_MINB lowers that threshold so
+    the 1-2 stream fixtures take the path.  Same bars as the plain streaming test, and the two paths agree."""
+    m, meta, a = _model(name, streaming=True, dtype=torch.bfloat16)
+    x = torch.from_numpy(golden_input(a)).cuda().bfloat16()
+    n = int(a["chunk"].item())
+    chunks = [x[..., c * n:(c + 1) * n].contiguous() for c in range(x.shape[-1] // n)]
+    l0 = m.kernel_launches()
+    plain = torch.cat([m(c) for c in chunks], -1).float().cpu().numpy()
+    l_plain = m.kernel_launches() - l0
+    monkeypatch.setenv("RB_TC_SR_MINB", "1")
+    m.reset_streams()
+    l0 = m.kernel_launches()
+    sr = torch.cat([m(c) for c in chunks], -1).float().cpu().numpy()
+    assert m.kernel_launches() - l0 != l_plain, "stream-as-row path not taken"
+    assert rel_l2(sr, a["y_stream"]) < 2 * BF16_TOL
+    assert rel_l2(sr, plain) < BF16_TOL
+    m.reset_streams()
+    zs = torch.cat([m.encode(c) for c in chunks], -1).float().cpu().numpy()
+    assert rel_l2(zs, a["z_stream"]) < BF16_TOL
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_host_pipeline_equals_device_forward(dtype):
