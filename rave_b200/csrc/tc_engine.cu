@@ -247,7 +247,7 @@ static void free_layer(Layer& L) {
 
 // Pack Wv into [N_TILE][KC] blocks (UMMA K-major no-swizzle core-matrix order) in the order
 // the kernel consumes them: n-tile, K chunk, active tap.  `extra` (fused 1x1 conv) appended.
-static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, Layer& L) {
+static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, Layer& L, int ncap_arg = 0) {
   L.fin = v.fin; L.fout = v.fout; L.cin_v = v.cin_v; L.n_taps = v.n_taps; L.dil = v.dil; L.off = v.off;
   L.N_total = v.N_total; L.out_mask = v.out_mask;
   RB_CHECK(v.n_taps <= 64, RB_ERR_UNSUPPORTED, "conv with %d row taps (max 64)", v.n_taps);
@@ -257,6 +257,7 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
     const int fo = atoi(e) / 1000, cap = atoi(e) % 1000;     // "4128": layers with fout >= 4 get cap 128
     if (v.fout >= fo) ncap = cap;
   }
+  if (ncap_arg > 0) ncap = ncap_arg;
   L.N_TILE = largest_div16(v.N_total, ncap);
   L.n_ntiles = v.N_total / L.N_TILE;
   RB_CHECK(L.n_ntiles <= TC_MAX_NT, RB_ERR_UNSUPPORTED, "too many output-channel tiles");
@@ -426,7 +427,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     RB_CHECK(resident || !L.fused, RB_ERR_UNSUPPORTED, "fused unit does not fit in shared memory");
     p.w_resident = resident ? 1 : 0;
     p.dual_g1 = (resident && L.N_TILE <= 64 && !getenv("RB_TC_NODUAL")) ? 1 : 0;
-    p.MT = (!resident && p.y.n >= 256) ? 2 : 1;
+    p.MT = (!resident && p.y.n >= 256 && sr_t0 < 0) ? 2 : 1;   // stream-as-row: few row tiles, keep them all busy
     // streamed transposed convs run as cluster pairs: the two CTAs split every weight block (half
     // the L2 -> SM weight traffic each), which pays for one sub-tile per accumulator stage and so
     // for two stages at N_TILE = 256 -- the MMAs of the next work item overlap the epilogue, and
@@ -793,12 +794,20 @@ int tc_pack_weights(rb_handle* h) {
       u.bias = v.bias;
       if (!v.alpha.empty())
         for (int j = 0; j < v.n_taps; ++j) u.alpha.insert(u.alpha.end(), v.alpha.begin(), v.alpha.end());
+      // 1024 streams are only 8 row tiles: narrow output tiles spread one launch over many SMs (each CTA
+      // streams its slice of the weights serially).  A K chunk must stay inside one tap / sub-row phase
+      // and the kernel's mask table holds 128 (n-tile, chunk) pairs: first shape that fits.
       Layer& S = pl->sr_layers[i];
-      rc = pack_layer(u, largest_div16(pl->cp[op.src], 64), nullptr, S);
-      if (rc) return rc;
+      const int cps = pl->cp[op.src];
+      const int n_small = std::max(64, round16((u.N_total + TC_MAX_NT - 1) / TC_MAX_NT));
+      const int shapes[4][2] = {{n_small, 64}, {n_small, 128}, {256, 64}, {256, 128}};
+      for (int a = 0; a < 4 && !S.valid; ++a) {
+        const int nt = largest_div16(u.N_total, shapes[a][0]), kc = largest_div16(u.cin_v, largest_div16(cps, shapes[a][1]));
+        if (cps % kc != 0 || (u.N_total / nt) > TC_MAX_NT || (u.N_total / nt) * (u.cin_v / kc) > 128) continue;
+        rc = pack_layer(u, largest_div16(cps, shapes[a][1]), nullptr, S, shapes[a][0]);
+        if (rc) return rc;
+      }
       S.sr_taps = v.n_taps; S.sr_dil = v.dil; S.sr_off = v.off;
-      // a K chunk must stay inside one tap / sub-row phase; the kernel's mask table holds 128 (n-tile, chunk) pairs
-      if (pl->cp[op.src] % S.KC != 0 || S.n_ntiles * S.n_kchunks > 128) free_layer(S);
     }
     // conv -> HEAD_V2 (no noise branch, amplitude modulation, 16 bands): the head runs in the epilogue
     if (!fuse && op.kind == RB_OP_CONV && op.res < 0 && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {
@@ -850,7 +859,11 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
         const Buf& src = bufs[op.src];
         const int rows = bufs[op.dst].n / L.fout;
         const int sr_min_b = getenv("RB_TC_SR_MINB") ? atoi(getenv("RB_TC_SR_MINB")) : 128;   // tests lower it
-        if (S.valid && src.lo < 0 && B >= sr_min_b && rows >= 1 && rows <= 4) {
+        if (getenv("RB_TC_SR_DEBUG"))
+          fprintf(stderr, "op %d conv %d->%d k%d s%d il%d rows %d sr_valid %d lo %d N_TILE %d KC %d nk %d\n", i, op.c_in,
+                  op.c_out, op.k, op.stride, op.ileave, rows, (int)S.valid, src.lo, S.valid ? S.N_TILE : L.N_TILE,
+                  S.valid ? S.KC : L.KC, S.valid ? S.n_kchunks : L.n_kchunks);
+        if (S.valid && h->spec.streaming && B >= sr_min_b && rows >= 1 && rows <= 4) {
           for (int t0 = 0; t0 < rows; ++t0) {
             const int rc = run_layer(S, op, nullptr, src, bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,
                                      sa[op.src], op.res >= 0 ? sa[op.res] : 0, sa[op.dst], t0);
@@ -1068,18 +1081,21 @@ struct RollSet {
   int ld[ROLL_MAX], hist[ROLL_MAX], n[ROLL_MAX], first[ROLL_MAX + 1];
   int count;
 };
-__global__ void __launch_bounds__(128) roll_many_kernel(const __grid_constant__ RollSet rs) {
+__global__ void __launch_bounds__(256) roll_many_kernel(const __grid_constant__ RollSet rs) {
+  // one WARP per (slot, stream, channel group) block of ld rows: 32 rows (512 B) per pass, read before write
+  const int gw = (int)((blockIdx.x * 256u + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (gw >= rs.first[rs.count]) return;
   int k = 0;
-  while (k + 1 < rs.count && (int)blockIdx.x >= rs.first[k + 1]) ++k;
-  uint4* base = rs.base[k] + (size_t)(blockIdx.x - rs.first[k]) * rs.ld[k];
+  while (k + 1 < rs.count && gw >= rs.first[k + 1]) ++k;
+  uint4* base = rs.base[k] + (size_t)(gw - rs.first[k]) * rs.ld[k];
   const int hist = rs.hist[k], n = rs.n[k];
-  for (int r0 = 0; r0 < hist; r0 += blockDim.x) {
-    const int r = r0 + threadIdx.x;
+  for (int r0 = 0; r0 < hist; r0 += 32) {
+    const int r = r0 + lane;
     uint4 v = make_uint4(0, 0, 0, 0);
     if (r < hist) v = base[r + n];
-    __syncthreads();
+    __syncwarp();
     if (r < hist) base[r] = v;
-    __syncthreads();
+    __syncwarp();
   }
 }
 __global__ void roll_audio_kernel(__nv_bfloat16* p, int ld, int hist, int n) {
@@ -1203,7 +1219,7 @@ int tc_stream_run(rb_handle* h, int ob, int oe, int B, int F, const void* in, vo
   rs.first[0] = 0;
   auto flush = [&]() -> int {
     if (rs.count == 0) return RB_OK;
-    roll_many_kernel<<<rs.first[rs.count], 128, 0, s>>>(rs);
+    roll_many_kernel<<<(rs.first[rs.count] + 7) / 8, 256, 0, s>>>(rs);
     RB_CUDA(cudaGetLastError());
     ++g_launches;
     rs.count = 0;
