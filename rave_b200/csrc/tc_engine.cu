@@ -52,9 +52,9 @@ struct Layer {
 
 struct Plan {
   std::vector<Layer> layers;      // per op
-  // Streaming, deep layers (<= 4 rows per stream and chunk): the same conv with its taps unrolled into
+  // Streaming, deep layers (<= 8 rows per stream and chunk): the same conv with its taps unrolled into
   // the K dimension (im2col over taps, n_taps = 1), run with the STREAM index as the row axis of the
-  // views -- one launch per row of the chunk fills 128-row tiles with 128 streams instead of running
+  // views (and the rows of the chunk as its stream axis) -- 128 streams fill a 128-row tile instead of running
   // one nearly empty tile (and one pass over the whole weight set) per stream.  See run_layer.
   std::vector<Layer> sr_layers;
   std::vector<int> skip;          // op is the tail of a fused pair
@@ -352,29 +352,33 @@ static uint32_t align_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
 static unsigned long long* g_trace = nullptr;   // debug hook only: device buffer [64][16] of clock stamps
 
 // x_act / res_act / out_act: the tensor is (to be) stored LeakyReLU-activated (Plan::sact).
-// sr_t0 >= 0: L is a stream-as-row twin (Plan::sr_layers); computes row sr_t0 of the chunk for all streams.
+// sr_rows > 0: L is a stream-as-row twin (Plan::sr_layers); computes the sr_rows rows of the chunk for all
+// streams in one launch (rows of the views = streams, "streams" of the views = rows of the chunk).
 static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Buf& src, const Buf& dst,
                      const Buf* res, int B, cudaStream_t s, int x_act = 0, int res_act = 0, int out_act = 0,
-                     int sr_t0 = -1) {
+                     int sr_rows = 0) {
   TcParams p;
   memset(&p, 0, sizeof(p));
   int rc = make_view(src, L.fin, &p.x);
   if (rc) return rc;
   if ((rc = make_view(dst, L.fout, &p.y))) return rc;
   const int n_streams = B;
-  if (sr_t0 >= 0) {
+  if (sr_rows > 0) {
     // rows = streams: row stride = the per-stream stride; tap j (and sub-row of a strided view) becomes
-    // the phase g / G1 of the view, `sB` units apart; the first tap's row is folded into the pointer
+    // the phase g / G1 of the view, `sB` units apart; the first tap's row is folded into the pointer;
+    // the chunk's rows take the place of the stream index (stride = one view row)
     TcView& x = p.x;
     RB_CHECK(src.cp != 1 && dst.cp != 1 && L.sr_taps > 0, RB_ERR_INVALID, "stream-as-row layer on an audio slot");
-    RB_CHECK(x.hist + sr_t0 - L.sr_off >= 0, RB_ERR_INVALID, "stream-as-row: history shorter than the filter");
-    x.p = src.p + (long long)(x.hist + sr_t0 - L.sr_off) * x.sT * 8;
+    RB_CHECK(x.hist - L.sr_off >= 0, RB_ERR_INVALID, "stream-as-row: history shorter than the filter");
+    x.p = src.p + (long long)(x.hist - L.sr_off) * x.sT * 8;
     x.sB = L.fin == 1 ? L.sr_dil : 1;
-    x.sT = (int)x.sb; x.sb = 0; x.hist = 0; x.lo = 0; x.n = n_streams; x.C = L.cin_v;
+    { const int row_units = x.sT; x.sT = (int)x.sb; x.sb = row_units; }
+    x.hist = 0; x.lo = 0; x.n = n_streams; x.C = L.cin_v;
     TcView& y = p.y;
-    y.p = dst.p + (long long)(y.hist + sr_t0) * y.sT * 8;
-    y.sT = (int)y.sb; y.sb = 0; y.hist = 0; y.lo = 0; y.n = n_streams;
-    B = 1;
+    y.p = dst.p + (long long)y.hist * y.sT * 8;
+    { const int row_units = y.sT; y.sT = (int)y.sb; y.sb = row_units; }
+    y.hist = 0; y.lo = 0; y.n = n_streams;
+    B = sr_rows;
   }
   RB_CHECK(p.x.C == L.cin_v && p.y.C == (L.head ? L.N_total / 2 : L.N_total), RB_ERR_INVALID,
            "layer/view channel mismatch (%d vs %d, %d vs %d)", p.x.C, L.cin_v, p.y.C, L.N_total);
@@ -384,11 +388,12 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     if ((rc = make_view(*res, 1, &p.res))) return rc;
     RB_CHECK(L.fout == 1 && p.res.C == L.N_total, RB_ERR_INVALID, "residual shape mismatch");
     p.res_delay = rop.res_delay;
-    if (sr_t0 >= 0) {
+    if (sr_rows > 0) {
       TcView& r = p.res;
-      RB_CHECK(res->cp != 1 && r.hist + sr_t0 - rop.res_delay >= 0, RB_ERR_INVALID, "stream-as-row: residual history");
-      r.p = res->p + (long long)(r.hist + sr_t0 - rop.res_delay) * 8;
-      r.sT = (int)r.sb; r.sb = 0; r.hist = 0; r.lo = 0; r.n = n_streams;
+      RB_CHECK(res->cp != 1 && r.hist - rop.res_delay >= 0, RB_ERR_INVALID, "stream-as-row: residual history");
+      r.p = res->p + (long long)(r.hist - rop.res_delay) * 8;
+      { const int row_units = r.sT; r.sT = (int)r.sb; r.sb = row_units; }
+      r.hist = 0; r.lo = 0; r.n = n_streams;
       p.res_delay = 0;
     }
   }
@@ -427,14 +432,14 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     RB_CHECK(resident || !L.fused, RB_ERR_UNSUPPORTED, "fused unit does not fit in shared memory");
     p.w_resident = resident ? 1 : 0;
     p.dual_g1 = (resident && L.N_TILE <= 64 && !getenv("RB_TC_NODUAL")) ? 1 : 0;
-    p.MT = (!resident && p.y.n >= 256 && sr_t0 < 0) ? 2 : 1;   // stream-as-row: few row tiles, keep them all busy
+    p.MT = (!resident && p.y.n >= 256 && sr_rows == 0) ? 2 : 1;   // stream-as-row: few row tiles, keep them all busy
     // streamed transposed convs run as cluster pairs: the two CTAs split every weight block (half
     // the L2 -> SM weight traffic each), which pays for one sub-tile per accumulator stage and so
     // for two stages at N_TILE = 256 -- the MMAs of the next work item overlap the epilogue, and
     // these layers (r phases of output per input row) are epilogue-heavy.  Measured neutral or
     // worse on the plain k = 1 / k = 3 layers (the 4-deep weight ring is then consumed in ~2000
     // cycles, about its refill latency), so those keep two sub-tiles per weight block.
-    p.pair = (!resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256 && L.fout >= 2 && sr_t0 < 0 &&
+    p.pair = (!resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256 && L.fout >= 2 && sr_rows == 0 &&
               !getenv("RB_TC_NOPAIR")) ? 1 : 0;
     if (const char* e = getenv("RB_TC_PAIRALL"))           // experiments only
       p.pair = (atoi(e) && !resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256) ? 1 : 0;
@@ -781,7 +786,7 @@ int tc_pack_weights(rb_handle* h) {
     rc = pack_layer(v, 64, fuse ? &v2 : nullptr, L);
     if (rc) return rc;
     if (h->spec.streaming && !fuse && op.kind == RB_OP_CONV && v.out_mask == 0 &&
-        pl->cp[op.src] != 1 && pl->cp[op.dst] != 1 && h->slots[op.dst].per_frame / v.fout <= 4 &&
+        pl->cp[op.src] != 1 && pl->cp[op.dst] != 1 && h->slots[op.dst].per_frame / v.fout <= 8 &&
         (size_t)v.cin_v * v.n_taps <= 16384 && !getenv("RB_TC_NOSR")) {
       ViewWeight u;                                    // taps unrolled into channels: c' = j * cin_v + c
       u.N_total = v.N_total; u.cin_v = v.cin_v * v.n_taps; u.n_taps = 1; u.dil = 1; u.off = 0;
@@ -863,13 +868,9 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
           fprintf(stderr, "op %d conv %d->%d k%d s%d il%d rows %d sr_valid %d lo %d N_TILE %d KC %d nk %d\n", i, op.c_in,
                   op.c_out, op.k, op.stride, op.ileave, rows, (int)S.valid, src.lo, S.valid ? S.N_TILE : L.N_TILE,
                   S.valid ? S.KC : L.KC, S.valid ? S.n_kchunks : L.n_kchunks);
-        if (S.valid && h->spec.streaming && B >= sr_min_b && rows >= 1 && rows <= 4) {
-          for (int t0 = 0; t0 < rows; ++t0) {
-            const int rc = run_layer(S, op, nullptr, src, bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,
-                                     sa[op.src], op.res >= 0 ? sa[op.res] : 0, sa[op.dst], t0);
-            if (rc) return rc;
-          }
-          return RB_OK;
+        if (S.valid && h->spec.streaming && B >= sr_min_b && rows >= 1 && rows <= 8) {
+          return run_layer(S, op, nullptr, src, bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,
+                           sa[op.src], op.res >= 0 ? sa[op.res] : 0, sa[op.dst], rows);
         }
       }
       return run_layer(L, op, nullptr, bufs[op.src], bufs[op.dst], op.res >= 0 ? &bufs[op.res] : nullptr, B, s,

@@ -223,27 +223,43 @@ def test_streaming_bf16_matches_golden_chunk_by_chunk(name):
 
 
 @pytest.mark.parametrize("name", ["v2_c8", "v2causal_c8", "raspberry_causal_c16"])
-def test_streaming_bf16_stream_as_row_layers(name, monkeypatch):
-    """Deep layers of a streaming step (<= 4 rows per stream and chunk) run with the stream index as the row
+def test_streaming_bf16_stream_as_row_layers(name, monkeypatch, capfd):
+    """Deep layers of a streaming step (<= 8 rows per stream and chunk) run with the stream index as the row
     axis and the taps unrolled into K once there are >= 128 streams; RB_TC_SR_MINB lowers that threshold so
     the 1-2 stream fixtures take the path.  Same bars as the plain streaming test, and the two paths agree."""
     m, meta, a = _model(name, streaming=True, dtype=torch.bfloat16)
     x = torch.from_numpy(golden_input(a)).cuda().bfloat16()
     n = int(a["chunk"].item())
     chunks = [x[..., c * n:(c + 1) * n].contiguous() for c in range(x.shape[-1] // n)]
-    l0 = m.kernel_launches()
     plain = torch.cat([m(c) for c in chunks], -1).float().cpu().numpy()
-    l_plain = m.kernel_launches() - l0
     monkeypatch.setenv("RB_TC_SR_MINB", "1")
     m.reset_streams()
-    l0 = m.kernel_launches()
     sr = torch.cat([m(c) for c in chunks], -1).float().cpu().numpy()
-    assert m.kernel_launches() - l0 != l_plain, "stream-as-row path not taken"
+    monkeypatch.setenv("RB_TC_SR_DEBUG", "1")              # the engine reports its choice per op on stderr
+    capfd.readouterr()
+    m(chunks[0])
+    torch.cuda.synchronize()
+    assert "sr_valid 1" in capfd.readouterr().err, "stream-as-row path not taken"
+    monkeypatch.delenv("RB_TC_SR_DEBUG")
     assert rel_l2(sr, a["y_stream"]) < 2 * BF16_TOL
     assert rel_l2(sr, plain) < BF16_TOL
     m.reset_streams()
     zs = torch.cat([m.encode(c) for c in chunks], -1).float().cpu().numpy()
     assert rel_l2(zs, a["z_stream"]) < BF16_TOL
+
+
+def test_streaming_bf16_many_streams_fill_row_tiles():
+    """256 streams (128 copies of the 2-stream fixture): above the default threshold the deep layers run
+    stream-as-row over two 128-stream row tiles; every copy must equal the first bit for bit and match
+    the oracle's streaming run."""
+    m, meta, a = _model("v2causal_c8", streaming=True, dtype=torch.bfloat16)
+    x = torch.from_numpy(golden_input(a)).cuda().bfloat16().repeat(128, 1, 1).contiguous()
+    n = int(a["chunk"].item())
+    m.alloc_streams(256, n)
+    y = torch.cat([m(x[..., c * n:(c + 1) * n].contiguous()) for c in range(x.shape[-1] // n)], -1)
+    assert torch.equal(y[2:], y[:2].repeat(127, 1, 1))
+    assert rel_l2(y[:2].float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
+    assert rel_l2(y[-2:].float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
 
 
 @pytest.mark.gpu
