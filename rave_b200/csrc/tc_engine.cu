@@ -1080,6 +1080,7 @@ constexpr int ROLL_MAX = 56;
 struct RollSet {
   uint4* base[ROLL_MAX];
   int ld[ROLL_MAX], hist[ROLL_MAX], n[ROLL_MAX], first[ROLL_MAX + 1];
+  int skip[ROLL_MAX];     // hist is rounded up to 16 rows for alignment; only the last hist - skip rows are state
   int count;
 };
 __global__ void __launch_bounds__(256) roll_many_kernel(const __grid_constant__ RollSet rs) {
@@ -1090,7 +1091,7 @@ __global__ void __launch_bounds__(256) roll_many_kernel(const __grid_constant__ 
   while (k + 1 < rs.count && gw >= rs.first[k + 1]) ++k;
   uint4* base = rs.base[k] + (size_t)(gw - rs.first[k]) * rs.ld[k];
   const int hist = rs.hist[k], n = rs.n[k];
-  for (int r0 = 0; r0 < hist; r0 += 32) {
+  for (int r0 = rs.skip[k]; r0 < hist; r0 += 32) {
     const int r = r0 + lane;
     uint4 v = make_uint4(0, 0, 0, 0);
     if (r < hist) v = base[r + n];
@@ -1246,6 +1247,7 @@ int tc_stream_run(rb_handle* h, int ob, int oe, int B, int F, const void* in, vo
         const int k = rs.count++;
         rs.base[k] = reinterpret_cast<uint4*>(b.p);
         rs.ld[k] = b.ld; rs.hist[k] = b.hist; rs.n[k] = b.n;
+        rs.skip[k] = std::max(0, b.hist - h->slots[u].hist);
         rs.first[k + 1] = rs.first[k] + B * (b.cp / 8);
         if (rs.count == ROLL_MAX) { int rc = flush(); if (rc) return rc; }
       }
