@@ -473,6 +473,14 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     // W ring depth: a single-tap layer consumes one A chunk per W block, so it needs A stages in
     // flight (HBM latency) more than W stages (L2 latency); multi-tap layers the other way round
     p.SW = resident ? 0 : (L.n_taps == 1 ? 2 : 4);
+    if (!resident && sr_rows > 0) {
+      // stream-as-row: a CTA's work is one short pass over its slice of the weights, bound by the L2
+      // round trip of each block -- keep as many blocks in flight as fit beside three A stages
+      int sw = 4;                                                               // the kernel has 4 W barriers
+      if (const char* e = getenv("RB_TC_SR_SW")) sw = std::min(4, std::max(2, atoi(e)));   // experiments only
+      p.SW = sw;
+      while (p.SW > 2 && fixed + p.SW * L.blk_bytes + 3 * p.a_stage_bytes > budget) --p.SW;
+    }
     uint32_t w_bytes = resident ? align_up(w_total, 128) : p.SW * L.blk_bytes;
     if (!resident && fixed + w_bytes + 2 * p.a_stage_bytes > budget) { p.SW = 2; w_bytes = p.SW * L.blk_bytes; }
     if (L.fused) {
