@@ -793,8 +793,9 @@ int tc_pack_weights(rb_handle* h) {
     Layer& L = pl->layers[i];
     rc = pack_layer(v, 64, fuse ? &v2 : nullptr, L);
     if (rc) return rc;
-    if (h->spec.streaming && !fuse && op.kind == RB_OP_CONV && v.out_mask == 0 &&
-        pl->cp[op.src] != 1 && pl->cp[op.dst] != 1 && h->slots[op.dst].per_frame / v.fout <= 8 &&
+    if (h->spec.streaming && op.kind == RB_OP_CONV && v.out_mask == 0 &&
+        pl->cp[op.src] != 1 && pl->cp[op.dst] != 1 &&
+        h->slots[op.dst].per_frame / v.fout <= (fuse ? 32 : 8) &&      // fused units: also the 32-row C = 128 stage
         (size_t)v.cin_v * v.n_taps <= 16384 && !getenv("RB_TC_NOSR")) {
       ViewWeight u;                                    // taps unrolled into channels: c' = j * cin_v + c
       u.N_total = v.N_total; u.cin_v = v.cin_v * v.n_taps; u.n_taps = 1; u.dil = 1; u.off = 0;
@@ -814,13 +815,25 @@ int tc_pack_weights(rb_handle* h) {
       const int cps = pl->cp[op.src];
       const int n_small = std::max(64, round16((u.N_total + TC_MAX_NT - 1) / TC_MAX_NT));
       const int shapes[4][2] = {{n_small, 64}, {n_small, 128}, {256, 64}, {256, 128}};
-      for (int a = 0; a < 4 && !S.valid; ++a) {
+      if (fuse) {                                       // a fused unit is one n-tile; 64-channel K chunks
+        const int kc = largest_div16(u.cin_v, largest_div16(cps, 64));
+        if (cps % kc == 0 && u.cin_v / kc <= 128) {
+          rc = pack_layer(u, largest_div16(cps, 64), &v2, S, 256);
+          if (rc) return rc;
+        }
+      }
+      for (int a = 0; a < 4 && !S.valid && !fuse; ++a) {
         const int nt = largest_div16(u.N_total, shapes[a][0]), kc = largest_div16(u.cin_v, largest_div16(cps, shapes[a][1]));
         if (cps % kc != 0 || (u.N_total / nt) > TC_MAX_NT || (u.N_total / nt) * (u.cin_v / kc) > 128) continue;
         rc = pack_layer(u, largest_div16(cps, shapes[a][1]), nullptr, S, shapes[a][0]);
         if (rc) return rc;
       }
       S.sr_taps = v.n_taps; S.sr_dil = v.dil; S.sr_off = v.off;
+      if (fuse && S.valid) {
+        S.fused = true; S.fused_with = i + 1; S.tail = i + 1; S.act2 = h->ops[i + 1].pre_act;
+        if (!v2.bias.empty() && (rc = dev_upload(v2.bias, &S.bias2))) return rc;
+        if (!v2.alpha.empty() && (rc = dev_upload(v2.alpha, &S.alpha2))) return rc;
+      }
     }
     // conv -> HEAD_V2 (no noise branch, amplitude modulation, 16 bands): the head runs in the epilogue
     if (!fuse && op.kind == RB_OP_CONV && op.res < 0 && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {
@@ -862,6 +875,14 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
       const std::vector<int>& sa = pl->sact;
       if (L.fused) {
         const rb_op& o2 = h->ops[L.fused_with];
+        const Layer& S = pl->sr_layers[i];
+        const int rows = bufs[o2.dst].n;
+        const int sr_min_b = getenv("RB_TC_SR_MINB") ? atoi(getenv("RB_TC_SR_MINB")) : 128;
+        if (S.valid && S.fused && h->spec.streaming && B >= sr_min_b && rows >= 1 && rows <= 32) {
+          if (getenv("RB_TC_SR_DEBUG")) fprintf(stderr, "op %d fused unit C %d rows %d sr_valid 1\n", i, op.c_in, rows);
+          return run_layer(S, op, &o2, bufs[op.src], bufs[o2.dst], &bufs[o2.res], B, s, sa[op.src], sa[o2.res],
+                           sa[o2.dst], rows);
+        }
         return run_layer(L, op, &o2, bufs[op.src], bufs[o2.dst], &bufs[o2.res], B, s, sa[op.src], sa[o2.res],
                          sa[o2.dst]);
       }
