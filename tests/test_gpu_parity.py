@@ -260,6 +260,13 @@ def test_streaming_bf16_many_streams_fill_row_tiles():
     assert torch.equal(y[2:], y[:2].repeat(127, 1, 1))
     assert rel_l2(y[:2].float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
     assert rel_l2(y[-2:].float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
+    # a stream count that is not a multiple of the 128-row tile, two frames per chunk (twice the rows per layer)
+    m2, _, _ = _model("v2causal_c8", streaming=True, dtype=torch.bfloat16)
+    m2.alloc_streams(130, 2 * n)
+    x2 = x[:130].contiguous()
+    y2 = torch.cat([m2(x2[..., c * 2 * n:(c + 1) * 2 * n].contiguous()) for c in range(x.shape[-1] // (2 * n))], -1)
+    assert torch.equal(y2[2:], y2[:2].repeat(64, 1, 1))
+    assert rel_l2(y2[:2].float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
 
 
 @pytest.mark.gpu
