@@ -240,6 +240,20 @@ int rb_yin_estimate(const float* x, int B, int T, int sample_rate, double pitch_
 int rb_f0_one_hot(const float* f0, int B, int F, int num_bins, int channels_first, float* one_hot,
                   float* log_f0_norm, void* stream);
 
+/* Export-time latent post / pre-processing (scripts/export.py:482-539; defined upstream but not on this fork's
+ * live `myforward` path).  rb_latent_*: VariationalScriptedRAVE :484-499 after reparametrize -- pca [C][C] =
+ * latent_pca, mean [C] = latent_mean (host); post: z device fp32 [B,C,F] -> out [B,n_keep,F] = pca[:n_keep] (z - mean);
+ * pre: z [B,n_keep,F], noise [B,C-n_keep,F] (the reference draws randn; NULL = zeros) -> out [B,C,F] =
+ * pca^T cat(z, noise) + mean.  rb_unit_norm_to_angles / rb_angles_to_unit_norm: rave/blocks.py:926-956
+ * (SphericalScriptedRAVE :533-539): x [B,C,F] <-> angles [B,C-1,F]. */
+typedef struct rb_latent rb_latent;
+int rb_latent_create(int device, int C, const float* pca, const float* mean, rb_latent** out);
+int rb_latent_destroy(rb_latent* h);
+int rb_latent_post(rb_latent* h, const float* z, int B, int F, int n_keep, float* out, void* stream);
+int rb_latent_pre(rb_latent* h, const float* z, const float* noise, int B, int F, int n_keep, float* out, void* stream);
+int rb_unit_norm_to_angles(const float* x, int B, int C, int F, float* angles, void* stream);
+int rb_angles_to_unit_norm(const float* angles, int B, int C, int F, float* x, void* stream);
+
 /* Per-op device timing (CUDA events on the launching stream around every op of the
  * program).  enable!=0 starts recording; rb_op_times synchronises, writes the accumulated
  * milliseconds per op (n = number of ops) and clears the record. */

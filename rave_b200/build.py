@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librave_b200.so")
-SOURCES = ["engine.cu", "stream.cu", "kernels_f32.cu", "rvq.cu", "tc_engine.cu", "tc_conv.cu", "speaker.cu", "resampler.cu", "pitch.cu"]
+SOURCES = ["engine.cu", "stream.cu", "kernels_f32.cu", "rvq.cu", "tc_engine.cu", "tc_conv.cu", "speaker.cu", "resampler.cu", "pitch.cu", "latent.cu"]
 NVCC_FLAGS = (["-DRB_SPIN_WAIT"] if os.environ.get("RB_SPIN_WAIT") else []) + ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--expt-relaxed-constexpr"]
 

@@ -99,6 +99,12 @@ EXPORTS = {
     "rb_yin_estimate": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
                         C.c_void_p, C.c_int, C.c_void_p],
     "rb_f0_one_hot": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p],
+    "rb_latent_create": [C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_void_p)],
+    "rb_latent_destroy": [C.c_void_p],
+    "rb_latent_post": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
+    "rb_latent_pre": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
+    "rb_unit_norm_to_angles": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
+    "rb_angles_to_unit_norm": [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_profile_ops": [C.c_void_p, C.c_int],
     "rb_op_times": [C.c_void_p, C.POINTER(C.c_float), C.c_int],
     "rb_last_error": [],

@@ -554,3 +554,36 @@ def test_from_run_loads_config_checkpoint_and_speaker_encoder(tmp_path):
         m2.encode(x)
     m2.set_speaker(sd["speaker"])
     assert rel_l2(m2.encode(x).cpu().numpy()[:, :-256], a["z"][:, :-256]) > 0.1
+
+
+# ----------------------------------------------------------------------------- latent processing
+def test_latent_post_pre_processing_vs_oracle():
+    """scripts/export.py:484-499 (PCA projection / crop, inverse with the noise draw) and blocks.py:926-956."""
+    from oracle import latent_oracle as L
+    from oracle.weights_recipe import recipe_input
+    from rave_b200 import latent
+    g = torch.Generator().manual_seed(9)
+    C, n = 128, 16
+    q, _ = torch.linalg.qr(torch.randn(C, C, generator=g))
+    mean = 0.3 * torch.randn(C, generator=g)
+    z = torch.from_numpy(recipe_input((3, C, 50), 31, scale=1.0))
+    noise = torch.from_numpy(recipe_input((3, C - n, 50), 32, scale=1.0))
+    pca = latent.LatentPCA(q, mean)
+    y = pca.post_process_latent(z.cuda(), n)
+    want = L.post_process_latent(z, q, mean, n)
+    assert tuple(y.shape) == (3, n, 50) and rel_l2(y.cpu().numpy(), want.numpy()) < 1e-5
+    back = pca.pre_process_latent(y, noise.cuda())
+    assert rel_l2(back.cpu().numpy(), L.pre_process_latent(want, noise, q, mean).numpy()) < 1e-5
+    zero = pca.pre_process_latent(y)
+    assert rel_l2(zero.cpu().numpy(), L.pre_process_latent(want, torch.zeros_like(noise), q, mean).numpy()) < 1e-5
+    with pytest.raises(ValueError):
+        pca.post_process_latent(z[:, :64].cuda(), n)
+    # spherical latents
+    x = torch.from_numpy(recipe_input((4, 16, 70), 33, scale=1.0))
+    x = x / x.norm(dim=1, keepdim=True)
+    a = latent.unit_norm_vector_to_angles(x.cuda())
+    a_ref = L.unit_norm_vector_to_angles(x.clone())
+    assert tuple(a.shape) == (4, 15, 70) and float((a.cpu() - a_ref).abs().max()) < 2e-4   # acos is steep near +-1
+    v = latent.angles_to_unit_norm_vector(a_ref.cuda())
+    assert rel_l2(v.cpu().numpy(), L.angles_to_unit_norm_vector(a_ref.clone()).numpy()) < 1e-5
+    assert rel_l2(latent.angles_to_unit_norm_vector(a).cpu().numpy(), x.numpy()) < 1e-4     # device round trip

@@ -332,3 +332,29 @@ def test_pitch_oracle_matches_live_reference():
     oh, ln = pu.get_f0_norm(x, torch.zeros(4, 1), torch.ones(4, 1), 44100, 1024)
     oh2, ln2 = P.f0_norm_one_hot(f0)
     assert torch.equal(oh, oh2) and torch.equal(torch.nan_to_num(ln, nan=-9.), torch.nan_to_num(ln2, nan=-9.))
+
+
+# ----------------------------------------------------------------------------- latent processing
+@needs_ref
+@pytest.mark.reference
+def test_latent_oracle_angles_match_live_reference():
+    from oracle import latent_oracle as L
+    blocks = R.load("blocks")
+    x = torch.from_numpy(recipe_input((3, 16, 40), 21, scale=1.0))
+    x = x / x.norm(dim=1, keepdim=True)
+    a_ref = blocks.unit_norm_vector_to_angles(x.clone())
+    assert torch.equal(a_ref, L.unit_norm_vector_to_angles(x.clone()))
+    assert torch.equal(blocks.angles_to_unit_norm_vector(a_ref.clone()), L.angles_to_unit_norm_vector(a_ref.clone()))
+    assert rel_l2(L.angles_to_unit_norm_vector(a_ref.clone()).numpy(), x.numpy()) < 1e-5     # round trip
+
+
+def test_latent_oracle_pca_round_trip():
+    from oracle import latent_oracle as L
+    g = torch.Generator().manual_seed(5)
+    q, _ = torch.linalg.qr(torch.randn(16, 16, generator=g))
+    mean = torch.randn(16, generator=g)
+    z = torch.randn(2, 16, 30, generator=g)
+    y = L.post_process_latent(z, q, mean, 16)
+    back = L.pre_process_latent(y, z.new_zeros(2, 0, 30), q, mean)
+    assert rel_l2(back.numpy(), z.numpy()) < 1e-5                                          # orthonormal PCA
+    assert L.post_process_latent(z, q, mean, 4).shape == (2, 4, 30)
