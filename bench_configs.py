@@ -38,6 +38,25 @@ def _time(fn, warmup, steps):
     return e0.elapsed_time(e1) / steps
 
 
+def c0(args):
+    """BASELINE configs[0]: the reference's own CPU-runnable case, one stream x 2^17 samples (latency-bound)."""
+    import torch
+    from rave_b200 import RAVE
+    _, sd = _sd("v2_c64")
+    out = []
+    for dtype, tag in ((torch.bfloat16, "bf16"), (torch.float32, "f32")):
+        m = RAVE.from_gin(["v2.gin"], dtype=dtype)
+        m.load_state_dict(sd)
+        x = (torch.rand(1, 1, 2 ** 17, device="cuda") - 0.5).to(dtype)
+        l0 = m.kernel_launches()
+        ms = _time(lambda: m(x), 5, args.steps)
+        out.append({"config": "C0 v2 offline, 1 stream x 2^17 samples, CAPACITY=64 (BASELINE configs[0])", "dtype": tag,
+                    "ms_per_step": ms, "value": 2 ** 17 / SR / (ms / 1e3), "unit": "audio-sec/sec",
+                    "launches_per_step": (m.kernel_launches() - l0) // (5 + args.steps)})
+        del m
+    return out
+
+
 def c3(args):
     import torch
     from rave_b200 import RAVE
@@ -153,13 +172,13 @@ def c7(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--legs", default="c3,c4,c5,c6,c7")
+    ap.add_argument("--legs", default="c0,c3,c4,c5,c6,c7")
     ap.add_argument("--steps", type=int, default=32)
     ap.add_argument("--streams", type=int, default=1024)
     ap.add_argument("--batch", type=int, default=512)
     args = ap.parse_args()
     for leg in args.legs.split(","):
-        for row in {"c3": c3, "c4": c4, "c5": c5, "c6": c6, "c7": c7}[leg](args):
+        for row in {"c0": c0, "c3": c3, "c4": c4, "c5": c5, "c6": c6, "c7": c7}[leg](args):
             print(json.dumps(row), flush=True)
 
 
