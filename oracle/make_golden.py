@@ -56,7 +56,7 @@ def offline_and_stream(name, cfg, B, T, chunk=None, x_seed=1234, with_stream=Tru
         z = model.encode(x)
         y = model.decode(z)
     arrays.update(z=z.numpy(), y=y.numpy())
-    if with_stream and not cfg.get("noise", False):
+    if with_stream:
         ms = R.build_reference(cfg, streaming=True)
         ms.load_state_dict(_sd(model), strict=False)
         zs, ys = [], []
@@ -64,7 +64,14 @@ def offline_and_stream(name, cfg, B, T, chunk=None, x_seed=1234, with_stream=Tru
             xc = x[..., c * chunk:(c + 1) * chunk]
             zc = ms.encode(xc)
             zs.append(zc)
-            ys.append(ms.decode(zc))
+            if noise is not None:
+                # the chunk's slice of the injected draw (blocks.py:287 rand_like inside the cached module)
+                q = chunk // cfg["n_band"] // 8
+                nc = noise[:, c * q:(c + 1) * q]
+                with mock.patch("torch.rand_like", side_effect=lambda t: (nc + 1) / 2):
+                    ys.append(ms.decode(zc))
+            else:
+                ys.append(ms.decode(zc))
         arrays.update(chunk=np.int64(chunk), z_stream=torch.cat(zs, -1).numpy(),
                       y_stream=torch.cat(ys, -1).numpy())
     if cfg.get("encoder_type") == "discrete":
@@ -157,6 +164,12 @@ def main():
     if not R.available():
         sys.exit("reference tree not available; golden files can only be made in the build container")
     torch.manual_seed(0)
+    only = set(sys.argv[1:])
+    if only:                      # python -m oracle.make_golden v2_c64 discrete_c96 ...: just these
+        for name, args in SIZED.items():
+            if name in only:
+                offline_and_stream(name, *args)
+        return
     pqmf_fixture()
     speaker_fixture()
     resampler_fixture()
@@ -166,12 +179,24 @@ def main():
     offline_and_stream("v3_c8", C.v3(8), 2, 16384, 2048)
     offline_and_stream("v3causal_c8", C.v3(8, causal=True), 1, 8192, 2048)
     offline_and_stream("discrete_c8", C.discrete(8), 1, 8192, 2048)
-    offline_and_stream("v2noise_c8", C.v2(8, noise=True), 2, 8192, None)
+    offline_and_stream("v2noise_c8", C.v2(8, noise=True), 2, 8192, 2048)
     offline_and_stream("v1_c8", C.v1(8), 1, 8192, 2048)
     offline_and_stream("raspberry_c16", C.raspberry(16), 1, 8192, 1024)
     offline_and_stream("raspberry_causal_c16", C.raspberry(16, causal=True), 1, 8192, 1024)
-    # the real sizes of BASELINE.json configs[0] (fp32, B=1), shortened to 2^15 samples
-    offline_and_stream("v2_c64", C.v2(64), 1, 32768, None, with_stream=False)
+    for name, args in SIZED.items():
+        offline_and_stream(name, *args)
+
+
+# The configurations BASELINE.json quotes numbers on, at their REAL channel widths (shortened in time):
+# configs[0]/[1] v2 CAPACITY 64, configs[2] causal v2 in 2048-sample chunks, configs[3] discrete
+# (discrete.gin:13-19: CAPACITY 96, LATENT_SIZE 128), configs[4] v3 (Snake + AdaIN) CAPACITY 64.
+SIZED = {
+    "v2_c64": (C.v2(64), 1, 32768, 2048),
+    "v2causal_c64": (C.v2(64, causal=True), 2, 8192, 2048),
+    "discrete_c96": (C.discrete(96), 1, 8192, 2048),
+    "v3_c64": (C.v3(64), 1, 8192, 2048),
+    "v3causal_c64": (C.v3(64, causal=True), 1, 8192, 2048),
+}
 
 
 if __name__ == "__main__":

@@ -17,7 +17,9 @@ from oracle.weights_recipe import recipe_input
 from .util import golden_input, golden_state_dict, load_golden, rel_l2
 
 FIXTURES = ["v2_c8", "v2causal_c8", "v3_c8", "v3causal_c8", "discrete_c8", "v2noise_c8",
-            "v1_c8", "raspberry_c16", "raspberry_causal_c16", "v2_c64"]
+            "v1_c8", "raspberry_c16", "raspberry_causal_c16",
+            # BASELINE.json configs at their real channel widths (oracle/make_golden.py SIZED)
+            "v2_c64", "v2causal_c64", "discrete_c96", "v3_c64", "v3causal_c64"]
 needs_ref = pytest.mark.skipif(not R.available(), reason="reference tree not present")
 
 
@@ -49,17 +51,22 @@ def test_oracle_offline_matches_golden(name):
     assert rel_l2(y.numpy(), a["y"]) < 5e-5
 
 
-@pytest.mark.parametrize("name", [f for f in FIXTURES if f not in ("v2noise_c8", "v2_c64")])
+@pytest.mark.parametrize("name", FIXTURES)
 def test_oracle_streaming_matches_golden(name):
     meta, a = load_golden(name)
     o = OracleRAVE(meta["cfg"], golden_state_dict(meta), streaming=True)
     x = torch.from_numpy(golden_input(a))
     n = int(a["chunk"].item())
+    noise = None
+    if meta["cfg"].get("noise"):
+        B, _, T = x.shape
+        noise = torch.from_numpy(recipe_input((B, T // 16 // 8, 16, 8), int(a["noise_seed"].item()), uniform=True))
     zs, ys = [], []
     for c in range(x.shape[-1] // n):
         z = o.encode(x[..., c * n:(c + 1) * n])
         zs.append(z)
-        ys.append(o.decode(z))
+        q = n // 16 // 8
+        ys.append(o.decode(z, None if noise is None else noise[:, c * q:(c + 1) * q]))
     assert rel_l2(torch.cat(zs, -1).numpy(), a["z_stream"]) < 2e-5
     assert rel_l2(torch.cat(ys, -1).numpy(), a["y_stream"]) < 5e-5
 
@@ -74,8 +81,9 @@ def test_causal_stream_equals_offline_after_delay():
     assert rel_l2(ys[..., 14336:], y[..., 14336 - d:-d]) < 1e-5   # transient: 4e-2 @4096, 1e-4 @12288
 
 
-def test_rvq_oracle_matches_golden_bit_exact():
-    meta, a = load_golden("discrete_c8")
+@pytest.mark.parametrize("name", ["discrete_c8", "discrete_c96"])
+def test_rvq_oracle_matches_golden_bit_exact(name):
+    meta, a = load_golden(name)
     o = OracleRAVE(meta["cfg"], golden_state_dict(meta))
     zq = torch.from_numpy(recipe_input((4, 128, 64), int(a["rvq_z_seed"].item()), scale=1.0))
     idx = o.rvq_encode(zq)
