@@ -6,10 +6,12 @@
                               (SphericalScriptedRAVE, export.py:533-539)
 
 PINNING: the angle maps are compared with the live rave/blocks.py functions
-(tests/test_oracle_pins.py::test_latent_oracle_angles_match_live_reference); scripts/export.py itself
-cannot be imported here (absl flags, cached_conv, nn_tilde), so the two PCA methods -- four tensor
-statements each -- are restated from the source lines cited above: "parity unpinned" for those two,
-pinned for the angle maps.  rave_b200/ never imports this file.
+(tests/test_oracle_pins.py::test_latent_oracle_angles_match_live_reference).  scripts/export.py itself
+cannot be imported here (absl flags, cached_conv, nn_tilde), so its `*ScriptedRAVE` class definitions are
+cut out of the file's syntax tree and executed over a stub base (oracle/ref_loader.py:
+load_export_latent_classes): the two PCA methods below are compared bit for bit with the reference's own
+method bodies, randn draw included (::test_latent_oracle_pca_matches_live_export_methods).  Pinned.
+rave_b200/ never imports this file.
 """
 import numpy as np
 import torch

@@ -68,7 +68,7 @@ class OracleRAVE:
         """CachedPQMF.forward, pqmf.py:269-273."""
         w = self.sd["pqmf.forward_conv.weight"]
         M, k = w.shape[0], w.shape[-1]
-        pl, pr = O.get_padding(k, 1, self.causal)
+        pl, pr = O.get_padding(k, 1, self.causal and self.cfg.get("pqmf", "CachedPQMF") != "PQMF")
         if self.stream is None:
             x = F.pad(x, (pl, pr))
         else:
@@ -79,12 +79,16 @@ class OracleRAVE:
         """CachedPQMF.inverse, pqmf.py:275-284."""
         w = self.sd["pqmf.inverse_conv.weight"]
         M, k = w.shape[0], w.shape[-1]
-        pl, pr = O.get_padding(k, 1, self.causal)
+        pl, pr = O.get_padding(k, 1, self.causal and self.cfg.get("pqmf", "CachedPQMF") != "PQMF")
         y = O._reverse_half(y)
         if self.stream is None:
             y = F.pad(y, (pl, pr))
         else:
             y = self.stream.pad("pqmf.inverse_conv.cache", y, pl + pr)
+        if self.cfg.get("pqmf", "CachedPQMF") == "PQMF" and self.stream is None:
+            # pqmf.PQMF.inverse (pqmf.py:111-135): the same polyphase synthesis one sub-band row earlier
+            # (pinned against the live class in tests/test_oracle_pins.py)
+            y = F.pad(y[..., 1:], (0, 1))
         y = F.conv1d(y, w) * M
         y = y.flip(1)                                          # [B, M, L]
         B, _, L = y.shape

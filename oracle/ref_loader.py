@@ -272,3 +272,29 @@ def fill_deterministic(model: torch.nn.Module, seed: int = 0):
             new[name] = torch.from_numpy(v).to(t.dtype)
     model.load_state_dict(new, strict=False)
     return model
+
+
+def load_export_latent_classes():
+    """The REAL `post_process_latent` / `pre_process_latent` methods of scripts/export.py:482-539.
+
+    scripts/export.py cannot be imported (absl flags at import, nn_tilde, cached_conv, librosa), so the
+    four `*ScriptedRAVE` class definitions are cut out of its syntax tree and executed against a stub
+    base class: the method bodies that run are the reference's own lines, not a restatement.  Returns
+    {class name: class}; instances need the attributes the methods read (latent_pca, latent_mean,
+    latent_size, full_latent_size, encoder)."""
+    import ast
+    import torch.nn.functional as F
+    path = os.path.join(REFERENCE_ROOT, "scripts", "export.py")
+    tree = ast.parse(open(path).read(), path)
+    want = ("VariationalScriptedRAVE", "DiscreteScriptedRAVE", "WasserteinScriptedRAVE", "SphericalScriptedRAVE")
+    body = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name in want]
+    if len(body) != len(want):
+        raise RuntimeError("scripts/export.py no longer defines the four *ScriptedRAVE classes")
+
+    class ScriptedRAVE:                                    # stub base: the methods only touch attributes
+        pass
+
+    rave_ns = types.SimpleNamespace(blocks=load("blocks"))
+    ns = {"ScriptedRAVE": ScriptedRAVE, "torch": torch, "F": F, "rave": rave_ns, "np": np}
+    exec(compile(ast.Module(body=body, type_ignores=[]), path, "exec"), ns)
+    return {k: ns[k] for k in want}

@@ -10,21 +10,24 @@
 `split_state_dict` separates the `speaker_encoder.*` tensors (model.py:164-174) from the model's own.
 """
 import os
-from pathlib import Path
 
 
 def search_for_run(run_path, mode="last"):
-    """rave/core.py:132-139."""
+    """What rave/core.py:132-139 returns: `run_path` itself when it already names a checkpoint, else the
+    lexicographically last `*.ckpt` anywhere below it whose file name contains `mode`, else None."""
     if run_path is None:
         return None
+    run_path = str(run_path)
     if ".ckpt" in run_path:
         return run_path
-    ckpts = map(str, Path(run_path).rglob("*.ckpt"))
-    ckpts = filter(lambda e: mode in os.path.basename(str(e)), ckpts)
-    ckpts = sorted(ckpts)
-    if len(ckpts):
-        return ckpts[-1]
-    return None
+    best = None
+    for root, _dirs, files in os.walk(run_path):
+        for name in files:
+            if name.endswith(".ckpt") and mode in name:
+                full = os.path.join(root, name)
+                if best is None or full > best:
+                    best = full
+    return best
 
 
 def load_checkpoint(path, ema_weights=False):
@@ -33,9 +36,11 @@ def load_checkpoint(path, ema_weights=False):
     values upstream, hence strict=False there and here)."""
     import torch
     try:
+        # tensors-only unpickling first: a checkpoint may come from a downloaded run directory
+        ckpt = torch.load(path, map_location="cpu", weights_only=True)
+    except Exception:
+        # Lightning checkpoints pickle callback / hyper-parameter objects next to the tensors
         ckpt = torch.load(path, map_location="cpu", weights_only=False)
-    except TypeError:                      # torch < 1.13 has no weights_only
-        ckpt = torch.load(path, map_location="cpu")
     if ema_weights and "EMA" in ckpt.get("callbacks", {}):
         return dict(ckpt["callbacks"]["EMA"])
     return dict(ckpt["state_dict"])

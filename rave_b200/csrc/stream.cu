@@ -105,6 +105,10 @@ int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype) {
   RB_CHECK(max_chunk % h->spec.samples_per_frame == 0, RB_ERR_INVALID,
            "chunk %d is not a multiple of the model ratio %d", max_chunk, h->spec.samples_per_frame);
   RB_CUDA(cudaSetDevice(h->device));
+  // not ready until every buffer of the new arena exists: a failed (re)allocation must not leave
+  // rb_stream_* running on freed or partially allocated state
+  h->stream_ready = false;
+  RB_CUDA(cudaDeviceSynchronize());               // no step of the old arena may still be in flight
   for (void* p : h->sbuf) cudaFree(p);
   const int ns = (int)h->slots.size();
   h->sbuf.assign(ns, nullptr);
@@ -113,9 +117,12 @@ int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype) {
   h->max_streams = max_streams;
   h->max_frames = max_chunk / h->spec.samples_per_frame;
   h->stream_dtype = dtype;
+  auto release = [&]() {
+    for (void*& p : h->sbuf) { cudaFree(p); p = nullptr; }
+  };
   if (dtype == RB_BF16) {
     int rc = tc_stream_alloc(h);
-    if (rc) return rc;
+    if (rc) { release(); return rc; }
     h->stream_ready = true;
     return RB_OK;
   }
@@ -125,8 +132,13 @@ int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype) {
     h->s_hist[sl] = round4(s.hist);
     h->s_ld[sl] = h->s_hist[sl] + round4(s.per_frame * h->max_frames);
     const size_t bytes = (size_t)max_streams * s.channels * h->s_ld[sl] * sizeof(float);
-    RB_CUDA(cudaMalloc(&h->sbuf[sl], bytes));
-    RB_CUDA(cudaMemset(h->sbuf[sl], 0, bytes));
+    cudaError_t e = cudaMalloc(&h->sbuf[sl], bytes);
+    if (e == cudaSuccess) e = cudaMemset(h->sbuf[sl], 0, bytes);
+    if (e != cudaSuccess) {
+      release();
+      set_error("rb_stream_alloc: %s (%zu bytes for slot %d)", cudaGetErrorString(e), bytes, sl);
+      return RB_ERR_CUDA;
+    }
   }
   h->stream_ready = true;
   return RB_OK;
@@ -135,6 +147,9 @@ int rb_stream_alloc(rb_handle* h, int max_streams, int max_chunk, int dtype) {
 int rb_stream_reset(rb_handle* h, const int32_t* ids, int n) {
   RB_CHECK(h && h->stream_ready, RB_ERR_STATE, "streams are not allocated");
   RB_CUDA(cudaSetDevice(h->device));
+  // the memsets below run on the legacy stream, which does not order against cudaStreamNonBlocking
+  // caller streams: drain the device so a reset can never race with a step still in flight
+  RB_CUDA(cudaDeviceSynchronize());
   if (h->stream_dtype == RB_BF16) return tc_stream_reset(h, ids, n);
   for (size_t sl = 0; sl < h->slots.size(); ++sl) {
     if (!h->sbuf[sl]) continue;

@@ -11,6 +11,7 @@ params), references `@module.Class`, scoped `@scope/module.Class` and evaluated
 Selectors are matched on their last identifier (`blocks.EncoderV2` and
 `rave.blocks.EncoderV2` both mean `EncoderV2`), which is unambiguous for these files.
 """
+import ast
 import os
 import re
 
@@ -76,13 +77,44 @@ def _balanced(text):
     return depth <= 0
 
 
+def _literal(node):
+    """Value of a literal-only expression tree.  gin itself parses literals only; a config.gin comes from a
+    run directory that may have been downloaded, so nothing here is ever evaluated as code: attribute
+    access, subscripts, operators other than a numeric sign, and calls other than the two placeholders
+    that stand for `@ref` / `%macro` are rejected."""
+    if isinstance(node, ast.Constant):
+        return node.value
+    if isinstance(node, ast.List):
+        return [_literal(e) for e in node.elts]
+    if isinstance(node, ast.Tuple):
+        return tuple(_literal(e) for e in node.elts)
+    if isinstance(node, ast.Set):
+        return {_literal(e) for e in node.elts}
+    if isinstance(node, ast.Dict):
+        if any(k is None for k in node.keys):
+            raise ValueError("dict unpacking")
+        return {_literal(k): _literal(v) for k, v in zip(node.keys, node.values)}
+    if isinstance(node, ast.UnaryOp) and isinstance(node.op, (ast.USub, ast.UAdd)):
+        v = _literal(node.operand)
+        if isinstance(v, bool) or not isinstance(v, (int, float)):
+            raise ValueError("sign on a non-number")
+        return -v if isinstance(node.op, ast.USub) else v
+    if isinstance(node, ast.Call) and isinstance(node.func, ast.Name) and not node.keywords:
+        args = [a.value for a in node.args if isinstance(a, ast.Constant)]
+        if len(args) == len(node.args):
+            if node.func.id == "__REF__" and len(args) == 2:
+                return Ref(str(args[0]), bool(args[1]))
+            if node.func.id == "__MACRO__" and len(args) == 1:
+                return Macro(str(args[0]))
+    raise ValueError(f"{type(node).__name__} is not a literal")
+
+
 def parse_value(text):
     text = text.strip()
     src = _REF_RE.sub(lambda m: f"__REF__({m.group(1)!r}, {bool(m.group(2))})", text)
     src = _MACRO_RE.sub(lambda m: f"__MACRO__({m.group(1)!r})", src)
     try:
-        return eval(src, {"__builtins__": {}}, {"__REF__": Ref, "__MACRO__": Macro,
-                                                "True": True, "False": False, "None": None})
+        return _literal(ast.parse(src, mode="eval").body)
     except Exception as e:
         raise ValueError(f"gin_lite: cannot parse value {text!r}: {e}")
 
@@ -135,7 +167,20 @@ class Config:
             self.macros[lhs] = value
 
     def parse_string(self, text, relative_to=None):
-        lines = text.split("\n")
+        # gin.operative_config_str() (what train_rave.py:287-288 writes to run/config.gin) wraps long
+        # bindings with a trailing backslash: `blocks.EncoderV2.dilations = \` + the value on the next line
+        lines, cont = [], None
+        for raw in text.split("\n"):
+            raw = _strip_comment(raw)
+            if cont is not None:
+                raw = cont + " " + raw.strip()
+                cont = None
+            if raw.endswith("\\"):
+                cont = raw[:-1].rstrip()
+                continue
+            lines.append(raw)
+        if cont is not None:
+            lines.append(cont)
         i, block = 0, None
         while i < len(lines):
             raw = _strip_comment(lines[i])
@@ -160,6 +205,9 @@ class Config:
             if "=" not in line:
                 raise ValueError(f"gin_lite: cannot parse line {line!r}")
             lhs, _, rhs = line.partition("=")
+            if not rhs.strip() and i < len(lines) and lines[i][:1] in (" ", "\t") and "=" not in lines[i]:
+                rhs = lines[i].strip()                      # value alone on the following indented line
+                i += 1
             while not _balanced(rhs) and i < len(lines):
                 rhs += " " + _strip_comment(lines[i]).strip()
                 i += 1

@@ -146,8 +146,10 @@ class RAVE:
 
     def load_state_dict(self, state_dict, strict=True):
         """Accepts a reference checkpoint's `state_dict` (weight-norm pairs or folded)."""
+        self.skipped_keys = []          # strict=False: what the state_dict did not provide (upstream's missing_keys)
         self._load(collect(self.spec, state_dict, (self.pqmf.forward_conv_weight,
-                                                   self.pqmf.inverse_conv_weight), strict=strict))
+                                                   self.pqmf.inverse_conv_weight), strict=strict,
+                           skipped=self.skipped_keys))
         return self
 
     @classmethod

@@ -421,14 +421,31 @@ def build_netspec(cfg: "gin_lite.Config", streaming: bool = False) -> NetSpec:
     norm_mode = cfg.params("normalization").get("mode", "identity")
     if norm_mode not in ("identity", "weight_norm"):
         raise Exception(f"Normalization mode {norm_mode} not supported")     # blocks.py:24
+    # blocks.leaky_relu(dim, alpha) takes its slope from gin; the kernels (and the activated-storage inverse
+    # x = min(z, 5z)) are written for the 0.2 every shipped config uses
+    slope = cfg.params("leaky_relu").get("alpha", 0.2)
+    if abs(float(slope) - 0.2) > 1e-9:
+        raise NotImplementedError(f"blocks.leaky_relu.alpha = {slope}: only the default slope 0.2 is implemented")
     conv_bias = bool(cfg.params("Conv1d").get("bias", True))
     convt_bias = bool(cfg.params("ConvTranspose1d").get("bias", True))
     if not conv_bias:
         raise NotImplementedError("cc.Conv1d.bias = False")
 
-    pq = cfg.params(R["pqmf"].name, R["pqmf"].scope)
+    pq_name = R["pqmf"].name
+    if pq_name not in ("CachedPQMF", "PQMF"):
+        raise ValueError(f"rave.RAVE.pqmf = @{pq_name}: only pqmf.CachedPQMF and pqmf.PQMF exist (pqmf.py:179-284)")
+    pq = cfg.params(pq_name, R["pqmf"].scope)
     n_band = int(pq["n_band"])
     atten = pq.get("attenuation", 100)
+    # pqmf.PQMF (pqmf.py:179-231), the non-cached class no shipped config binds: its own symmetric padding
+    # whatever cc.get_padding.mode says, the same analysis as CachedPQMF, and a synthesis that is
+    # CachedPQMF.inverse advanced by one sub-band row (n_band samples; SURVEY 8(c) probe)
+    plain_pqmf = pq_name == "PQMF"
+    if plain_pqmf and streaming:
+        raise NotImplementedError("pqmf.PQMF has no cached_conv mode: bind pqmf.CachedPQMF for streaming")
+    if plain_pqmf and not pq.get("polyphase", True):
+        raise NotImplementedError("pqmf.PQMF(polyphase=False): the classic_* path is not implemented")
+    pq_mode = "centered" if plain_pqmf else mode
 
     enc_ref = R["encoder"]
     if enc_ref.name not in _ENCODER_WRAPPERS:
@@ -457,7 +474,7 @@ def build_netspec(cfg: "gin_lite.Config", streaming: bool = False) -> NetSpec:
     b = _Builder(streaming, mode)
     audio_in = b.slot(1, spf)
     xb = b.slot(enc_bands, spf // n_band)
-    pl, pr = get_padding(kf, mode=mode)
+    pl, pr = get_padding(kf, mode=pq_mode)
     off = pl + pr if streaming else pl
     b.need_hist(audio_in, off)
     b.ops.append(Op(OP_PQMF_FWD, audio_in, xb, c_in=1, c_out=enc_bands, k=kf, stride=n_band, off=off,
@@ -488,8 +505,8 @@ def build_netspec(cfg: "gin_lite.Config", streaming: bool = False) -> NetSpec:
     if b.slots[y].channels != n_band:
         raise ValueError("decoder data_size must equal the number of PQMF bands")
     audio_out = b.slot(1, spf)
-    pl, pr = get_padding(ki, mode=mode)
-    off = pl + pr if streaming else pl
+    pl, pr = get_padding(ki, mode=pq_mode)
+    off = pl + pr if streaming else (pl - 1 if plain_pqmf else pl)
     b.need_hist(y, off)
     b.ops.append(Op(OP_PQMF_INV, y, audio_out, c_in=n_band, c_out=n_band, k=ki, off=off, n_band=n_band,
                     params={"pqmf_inv": "pqmf.inverse_conv."}, name="pqmf.inverse_conv"))

@@ -52,10 +52,11 @@ def _phase_pack(w, r, p, k_taps):
     return out
 
 
-def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True):
+def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True, skipped=None):
     """Returns a list of (op_index, role, float32 ndarray) for everything found in `sd`."""
     out = []
     missing = []
+    defaulted = []
     if spec.arch == "v1" and "decoder.warmed_up" in sd and "decoder.synth.branches.2.net.0.weight" in sd \
             and int(np.asarray(_np(sd["decoder.warmed_up"])).reshape(-1)[0]) != 0:
         raise NotImplementedError("v1 Generator with an active NoiseGenerator branch (warmed_up=1)")
@@ -66,9 +67,17 @@ def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True):
                 w, b = _folded(sd, P["conv"])
                 if "bn" in P:
                     bn = P["bn"]
-                    scale = _np(sd[bn + "weight"]) / np.sqrt(_np(sd[bn + "running_var"]) + np.float32(1e-5))
+                    gamma = _np(sd[bn + "weight"])
+                    if strict or bn + "running_var" in sd:
+                        var, mean = _np(sd[bn + "running_var"]), _np(sd[bn + "running_mean"])
+                    else:
+                        # parameter-only dicts (the EMA callback, train_rave.py:85): upstream's
+                        # load_state_dict(strict=False) leaves the buffers as constructed (mean 0, var 1)
+                        var, mean = np.ones_like(gamma), np.zeros_like(gamma)
+                        defaulted.append(bn + "running_mean/var")
+                    scale = gamma / np.sqrt(var + np.float32(1e-5))
                     w = w * scale[:, None, None]
-                    b = (b - _np(sd[bn + "running_mean"])) * scale + _np(sd[bn + "bias"])
+                    b = (b - mean) * scale + _np(sd[bn + "bias"])
                 out.append((i, capi.RB_W_CONV, w))
                 if op.has_bias:
                     if b is None:
@@ -117,4 +126,6 @@ def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True):
     if missing and strict:
         raise KeyError("missing keys in state_dict: " + ", ".join(missing[:8]) +
                        (" ..." if len(missing) > 8 else ""))
+    if skipped is not None:                 # strict=False callers can see what was not loaded
+        skipped.extend(missing + ["(defaulted) " + d for d in defaulted])
     return [(i, r, np.ascontiguousarray(a, dtype=np.float32)) for i, r, a in out]

@@ -157,6 +157,25 @@ def test_v2_ragged_sizes_vs_oracle(B, T):
     assert rel_l2(y.cpu().numpy(), o.forward(x).numpy()) < F32_TOL
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_plain_pqmf_binding_vs_oracle(dtype):
+    """`rave.RAVE.pqmf = @pqmf.PQMF` (pqmf.py:179-231; no shipped config binds it): same analysis, synthesis
+    16 samples earlier than CachedPQMF.  Oracle branch pinned live in tests/test_oracle_pins.py."""
+    from oracle.model import OracleRAVE
+    from rave_b200 import RAVE
+    meta, a = load_golden("v2_c8")
+    sd = golden_state_dict(meta)
+    m = RAVE.from_gin(["v2.gin"], ["CAPACITY=8", "rave.RAVE.pqmf = @pqmf.PQMF", "pqmf.PQMF.n_band = 16",
+                                   "pqmf.PQMF.attenuation = 100"], dtype=dtype)
+    m.load_state_dict(sd)
+    o = OracleRAVE(dict(meta["cfg"], pqmf="PQMF"), sd)
+    x = torch.from_numpy(golden_input(a))
+    y = m(x.cuda().to(dtype)).float().cpu().numpy()
+    yo = o.forward(x).numpy()
+    assert rel_l2(y, yo) < (F32_TOL if dtype == torch.float32 else 2e-2)
+    assert rel_l2(yo[..., :-16], a["y"][..., 16:]) < 1e-4          # the 16-sample advance against CachedPQMF
+
+
 def test_error_conventions():
     from rave_b200 import RAVE
     m, meta, a = _model("v2_c8")

@@ -190,3 +190,83 @@ def test_resampler_design_matches_oracle_and_rejects_what_upstream_rejects():
         assert np.array_equal(d, do.numpy()) and np.array_equal(u, uo.numpy())
     with pytest.raises(RuntimeError):
         design(4)                        # upstream's reshape(-1, ratio) fails for this filter length too
+
+
+OPERATIVE = '''import rave
+import cached_conv
+
+# Macros:
+# ==============================================================================
+CAPACITY = 8
+N_BAND = 16
+
+# Parameters for variational/blocks.EncoderV2:
+# ==============================================================================
+variational/blocks.EncoderV2.n_out = 1
+
+# Parameters for blocks.EncoderV2:
+# ==============================================================================
+blocks.EncoderV2.dilations = \\
+    [[1, 3, 9], [1, 3, 9], [1, 3, 9], [1, 3]]
+blocks.EncoderV2.capacity = %CAPACITY
+
+# Parameters for pqmf.CachedPQMF:
+# ==============================================================================
+pqmf.CachedPQMF.n_band = \\
+    %N_BAND
+'''
+
+
+def test_gin_lite_reads_operative_config_dumps_and_never_evaluates_code():
+    """run/config.gin is gin.operative_config_str() (train_rave.py:287-288): `# Parameters for ...` headers,
+    scoped selectors and long bindings wrapped with a trailing backslash.  Values are literals only."""
+    cfg = gin_lite.Config().parse_string('include "v2.gin"\n' + OPERATIVE)
+    assert cfg.params("EncoderV2")["dilations"] == [[1, 3, 9], [1, 3, 9], [1, 3, 9], [1, 3]]
+    assert cfg.params("EncoderV2")["capacity"] == 8
+    assert cfg.params("EncoderV2", "variational")["n_out"] == 1
+    assert cfg.params("CachedPQMF")["n_band"] == 16
+    spec = netspec.build_netspec(cfg)
+    assert spec.samples_per_frame == 1024
+    for bad in ("().__class__.__base__.__subclasses__()", "__import__('os').system('true')", "[1, 2][0]", "1 + 2",
+                "open('/etc/passwd')", "{**{}}", "-'a'"):
+        with pytest.raises(ValueError):
+            gin_lite.parse_value(bad)
+    assert gin_lite.parse_value("{'a': (-1.5e-3, [True, None]), 2: 'x'}") == {"a": (-1.5e-3, [True, None]), 2: "x"}
+
+
+def test_plain_pqmf_alias_and_leaky_slope():
+    """pqmf.PQMF (pqmf.py:179-231): symmetric padding whatever the conv padding mode, synthesis one row early,
+    no streaming twin; blocks.leaky_relu.alpha other than 0.2 is refused instead of silently ignored."""
+    from rave_b200.netspec import OP_PQMF_FWD, OP_PQMF_INV
+    a = _spec(["v2.gin"], ["CAPACITY=8"])
+    b = _spec(["v2.gin", "causal.gin"], ["CAPACITY=8", "rave.RAVE.pqmf = @pqmf.PQMF", "pqmf.PQMF.n_band = 16",
+                                          "pqmf.PQMF.attenuation = 100"])
+    fa = [o for o in a.ops if o.kind == OP_PQMF_FWD][0]
+    fb = [o for o in b.ops if o.kind == OP_PQMF_FWD][0]
+    ia = [o for o in a.ops if o.kind == OP_PQMF_INV][0]
+    ib = [o for o in b.ops if o.kind == OP_PQMF_INV][0]
+    assert fb.off == fa.off and ib.off == ia.off - 1
+    with pytest.raises(NotImplementedError):
+        _spec(["v2.gin"], ["rave.RAVE.pqmf = @pqmf.PQMF", "pqmf.PQMF.n_band = 16"], streaming=True)
+    with pytest.raises(NotImplementedError):
+        _spec(["v2.gin"], ["blocks.leaky_relu.alpha = 0.1"])
+
+
+def test_ema_state_dict_defaults_batchnorm_buffers():
+    """EMA dicts hold parameters only (train_rave.py:85): with strict=False the v1 encoder's convs still load,
+    their BatchNorm buffers default to the constructed mean 0 / var 1, and the caller sees what was skipped."""
+    from rave_b200 import capi
+    from rave_b200.synth import golden_state_dict
+    from rave_b200.weights import collect
+    spec = _spec(["v1.gin"], ["CAPACITY=8"])
+    _, sd = golden_state_dict("v1_c8")
+    ema = {k: v for k, v in sd.items() if "running_" not in k and "num_batches" not in k}
+    from rave_b200.pqmf_design import design
+    _, _, wa, ws = design(100, 16)
+    skipped = []
+    got = collect(spec, ema, (wa, ws), strict=False, skipped=skipped)
+    convs = {i for i, role, _ in got if role == capi.RB_W_CONV}
+    full = {i for i, role, _ in collect(spec, sd, (wa, ws)) if role == capi.RB_W_CONV}
+    assert convs == full and any("defaulted" in s for s in skipped)
+    with pytest.raises(KeyError):
+        collect(spec, ema, (wa, ws), strict=True)

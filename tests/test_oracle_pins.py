@@ -356,6 +356,56 @@ def test_latent_oracle_angles_match_live_reference():
     assert rel_l2(L.angles_to_unit_norm_vector(a_ref.clone()).numpy(), x.numpy()) < 1e-5     # round trip
 
 
+@needs_ref
+def test_latent_oracle_pca_matches_live_export_methods():
+    """Pins oracle/latent_oracle.py's two PCA methods against the reference's OWN method bodies
+    (scripts/export.py:484-499, cut out of the file's syntax tree by ref_loader.load_export_latent_classes),
+    with the reference's torch.randn draw reproduced by seeding."""
+    from types import SimpleNamespace
+    from oracle import latent_oracle as L
+    cls = R.load_export_latent_classes()["VariationalScriptedRAVE"]
+    g = torch.Generator().manual_seed(3)
+    C_, n = 32, 8
+    q, _ = torch.linalg.qr(torch.randn(C_, C_, generator=g))
+    mean = 0.2 * torch.randn(C_, generator=g)
+    m = cls()
+    m.latent_pca, m.latent_mean, m.latent_size, m.full_latent_size = q, mean, n, C_
+    m.encoder = SimpleNamespace(reparametrize=lambda z: (z, None))       # blocks.py:720-729 returns (z, kl)
+    z = torch.randn(3, C_, 11, generator=g)
+    want = m.post_process_latent(z)
+    got = L.post_process_latent(z, q, mean, n)
+    assert want.shape == (3, n, 11) and torch.equal(got, want)
+    torch.manual_seed(77)
+    back = m.pre_process_latent(want)
+    torch.manual_seed(77)
+    noise = torch.randn(3, C_ - n, 11)
+    assert torch.equal(L.pre_process_latent(want, noise, q, mean), back)
+    # discrete wrapper (export.py:503-517): clamp + .long() in front of rvq.decode, encode -> float
+    dcls = R.load_export_latent_classes()["DiscreteScriptedRAVE"]
+    quant = R.load("quantization")
+    torch.manual_seed(0)
+    rvq = quant.ResidualVectorQuantization(num_quantizers=4, dim=16, codebook_size=32, kmeans_init=False)
+    d = dcls()
+    d.encoder = SimpleNamespace(rvq=rvq, noise_augmentation=0)
+    zz = torch.randn(2, 16, 5)
+    idx = d.post_process_latent(zz)
+    assert idx.dtype == torch.float32 and torch.equal(idx.long(), rvq.encode(zz))
+    assert torch.equal(d.pre_process_latent(idx + 0.25), rvq.decode(idx.long()))
+
+
+@needs_ref
+def test_plain_pqmf_alias_matches_live_class():
+    """pqmf.PQMF (pqmf.py:179-231, bound by no shipped config): analysis identical to CachedPQMF, synthesis =
+    CachedPQMF.inverse advanced by one sub-band row (16 samples).  Pins the oracle's `pqmf="PQMF"` branch."""
+    pm = R.load("pqmf")
+    pq = pm.PQMF(100, 16)
+    o = OracleRAVE(dict(C.v2(8), pqmf="PQMF"), {"speaker": torch.zeros(1, 256, 1)})
+    x = torch.from_numpy(recipe_input((2, 1, 4096), 3))
+    yb = torch.from_numpy(recipe_input((2, 16, 256), 4, scale=1.0))
+    assert rel_l2(o.pqmf_forward(x).numpy(), pq(x).numpy()) < 1e-6
+    assert rel_l2(o.pqmf_inverse(yb).numpy(), pq.inverse(yb).numpy()) < 1e-5
+
+
 def test_latent_oracle_pca_round_trip():
     from oracle import latent_oracle as L
     g = torch.Generator().manual_seed(5)

@@ -1,5 +1,5 @@
 import sys, torch, numpy as np
-import os; R = os.path.dirname(os.path.abspath(__file__)); sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, 'tests'))
+import os; R = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, 'tests'))
 import tests.test_gpu_parity as T
 for name in T.GIN:
     m, meta, a = T._model(name, dtype=torch.bfloat16)

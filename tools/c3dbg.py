@@ -1,3 +1,4 @@
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))  # repo root
 import os, torch
 from rave_b200 import RAVE
 from rave_b200.synth import golden_state_dict, recipe_input

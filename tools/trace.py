@@ -1,11 +1,13 @@
 """Pipeline event trace of CTA 0 of one tc_conv launch (through rb_debug_conv_bf16's trace buffer).
-usage: python tools_trace.py du C dil | conv c_in c_out k [res]
+usage: python tools/trace.py du C dil | conv c_in c_out k [res]
 Prints, per work item, the clock stamps (relative, in cycles) of:
   0 MMA: D_EMPTY ok   1 MMA: A_FULL ok(last chunk)   2 MMA: G1 issued   3 MMA: H_FULL ok
   4 MMA: D2_EMPTY ok  5 MMA: G2 issued   6 E1: D_FULL ok   7 E1: done   8 E2/out: start
   9 E2/out: done     10 A prod: A_EMPTY ok   11 A prod: issued
   12 out: acc barrier ok   13 out: first acc in registers   14 out: math done   15 out: stores issued
 """
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))  # repo root
+
 import ctypes as C
 import os
 import sys
