@@ -4,15 +4,18 @@
     python bench.py --gpus N --steps K --warmup W [--impl reference] [--dtype bf16|f32]
 
 A step = one pass of RAVE.forward (encode -> decode) over the synthetic batch of
-BASELINE.json configs[1]: 512 streams x 2^18 samples @44.1 kHz per GPU, random-init v2 weights
-(name-keyed recipe, rave_b200/synth.py).  Streams are independent (tests: bitwise), so
-N GPUs run N shards of 512 streams each with no data-path collective (weak scaling); the only
-collectives are the barrier and the max-over-ranks of the device time.  Prints ONE JSON line
-on rank 0.
+BASELINE.json configs[1]: 512 streams x 2^18 samples @44.1 kHz, random-init v2 weights
+(name-keyed recipe, rave_b200/synth.py).  Default (`--scaling strong`) is the literal
+configs[1]: the 512 streams are SHARDED over the N GPUs (contiguous blocks) and
+every step ends with the NCCL all-gather of the output waveforms, inside the timed region.
+With N > 1 the same line also carries a `weak` record (512 streams per GPU, no data-path
+collective).  Ranks bind to the CPU cores NVML reports as local to their GPU before any pinned
+buffer is allocated.  Prints ONE JSON line on rank 0.
 
 --impl reference: the reference's own CPU path (the oracle port of its PyTorch modules --
 the reference itself is not importable) on the host cores, each step a
-bounded sample (2 streams x 2^17 samples) of the same workload.
+bounded sample (REF_STREAMS streams x 2^18 samples) of the same workload.  `cpu_baseline` of
+the product arm is the same function on the same sample: one CPU number, not two.
 """
 import argparse
 import json
@@ -29,11 +32,13 @@ SR = 44100
 STREAMS = 512
 SAMPLES = 2 ** 18
 METRIC = "audio-sec/sec v2 encode+decode"
+REF_STREAMS = 32          # CPU sample: 32 of the 512 streams at the full 2^18 length
 
 
 def _workload(B, T, streams, gathered):
-    return (f"v2 encode+decode (BASELINE configs[1]), {B} streams x {T} samples @44.1 kHz per GPU, {streams} streams in all, " +
-            ("NCCL all-gather of every step's outputs, overlapped with the next step" if gathered else "no data-path collective"))
+    return (f"v2 encode+decode (BASELINE configs[1]), {streams} streams x {T} samples @44.1 kHz in all, {B} per GPU, " +
+            ("NCCL all-gather of every step's outputs inside the timed region (overlapped with the next step's compute)"
+             if gathered else "no data-path collective"))
 
 
 def _peaks():
@@ -48,6 +53,38 @@ def _peaks():
 def _state_dict():
     from rave_b200.synth import golden_state_dict
     return golden_state_dict("v2_c64")         # only the (name, shape) list is read from the fixture
+
+
+def _synthetic_rows(rows, T, seed=1234):
+    """Rows `rows` (global stream ids) of the synthetic batch, fp32 numpy [len(rows), 1, T]: one seeded
+    pattern per id modulo 64 plus a per-stream offset, identical on every rank and for every N."""
+    import numpy as np
+    from rave_b200.synth import recipe_input
+    base = recipe_input((64, 1, T), seed)
+    rows = np.asarray(rows)
+    return base[rows % 64] + (0.001 * rows).astype(np.float32).reshape(-1, 1, 1)
+
+
+def bind_to_gpu_numa(local):
+    """Pin this process to the CPU cores local to its GPU (NVML affinity mask) so that pinned host
+    buffers allocated afterwards live on that socket.  Returns the number of cores (None: unchanged)."""
+    try:
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        pr = torch.cuda.get_device_properties(local)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(
+            f"{pr.pci_domain_id:08x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0".encode())
+        n = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
 
 
 class ClockSampler(threading.Thread):
@@ -78,54 +115,105 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
-def cpu_baseline(meta, sd, budget_s=20.0):
-    """Oracle (port of the reference's PyTorch CPU path) on BASELINE configs[0]: B=1, 2^17, fp32."""
+# ------------------------------------------------------- CPU legs (the oracle as checker / baseline)
+def _cpu_sample(T):
+    return f"{REF_STREAMS} of the {STREAMS} streams x {T} samples (full length), fp32, torch CPU, all host threads"
+
+
+def cpu_reference_pass(steps, warmup, T, budget_s=None):
+    """The reference's CPU path (oracle port) on REF_STREAMS streams of the workload.  Returns
+    (audio-s/s, seconds per pass, cores, passes timed)."""
     import torch
     from oracle.model import OracleRAVE
-    from oracle.weights_recipe import recipe_input
-    cores = os.cpu_count() or 1
+    meta, sd = _state_dict()
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     torch.set_num_threads(cores)
     o = OracleRAVE(meta["cfg"], sd)
-    x = torch.from_numpy(recipe_input((1, 1, 2 ** 17), 1234))
-    o.forward(x)
-    times, t_end = [], time.time() + budget_s
-    while len(times) < 5 or (time.time() < t_end and len(times) < 20):
+    x = torch.from_numpy(_synthetic_rows(range(REF_STREAMS), T))
+    for _ in range(max(warmup, 1)):
+        o.forward(x)
+    times = []
+    t_end = time.time() + (budget_s or 1e9)
+    for _ in range(steps):
         t0 = time.perf_counter()
         o.forward(x)
         times.append(time.perf_counter() - t0)
-    times.sort()
-    med = times[len(times) // 2]
-    return {"value": (2 ** 17 / SR) / med, "unit": "audio-sec/sec", "cores": cores, "kind": "port",
-            "sample": f"v2 fp32 B=1 T=2^17 (configs[0]), median of {len(times)} calls after 1 warm-up"}
+        if budget_s and time.time() > t_end and len(times) >= 3:
+            break
+    dt = sum(times) / len(times)
+    return REF_STREAMS * T / SR / dt, dt, cores, len(times)
+
+
+def parity_check(m, x, rows, first_stream, T):
+    """Outside the timed region: rows `rows` of this rank's step output against OracleRAVE.forward (fp32
+    CPU) on the same rows.  BASELINE.json's bf16 bar is rel-L2 <= 1e-2 per program (encode, decode); the
+    forward chains both, so its bar is 2e-2 (as in tests/test_gpu_parity.py)."""
+    import numpy as np
+    import torch
+    from oracle.model import OracleRAVE
+    meta, sd = _state_dict()
+    y = m(x)
+    torch.cuda.synchronize()
+    got = y[rows].float().cpu().numpy()
+    xin = x[rows].float().cpu()                     # the exact (bf16-rounded) input rows the device saw
+    want = OracleRAVE(meta["cfg"], sd).forward(xin).numpy()
+    rel = [float(np.linalg.norm(got[i].astype(np.float64) - want[i]) / np.linalg.norm(want[i]))
+           for i in range(len(rows))]
+    tol = 2e-2 if x.dtype == torch.bfloat16 else 1e-3
+    return {"rows": [int(first_stream + r) for r in rows], "rel_l2": rel, "tolerance": tol,
+            "against": "OracleRAVE.forward (fp32 CPU port of the reference) on the same input rows, full length",
+            "ok": bool(max(rel) < tol)}
+
+
+def eager_gpu(T, streams=32):
+    """Informational: 'what you get without this repo' -- the reference's PyTorch modules (oracle port, plain
+    F.conv1d / F.conv_transpose1d -> cuDNN) on this GPU, fp32 and bf16 autocast, `streams` streams."""
+    import torch
+    from oracle.model import OracleRAVE
+    meta, sd = _state_dict()
+    out = {}
+    try:
+        o = OracleRAVE(meta["cfg"], sd)
+        o.sd = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in o.sd.items()}
+        x = torch.from_numpy(_synthetic_rows(range(streams), T)).cuda()
+        for tag, ctx in (("f32", torch.autocast("cuda", enabled=False)),
+                         ("bf16_autocast", torch.autocast("cuda", dtype=torch.bfloat16))):
+            with ctx:
+                for _ in range(2):
+                    o.forward(x)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(3):
+                    o.forward(x)
+                e1.record()
+                torch.cuda.synchronize()
+            out[tag] = streams * T / SR / (e0.elapsed_time(e1) / 3e3)
+        out["unit"] = "audio-sec/sec"
+        out["sample"] = f"{streams} streams x {T} samples, eager PyTorch (cuDNN) on the same GPU, oracle modules"
+    except Exception as e:                      # informational leg: never fails the bench
+        out["error"] = repr(e)[:200]
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
-    from oracle.model import OracleRAVE
-    from oracle.weights_recipe import recipe_input
-    meta, sd = _state_dict()
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    o = OracleRAVE(meta["cfg"], sd)
-    B, T = 2, 2 ** 17
-    x = torch.from_numpy(recipe_input((B, 1, T), 1234))
-    for _ in range(max(args.warmup, 1)):
-        o.forward(x)
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        o.forward(x)
-    dt = time.perf_counter() - t0
-    val = args.steps * B * T / SR / dt
-    sample = f"each step = {B} streams x 2^17 samples of the {STREAMS} x 2^18 workload, fp32, torch CPU"
+    val, dt, cores, n = cpu_reference_pass(args.steps, args.warmup, args.samples)
+    sample = "each step = " + _cpu_sample(args.samples)
+    strong = args.scaling == "strong"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "audio-sec/sec", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "steps": n, "warmup": args.warmup, "ms_per_step": 1e3 * dt,
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": _workload(args.streams, args.samples, args.streams * args.gpus, False), "sample": sample},
+        "config": {"workload": _workload(args.streams // args.gpus if strong else args.streams, args.samples,
+                                         args.streams if strong else args.streams * args.gpus,
+                                         strong and args.gpus > 1),
+                   "sample": sample, "same_config": False,
+                   "note": "one CPU process (rank 0) whatever N is: a baseline, not a scaling curve"},
         "cpu_baseline": {"value": val, "unit": "audio-sec/sec", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
