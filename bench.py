@@ -220,15 +220,16 @@ def run_reference(args):
 
 
 def run_ours(args):
+    import numpy as np
     import torch
     import torch.distributed as dist
     from rave_b200 import RAVE
-    from rave_b200.synth import recipe_input
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    numa_cores = bind_to_gpu_numa(local)          # before any pinned allocation
     if world > 1:
         # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...") goes to stderr
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
@@ -237,56 +238,69 @@ def run_ours(args):
     esz = 2 if args.dtype == "bf16" else 4
     T = args.samples
     from rave_b200.shard import OverlappedGather, max_over_ranks, stream_shard
-    # weak (default): every rank runs the full configuration, no collective;
-    # strong: SURVEY 8(e) variant, 512 / N streams per GPU + final all-gather of the outputs
-    _, B = stream_shard(args.streams, world, rank, args.scaling)
-    streams = B * world
-    meta, sd = _state_dict()
     m = RAVE.from_gin(["v2.gin"], device=f"cuda:{local}", dtype=dtype)
-    m.load_state_dict(sd)
+    m.load_state_dict(_state_dict()[1])
     if args.microbatch:
         m.set_microbatch(args.microbatch)
-    # synthetic audio: one seeded second-long pattern per stream row, resident in HBM
-    base = torch.from_numpy(recipe_input((64, 1, T), 1234 + rank)).cuda()
-    x = base.repeat((B + 63) // 64, 1, 1)[:B].contiguous().to(dtype)
-    x += (0.001 * torch.arange(B, device="cuda").view(B, 1, 1)).to(dtype)
-    gathered = world > 1 and args.scaling == "strong"
-    gather = OverlappedGather(world) if gathered else None
-
-    def step():
-        y = m(x)
-        return gather(y) if gathered else y
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    l0 = m.kernel_launches()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(args.steps):
-        step()
-    if gathered:
-        gather.finish()                    # the last step's gather is inside the timed region
-    ev1.record()
-    barrier()
-    ms = ev0.elapsed_time(ev1)
-    launches = m.kernel_launches() - l0
-    sampler.stop = True
-    ms = max_over_ranks(ms, "cuda")
+
+    def make_input(first, B):
+        return torch.from_numpy(_synthetic_rows(np.arange(first, first + B), T)).cuda().to(dtype)
+
+    def timed(scaling, sampler=None):
+        """K timed steps of one scaling mode (ms per step = max over ranks of the device time)."""
+        first, B = stream_shard(args.streams, world, rank, scaling)
+        x = make_input(first, B)
+        gathered = world > 1 and scaling == "strong"
+        gather = OverlappedGather(world) if gathered else None
+
+        def step():
+            y = m(x)
+            return gather(y) if gathered else y
+
+        for _ in range(args.warmup):
+            step()
+        if gathered:
+            gather.finish()
+        barrier()
+        if sampler is not None:
+            sampler.start()
+        l0 = m.kernel_launches()
+        ev0.record()
+        for _ in range(args.steps):
+            step()
+        if gathered:
+            gather.finish()                    # the last step's gather is inside the timed region
+        ev1.record()
+        barrier()
+        if sampler is not None:
+            sampler.stop = True
+        ms = max_over_ranks(ev0.elapsed_time(ev1), "cuda") / args.steps
+        return ms, m.kernel_launches() - l0, first, B, B * world, x, gathered
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, launches, first, B, streams, x, gathered = timed(args.scaling, sampler)
     audio_s = streams * T / SR
-    value = args.steps * audio_s / (ms / 1e3)
+    value = audio_s / (ms / 1e3)
+    weak = None
+    if world > 1 and args.scaling == "strong" and not args.no_weak:
+        del x
+        wms, _, _, wB, wstreams, wx, _ = timed("weak")
+        weak = {"value": wstreams * T / SR / (wms / 1e3), "unit": "audio-sec/sec", "ms_per_step": wms,
+                "streams_per_gpu": wB, "streams": wstreams, "collective": "none"}
+        del wx
+        x = make_input(first, B)
 
     # ---- per-op device times (CUDA events around every op on the launching stream)
     macs = m.spec.macs_per_frame()
-    flops_step = 2.0 * (macs["enc"] + macs["dec"]) * (B * T // m.spec.samples_per_frame)
+    frames = B * T // m.spec.samples_per_frame
+    flops_step = 2.0 * (macs["enc"] + macs["dec"]) * frames
     m.profile_ops(True)
     m(x)
     torch.cuda.synchronize()
@@ -294,7 +308,6 @@ def run_ours(args):
     m.profile_ops(False)
     # every conv / PQMF op is one launch of tc_conv_kernel (a fused DilatedUnit: one launch for two
     # ops -- the second op then reports 0 ms): algorithmic flops and HBM bytes of those launches
-    frames = B * T // m.spec.samples_per_frame
     slots = m.spec.slots
 
     def slot_bytes(sl):
@@ -328,27 +341,54 @@ def run_ours(args):
         os.makedirs(os.path.dirname(os.path.abspath(args.dump_ops)), exist_ok=True)
         json.dump(rows, open(args.dump_ops, "w"), indent=1)
     pk = _peaks()
-    achieved = conv_flops / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
-    traffic = None
-    tp = os.path.join(ROOT, "profiles", "r01_tc_conv_traffic.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("dram_bytes_per_step")
+    # achieved = algorithmic flops of one step (81.51 MFLOP per latent frame) / the measured step
+    achieved = flops_step / (ms / 1e3) / 1e12
+    traffic, traffic_src = None, None
+    for name in ("r02_tc_conv_traffic.json", "r01_tc_conv_traffic.json"):
+        tp = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("dram_bytes_per_step")
+            traffic_src = f"profiles/{name} (ncu --set full capture of an earlier run of this command; not measured in this run)"
+            break
+    per_op_tf = conv_flops / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
+    hbm_gbs = conv_bytes / (conv_ms / 1e3) / 1e9 if conv_ms > 0 else 0.0
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["tf_sus"], "unit": "TFLOP/s",
-                "frac": achieved / pk["tf_sus"], "traffic": traffic,
-                "kernel": "tc_conv_kernel (the %d launches of one step, %.2f of %.2f ms; achieved = their "
-                          "algorithmic flops / their summed CUDA-event time)" % (n_launch, conv_ms, sum(op_ms)),
+                "frac": achieved / pk["tf_sus"], "traffic": traffic, "traffic_source": traffic_src,
+                "kernel": "tc_conv_kernel: the %d launches of one step (%.2f of %.2f ms of per-op CUDA-event time); "
+                          "achieved = algorithmic flops of the step / ms_per_step" % (n_launch, conv_ms, sum(op_ms)),
                 "peak_source": pk["src"] + ", sustained bf16",
-                "algorithmic_bytes": conv_bytes,
-                "hbm": {"achieved": conv_bytes / (conv_ms / 1e3) / 1e9 if conv_ms > 0 else 0.0, "peak": pk["hbm"],
-                        "unit": "GB/s", "frac": (conv_bytes / (conv_ms / 1e3) / 1e9) / pk["hbm"] if conv_ms > 0 else 0.0},
-                "whole_path_frac": (flops_step * world / (ms / args.steps / 1e3) / 1e12) / (pk["tf_sus"] * world)}
+                "algorithmic_flops_per_step_per_gpu": flops_step,
+                "layer_by_layer_bytes": conv_bytes, "fused_path_bytes": 2.0 * B * T * esz,
+                "hbm": {"achieved": hbm_gbs, "peak": pk["hbm"], "unit": "GB/s", "frac": hbm_gbs / pk["hbm"],
+                        "note": "layer-by-layer algorithmic bytes / summed per-op time"},
+                "per_op_profile_frac": per_op_tf / pk["tf_sus"]}
 
     # ---- end to end through the public API with HOST buffers (pinned), H2D + D2H inside
     xh = x.float().cpu().pin_memory() if esz == 4 else x.cpu().pin_memory()
     yh = torch.empty_like(xh).pin_memory()
     e2e_steps = max(2, min(args.steps, 10))
 
-    # every step copies its 512-stream input from pinned host memory and its output back; the
+    # raw copy bandwidth of this rank's pinned buffers, all ranks copying at once (names the e2e limiter)
+    def copy_gbs(dst, src):
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        ev0.record()
+        for _ in range(3):
+            dst.copy_(src, non_blocking=True)
+        ev1.record()
+        torch.cuda.synchronize()
+        return 3 * src.numel() * src.element_size() / (ev0.elapsed_time(ev1) / 1e3) / 1e9
+
+    xd = torch.empty_like(x)
+    barrier()
+    h2d = copy_gbs(xd, xh)
+    barrier()
+    d2h = copy_gbs(yh, xd)
+    del xd
+    h2d_min = -max_over_ranks(-h2d, "cuda")         # the slowest rank sets the pace
+    d2h_min = -max_over_ranks(-d2h, "cuda")
+
+    # every step copies its input shard from pinned host memory and its output back; the
     # public host-buffer call pipelines blocks of streams over three streams (H2D | forward | D2H)
     chunks = args.host_chunks if B % args.host_chunks == 0 else 1
 
@@ -370,19 +410,33 @@ def run_ours(args):
         sampler.join(timeout=2)
         out = {
             "metric": METRIC, "value": value, "unit": "audio-sec/sec", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
             "config": {"workload": _workload(B, T, streams, gathered),
-                       "l2": f"inputs {B * T * esz >> 20} MiB per GPU > 126 MB L2, no flush needed",
-                       "weights": "random-init (name-keyed recipe), CAPACITY=64"},
+                       "l2": f"input {B * T * esz >> 20} MiB + layer activations (up to {B * T * esz * 4 >> 20} MiB each) "
+                             "per GPU and step > 126 MB L2: no flush needed",
+                       "weights": "random-init (name-keyed recipe), CAPACITY=64",
+                       "numa": (f"rank bound to its GPU's {numa_cores} local cores before pinned allocation"
+                                if numa_cores else "no NUMA binding (NVML affinity unavailable)")},
             "clocks": sampler.summary(),
             "e2e": {"value": e2e_val, "unit": "audio-sec/sec", "h2d_bytes_per_step": B * T * esz * world,
-                    "d2h_bytes_per_step": B * T * esz * world, "steps": e2e_steps},
+                    "d2h_bytes_per_step": B * T * esz * world, "steps": e2e_steps,
+                    "h2d_gbs_per_rank_min": h2d_min, "d2h_gbs_per_rank_min": d2h_min},
             "gpu_launches": int(launches),
             "roofline": roofline,
         }
+        if weak is not None:
+            out["weak"] = weak
+        if not args.no_cpu:
+            # the oracle as the CHECKER: two rows of this rank's step output, outside the timed region
+            out["parity_check"] = parity_check(m, x, [0, B - 1], first, T)
         if world == 1 and not args.no_cpu:
-            out["cpu_baseline"] = cpu_baseline(meta, sd)
+            val, dt, cores, n = cpu_reference_pass(20, 1, T, budget_s=20.0)
+            out["cpu_baseline"] = {"value": val, "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+                                   "sample": _cpu_sample(T) + f", mean of {n} passes after 1 warm-up"}
+            del x
+            torch.cuda.empty_cache()
+            out["eager_gpu"] = eager_gpu(T)
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -399,11 +453,12 @@ def main():
     ap.add_argument("--samples", type=int, default=SAMPLES)
     ap.add_argument("--microbatch", type=int, default=0)
     ap.add_argument("--host-chunks", type=int, default=2, help="stream blocks per step of the host-buffer (e2e) call")
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="weak (default): --streams per GPU, streams never interact so there is no data-path collective; "
-                         "strong: --streams in all, sharded over the ranks, final NCCL all-gather of the outputs "
-                         "(the literal reading of BASELINE configs[1]; identical at N = 1)")
-    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="strong (default, the literal BASELINE configs[1]): --streams in all, sharded over the ranks, "
+                         "NCCL all-gather of every step's outputs inside the timed region; weak: --streams per GPU, "
+                         "no data-path collective (identical at N = 1)")
+    ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the additional weak-scaling record")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the oracle legs (parity check, CPU baseline, eager GPU)")
     ap.add_argument("--dump-ops", default="", help="write per-op device times (JSON) to this file")
     args = ap.parse_args()
     if args.impl == "reference":
