@@ -430,6 +430,77 @@ __device__ __forceinline__ void drain_smem16(const TcParams& p, uint32_t bar_ful
   tc_fence_before();
 }
 
+// Fused unit whose residual comes from global memory (C = 96 / 128: the A tiles cannot wait in smem until
+// E2): 16-column pieces like drain_smem16, with the residual of the warp's first FOUR pieces (its whole share
+// of a C = 128 tile) requested BEFORE the accumulator barrier.  The event trace of the 32-column / one-chunk-
+// ahead drain showed E2 at 5200-6300 cycles per tile against ~1800 for E1 on the same amount of data: the
+// second chunk's residual load was only issued after the first chunk's math, so its full L2 / HBM latency
+// sat on the critical path of the output warps (and through D2_EMPTY / H_EMPTY on everything else).
+__device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
+                                            const float* bs, const Work& wk, int rit, int part, int nparts, int NT,
+                                            uint32_t tr) {
+  constexpr uint32_t tmask = 0;                             // `tr` already carries the trace mask
+  const int row = wk.t0 + rit;
+  const uint32_t yoff = (uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT);
+  const uint32_t roff = (uint32_t)((long long)wk.b * p.res.sb) +
+                        (uint32_t)((p.res.hist - p.res_delay + row) * p.res.sT);
+  uint4* const ybase = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p));
+  const uint4* const rbase = reinterpret_cast<const uint4*>(p.res.p);
+  const bool valid = row < p.y.n;
+  const bool ract = p.res_act != 0, oact = p.out_act != 0;
+  const int jump = 16 + (nparts - 1) * 32;                  // from the second piece of a chunk to the next chunk
+  uint4 rr[8];
+  int cq = part * 32;                                       // column of the next piece to request
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (cq < NT && valid) {
+      const uint32_t o = roff + (uint32_t)goff32(p.res, cq >> 3);
+      rr[2 * i] = __ldg(rbase + o);
+      rr[2 * i + 1] = __ldg(rbase + (o + (uint32_t)p.res.sA));
+    }
+    cq += (cq & 16) ? jump : 16;
+  }
+  mbar_wait(bar_full, parity);
+  tc_fence_after();
+  TRACE(tr, 12);
+#pragma unroll 1
+  for (int c = part * 32; c < NT; c += (c & 16) ? jump : 16) {
+    float v[16];
+    load_acc<16>(tbase + (uint32_t)c, bs + c, v);
+    TRACE(tr, 13);
+    const uint32_t w[8] = {rr[0].x, rr[0].y, rr[0].z, rr[0].w, rr[1].x, rr[1].y, rr[1].z, rr[1].w};
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
+      if (ract) {                                           // stored as leaky(x): x = min(z, 5 z), exact in fp32
+        float l5, h5;
+        mul2(l5, h5, lo, hi, 5.f, 5.f);
+        lo = fminf(lo, l5);
+        hi = fminf(hi, h5);
+      }
+      add2(v[2 * e], v[2 * e + 1], lo, hi);
+    }
+    if (oact) leaky_n<16>(v);
+    TRACE(tr, 14);
+    if (valid) {
+      const uint32_t o = yoff + (uint32_t)goff32(p.y, c >> 3);
+      ybase[o] = pack8(v);
+      ybase[o + (uint32_t)p.y.sA] = pack8(v + 8);
+    }
+    // shift the queue, request the piece four ahead
+#pragma unroll
+    for (int i = 0; i < 6; ++i) rr[i] = rr[i + 2];
+    if (cq < NT && valid) {
+      const uint32_t o = roff + (uint32_t)goff32(p.res, cq >> 3);
+      rr[6] = __ldg(rbase + o);
+      rr[7] = __ldg(rbase + (o + (uint32_t)p.res.sA));
+    }
+    cq += (cq & 16) ? jump : 16;
+  }
+  TRACE(tr, 15);
+  tc_fence_before();
+}
+
 // Drains part `part` of `nparts` of the 32-column chunks of `MTn` sub-tiles x `NT` accumulator
 // columns (TMEM address `tbase`, lane base included) into y at channel offset ch0: accumulator
 // + bias (+ residual) -> sign mask / output activation -> bf16 -> 16-byte stores.  The residual
@@ -597,7 +668,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_COUNT * 8);
-  uint64_t* mask_s = reinterpret_cast<uint64_t*>(smem + 640);   // [n_ntiles][n_kchunks] <= 128 entries
+  uint64_t* mask_s = reinterpret_cast<uint64_t*>(smem + 640);   // [n_ntiles][n_kchunks] <= TC_MAX_MASKS entries
   float* bias_s = reinterpret_cast<float*>(smem + p.off_bias);
   const int N_total = p.N_TILE * p.n_ntiles;
   float* bias2_s = bias_s + N_total;              // fused only: [C]
@@ -1007,8 +1078,8 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           drain_smem16(p, BAR(BAR_D2_FULL + sd), rd_.ph, tb, bias2_s, wk, rit, part, OUT_PARTS, C2, rs);
         else if (DR == 2)
           drain_fast<2>(p, BAR(BAR_D2_FULL + sd), rd_.ph, tb, bias2_s, wk, rit, part, OUT_PARTS, 0, 1, C2, rs, trc);
-        else
-          drain_fast<1>(p, BAR(BAR_D2_FULL + sd), rd_.ph, tb, bias2_s, wk, rit, part, OUT_PARTS, 0, 1, C2, rs, trc);
+        else      // DR == 1: residual from global memory
+          drain_res16(p, BAR(BAR_D2_FULL + sd), rd_.ph, tb, bias2_s, wk, rit, part, OUT_PARTS, C2, trc);
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(BAR(BAR_D2_EMPTY + sd));

@@ -19,6 +19,9 @@ namespace rb {
 namespace tc {
 
 constexpr int TC_MAX_NT = 8;        // output-channel tiles per layer
+// (n-tile, K-chunk) tap-mask entries the kernel keeps in smem: the widest layer of the path is the discrete
+// config's 768 -> 1536 strided conv (CAPACITY 96): 6 n-tiles x 24 chunks of 64 channels = 144
+constexpr int TC_MAX_MASKS = 256;
 constexpr int TC_THREADS = 640;     // warps 0-15 output (12-15: activation pass if needed), 16 MMA, 17 W, 18 A producer, 19 MMA (fused GEMM2)
 
 // A row view of an activation tensor, addressed in 16-byte units (8 bf16 = one channel group):

@@ -417,8 +417,9 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   const uint32_t budget = 224u * 1024u;
   const uint32_t w_total = (uint32_t)(L.total_blocks + (L.fused ? L.N_TILE / L.KC : 0)) * L.blk_bytes;
   p.w_blk_bytes = L.blk_bytes;
-  p.off_bias = 640 + 1024;    // after the mbarriers, the TMEM address slot and the tap masks
-  RB_CHECK(L.n_ntiles * L.n_kchunks <= 128, RB_ERR_UNSUPPORTED, "too many (n-tile, K-chunk) pairs");
+  p.off_bias = 640 + TC_MAX_MASKS * 8;    // after the mbarriers, the TMEM address slot and the tap masks
+  RB_CHECK(L.n_ntiles * L.n_kchunks <= TC_MAX_MASKS, RB_ERR_UNSUPPORTED, "too many (n-tile, K-chunk) pairs (%d x %d)",
+           L.n_ntiles, L.n_kchunks);
   const uint32_t fixed = align_up(p.off_bias + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
   // accumulator stages: as many as TMEM holds (<= 4); the fused unit keeps one h tile per stage
   const int acc_cols1 = L.fused ? 2 * L.N_TILE : L.N_TILE;
@@ -817,14 +818,14 @@ int tc_pack_weights(rb_handle* h) {
       const int shapes[4][2] = {{n_small, 64}, {n_small, 128}, {256, 64}, {256, 128}};
       if (fuse) {                                       // a fused unit is one n-tile; 64-channel K chunks
         const int kc = largest_div16(u.cin_v, largest_div16(cps, 64));
-        if (cps % kc == 0 && u.cin_v / kc <= 128) {
+        if (cps % kc == 0 && u.cin_v / kc <= TC_MAX_MASKS) {
           rc = pack_layer(u, largest_div16(cps, 64), &v2, S, 256);
           if (rc) return rc;
         }
       }
       for (int a = 0; a < 4 && !S.valid && !fuse; ++a) {
         const int nt = largest_div16(u.N_total, shapes[a][0]), kc = largest_div16(u.cin_v, largest_div16(cps, shapes[a][1]));
-        if (cps % kc != 0 || (u.N_total / nt) > TC_MAX_NT || (u.N_total / nt) * (u.cin_v / kc) > 128) continue;
+        if (cps % kc != 0 || (u.N_total / nt) > TC_MAX_NT || (u.N_total / nt) * (u.cin_v / kc) > TC_MAX_MASKS) continue;
         rc = pack_layer(u, largest_div16(cps, shapes[a][1]), nullptr, S, shapes[a][0]);
         if (rc) return rc;
       }
