@@ -210,6 +210,15 @@ int rb_speaker_embed(rb_speaker* s, const float* x, int B, int T, float* emb, vo
 int rb_speaker_load_pqmf(rb_speaker* s, const float* w, int n_band, int k);
 int rb_speaker_embed_audio(rb_speaker* s, const float* audio, int B, int T, float* emb, void* stream);
 int rb_speaker_launches(rb_speaker* s, int64_t* count);
+/* rb_speaker_embed without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same result; the workspace is a file-scope static device
+ * array of RB_SPEAKER_NOALLOC_MAX_FLOATS floats (9.4 MB, held by every GPU that loads the library until
+ * exit).  Sizes whose workspace exceeds it (about B * T > 4096 band samples) return RB_ERR_INVALID.
+ * Calls no cudaMalloc / cudaFree / allocating library routine and never synchronises.  All calls on one
+ * GPU share the array: calls that overlap on the device (different streams) race -- serialise them. */
+#define RB_SPEAKER_NOALLOC_MAX_FLOATS (576 * 4096 + 1536 * 16)
+int rb_speaker_embed_noalloc(rb_speaker* s, const float* x, int B, int T, float* emb, void* stream);
 
 /* `rave.resampler.Resampler` (rave/resampler.py:9-66), wrapped around encode / decode by the exported
  * model (scripts/export.py:377-378, :407-408).  down_w [k_down] = downsample.weight, up_w [ratio][k_up] =

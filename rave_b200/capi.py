@@ -88,6 +88,7 @@ EXPORTS = {
     "rb_speaker_embed": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_speaker_embed_audio": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_speaker_launches": [C.c_void_p, C.POINTER(C.c_int64)],
+    "rb_speaker_embed_noalloc": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_resampler_create": [C.c_int, C.c_int, C.POINTER(C.c_float), C.c_int, C.POINTER(C.c_float), C.c_int,
                             C.c_int, C.c_int, C.POINTER(C.c_void_p)],
     "rb_resampler_destroy": [C.c_void_p],

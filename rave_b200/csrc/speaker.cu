@@ -298,20 +298,33 @@ static int spk_conv(rb_speaker* s, int layer, const float* x, int n_in, float* y
   return launch_conv_f32(a, st);
 }
 
-extern "C" int rb_speaker_embed(rb_speaker* s, const float* x, int B, int T, float* emb, void* stream) {
+// workspace of one rb_speaker_embed call in floats: three ping-pong buffers sized for the widest stage +
+// the tail tensors (every one of them is written by its producer before it is read: nothing needs zeroing)
+static size_t spk_ws_floats(int B, int T) {
+  const size_t n0 = T, n1 = T / 4, n2 = T / 16, n3 = T / 32;
+  const size_t stage = std::max((size_t)128 * n0, (size_t)256 * n1);
+  return (size_t)B * (3 * stage + 256 * n2 + 2 * 256 * n3 + 2 * SPK_C * n3 + 3 * SPK_C * n3 +
+                      128 * n3 + SPK_C * n3 + 2 * SPK_C);
+}
+
+static int spk_check(rb_speaker* s, const float* x, int B, int T, float* emb) {
   RB_CHECK(s && x && emb, RB_ERR_INVALID, "rb_speaker_embed: null argument");
   RB_CHECK(B > 0 && T >= 64 && T % 32 == 0, RB_ERR_INVALID,
            "rb_speaker_embed: T = %d band samples must be a multiple of 32 (the strides) and >= 64", T);
   for (int i = 0; i < RB_SPK_N_LAYERS; ++i)
     RB_CHECK(s->w[i] && s->bias[i], RB_ERR_STATE, "speaker layer %d has no weights", i);
   RB_CHECK(s->bn_scale[0] && s->bn_scale[1], RB_ERR_STATE, "speaker batch norms not loaded");
+  return RB_OK;
+}
+
+static int spk_embed_ws(rb_speaker* s, const float* x, int B, int T, float* emb, float* ws, cudaStream_t st);
+
+extern "C" int rb_speaker_embed(rb_speaker* s, const float* x, int B, int T, float* emb, void* stream) {
+  int rc0 = spk_check(s, x, B, T, emb);
+  if (rc0) return rc0;
   RB_CUDA(cudaSetDevice(s->device));
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t n0 = T, n1 = T / 4, n2 = T / 16, n3 = T / 32;
-  // workspace: three ping-pong buffers sized for the widest stage + the tail tensors
-  const size_t stage = std::max((size_t)128 * n0, (size_t)256 * n1);
-  const size_t total = (size_t)B * (3 * stage + 256 * n2 + 2 * 256 * n3 + 2 * SPK_C * n3 + 3 * SPK_C * n3 +
-                                    128 * n3 + SPK_C * n3 + 2 * SPK_C);
+  const size_t total = spk_ws_floats(B, T);
   if (total * sizeof(float) > s->ws_bytes) {
     RB_CUDA(cudaStreamSynchronize(st));
     cudaFree(s->ws);
@@ -319,7 +332,42 @@ extern "C" int rb_speaker_embed(rb_speaker* s, const float* x, int B, int T, flo
     RB_CUDA(cudaMalloc((void**)&s->ws, total * sizeof(float)));
     s->ws_bytes = total * sizeof(float);
   }
-  float* p = s->ws;
+  return spk_embed_ws(s, x, B, T, emb, s->ws, st);
+}
+
+// ---- allocation-free variant.  No counterpart in the reference: added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops).  The
+// workspace is ONE file-scope device array, held by every GPU that loads the library until exit and shared by
+// every call on that GPU: calls that overlap on the device race.  Each buffer inside it is written by its
+// producer before it is read, so nothing left over from the previous call is ever consumed.
+static __device__ __align__(256) float g_spk_scratch[RB_SPEAKER_NOALLOC_MAX_FLOATS];
+
+extern "C" int rb_speaker_embed_noalloc(rb_speaker* s, const float* x, int B, int T, float* emb, void* stream) {
+  int rc0 = spk_check(s, x, B, T, emb);
+  if (rc0) return rc0;
+  const size_t total = spk_ws_floats(B, T);
+  RB_CHECK(total <= (size_t)RB_SPEAKER_NOALLOC_MAX_FLOATS, RB_ERR_INVALID,
+           "rb_speaker_embed_noalloc: B = %d x T = %d band samples needs %zu floats of workspace, the static "
+           "scratch holds %zu (about B * T <= 4096); use rb_speaker_embed", B, T, total,
+           (size_t)RB_SPEAKER_NOALLOC_MAX_FLOATS);
+  RB_CHECK(s->device >= 0 && s->device < 64, RB_ERR_INVALID, "device index %d out of range", s->device);
+  RB_CUDA(cudaSetDevice(s->device));
+  // In host code `g_spk_scratch` is a host-side stand-in, not a device address: resolve it once per device,
+  // with that device current
+  static float* scratch_of[64] = {};
+  if (!scratch_of[s->device]) {
+    float* ptr = nullptr;
+    RB_CUDA(cudaGetSymbolAddress((void**)&ptr, g_spk_scratch));
+    RB_CHECK(ptr, RB_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch pointer");
+    scratch_of[s->device] = ptr;
+  }
+  return spk_embed_ws(s, x, B, T, emb, scratch_of[s->device], (cudaStream_t)stream);
+}
+
+static int spk_embed_ws(rb_speaker* s, const float* x, int B, int T, float* emb, float* ws, cudaStream_t st) {
+  const size_t n0 = T, n1 = T / 4, n2 = T / 16, n3 = T / 32;
+  const size_t stage = std::max((size_t)128 * n0, (size_t)256 * n1);
+  float* p = ws;
   auto take = [&](size_t n) { float* r = p; p += (size_t)B * n; return r; };
   float *a = take(stage), *h = take(stage), *c = take(stage);
   float* x2 = take(256 * n2);
