@@ -57,11 +57,34 @@ def c0(args):
     return out
 
 
+def _c3_parity(sd, meta):
+    """Outside every timed region: streams 0 and 1 over 8 chunks of 2048 samples on the bf16 engine against the
+    CPU oracle's streaming run of the same chunks (the checker, as in bench.py's parity_check)."""
+    import torch
+    from oracle.model import OracleRAVE
+    from rave_b200 import RAVE
+    from rave_b200.synth import recipe_input
+    m = RAVE.from_gin(["v2.gin", "causal.gin"], streaming=True, dtype=torch.bfloat16)
+    m.load_state_dict(sd)
+    m.alloc_streams(64, 2048)
+    o = OracleRAVE(dict(meta["cfg"], causal=True), sd, streaming=True)
+    x = torch.from_numpy(recipe_input((2, 1, 8 * 2048), 98))
+    ys, yo = [], []
+    for c in range(8):
+        xc = x[..., c * 2048:(c + 1) * 2048].contiguous()
+        ys.append(m(xc.cuda().bfloat16()).float().cpu())
+        yo.append(o.forward(xc))
+    ys, yo = torch.cat(ys, -1).double(), torch.cat(yo, -1).double()
+    err = [float((ys[b] - yo[b]).norm() / yo[b].norm()) for b in range(2)]
+    return {"streams": [0, 1], "chunks": 8, "rel_l2": err, "tolerance": 1e-2, "ok": max(err) < 1e-2,
+            "against": "OracleRAVE streaming (fp32 CPU port of the reference), chunk by chunk"}
+
+
 def c3(args):
     import torch
     from rave_b200 import RAVE
     from rave_b200.synth import recipe_input
-    _, sd = _sd("v2_c64")
+    meta, sd = _sd("v2_c64")
     out = []
     for dtype, tag in ((torch.bfloat16, "bf16"), (torch.float32, "f32")):
         m = RAVE.from_gin(["v2.gin", "causal.gin"], streaming=True, dtype=dtype)
@@ -71,12 +94,19 @@ def c3(args):
         x = torch.from_numpy(recipe_input((64, 1, n), 99)).cuda().repeat(B // 64, 1, 1).contiguous().to(dtype)
         l0 = m.kernel_launches()
         ms = _time(lambda: m(x), 8, args.steps)
+        # the same step replayed from a CUDA graph (what a serving loop would do)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            m(x)
+        ms_graph = _time(g.replay, 8, args.steps)
         out.append({"config": "C3 v2 causal streaming, %d streams x 2048-sample chunks, CAPACITY=64" % B,
+                    "ms_per_step_cuda_graph": ms_graph,
                     "dtype": tag, "ms_per_step": ms, "value": B * n / SR / (ms / 1e3), "unit": "audio-sec/sec",
                     "real_time_factor_per_stream": (n / SR) / (ms / 1e3),
                     "state_elements_per_stream": m.stream_state_elements(),
                     "launches_per_step": (m.kernel_launches() - l0) // (8 + args.steps)})
         del m
+    out[0]["parity_check"] = _c3_parity(sd, meta)
     return out
 
 
@@ -84,8 +114,8 @@ def c4(args):
     import torch
     from rave_b200 import RAVE
     from rave_b200.synth import recipe_input
-    meta, sd = _sd("discrete_c8")
-    m = RAVE.from_gin(["discrete.gin"], ["CAPACITY=8"], dtype=torch.bfloat16)
+    meta, sd = _sd("discrete_c96")        # BASELINE configs[3] at its stated size (discrete.gin:13-19)
+    m = RAVE.from_gin(["discrete.gin"], [], dtype=torch.bfloat16)
     m.load_state_dict(sd)
     B, T = args.batch, 2 ** 18
     x = torch.from_numpy(recipe_input((64, 1, T), 7)).cuda().repeat(B // 64, 1, 1).contiguous().bfloat16()
@@ -102,26 +132,34 @@ def c4(args):
         return m.decode(zz)
 
     ms_dec = _time(dec, 3, args.steps)
-    return [{"config": "C4 discrete (RVQ %dx%d, dim %d), CAPACITY=8, %d streams x 2^18" %
+    ms_fwd = _time(lambda: m(x), 3, args.steps)
+    mf = m.spec.macs_per_frame()
+    flops = 2.0 * (mf["enc"] + mf["dec"]) * B * (T // m.spec.samples_per_frame)
+    return [{"config": "C4 discrete (RVQ %dx%d, dim %d), CAPACITY=96, %d streams x 2^18" %
                        (idx.shape[1], m.spec.rvq["codebook_size"], nl, B),
              "dtype": "bf16 net / fp32 RVQ", "rvq_encode_ms": ms_enc, "vectors": int(B * idx.shape[2]),
              "rvq_encode_Mvec_per_s": B * idx.shape[2] / ms_enc / 1e3,
-             "decode_from_indices_ms": ms_dec, "value": B * T / SR / (ms_dec / 1e3), "unit": "audio-sec/sec (decode)"}]
+             "decode_from_indices_ms": ms_dec, "value": B * T / SR / (ms_dec / 1e3), "unit": "audio-sec/sec (decode)",
+             "forward_ms": ms_fwd, "forward_audio_sec_per_sec": B * T / SR / (ms_fwd / 1e3),
+             "forward_TFLOPs": flops / ms_fwd / 1e9}]
 
 
 def c5(args):
     import torch
     from rave_b200 import RAVE
-    meta, sd = _sd("v3_c8")
-    m = RAVE.from_gin(["v3.gin"], ["CAPACITY=8"], dtype=torch.bfloat16)
-    m.load_state_dict(sd)
-    B, F = min(args.batch, 64), 256       # AdaIN statistics rows: cc.MAX_BATCH_SIZE = 64 streams
+    meta, sd = _sd("v3_c64")              # BASELINE configs[4] at its stated size (v3.gin: CAPACITY 64)
+    m = RAVE.from_gin(["v3.gin"], [], dtype=torch.bfloat16)
+    B, F = args.batch, 256
+    # the checkpoint's AdaIN tables hold cc.MAX_BATCH_SIZE = 64 rows; rows 64.. get the constructor's values
+    m.load_state_dict(sd, max_batch_size=B)
     g = torch.Generator(device="cuda").manual_seed(5)
     z = torch.randn(B, m.spec.dec_latent_size, F, generator=g, device="cuda").bfloat16()
     ms = _time(lambda: m.decode(z), 3, args.steps)
     T = F * m.spec.samples_per_frame
-    return [{"config": "C5 v3 (Snake + AdaIN) decode-only, CAPACITY=8, %d streams x %d frames" % (B, F),
-             "dtype": "bf16", "ms_per_step": ms, "value": B * T / SR / (ms / 1e3), "unit": "audio-sec/sec (decode)"}]
+    flops = 2.0 * m.spec.macs_per_frame()["dec"] * B * F
+    return [{"config": "C5 v3 (Snake + AdaIN) decode-only, CAPACITY=64, %d streams x %d frames" % (B, F),
+             "dtype": "bf16", "ms_per_step": ms, "value": B * T / SR / (ms / 1e3), "unit": "audio-sec/sec (decode)",
+             "TFLOPs": flops / ms / 1e9}]
 
 
 def c6(args):

@@ -154,6 +154,19 @@ int rb_host_sync(rb_handle* h);
  * (the reference draws it unseeded, blocks.py:287); NULL = engine-generated (Philox). */
 int rb_set_noise(rb_handle* h, const float* noise, int64_t numel);
 
+/* Per-stream conditioning of the calls that follow (rave/model.py:615-620: emb = speaker.repeat(B, 1, F),
+ * z = cat(z, emb); scripts/export.py:381-397: z = cat(z, target_emb, f0_norm)).
+ *   spk: DEVICE fp32 [spk_rows][cond_channels]; spk_rows = 1 conditions every stream with the same vector
+ *        (what RB_W_COND loads, the reference's single `speaker` buffer), spk_rows >= B conditions stream b
+ *        with row b (offline batch row / streaming state row).  NULL keeps the current table.
+ *   f0:  DEVICE fp32 [B][f0_channels][F], the pitch channels appended behind the speaker channels;
+ *        f0_channels must equal decoder latent_size - latent - cond_channels as the config binds it, and B / F
+ *        the streams and latent frames of the calls that use it (a streaming caller sets each chunk's f0
+ *        before the step).  NULL clears it: nets with pitch channels then feed zeros.
+ * Both are copied (enqueued on `stream`), so the caller's buffers are free after the call returns to the stream. */
+int rb_set_conditioning(rb_handle* h, const float* spk, int spk_rows, const float* f0, int B, int f0_channels,
+                        int F, void* stream);
+
 /* Discrete boundary (scripts/export.py:503-517). z fp32 [B,D,F]; idx int64 [B,Q,F]. */
 int rb_rvq_encode(rb_handle* h, const float* z, int B, int F, int64_t* idx, void* stream);
 int rb_rvq_decode(rb_handle* h, const int64_t* idx, int B, int F, float* zq, void* stream);

@@ -109,19 +109,26 @@ class OracleRAVE:
 
     # -- public surface (rave/model.py:594-634) ------------------------------------------
     @torch.no_grad()
-    def encode(self, x):
+    def encode(self, x, speaker=None, f0=None):
+        """model.py:594-622.  `speaker` [B, S, 1]: one embedding per stream instead of the module's single
+        buffer (the export wrapper swaps `target_emb` per call, scripts/export.py:381-394); `f0` [B, C, F]:
+        the pitch channels of scripts/export.py:397 `z = cat(z, emb, f0_norm)`."""
         xb = self.pqmf_forward(x)
         z = self.encoder(xb[:, :self.cfg["enc_data_size"], :])
-        emb = self.sd["speaker"].repeat(z.shape[0], 1, z.shape[-1])
-        return torch.cat((z, emb), dim=1)
+        if speaker is None:
+            emb = self.sd["speaker"].repeat(z.shape[0], 1, z.shape[-1])
+        else:
+            emb = speaker.reshape(z.shape[0], -1, 1).repeat(1, 1, z.shape[-1])
+        parts = (z, emb) if f0 is None else (z, emb, f0)
+        return torch.cat(parts, dim=1)
 
     @torch.no_grad()
     def decode(self, z, noise=None):
         return self.pqmf_inverse(self.decoder(z, noise))
 
     @torch.no_grad()
-    def forward(self, x, noise=None):
-        return self.decode(self.encode(x), noise)
+    def forward(self, x, noise=None, speaker=None, f0=None):
+        return self.decode(self.encode(x, speaker, f0), noise)
 
     __call__ = forward
 

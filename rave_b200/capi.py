@@ -65,6 +65,7 @@ EXPORTS = {
     "rb_host_join": [C.c_void_p, C.c_void_p],
     "rb_host_sync": [C.c_void_p],
     "rb_set_noise": [C.c_void_p, C.c_void_p, C.c_int64],
+    "rb_set_conditioning": [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p],
     "rb_rvq_encode": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_rvq_decode": [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p],
     "rb_stream_alloc": [C.c_void_p, C.c_int, C.c_int, C.c_int],

@@ -69,7 +69,17 @@ int launch_head_v1_f32(const View& wave, const View& loud, const View& y, int B,
                        cudaStream_t s);
 int launch_noise_v2_f32(const View& amp, const float* noise, int64_t noise_b_stride, const View& y,
                         int B, int data, unsigned long long seed, cudaStream_t s);
-int launch_concat_f32(const View& z, const View& y, const float* cond, int B, int c_z, int c_cond,
+// Conditioning channels CONCAT_COND appends behind the latent (model.py:615-620, scripts/export.py:393-397):
+// c_spk speaker channels, constant over time -- row b0 + b of the table, or its only row (stride 0) --
+// then f0_C pitch channels read from f0 [streams][f0_C][f0_F] at the frame index (nullptr: zeros).
+struct CondArgs {
+  const float* spk;
+  long long spk_stride;
+  const float* f0;
+  int c_spk, f0_C, f0_F;
+  int b0;                   // first stream of the running microbatch
+};
+int launch_concat_f32(const View& z, const View& y, const CondArgs& ca, int B, int c_z, int c_out,
                       cudaStream_t s);
 int launch_copy_rows_f32(const float* src, int src_ld, float* dst, int dst_ld, int rows, int n,
                          cudaStream_t s);

@@ -115,9 +115,12 @@ int exec_op_f32(RunCtx& c, int oi) {
     case RB_OP_NOISE_V2:
       return launch_noise_v2_f32(x, c.noise, c.noise_bstride, y, c.B, op.c_out,
                                  c.h->noise_seed++, c.s);
-    case RB_OP_CONCAT_COND:
-      RB_CHECK(w.cond, RB_ERR_STATE, "conditioning vector (speaker embedding) not loaded");
-      return launch_concat_f32(x, y, w.cond, c.B, op.c_in, op.c_out - op.c_in, c.s);
+    case RB_OP_CONCAT_COND: {
+      CondArgs ca;
+      int rc = cond_args(c.h, oi, c.B, y.n, &ca);
+      if (rc) return rc;
+      return launch_concat_f32(x, y, ca, c.B, op.c_in, op.c_out, c.s);
+    }
   }
   set_error("op %d: unknown kind %d", oi, op.kind);
   return RB_ERR_INVALID;
@@ -247,6 +250,33 @@ void adain_finalize(rb_handle* h, int ob, int oe) {
 using namespace rb;
 
 // ================================================================================ C-ABI
+namespace rb {
+int cond_args(rb_handle* h, int oi, int B, int n, CondArgs* out) {
+  const rb_op& op = h->ops[oi];
+  const OpWeights& w = h->w[oi];
+  const int c_spk = h->spec.cond_channels, f0_C = op.c_out - op.c_in - c_spk;
+  RB_CHECK(w.cond, RB_ERR_STATE, "conditioning vector (speaker embedding) not loaded");
+  RB_CHECK(w.cond_rows == 1 || h->cur_b0 + B <= w.cond_rows, RB_ERR_INVALID,
+           "batch %d exceeds the %d rows of the speaker table (rb_set_conditioning)", h->cur_b0 + B, w.cond_rows);
+  out->spk = w.cond;
+  out->spk_stride = w.cond_rows == 1 ? 0 : c_spk;
+  out->c_spk = c_spk;
+  out->f0 = nullptr;
+  out->f0_C = f0_C;
+  out->f0_F = n;
+  out->b0 = h->cur_b0;
+  if (h->f0_B > 0) {
+    RB_CHECK(f0_C > 0, RB_ERR_INVALID, "pitch channels are set but the decoder takes none (latent_size %d = %d + %d)",
+             op.c_out, op.c_in, c_spk);
+    RB_CHECK(h->f0_C == f0_C && h->f0_F == n && h->cur_b0 + B <= h->f0_B, RB_ERR_INVALID,
+             "pitch channels are [%d, %d, %d], this call needs [>= %d, %d, %d]", h->f0_B, h->f0_C, h->f0_F,
+             h->cur_b0 + B, f0_C, n);
+    out->f0 = h->f0;
+  }
+  return RB_OK;
+}
+}  // namespace rb
+
 extern "C" {
 
 const char* rb_last_error(void) { return g_err; }
@@ -295,6 +325,7 @@ int rb_destroy(rb_handle* h) {
     cudaFree(w.w); cudaFree(w.bias); cudaFree(w.alpha); cudaFree(w.aff_a); cudaFree(w.aff_b); cudaFree(w.stats);
     cudaFree(w.cond);
   }
+  cudaFree(h->f0);
   cudaFree(h->codebooks); cudaFree(h->cb_norms); cudaFree(h->rvq_ws);
   for (auto& p : h->pool) cudaFree(p.p);
   for (void* p : h->sbuf) cudaFree(p);
@@ -409,9 +440,10 @@ int rb_load_weights(rb_handle* h, const rb_tensor_desc* t, int n) {
         break;
       }
       case RB_W_COND:
-        RB_CHECK(op.kind == RB_OP_CONCAT_COND && d.numel == op.c_out - op.c_in, RB_ERR_INVALID,
+        RB_CHECK(op.kind == RB_OP_CONCAT_COND && d.numel == h->spec.cond_channels, RB_ERR_INVALID,
                  "conditioning vector size");
         rc = upload(d.data, d.numel, &w.cond);
+        w.cond_rows = 1;
         break;
       default:
         set_error("tensor %d: unknown role %d", i, d.role);
@@ -612,6 +644,45 @@ int rb_host_sync(rb_handle* h) {
   RB_CHECK(h, RB_ERR_INVALID, "null handle");
   if (!h->pipe.ready) return RB_OK;
   RB_CUDA(cudaStreamSynchronize(h->pipe.s_out));
+  return RB_OK;
+}
+
+// model.py:615-620 / scripts/export.py:381-397 (see include/rave_b200.h)
+int rb_set_conditioning(rb_handle* h, const float* spk, int spk_rows, const float* f0, int B, int f0_channels,
+                        int F, void* stream) {
+  RB_CHECK(h, RB_ERR_INVALID, "null handle");
+  BusyGuard g(h);
+  RB_CHECK(g.ok, RB_ERR_STATE, "handle is busy");
+  cudaStream_t s = (cudaStream_t)stream;
+  int oi = -1;
+  for (size_t i = 0; i < h->ops.size(); ++i)
+    if (h->ops[i].kind == RB_OP_CONCAT_COND) oi = (int)i;
+  RB_CHECK(oi >= 0, RB_ERR_INVALID, "the net has no conditioning channels");
+  RB_CUDA(cudaSetDevice(h->device));
+  if (spk) {
+    OpWeights& w = h->w[oi];
+    RB_CHECK(spk_rows >= 1, RB_ERR_INVALID, "spk_rows must be >= 1");
+    const size_t n = (size_t)spk_rows * h->spec.cond_channels;
+    if (spk_rows != w.cond_rows || !w.cond) {
+      if (w.cond) { RB_CUDA(cudaStreamSynchronize(s)); cudaFree(w.cond); w.cond = nullptr; }
+      RB_CUDA(cudaMalloc((void**)&w.cond, n * sizeof(float)));
+      w.cond_rows = spk_rows;
+    }
+    RB_CUDA(cudaMemcpyAsync(w.cond, spk, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  }
+  if (f0) {
+    RB_CHECK(B >= 1 && f0_channels >= 1 && F >= 1, RB_ERR_INVALID, "f0 must be [B, f0_channels, F]");
+    const size_t n = (size_t)B * f0_channels * F;
+    if (n > h->f0_cap) {
+      if (h->f0) { RB_CUDA(cudaStreamSynchronize(s)); cudaFree(h->f0); h->f0 = nullptr; h->f0_cap = 0; }
+      RB_CUDA(cudaMalloc((void**)&h->f0, n * sizeof(float)));
+      h->f0_cap = n;
+    }
+    RB_CUDA(cudaMemcpyAsync(h->f0, f0, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    h->f0_B = B; h->f0_C = f0_channels; h->f0_F = F;
+  } else {
+    h->f0_B = h->f0_C = h->f0_F = 0;
+  }
   return RB_OK;
 }
 

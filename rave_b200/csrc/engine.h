@@ -32,6 +32,8 @@ int adain_step(rb_handle* h, OpWeights& w, int C, cudaStream_t s,
                const std::function<int(float*, float*, int)>& stats_fn, bool* apply);
 void adain_finalize(rb_handle* h, int ob, int oe);
 int pool_get(rb_handle* h, size_t bytes, int* idx);   // offline workspace pool (engine.cu)
+// the conditioning channels CONCAT_COND op `oi` appends for B streams x n frames (rb_set_conditioning)
+int cond_args(rb_handle* h, int oi, int B, int n, CondArgs* out);
 
 // RAII: records a start/stop event pair for op `oi` when profiling is on
 struct OpTimer {
@@ -52,7 +54,8 @@ struct OpWeights {
   float* stats = nullptr;
   int nx = 0, ny = 0;
   bool touch_x = false, touch_y = false;   // learned during the running call: counted once at its end
-  float* cond = nullptr;
+  float* cond = nullptr;    // CONCAT_COND: speaker table [cond_rows][cond_channels]
+  int cond_rows = 0;        // 1: the same vector for every stream (RB_W_COND); else row b <-> stream b
   // host copies kept for the bf16 tensor-core packer (tc_engine.cu)
   std::vector<float> w_host;   // folded fp32 [c_out][c_in][k] (PQMF: as loaded)
   std::vector<float> bias_host, alpha_host;
@@ -82,6 +85,11 @@ struct rb_handle {
   const float* noise = nullptr;  // user noise, device
   int64_t noise_numel = 0;
   unsigned long long noise_seed = 0x1234;
+
+  // rb_set_conditioning: pitch channels of the coming calls, device copy [f0_B][f0_C][f0_F]
+  float* f0 = nullptr;
+  size_t f0_cap = 0;
+  int f0_B = 0, f0_C = 0, f0_F = 0;
 
   std::vector<rb::PoolBuf> pool;  // offline activation workspace
   int microbatch = 0;

@@ -457,21 +457,23 @@ int launch_noise_v2_f32(const View& amp, const float* noise, int64_t nbs, const 
   return RB_OK;
 }
 
-// model.py:618-620: z = cat(z, speaker.repeat(B, 1, F))
-__global__ void concat_f32_kernel(View z, View y, const float* __restrict__ cond, int c_z) {
+// model.py:618-620: z = cat(z, speaker.repeat(B, 1, F)); scripts/export.py:393-397: cat(z, emb, f0_norm)
+__global__ void concat_f32_kernel(View z, View y, CondArgs ca, int c_z) {
   const int b = blockIdx.z, c = blockIdx.y;
   float* yp = y.p + ((size_t)b * y.C + c) * y.ld + y.hist;
   const float* zp = c < c_z ? z.p + ((size_t)b * z.C + c) * z.ld + z.hist : nullptr;
-  const float cv = c < c_z ? 0.f : cond[c - c_z];
+  const int cf = c - c_z - ca.c_spk;
+  const float* fp = (cf >= 0 && ca.f0) ? ca.f0 + ((size_t)(ca.b0 + b) * ca.f0_C + cf) * ca.f0_F : nullptr;
+  const float cv = (c >= c_z && cf < 0) ? ca.spk[(size_t)(ca.b0 + b) * ca.spk_stride + (c - c_z)] : 0.f;
   for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < y.n; t += gridDim.x * blockDim.x)
-    yp[t] = zp ? zp[t] : cv;
+    yp[t] = zp ? zp[t] : (fp ? fp[t] : cv);
 }
 
-int launch_concat_f32(const View& z, const View& y, const float* cond, int B, int c_z, int c_cond,
+int launch_concat_f32(const View& z, const View& y, const CondArgs& ca, int B, int c_z, int c_out,
                       cudaStream_t s) {
   if (y.n <= 0 || B <= 0) return RB_OK;
-  dim3 grid(min((y.n + 127) / 128, 64), c_z + c_cond, B);
-  concat_f32_kernel<<<grid, 128, 0, s>>>(z, y, cond, c_z);
+  dim3 grid(min((y.n + 127) / 128, 64), c_out, B);
+  concat_f32_kernel<<<grid, 128, 0, s>>>(z, y, ca, c_z);
   ++g_launches;
   RB_CUDA(cudaGetLastError());
   return RB_OK;

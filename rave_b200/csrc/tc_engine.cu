@@ -556,7 +556,8 @@ __global__ void gm_to_cf_kernel(Buf src, __nv_bfloat16* __restrict__ dst, int C,
 // model.py:618-620: z = cat(z, speaker.repeat(B, 1, F)) (+ zero pad channels)
 // One thread per 16-byte unit (8 channels of one row): z groups are copied, conditioning groups are
 // the same 8 values for every row of every stream, pad groups are zero.
-__global__ void concat_gm_kernel(Buf z, Buf y, const float* __restrict__ cond, int c_z, int c_cond, int B) {
+__global__ void concat_gm_kernel(Buf z, Buf y, CondArgs ca, int c_z, int B) {
+  const int c_cond = ca.c_spk;
   const int G = y.cp >> 3, Gz = z.cp >> 3;
   const long long units = (long long)B * G * y.n;
   for (long long u = blockIdx.x * (long long)blockDim.x + threadIdx.x; u < units; u += (long long)gridDim.x * blockDim.x) {
@@ -572,8 +573,12 @@ __global__ void concat_gm_kernel(Buf z, Buf y, const float* __restrict__ cond, i
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const int c = c0 + k;
-        e[k] = c < c_z ? z.p[eidx(z, b, t, c)]
-                       : (c < c_z + c_cond ? __float2bfloat16_rn(cond[c - c_z]) : __float2bfloat16_rn(0.f));
+        float v32 = 0.f;
+        if (c < c_z) v32 = __bfloat162float(z.p[eidx(z, b, t, c)]);
+        else if (c < c_z + c_cond) v32 = ca.spk[(size_t)(ca.b0 + b) * ca.spk_stride + (c - c_z)];
+        else if (ca.f0 && c < c_z + c_cond + ca.f0_C)
+          v32 = ca.f0[((size_t)(ca.b0 + b) * ca.f0_C + (c - c_z - c_cond)) * ca.f0_F + t];
+        e[k] = __float2bfloat16_rn(v32);
       }
       v = *reinterpret_cast<const uint4*>(e);
     }
@@ -948,11 +953,11 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
       return RB_OK;
     }
     case RB_OP_CONCAT_COND: {
-      const OpWeights& w = h->w[i];
-      RB_CHECK(w.cond, RB_ERR_STATE, "conditioning vector (speaker embedding) not loaded");
       const Buf& y = bufs[op.dst];
-      RB_LAUNCH_EW(concat_gm_kernel, (size_t)B * y.n * (y.cp / 8), s, bufs[op.src], y, w.cond, op.c_in,
-                   op.c_out - op.c_in, B);
+      CondArgs ca;
+      int rc = cond_args(h, i, B, y.n, &ca);
+      if (rc) return rc;
+      RB_LAUNCH_EW(concat_gm_kernel, (size_t)B * y.n * (y.cp / 8), s, bufs[op.src], y, ca, op.c_in, B);
       return RB_OK;
     }
   }

@@ -144,12 +144,15 @@ class RAVE:
                 self._adain_rows[int(op)] = (a.size - 2) // (4 * self.spec.ops[int(op)].c_in)
         capi.check(self._lib.rb_load_weights(self._h, arr, len(items)))
 
-    def load_state_dict(self, state_dict, strict=True):
-        """Accepts a reference checkpoint's `state_dict` (weight-norm pairs or folded)."""
+    def load_state_dict(self, state_dict, strict=True, max_batch_size=None):
+        """Accepts a reference checkpoint's `state_dict` (weight-norm pairs or folded).  `max_batch_size`:
+        what `cc.MAX_BATCH_SIZE` would be set to before construction -- the per-stream AdaIN statistics tables
+        (blocks.py:860-866, 64 rows in a shipped checkpoint) are extended to that many rows with the
+        constructor's values, so more than 64 streams can run (and learn their own statistics)."""
         self.skipped_keys = []          # strict=False: what the state_dict did not provide (upstream's missing_keys)
         self._load(collect(self.spec, state_dict, (self.pqmf.forward_conv_weight,
                                                    self.pqmf.inverse_conv_weight), strict=strict,
-                           skipped=self.skipped_keys))
+                           skipped=self.skipped_keys, max_batch_size=max_batch_size))
         return self
 
     @classmethod
@@ -179,8 +182,35 @@ class RAVE:
         return self
 
     def set_speaker(self, emb):
-        """`self.speaker` of the reference (model.py:246-247): the fixed [1, S, 1] embedding."""
-        self.load_state_dict({"speaker": emb}, strict=False)
+        """`self.speaker` of the reference (model.py:246-247): the fixed [1, S, 1] embedding -- or one row
+        per stream, [B, S] / [B, S, 1]: stream b of the following calls is conditioned on row b (the reference
+        repeats its single vector over the batch, model.py:615-618; the export wrapper swaps it per call,
+        scripts/export.py:381-394)."""
+        S = self.spec.cond_channels
+        if isinstance(emb, torch.Tensor):
+            t = emb.detach().to(device=self.device, dtype=torch.float32)
+        else:
+            t = torch.as_tensor(np.asarray(emb, dtype=np.float32), device=self.device)
+        if t.numel() % S or t.numel() == 0:
+            raise ValueError(f"set_speaker: expected [rows, {S}] values, got {tuple(t.shape)}")
+        t = t.reshape(-1, S).contiguous()
+        capi.check(self._lib.rb_set_conditioning(self._h, t.data_ptr(), t.shape[0], None, 0, 0, 0, _stream_ptr()))
+
+    def set_f0(self, f0):
+        """The pitch channels `f0_norm` the export wrapper appends behind the speaker channels
+        (scripts/export.py:358-359,397): [B, f0_channels, F] for the following calls of B streams x F frames
+        (each streaming chunk needs its own); None clears them (zeros).  Only nets whose decoder is bound
+        wider than latent + speaker take any (`spec.f0_channels`)."""
+        if f0 is None:
+            capi.check(self._lib.rb_set_conditioning(self._h, None, 0, None, 0, 0, 0, _stream_ptr()))
+            return
+        if not isinstance(f0, torch.Tensor) or not f0.is_cuda:
+            raise ValueError("set_f0: f0 must be a CUDA tensor")
+        if f0.dim() != 3 or f0.shape[1] != self.spec.f0_channels or self.spec.f0_channels == 0:
+            raise ValueError(f"set_f0: expected [B, {self.spec.f0_channels}, F], got {tuple(f0.shape)}")
+        t = f0.detach().to(torch.float32).contiguous()
+        capi.check(self._lib.rb_set_conditioning(self._h, None, 0, t.data_ptr(), t.shape[0], t.shape[1], t.shape[2],
+                                                 _stream_ptr()))
 
     def load_speaker_encoder(self, state_dict):
         """model.py:164-174: build the speaker encoder (CombinedRave.SpeakerRAVE) from its state_dict."""
@@ -245,7 +275,10 @@ class RAVE:
             capi.check(self._lib.rb_stream_reset(self._h, ids, len(stream_ids)))
 
     @torch.no_grad()
-    def encode(self, x):
+    def encode(self, x, f0=None):
+        """model.py:594-622; `f0` ([B, f0_channels, F], optional) = set_f0(f0) for this call."""
+        if f0 is not None:
+            self.set_f0(f0)
         x = self._check_input(x, 1, "encode")
         B, _, T = x.shape
         spf = self.spec.samples_per_frame
@@ -273,7 +306,10 @@ class RAVE:
         return y
 
     @torch.no_grad()
-    def forward(self, x):
+    def forward(self, x, f0=None):
+        """model.py:631-634; with `f0` the export wrapper's `myforward` core (scripts/export.py:380-404)."""
+        if f0 is not None:
+            self.set_f0(f0)
         x = self._check_input(x, 1, "forward")
         B, _, T = x.shape
         if T % self.spec.samples_per_frame:

@@ -90,6 +90,7 @@ class NetSpec:
     attenuation: int = 100
     activation: str = "leaky_relu"
     adain: bool = False
+    f0_channels: int = 0      # pitch channels the decoder takes behind the speaker channels (export.py:397)
 
     def macs_per_frame(self):
         """Algorithmic multiply-accumulates per latent frame."""
@@ -488,8 +489,12 @@ def build_netspec(cfg: "gin_lite.Config", streaming: bool = False) -> NetSpec:
     else:
         raise ValueError(f"encoder class {inner.name} not supported")
     latent = int(EP["latent_size"]) * int(EP["n_out"])
-    zc = b.slot(latent + cond, 1)
-    b.ops.append(Op(OP_CONCAT, z, zc, c_in=latent, c_out=latent + cond, params={"cond": "speaker"},
+    # scripts/export.py:393-397 `cat(z, emb, f0_norm)`: a decoder bound wider than latent + speaker takes
+    # pitch channels behind the speaker channels (this fork's get_augmented_latent_size, core.py:78-79,
+    # leaves pitch_embedding_size out, so the shipped configs have none)
+    f0_ch = max(0, int(DP["latent_size"]) - latent - cond)
+    zc = b.slot(latent + cond + f0_ch, 1)
+    b.ops.append(Op(OP_CONCAT, z, zc, c_in=latent, c_out=latent + cond + f0_ch, params={"cond": "speaker"},
                     name="speaker_concat"))
     n_enc = len(b.ops)
 
@@ -523,4 +528,4 @@ def build_netspec(cfg: "gin_lite.Config", streaming: bool = False) -> NetSpec:
                    dec_latent_size=int(DP["latent_size"]), n_band=n_band, enc_bands=enc_bands,
                    sr=int(R.get("sampling_rate", 44100)), noise_slot=noise_slot, rvq=rvq,
                    encoder_type=enc_type, arch=arch, attenuation=atten, activation=act_name,
-                   adain=EP.get("adain") is not None)
+                   adain=EP.get("adain") is not None, f0_channels=f0_ch)

@@ -52,8 +52,10 @@ def _phase_pack(w, r, p, k_taps):
     return out
 
 
-def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True, skipped=None):
-    """Returns a list of (op_index, role, float32 ndarray) for everything found in `sd`."""
+def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True, skipped=None, max_batch_size=None):
+    """Returns a list of (op_index, role, float32 ndarray) for everything found in `sd`.
+    `max_batch_size`: rows of the AdaIN statistics tables (cc.MAX_BATCH_SIZE at construction, blocks.py:860-866);
+    tables with fewer rows are extended with the constructor's values (mean 0, std 1)."""
     out = []
     missing = []
     defaulted = []
@@ -103,6 +105,10 @@ def collect(spec: NetSpec, sd, pqmf_weights=None, strict=True, skipped=None):
                 p = P["adain"]
                 mx, sx = _np(sd[p + "mean_x"])[..., 0], _np(sd[p + "std_x"])[..., 0]
                 my, sy = _np(sd[p + "mean_y"])[..., 0], _np(sd[p + "std_y"])[..., 0]
+                if max_batch_size and mx.shape[0] < max_batch_size:
+                    n = max_batch_size - mx.shape[0]
+                    ext = lambda t, v: np.concatenate([t, np.full((n, t.shape[1]), v, np.float32)], 0)  # noqa: E731
+                    mx, sx, my, sy = ext(mx, 0.), ext(sx, 1.), ext(my, 0.), ext(sy, 1.)
                 # the four buffers + the two counters travel as they are (blocks.py:860-868): the engine
                 # derives a = std_y / (std_x + 1e-5), b = mean_y - mean_x * a and can go on learning
                 nx = float(_np(sd[p + "num_update_x"]).reshape(-1)[0])

@@ -638,3 +638,92 @@ def test_latent_post_pre_processing_vs_oracle():
     v = latent.angles_to_unit_norm_vector(a_ref.cuda())
     assert rel_l2(v.cpu().numpy(), L.angles_to_unit_norm_vector(a_ref.clone()).numpy()) < 1e-5
     assert rel_l2(latent.angles_to_unit_norm_vector(a).cpu().numpy(), x.numpy()) < 1e-4     # device round trip
+
+
+@pytest.mark.parametrize("dtype,streaming", [(torch.float32, False), (torch.bfloat16, False), (torch.float32, True),
+                                             (torch.bfloat16, True)])
+def test_per_stream_conditioning_and_f0_channel_vs_oracle(dtype, streaming):
+    """rb_set_conditioning: one speaker row per stream and a pitch channel behind the speaker channels
+    (scripts/export.py:381-397 `z = cat(z, target_emb, f0_norm)`, rave/model.py:615-620), offline and chunk
+    by chunk, against the oracle's encode(x, speaker, f0)."""
+    from oracle.model import OracleRAVE
+    from oracle.weights_recipe import build_state_dict, recipe_input
+    from rave_b200 import RAVE
+    name = "v2causal_c8" if streaming else "v2_c8"
+    meta, _ = load_golden(name)
+    ns = [(n, (s[0], 321, s[2]) if n == "decoder.net.0.weight_v" else tuple(s)) for n, s in meta["names_shapes"]]
+    sd = build_state_dict(ns, meta["seed"])
+    files, binds = GIN[name]
+    m = RAVE.from_gin(files, binds + ["blocks.GeneratorV2.latent_size = 321"], streaming=streaming, dtype=dtype)
+    assert m.spec.f0_channels == 1
+    m.load_state_dict(sd)
+    o = OracleRAVE(dict(meta["cfg"], dec_latent_size=321), sd, streaming=streaming)
+    B, n_chunk, chunks = 3, 2048, 3 if streaming else 1
+    T = n_chunk * chunks
+    x = torch.from_numpy(recipe_input((B, 1, T), 91))
+    spk = torch.from_numpy(recipe_input((B, 256, 1), 92, scale=1.0))
+    f0 = torch.from_numpy(recipe_input((B, 1, T // 1024), 93, uniform=True)) * 0.5 + 0.5
+    tol = F32_TOL if dtype == torch.float32 else 1.5e-2
+    m.set_speaker(spk.cuda())                       # three different rows
+    if not streaming:
+        y = m.forward(x.cuda().to(dtype), f0=f0.cuda()).float().cpu().numpy()
+        yo = o.forward(x, speaker=spk, f0=f0).numpy()
+        assert rel_l2(y, yo) < tol
+        z = m.encode(x.cuda().to(dtype), f0=f0.cuda()).float().cpu().numpy()
+        zo = o.encode(x, speaker=spk, f0=f0).numpy()
+        assert z.shape == zo.shape == (B, 321, T // 1024)
+        assert rel_l2(z, zo) < tol
+        assert np.array_equal(z[:, 64:320, 0], spk[:, :, 0].to(dtype).float().numpy())
+        # a single row conditions every stream (the reference's one `speaker` buffer)
+        m.set_speaker(spk[1])
+        y1 = m.forward(x.cuda().to(dtype), f0=f0.cuda()).float().cpu().numpy()
+        yo1 = o.forward(x, speaker=spk[1:2].repeat(B, 1, 1), f0=f0).numpy()
+        assert rel_l2(y1, yo1) < tol
+        # no pitch channels set: zeros
+        m.set_f0(None)
+        y0 = m.forward(x.cuda().to(dtype)).float().cpu().numpy()
+        assert rel_l2(y0, o.forward(x, speaker=spk[1:2].repeat(B, 1, 1), f0=torch.zeros_like(f0)).numpy()) < tol
+        with pytest.raises(ValueError):
+            m.set_f0(torch.zeros(B, 2, T // 1024).cuda())
+        m.set_speaker(spk[:2].cuda())               # two rows, three streams
+        with pytest.raises(ValueError):
+            m.forward(x.cuda().to(dtype))
+        m.set_f0(f0[:, :, :2].cuda())               # frames of another call
+        m.set_speaker(spk.cuda())
+        with pytest.raises(ValueError):
+            m.forward(x.cuda().to(dtype))
+    else:
+        for c in range(chunks):
+            xs = x[..., c * n_chunk:(c + 1) * n_chunk].contiguous()
+            fs = f0[..., c * 2:(c + 1) * 2].contiguous()
+            y = m.forward(xs.cuda().to(dtype), f0=fs.cuda()).float().cpu().numpy()
+            yo = o.forward(xs, speaker=spk, f0=fs).numpy()
+            assert rel_l2(y, yo) < tol, c
+
+
+@pytest.mark.parametrize("name,dtype", [("v2causal_c8", torch.bfloat16), ("v2causal_c64", torch.bfloat16),
+                                        ("v2causal_c8", torch.float32)])
+def test_stream_step_is_cuda_graph_capturable(name, dtype):
+    """no hidden allocation or synchronisation in the hot call after rb_stream_alloc -- one
+    rb_stream_step is captured in a CUDA graph (cudaStreamCaptureModeThreadLocal through torch) and the replays,
+    chunk by chunk, return bit for bit what the eager steps return (the state arena advances in place)."""
+    m, meta, a = _model(name, streaming=True, dtype=dtype)
+    x = torch.from_numpy(golden_input(a)).cuda().to(dtype)
+    n = int(a["chunk"].item())
+    chunks = [x[..., c * n:(c + 1) * n].contiguous() for c in range(x.shape[-1] // n)]
+    m.alloc_streams(64, n)
+    eager = [m(c).clone() for c in chunks]
+    m.reset_streams()
+    xs = torch.zeros_like(chunks[0])
+    m(xs)                                            # warm-up outside the capture (function attributes, tensor maps)
+    m.reset_streams()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        ys = m(xs)
+    m.reset_streams()                                # capture does not execute; start from zero state anyway
+    for c, ye in zip(chunks, eager):
+        xs.copy_(c)
+        g.replay()
+        assert torch.equal(ys, ye)
+    torch.cuda.synchronize()
