@@ -658,7 +658,7 @@ def test_per_stream_conditioning_and_f0_channel_vs_oracle(dtype, streaming):
     assert m.spec.f0_channels == 1
     m.load_state_dict(sd)
     o = OracleRAVE(dict(meta["cfg"], dec_latent_size=321), sd, streaming=streaming)
-    B, n_chunk, chunks = 3, 2048, 3 if streaming else 1
+    B, n_chunk, chunks = 3, 2048, 3 if streaming else 2
     T = n_chunk * chunks
     x = torch.from_numpy(recipe_input((B, 1, T), 91))
     spk = torch.from_numpy(recipe_input((B, 256, 1), 92, scale=1.0))
