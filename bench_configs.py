@@ -6,8 +6,9 @@
   C5  v3 (Snake + AdaIN) batched decode-only from latents
 
 One JSON line per leg on stdout.  Synthetic weights (name-keyed recipe), CUDA-event timing.
-C4 / C5 use the CAPACITY=8 fixtures' parameter lists (the only discrete / v3 name lists committed),
-C3 the CAPACITY=64 v2 list.
+Every leg runs at the stated size of its config: C3 v2 causal CAPACITY 64, C4 discrete CAPACITY 96 /
+LATENT_SIZE 128 (discrete.gin:13-19), C5 v3 CAPACITY 64 with 512 streams (parameter lists of the sized
+golden fixtures).
 """
 import argparse
 import json
@@ -157,6 +158,16 @@ def c5(args):
     ms = _time(lambda: m.decode(z), 3, args.steps)
     T = F * m.spec.samples_per_frame
     flops = 2.0 * m.spec.macs_per_frame()["dec"] * B * F
+    m.profile_ops(True)                    # per-op CUDA-event times of one more pass (outside the timed region)
+    m.decode(z)
+    t = m.op_times_ms()
+    m.profile_ops(False)
+    top = sorted(((t[i], m.spec.ops[i].name, m.spec.ops[i].kind) for i in range(len(t)) if t[i] > 0), reverse=True)
+    by_kind = {}
+    for ms_i, _, k in top:
+        by_kind[k] = by_kind.get(k, 0.0) + ms_i
+    print(json.dumps({"c5_ops_ms_top": [(round(a, 3), n) for a, n, _ in top[:14]],
+                      "c5_ms_by_op_kind": {str(k): round(v, 3) for k, v in by_kind.items()}}), file=sys.stderr)
     return [{"config": "C5 v3 (Snake + AdaIN) decode-only, CAPACITY=64, %d streams x %d frames" % (B, F),
              "dtype": "bf16", "ms_per_step": ms, "value": B * T / SR / (ms / 1e3), "unit": "audio-sec/sec (decode)",
              "TFLOPs": flops / ms / 1e9}]

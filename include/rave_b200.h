@@ -162,7 +162,8 @@ int rb_set_noise(rb_handle* h, const float* noise, int64_t numel);
  *   f0:  DEVICE fp32 [B][f0_channels][F], the pitch channels appended behind the speaker channels;
  *        f0_channels must equal decoder latent_size - latent - cond_channels as the config binds it, and B / F
  *        the streams and latent frames of the calls that use it (a streaming caller sets each chunk's f0
- *        before the step).  NULL clears it: nets with pitch channels then feed zeros.
+ *        before the step).  NULL with B = 0 keeps the current ones, NULL with B < 0 clears them: nets with
+ *        pitch channels then feed zeros.
  * Both are copied (enqueued on `stream`), so the caller's buffers are free after the call returns to the stream. */
 int rb_set_conditioning(rb_handle* h, const float* spk, int spk_rows, const float* f0, int B, int f0_channels,
                         int F, void* stream);

@@ -680,7 +680,7 @@ int rb_set_conditioning(rb_handle* h, const float* spk, int spk_rows, const floa
     }
     RB_CUDA(cudaMemcpyAsync(h->f0, f0, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
     h->f0_B = B; h->f0_C = f0_channels; h->f0_F = F;
-  } else {
+  } else if (B < 0) {
     h->f0_B = h->f0_C = h->f0_F = 0;
   }
   return RB_OK;

@@ -41,11 +41,12 @@ namespace {
 
 constexpr int MAX_SA = 12;       // A stages: enough bytes in flight per SM to cover HBM latency
 constexpr int MAX_SD = 4;        // accumulator / h stages
+constexpr int MAX_SW = 8;        // streamed weight ring
 enum { BAR_A_FULL = 0, BAR_A_EMPTY = MAX_SA, BAR_RAW_FULL = 2 * MAX_SA, BAR_W_FULL = 3 * MAX_SA,
-       BAR_W_EMPTY = BAR_W_FULL + 4, BAR_D_FULL = BAR_W_EMPTY + 4, BAR_D_EMPTY = BAR_D_FULL + MAX_SD,
+       BAR_W_EMPTY = BAR_W_FULL + MAX_SW, BAR_D_FULL = BAR_W_EMPTY + MAX_SW, BAR_D_EMPTY = BAR_D_FULL + MAX_SD,
        BAR_H_FULL = BAR_D_EMPTY + MAX_SD, BAR_H_EMPTY = BAR_H_FULL + MAX_SD, BAR_D2_FULL = BAR_H_EMPTY + MAX_SD,
        BAR_D2_EMPTY = BAR_D2_FULL + MAX_SD, BAR_COUNT = BAR_D2_EMPTY + MAX_SD };
-static_assert(BAR_COUNT * 8 + 8 <= 640, "barriers + TMEM slot must fit below off_bias");
+static_assert(BAR_COUNT * 8 + 8 <= 640, "barriers + TMEM slot must fit below the tap masks (smem + 640)");
 constexpr int N_EPI = 256;       // epilogue threads
 constexpr int N_LOAD = 128;      // loader threads
 constexpr int W_LOAD0 = 12;      // activation-pass warps 12-15 (un-activated inputs only)
@@ -299,7 +300,7 @@ __device__ __forceinline__ int goff32(const TcView& v, int g) {
 // The common case of drain() below, with the address arithmetic hoisted out of the chunk loop:
 // NT a multiple of 32, channel groups of a chunk sA apart in y (and in the residual), no waveform
 // head, no sign mask.  RES: 0 none, 1 global (L2-prefetched), 2 the A tile in smem (fused unit).
-template <int RES>
+template <int RES, bool SPIN = false>
 __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                            const float* bs, const Work& wk, int rit, int part, int nparts, int ch0,
                                            int MTn, int NT, const uint8_t* res_s, uint32_t tr) {
@@ -336,7 +337,7 @@ __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full,
       }
   }
   if (RES == 1 && mt < MTn) load_rr(mt, c0);
-  mbar_wait(bar_full, parity);
+  mbar_wait_t<SPIN>(bar_full, parity);
   tc_fence_after();
   TRACE(tr, 12);
   while (mt < MTn) {
@@ -628,6 +629,115 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
   tc_fence_before();
 }
 
+// Two 16-column accumulator pieces + bias; both TMEM loads are in flight before the one wait.
+__device__ __forceinline__ void load_acc2x16(uint32_t ta, uint32_t tb, const float* ba, const float* bb, float* v) {
+  uint32_t r[32];
+  tmem_ld16(ta, r);
+  tmem_ld16(tb, r + 16);
+  tmem_ld_wait();
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const float* bp = h ? bb : ba;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const float4 b4 = *reinterpret_cast<const float4*>(bp + g * 4);
+      const int e = h * 16 + g * 4;
+      v[e + 0] = __uint_as_float(r[e + 0]); v[e + 1] = __uint_as_float(r[e + 1]);
+      v[e + 2] = __uint_as_float(r[e + 2]); v[e + 3] = __uint_as_float(r[e + 3]);
+      add2(v[e + 0], v[e + 1], b4.x, b4.y);
+      add2(v[e + 2], v[e + 3], b4.z, b4.w);
+    }
+  }
+}
+
+// Layers whose output rows interleave in memory -- row-batched narrow layers, transposed-conv phases, the
+// audio rows of the synthesis bank, the waveform head (TcParams::pair_mode).  drain() / drain_fast() give
+// every lane one 16-byte unit per store and the lanes of a warp sit 2, 4 or 8 units apart: each instruction
+// fills half of every 32-byte sector it touches, and since the L1 -> crossbar path moves sectors the layer
+// pays for twice its output (ncu on the first conv: l1tex__m_l1tex2xbar_write_bytes 2.15 GB for 1.07 GB of
+// output, request cycles 78 % busy, DRAM 39 %).  Here a lane gathers the two pieces that are neighbours in
+// memory -- phase 2i and 2i+1 of one channel group, or two consecutive groups of an audio row -- and writes
+// them with one 32-byte store.  Single n-tile, no residual.
+template <bool SPIN>
+__device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
+                                           const float* bs, const Work& wk, int rit, int part, int nparts, int MTn,
+                                           int NT) {
+  const int row = wk.t0 + rit;
+  uint4* const ybase = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p));
+  const uint32_t yoff = (uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT);
+  const bool oact = p.out_act != 0;
+  mbar_wait_t<SPIN>(bar_full, parity);
+  tc_fence_after();
+  if (p.pair_mode == 3) {
+    // waveform head (blocks.py:700-707) with two real rows per view row: columns [32 s, 32 s + 16) wave and
+    // [32 s + 16, 32 s + 32) amplitude of real row 2 t + s.  Part g < 2 takes channel group g of both rows:
+    // tanh(wave * sigmoid(amp)), reverse_half (pqmf.py:13-17: odd bands of even rows, i.e. s = 0), 32 bytes out.
+    // (tcgen05.ld is .sync.aligned: every lane of the warp executes it, rows past the end only skip the store)
+    if (part < 2) {
+      uint32_t r[32];
+      const uint32_t t0 = tbase + (uint32_t)(8 * part);
+      tmem_ld8(t0, r);
+      tmem_ld8(t0 + 16u, r + 8);
+      tmem_ld8(t0 + 32u, r + 16);
+      tmem_ld8(t0 + 48u, r + 24);
+      tmem_ld_wait();
+      float o[16];
+#pragma unroll
+      for (int sub = 0; sub < 2; ++sub) {
+        const float* bw = bs + 32 * sub + 8 * part;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float wv = __uint_as_float(r[16 * sub + e]) + bw[e];
+          const float am = __uint_as_float(r[16 * sub + 8 + e]) + bw[16 + e];
+          const float g = __fdividef(1.f, 1.f + __expf(-am));
+          const float x = wv * g;
+          const float th = 1.f - __fdividef(2.f, 1.f + __expf(2.f * x));
+          o[8 * sub + e] = ((e & 1) && sub == 0) ? -th : th;
+        }
+      }
+      if (row < p.y.n) st_global_256(ybase + (yoff + (uint32_t)(part * p.y.sA)), pack8(o), pack8(o + 8));
+    }
+  } else if (p.pair_mode == 2) {
+    // consecutive channel groups are consecutive units (audio rows): 32 columns = 64 contiguous bytes
+    for (int mt = 0; mt < MTn; ++mt) {
+      const bool valid = row + mt * 128 < p.y.n;
+      for (int c0 = part * 32; c0 < NT; c0 += nparts * 32) {
+        float v[32];
+        load_acc<32>(tbase + (uint32_t)(mt * NT + c0), bs + c0, v);
+        if (oact) leaky_n<32>(v);
+        uint4* yp = ybase + (yoff + (uint32_t)(mt * 128 * p.y.sT + (c0 >> 3)));
+        if (valid) {
+          st_global_256(yp, pack8(v), pack8(v + 8));
+          st_global_256(yp + 2, pack8(v + 16), pack8(v + 24));
+        }
+      }
+    }
+  } else {
+    // phases: view channel n = ph * cpo + c; unit(group g, phase ph) = g * sA + ph
+    const int cpo = p.pair_dcol, kper = cpo >> 4;
+    const int units = (NT / (2 * cpo)) * kper;
+    for (int mt = 0; mt < MTn; ++mt) {
+      const bool valid = row + mt * 128 < p.y.n;
+      int pp = part / kper, k = part - pp * kper;             // unit index = part, part + nparts, ...
+      for (int u = part; u < units; u += nparts) {
+        const int cA = 2 * pp * cpo + 16 * k;
+        float v[32];
+        load_acc2x16(tbase + (uint32_t)(mt * NT + cA), tbase + (uint32_t)(mt * NT + cA + cpo), bs + cA,
+                     bs + cA + cpo, v);
+        if (oact) leaky_n<32>(v);
+        uint4* yp = ybase + (yoff + (uint32_t)(mt * 128 * p.y.sT + 2 * k * p.y.sA + 2 * pp));
+        if (valid) {
+          st_global_256(yp, pack8(v), pack8(v + 16));
+          st_global_256(yp + p.y.sA, pack8(v + 8), pack8(v + 24));
+        }
+        k += nparts;
+        while (k >= kper) { k -= kper; ++pp; }
+      }
+    }
+  }
+  tc_fence_before();
+}
+
 // Fused E1 chunk: h = act2(D1 + bias) as bf16 into the h tile (core-matrix layout, 2048 B per
 // channel group).
 template <int ACT2, int NC>
@@ -659,10 +769,17 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
 // units: 5 warps per scheduler, 1.1 eligible, 9 cycles per issued instruction -- the serial
 // wait / tcgen05.ld / math / store chain of an E1 or E2 chunk is latency-bound, and the two sets
 // were busy all the time.  A third set (28 warps, 72 registers) puts a third tile in flight.
-template <int PRE, int ACT2, bool FUSED, int DR, bool TR, int NS>
+// CG2: the two CTAs of a cluster pair run ONE tcgen05.mma.cta_group::2 stream (M = 256: each CTA's own 128-row
+// tile, N_TILE = 256 with each CTA holding 128 rows of every weight block).  Per SM and MMA the tensor core then
+// reads 4 KB of A + 4 KB of B from shared memory instead of 4 + 8, and only half of every weight block lands in
+// each SM: the streamed wide layers were bound by the 128 B/clk shared-memory port (profiles/r01_ubench.txt), not
+// by the tensor pipe.  The leader (cluster rank 0) issues; the peer's MMA warp relays its barriers (below).
+// PTX wants one cta_group for every tcgen05 instruction of a kernel, hence a template parameter.
+template <int PRE, int ACT2, bool FUSED, int DR, bool TR, int NS, bool CG2>
 __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
     tc_conv_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcTmap tmx) {
   static_assert(NS == 2 || (NS == 3 && FUSED && PRE == RB_ACT_NONE), "three sets: fused units without activation pass");
+  static_assert(!CG2 || (!FUSED && PRE == RB_ACT_NONE && NS == 2), "cta_group::2: plain streamed layers");
   constexpr int W_MMA = NS == 3 ? 24 : 16, W_WPROD = W_MMA + 1, W_APROD = W_MMA + 2, W_MMA2 = W_MMA + 3;
   constexpr int N_THREADS = NS == 3 ? 896 : TC_THREADS;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -697,22 +814,24 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   constexpr int OUT_PARTS = (W_OUT_END - W_OUT0) / 4;
   constexpr int E1_PARTS = E1_WARPS / 4;
 
+  // cta_group::2: the leader's FULL / D_EMPTY barriers also count one relayed arrival from the peer
+  const uint32_t cg2_lead = (CG2 && cluster_ctarank() == 0) ? 1u : 0u;
   if (tid == 0) {
     for (int i = 0; i < MAX_SA; ++i) {
-      mbar_init(BAR(BAR_A_FULL + i), PRE == RB_ACT_NONE ? 1 : N_LOAD / 32);
+      mbar_init(BAR(BAR_A_FULL + i), (PRE == RB_ACT_NONE ? 1 : N_LOAD / 32) + cg2_lead);
       mbar_init(BAR(BAR_A_EMPTY + i), 1 + (p.res_smem ? W_OUT_END - W_OUT0 : 0));
       mbar_init(BAR(BAR_RAW_FULL + i), 1);
     }
-    for (int i = 0; i < 4; ++i) {
-      mbar_init(BAR(BAR_W_FULL + i), 1);
-      mbar_init(BAR(BAR_W_EMPTY + i), 1 + p.pair);        // pair: released by both CTAs' MMAs
+    for (int i = 0; i < MAX_SW; ++i) {
+      mbar_init(BAR(BAR_W_FULL + i), 1 + cg2_lead);
+      mbar_init(BAR(BAR_W_EMPTY + i), CG2 ? 1 : 1 + p.pair);   // multicast pair: released by both CTAs' MMAs
     }
     for (int i = 0; i < MAX_SD; ++i) {
       mbar_init(BAR(BAR_D_FULL + i), 1);
       // one arrival per WARP (lane 0 after __syncwarp): 32 per-thread arrivals on one mbarrier
       // serialise in the shared-memory atomic path -- at 768 arrivals per tile they, not the
       // math, set the tile rate of the narrow fused units
-      mbar_init(BAR(BAR_D_EMPTY + i), FUSED ? E1_WARPS : N_OUT / 32);
+      mbar_init(BAR(BAR_D_EMPTY + i), (FUSED ? E1_WARPS : N_OUT / 32) + cg2_lead);
       mbar_init(BAR(BAR_H_FULL + i), E1_WARPS);
       mbar_init(BAR(BAR_H_EMPTY + i), 1);
       mbar_init(BAR(BAR_D2_FULL + i), 1);
@@ -729,8 +848,13 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
     }
   }
   if (warp == W_MMA) {
-    tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
-    tmem_relinquish();
+    if (CG2) {
+      tmem_alloc2(smem_u32(tmem_slot), p.tmem_cols);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -742,7 +866,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   if (warp != W_WPROD) asm volatile("griddepcontrol.wait;" ::: "memory");
 
   const uint32_t lbo_a = (uint32_t)p.R_ALLOC * 16u;
-  const uint32_t lbo_w = (uint32_t)p.N_TILE * 16u;
+  const uint32_t lbo_w = (uint32_t)(CG2 ? p.N_TILE / 2 : p.N_TILE) * 16u;
   const int ksteps = p.KC >> 4;
   const int C2 = p.N_TILE;                        // fused: channels of the unit
   const uint32_t d_stage_cols = FUSED ? 2u * C2 : (uint32_t)(p.MT * p.N_TILE);
@@ -759,7 +883,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           if (mask_s[wk.nt * p.n_kchunks + kc] == 0) continue;
           const uint32_t sa = ra.idx;
-          mbar_wait(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1);
+          mbar_wait_t<CG2>(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1);
           TRACE(ti, 10);
           issue_a_tma(p, &tmx, wk.b, wk.t0 - p.off, kc, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes),
                       BAR((PRE == RB_ACT_NONE ? BAR_A_FULL : BAR_RAW_FULL) + sa), lane);
@@ -801,9 +925,15 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
             const int nb = __popcll(mask);
             for (int j = 0; j < nb; ++j) {
               const uint32_t sw = rw.idx;
-              mbar_wait(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
+              mbar_wait_t<CG2>(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
               mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
-              if (p.pair) {
+              if (CG2) {
+                // this CTA's 128 rows of the block (tc_engine.cu packs the two halves one after the other)
+                bulk_g2s(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes),
+                         reinterpret_cast<const uint8_t*>(p.w) +
+                             ((size_t)gblk * 2 + ((uint32_t)blockIdx.x & 1u)) * p.w_blk_bytes,
+                         p.w_blk_bytes, BAR(BAR_W_FULL + sw));
+              } else if (p.pair) {
                 // this CTA's half of the block, written into both CTAs' rings (the peer sends the other half)
                 const uint32_t half = p.w_blk_bytes >> 1, o = ((uint32_t)blockIdx.x & 1u) * half;
                 bulk_g2s_mc2(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes) + o,
@@ -990,8 +1120,90 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           if (mrow[kc] != 0) ra.next(p.SA);
         ++t1;
       };
+      // ---- cta_group::2 (CG2): leader issues for the pair, the peer relays
+      // GEMM1 of one work item of the PAIR (streamed weights, MT = 1): the waits see the leader's own producers
+      // and, through the relay, the peer's; every commit arrives in both CTAs.
+      auto gemm1_cg2 = [&](const Work& wk) {
+        const uint32_t idesc2 = make_idesc_bf16(256, p.N_TILE);
+        const uint32_t sd = rd1.idx;
+        mbar_wait_cl(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1);
+        rd1.next(p.SD);
+        tc_fence_after();
+        const uint32_t dcol = tmem + sd * d_stage_cols;
+        uint32_t acc = 0;
+        const uint64_t* mrow = mask_s + wk.nt * p.n_kchunks;
+        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+          uint64_t mask = mrow[kc];
+          if (mask == 0) continue;
+          const uint32_t sa = ra.idx;
+          mbar_wait_cl(BAR(BAR_A_FULL + sa), ra.ph);
+          ra.next(p.SA);
+          tc_fence_after();
+          const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
+          while (mask) {
+            const int j = __ffsll((long long)mask) - 1;
+            mask &= mask - 1;
+            const uint32_t sw = rw.idx;
+            mbar_wait_cl(BAR(BAR_W_FULL + sw), rw.ph);
+            rw.next(p.SW);
+            tc_fence_after();
+            const uint32_t blo = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+            uint32_t alo = alo0 + (uint32_t)j * tap_add;
+            for (int mt = 0; mt < p.MT; ++mt) {
+              uint32_t al = alo, bl = blo;
+              const uint32_t dc = dcol + (uint32_t)(mt * p.N_TILE);
+              if (leader) mma2_bf16_lohi(dc, al, bl, dhi, idesc2, acc);
+#pragma unroll 4
+              for (int kk = 1; kk < ksteps; ++kk) {
+                al += a_kadd;
+                bl += w_kadd;
+                if (leader) mma2_bf16_lohi(dc, al, bl, dhi, idesc2, 1u);
+              }
+              alo += 128u;                                        // next 128-row sub-tile
+            }
+            acc = 1;
+            if (leader) mma2_commit(BAR(BAR_W_EMPTY + sw));
+          }
+          if (leader) mma2_commit(BAR(BAR_A_EMPTY + sa));
+        }
+        if (leader) mma2_commit(BAR(BAR_D_FULL + sd));
+      };
+      // The peer's MMA warp: follows the same sequence of stages and, as each of ITS stages becomes ready
+      // (A tile landed, weight half landed, accumulator drained), arrives on the leader's barrier of the same
+      // name.  The first use of an accumulator stage needs no hand-over (the leader's wait passes on the fresh
+      // barrier, and an arrival now would be counted for the NEXT drain).
+      uint32_t n_item = 0;
+      auto relay_cg2 = [&](const Work& wk) {
+        const uint32_t sd = rd1.idx;
+        if (n_item >= (uint32_t)p.SD) {
+          mbar_wait_spin(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1);
+          if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_D_EMPTY + sd), 0));
+        }
+        ++n_item;
+        rd1.next(p.SD);
+        const uint64_t* mrow = mask_s + wk.nt * p.n_kchunks;
+        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+          uint64_t mask = mrow[kc];
+          if (mask == 0) continue;
+          const uint32_t sa = ra.idx;
+          mbar_wait_spin(BAR(BAR_A_FULL + sa), ra.ph);
+          ra.next(p.SA);
+          if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_A_FULL + sa), 0));
+          for (int nb = __popcll(mask); nb > 0; --nb) {
+            const uint32_t sw = rw.idx;
+            mbar_wait_spin(BAR(BAR_W_FULL + sw), rw.ph);
+            rw.next(p.SW);
+            if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_W_FULL + sw), 0));
+          }
+        }
+      };
       WorkIter wi;
-      if (warp == W_MMA2) {
+      if (CG2) {
+        if (warp == W_MMA) {
+          if (cg2_lead) for (wi.init(p); wi.left > 0; wi.next(p)) gemm1_cg2(wi.work(p));
+          else for (wi.init(p); wi.left > 0; wi.next(p)) relay_cg2(wi.work(p));
+        }
+      } else if (warp == W_MMA2) {
         if (FUSED)
           for (wi.init(p); wi.left > 0; wi.next(p)) gemm2();
       } else if (!p.dual_g1) {
@@ -1019,15 +1231,17 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         if (warp == 0) TRACE(ti, 8);
         const uint32_t trc = (warp == 0 ? ti : 0xffffffffu) | tmask;
         const uint32_t tb = tmem + lane_base + sd * d_stage_cols;
-        if (DR == 0)
+        if (DR == 3)
+          drain_pair<CG2>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, p.MT, p.N_TILE);
+        else if (DR == 0)
           drain(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
                 p.N_TILE, nullptr, trc);
         else if (p.res.p)
-          drain_fast<1>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
-                        p.N_TILE, nullptr, trc);
+          drain_fast<1, CG2>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
+                             p.N_TILE, nullptr, trc);
         else
-          drain_fast<0>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
-                        p.N_TILE, nullptr, trc);
+          drain_fast<0, CG2>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
+                             p.N_TILE, nullptr, trc);
         __syncwarp();
         if (lane == 0) mbar_arrive(BAR(BAR_D_EMPTY + sd));
         if (warp == 0) TRACE(ti, 9);
@@ -1136,15 +1350,16 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   if (p.pair) cluster_sync();                     // no CTA leaves while its peer may still signal it
   if (warp == W_MMA) {
     tc_fence_after();
-    tmem_dealloc(tmem, p.tmem_cols);
+    if (CG2) tmem_dealloc2(tmem, p.tmem_cols);
+    else tmem_dealloc(tmem, p.tmem_cols);
   }
 }
 
-template <int PRE, int ACT2, bool FUSED, int DR, bool TR = false, int NS = 2>
+template <int PRE, int ACT2, bool FUSED, int DR, bool TR = false, int NS = 2, bool CG2 = false>
 static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS>,
+    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS, CG2>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
@@ -1163,7 +1378,7 @@ static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStr
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = p.pair ? 2 : 1;
-  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS>, p, tm));
+  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS, CG2>, p, tm));
   return RB_OK;
 }
 
@@ -1242,7 +1457,14 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
     else if (p.res_smem) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 2, true>(p, tm, grid, s);
     else rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 1, true>(p, tm, grid, s);
   } else if (!p.fused) {
-    if (p.pre_act == RB_ACT_NONE) {
+    if (p.cg2) {
+      RB_CHECK(p.pair && p.pre_act == RB_ACT_NONE && !p.w_resident && p.N_TILE == 256 &&
+                   (fast || p.pair_mode), RB_ERR_INVALID, "cta_group::2 layer outside its envelope");
+      rc = p.pair_mode ? launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 3, false, 2, true>(p, tm, grid, s)
+                       : launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 1, false, 2, true>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_NONE && p.pair_mode) {
+      rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 3>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_NONE) {
       rc = fast ? launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 1>(p, tm, grid, s)
                 : launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 0>(p, tm, grid, s);
     } else if (p.pre_act == RB_ACT_LEAKY) {

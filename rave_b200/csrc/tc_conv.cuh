@@ -64,6 +64,8 @@ struct TcParams {
   int R, R_ALLOC;           // A rows per stage (MT*128 + max shift), allocated (odd)
   int w_resident;           // all blocks live in smem for the whole kernel
   int pair;                 // 1: clusters of two CTAs share each streamed weight block (half each, multicast)
+  int cg2;                  // pair + 1: the pair runs tcgen05.mma.cta_group::2 (M = 256; w holds the N-split block layout,
+                            // w_blk_bytes = one CTA's half block)
   int dual_g1;              // resident + narrow: two warps issue GEMM1 of alternate work items
   // A tile TMA boxes (tensor map over the input view, see launch_tc_conv): a chunk of KC/8
   // channel groups x R_ALLOC rows is fetched as boxes of a_gb groups x a_box_rows rows
@@ -76,6 +78,11 @@ struct TcParams {
   // > 0: every 32-column chunk is [16 wave | 16 amplitude] of one real row (head = chunks per view
   // row); the epilogue stores tanh(wave * sigmoid(amp)), reverse_half applied, as 16 channels
   int head;
+  // Sector-complete stores (drain_pair): 0 off; 1 the output view has an even number of phases one unit apart
+  // (row batching, transposed-conv phases): the pieces of phase 2i and 2i+1 (pair_dcol columns apart in the
+  // accumulator) are neighbours in memory and leave as one 32-byte store; 2 consecutive channel groups are
+  // neighbours (audio rows); 3 waveform head with two real rows per view row
+  int pair_mode, pair_dcol;
   int tiles_per_stream, n_work;
   // fused DilatedUnit (blocks.py:84-113 + Residual :32-46): second GEMM k=1 on act(D1 + bias)
   int fused;

@@ -9,6 +9,7 @@
 // row-shift GEMM (tc_conv.cuh).  LeakyReLU nets store tensors already activated (Plan::sact).
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -34,6 +35,8 @@ struct Layer {
   int total_blocks = 0;
   uint32_t blk_bytes = 0;
   __nv_bfloat16* w = nullptr;     // device, packed blocks
+  __nv_bfloat16* w2 = nullptr;    // the same blocks split by output rows for cta_group::2 pairs (N_TILE = 256:
+                                  // [half][KC/8][128][8] -- each CTA of a pair loads and holds one half), or nullptr
   uint64_t* masks = nullptr;      // device [n_ntiles][n_kchunks]
   float* bias = nullptr;          // device [N_total] (nullptr: none)
   float* alpha = nullptr;         // device [cin_v]   (Snake pre-activation)
@@ -241,7 +244,7 @@ static int largest_div16(int v, int cap) {
 }
 
 static void free_layer(Layer& L) {
-  cudaFree(L.w); cudaFree(L.masks); cudaFree(L.bias); cudaFree(L.alpha); cudaFree(L.bias2); cudaFree(L.alpha2);
+  cudaFree(L.w); cudaFree(L.w2); cudaFree(L.masks); cudaFree(L.bias); cudaFree(L.alpha); cudaFree(L.bias2); cudaFree(L.alpha2);
   L = Layer();
 }
 
@@ -314,6 +317,17 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
   }
   int rc = dev_upload(blocks, &L.w);
   if (rc) return rc;
+  if (!extra && L.N_TILE == 256) {
+    // N-split twin for cta_group::2: block [n][c] -> half n / 128, then the same core-matrix order over 128 rows
+    std::vector<__nv_bfloat16> b2(blocks.size());
+    const size_t be = (size_t)L.N_TILE * L.KC, he = be / 2;
+    for (int b = 0; b < nblk; ++b)
+      for (int n = 0; n < L.N_TILE; ++n)
+        for (int c = 0; c < L.KC; ++c)
+          b2[b * be + (size_t)(n >> 7) * he + (size_t)(c >> 3) * (128 * 8) + (size_t)(n & 127) * 8 + (c & 7)] =
+              blocks[b * be + (size_t)(c >> 3) * (L.N_TILE * 8) + (size_t)n * 8 + (c & 7)];
+    if ((rc = dev_upload(b2, &L.w2))) return rc;
+  }
   if ((rc = dev_upload(masks, &L.masks))) return rc;
   if (!v.bias.empty() && (rc = dev_upload(v.bias, &L.bias))) return rc;
   if (!v.alpha.empty() && (rc = dev_upload(v.alpha, &L.alpha))) return rc;
@@ -444,7 +458,21 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
               !getenv("RB_TC_NOPAIR")) ? 1 : 0;
     if (const char* e = getenv("RB_TC_PAIRALL"))           // experiments only
       p.pair = (atoi(e) && !resident && !L.fused && p.pre_act == RB_ACT_NONE && p.y.n >= 256) ? 1 : 0;
-    if (p.pair) p.MT = (2 * L.N_TILE <= 256 && p.y.n >= 512) ? 2 : 1;
+    // cta_group::2 (tc_conv.cu, CG2): every streamed plain layer with 256-wide output tiles whose pair gets two
+    // real row tiles.  One 128-row tile per CTA and accumulator stage (two stages of 256 columns: the MMAs of the
+    // next item run under the epilogue), each CTA loads half of every weight block.
+    p.cg2 = (!resident && !L.fused && L.w2 && L.N_TILE == 256 && p.pre_act == RB_ACT_NONE && p.y.n >= 256 &&
+             sr_rows == 0 && !g_trace && !getenv("RB_TC_NOCG2")) ? 1 : 0;
+    if (p.cg2) {
+      p.pair = 1;
+      // two sub-tiles per weight block (one accumulator stage of 512 columns) where a tile is long enough
+      // (>= 8 K chunks x taps) that the un-overlapped epilogue is the smaller cost than streaming every weight
+      // block twice as often; else one sub-tile and two accumulator stages (measured per layer,
+      // profiles/r02_cg2_cycles.txt)
+      p.MT = (p.y.n >= 512 && L.n_taps >= 2 && L.n_kchunks >= 8) ? 2 : 1;
+      if (const char* e = getenv("RB_TC_CG2_MT")) p.MT = (atoi(e) == 2 && p.y.n >= 512) ? 2 : 1;   // experiments only
+    }
+    if (p.pair && !p.cg2) p.MT = (2 * L.N_TILE <= 256 && p.y.n >= 512) ? 2 : 1;
     p.R = p.MT * 128 + halo;
     {
       // TMA boxes of the A tile: whole chunk in one box when the rows fit a box (<= 256), else
@@ -474,6 +502,10 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     // W ring depth: a single-tap layer consumes one A chunk per W block, so it needs A stages in
     // flight (HBM latency) more than W stages (L2 latency); multi-tap layers the other way round
     p.SW = resident ? 0 : (L.n_taps == 1 ? 2 : 4);
+    const uint32_t blk_bytes = p.cg2 ? L.blk_bytes / 2 : L.blk_bytes;      // one ring stage
+    if (p.cg2) { p.SW = 4; p.w = L.w2; p.w_blk_bytes = blk_bytes; }
+    if (!resident && sr_rows == 0)
+      if (const char* e = getenv("RB_TC_SW")) p.SW = std::min(8, std::max(2, atoi(e)));   // experiments only
     if (!resident && sr_rows > 0) {
       // stream-as-row: a CTA's work is one short pass over its slice of the weights, bound by the L2
       // round trip of each block -- keep as many blocks in flight as fit beside three A stages
@@ -482,8 +514,8 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       p.SW = sw;
       while (p.SW > 2 && fixed + p.SW * L.blk_bytes + 3 * p.a_stage_bytes > budget) --p.SW;
     }
-    uint32_t w_bytes = resident ? align_up(w_total, 128) : p.SW * L.blk_bytes;
-    if (!resident && fixed + w_bytes + 2 * p.a_stage_bytes > budget) { p.SW = 2; w_bytes = p.SW * L.blk_bytes; }
+    uint32_t w_bytes = resident ? align_up(w_total, 128) : p.SW * blk_bytes;
+    if (!resident && fixed + w_bytes + 2 * p.a_stage_bytes > budget) { p.SW = 2; w_bytes = p.SW * blk_bytes; }
     if (L.fused) {
       // fewer h stages when smem is tight (wide units): keep at least 3 A stages if possible
       while (p.SH > 1 && fixed + w_bytes + p.SH * p.h_stage_bytes + 3 * p.a_stage_bytes > budget) --p.SH;
@@ -511,9 +543,28 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   uint32_t cols = 32;
   while (cols < (uint32_t)(p.SD * acc_cols)) cols <<= 1;
   p.tmem_cols = cols;
+  // sector-complete stores (tc_conv.cu drain_pair): rows that interleave in memory leave in 32-byte pieces
+  p.pair_mode = 0;
+  if (!L.fused && !res && sr_rows == 0 && p.pre_act == RB_ACT_NONE && L.n_ntiles == 1 && !L.out_mask &&
+      (p.y.sT & 1) == 0 && (p.y.sb & 1) == 0 && ((p.y.hist * p.y.sT) & 1) == 0 &&
+      (reinterpret_cast<uintptr_t>(p.y.p) & 31) == 0 && !getenv("RB_TC_NOPAIRST")) {
+    if (L.head) {
+      if (L.head == 2 && L.N_total == 64 && p.MT == 1 && (p.y.sA & 1) == 0) p.pair_mode = 3;
+    } else if (dst.cp == 1) {
+      if ((L.N_total & 31) == 0) p.pair_mode = 2;
+    } else if (L.fout >= 2 && (L.fout & 1) == 0 && p.y.sB == 1 && (p.y.sA & 1) == 0) {
+      p.pair_mode = 1;
+      p.pair_dcol = L.N_total / L.fout;
+    }
+  }
   p.tiles_per_stream = (p.y.n + p.MT * 128 - 1) / (p.MT * 128);
   if (p.pair) p.tiles_per_stream = (p.tiles_per_stream + 1) / 2;   // work slots: two row tiles each
   p.n_work = L.n_ntiles * B * p.tiles_per_stream;
+  if (getenv("RB_TC_PLAN_DEBUG"))
+    fprintf(stderr, "tc layer: cin_v %d N %d x %d taps %d dil %d fin %d fout %d KC %d | resident %d fused %d pair %d cg2 %d MT %d "
+            "SA %d SW %d SD %d pair_mode %d rows %d work %d smem %u\n", L.cin_v, L.N_TILE, L.n_ntiles, L.n_taps, L.dil, L.fin,
+            L.fout, L.KC, p.w_resident, p.fused, p.pair, p.cg2, p.MT, p.SA, p.SW, p.SD, p.pair_mode, p.y.n, p.n_work,
+            p.smem_bytes);
   return launch_tc_conv(p, s);
 }
 

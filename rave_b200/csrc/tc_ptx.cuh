@@ -93,6 +93,54 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 #endif
 }
 
+// ---- cluster pair (cta_group::2): barriers of the peer CTA
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cluster address of this CTA's shared-memory address `local` in CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// Waits of the cta_group::2 kernels SPIN (test_wait).  The suspending try_wait of mbar_wait_slow is woken by
+// arrivals from the CTA's own threads, TMA and tcgen05.commit, but a waiter whose barrier is completed from the
+// peer CTA (multicast commit, mbarrier.arrive.shared::cluster) slept on towards its time limit: the first
+// cta_group::2 build ran the weight ring at ~1900 cycles per block -- half the speed of the one-CTA kernel -- with
+// 486 NANOSLEEP.SYNCS per peer CTA and launch (ncu source view), one per remotely released stage.
+__device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
+  uint32_t n = 0;
+  while (!mbar_test_wait(bar, parity)) {
+    if (++n > (1u << 27)) __trap();
+  }
+}
+// the same on a barrier that the peer arrives on with mbarrier.arrive.release.cluster: cluster-scope acquire
+__device__ __forceinline__ void mbar_wait_cl(uint32_t bar, uint32_t parity) {
+  uint32_t n = 0, ok = 0;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (++n > (1u << 27)) __trap();
+  } while (!ok);
+}
+template <bool SPIN>
+__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity) {
+  if (SPIN) mbar_wait_spin(bar, parity);
+  else mbar_wait(bar, parity);
+}
+
 // ------------------------------------------------------------------- async proxy / bulk copy
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -174,6 +222,18 @@ __device__ __forceinline__ void tmem_relinquish() {
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
+// cta_group::2: both CTAs of a pair execute these (same warp index), TMEM is allocated in both
+__device__ __forceinline__ void tmem_alloc2(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem),
+               "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish2() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -225,6 +285,30 @@ __device__ __forceinline__ void mma_bf16_lohi(uint32_t d_tmem, uint32_t a_lo, ui
       "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// cta_group::2: ONE thread of the pair's leader CTA issues for both SMs.  M = 256: rows 0-127 of D / A
+// live in the leader's TMEM / shared memory, rows 128-255 in the peer's, at the same addresses; each CTA
+// holds N/2 rows of B at the descriptor's address (tcgen05 reads both halves).
+__device__ __forceinline__ void mma2_bf16_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
+                                               uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b64 da, db;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "mov.b64 da, {%1, %3};\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], da, db, %4, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrives on the mbarrier at this offset in BOTH CTAs once every MMA issued so far has completed
+__device__ __forceinline__ void mma2_commit(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"((unsigned short)3)
+      : "memory");
+}
 __device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo) {
   return ((saddr >> 4) & 0x3FFF) | (((lbo >> 4) & 0x3FFF) << 16);
 }
@@ -263,6 +347,20 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
         "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr)
       : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* r) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+// One 32-byte store (two neighbouring 16-byte units): a whole sector per lane.  A warp whose lanes write 16
+// bytes each at a 32-byte (or wider) stride fills only half of every sector it touches per instruction, and
+// the L1 -> crossbar path moves sectors: twice the requests for the same bytes.
+__device__ __forceinline__ void st_global_256(void* ptr, const uint4& a, const uint4& b) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(ptr), "r"(a.x), "r"(a.y), "r"(a.z),
+               "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");

@@ -202,7 +202,7 @@ class RAVE:
         (each streaming chunk needs its own); None clears them (zeros).  Only nets whose decoder is bound
         wider than latent + speaker take any (`spec.f0_channels`)."""
         if f0 is None:
-            capi.check(self._lib.rb_set_conditioning(self._h, None, 0, None, 0, 0, 0, _stream_ptr()))
+            capi.check(self._lib.rb_set_conditioning(self._h, None, 0, None, -1, 0, 0, _stream_ptr()))
             return
         if not isinstance(f0, torch.Tensor) or not f0.is_cuda:
             raise ValueError("set_f0: f0 must be a CUDA tensor")

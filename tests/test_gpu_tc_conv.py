@@ -160,6 +160,17 @@ ACT_CASES = [
     dict(c_in=256, c_out=512, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=2, n=160, flags=3),
     dict(c_in=512, c_out=512, k=3, stride=1, dil=9, off=9, ileave=1, res=0, B=2, n=700, flags=1),
     dict(c_in=64, c_out=32, k=7, stride=1, dil=1, off=3, ileave=1, res=0, B=2, n=1000, flags=1),
+    # cta_group::2 pairs (streamed weights, 256-wide output tiles, >= 256 rows): odd tile counts, a pair whose
+    # second tile lies beyond the tensor, residual, two n-tiles, strided input view, transposed-conv phases
+    dict(c_in=256, c_out=256, k=3, stride=1, dil=3, off=3, ileave=1, res=0, B=3, n=1000, flags=3),
+    dict(c_in=512, c_out=512, k=1, stride=1, dil=1, off=0, ileave=1, res=1, B=1, n=300, flags=7),
+    dict(c_in=256, c_out=256, k=1, stride=1, dil=1, off=0, ileave=1, res=1, B=5, n=2048, flags=7),
+    dict(c_in=512, c_out=1024, k=4, stride=2, dil=1, off=1, ileave=1, res=0, B=2, n=1024, flags=3),
+    dict(c_in=1024, c_out=1024, k=3, stride=1, dil=1, off=1, ileave=2, res=0, B=2, n=300, flags=3),
+    # sector-complete stores of phase outputs (drain_pair), the second one also as a cta_group::2 pair
+    dict(c_in=128, c_out=256, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=2, n=520, flags=3),
+    dict(c_in=256, c_out=256, k=3, stride=1, dil=1, off=1, ileave=2, res=0, B=3, n=640, flags=3),
+    dict(c_in=6, c_out=64, k=7, stride=1, dil=1, off=3, ileave=1, res=0, B=2, n=4096, flags=2, pre=0),
 ]
 
 
@@ -180,7 +191,7 @@ def test_single_conv_activated_storage(c):
     if c["flags"] & 2:
         ref = F.leaky_relu(ref, 0.2)
     op = dict(c_in=c["c_in"], c_out=c["c_out"], k=c["k"], stride=c["stride"], dilation=c["dil"], off=c["off"],
-              ileave=r, pre_act=1, has_bias=1, res_delay=0)
+              ileave=r, pre_act=c.get("pre", 1), has_bias=1, res_delay=0)
     y, _ = _run([op], [w.numpy()], [b.numpy()], [None], z.numpy(), None if res is None else res.numpy(),
                 flags=c["flags"])
     assert np.isfinite(y).all()
