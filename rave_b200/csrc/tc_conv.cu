@@ -337,7 +337,7 @@ __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full,
       }
   }
   if (RES == 1 && mt < MTn) load_rr(mt, c0);
-  mbar_wait_t<SPIN>(bar_full, parity);
+  mbar_wait_t<SPIN>(bar_full, parity, p.cg2_spin);
   tc_fence_after();
   TRACE(tr, 12);
   while (mt < MTn) {
@@ -666,7 +666,7 @@ __device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full,
   uint4* const ybase = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p));
   const uint32_t yoff = (uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT);
   const bool oact = p.out_act != 0;
-  mbar_wait_t<SPIN>(bar_full, parity);
+  mbar_wait_t<SPIN>(bar_full, parity, p.cg2_spin);
   tc_fence_after();
   if (p.pair_mode == 3) {
     // waveform head (blocks.py:700-707) with two real rows per view row: columns [32 s, 32 s + 16) wave and
@@ -750,8 +750,17 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
 #pragma unroll
     for (int e = 0; e < NC; ++e) v[e] = act_f<ACT2>(v[e], alpha2[e]);
   }
+  if (hdst) {
 #pragma unroll
-  for (int q = 0; q < NC / 8; ++q) *reinterpret_cast<uint4*>(hdst + (size_t)q * 2048) = pack8(v + q * 8);
+    for (int q = 0; q < NC / 8; ++q) *reinterpret_cast<uint4*>(hdst + (size_t)q * 2048) = pack8(v + q * 8);
+  } else {
+    // h stays in tensor memory: the NC fp32 columns just read become NC / 2 columns of packed bf16 pairs at the
+    // same column base -- the A operand of the 1x1 conv's MMAs (K step k = columns [16 k, 16 k + 8))
+    static_assert(NC == 16, "h in TMEM: 16-column pieces");
+    const uint4 lo = pack8(v), hi = pack8(v + 8);
+    const uint32_t r[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    tmem_st8(taddr, r);
+  }
 }
 
 }  // namespace
@@ -831,7 +840,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
       // one arrival per WARP (lane 0 after __syncwarp): 32 per-thread arrivals on one mbarrier
       // serialise in the shared-memory atomic path -- at 768 arrivals per tile they, not the
       // math, set the tile rate of the narrow fused units
-      mbar_init(BAR(BAR_D_EMPTY + i), (FUSED ? E1_WARPS : N_OUT / 32) + cg2_lead);
+      mbar_init(BAR(BAR_D_EMPTY + i), (FUSED ? (p.h_tmem ? 1 : E1_WARPS) : N_OUT / 32) + cg2_lead);
       mbar_init(BAR(BAR_H_FULL + i), E1_WARPS);
       mbar_init(BAR(BAR_H_EMPTY + i), 1);
       mbar_init(BAR(BAR_D2_FULL + i), 1);
@@ -883,7 +892,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           if (mask_s[wk.nt * p.n_kchunks + kc] == 0) continue;
           const uint32_t sa = ra.idx;
-          mbar_wait_t<CG2>(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1);
+          mbar_wait_t<CG2>(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1, p.cg2_spin);
           TRACE(ti, 10);
           issue_a_tma(p, &tmx, wk.b, wk.t0 - p.off, kc, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes),
                       BAR((PRE == RB_ACT_NONE ? BAR_A_FULL : BAR_RAW_FULL) + sa), lane);
@@ -925,7 +934,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
             const int nb = __popcll(mask);
             for (int j = 0; j < nb; ++j) {
               const uint32_t sw = rw.idx;
-              mbar_wait_t<CG2>(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
+              mbar_wait_t<CG2>(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1, p.cg2_spin);
               mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
               if (CG2) {
                 // this CTA's 128 rows of the block (tc_engine.cu packs the two halves one after the other)
@@ -1092,20 +1101,36 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         rh.next(p.SH);
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols + (uint32_t)C2;
-        uint32_t al = (((h0 + sh * p.h_stage_bytes) >> 4) & 0x3FFFu) | h_lbo_bits;
         const int nkc = C2 / p.KC;
         uint32_t accum = 0;
-        for (int kc = 0; kc < nkc; ++kc) {
-          uint32_t bl = (((w0 + (uint32_t)(p.n_blk1 + kc) * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+        if (p.h_tmem) {
+          // A operand from tensor memory: K step k of h sits at columns [16 k, 16 k + 8) of this stage's D1 region
+          uint32_t at = tmem + sd * d_stage_cols;
+          for (int kc = 0; kc < nkc; ++kc) {
+            uint32_t bl = (((w0 + (uint32_t)(p.n_blk1 + kc) * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
 #pragma unroll 4
-          for (int kk = 0; kk < ksteps; ++kk) {
-            MMA(dcol, al, bl, dhi, idesc, accum);
-            accum = 1;
-            al += h_kadd;
-            bl += w_kadd;
+            for (int kk = 0; kk < ksteps; ++kk) {
+              if (leader) mma_bf16_ts(dcol, at, bl, dhi, idesc, accum);
+              accum = 1;
+              at += 16u;
+              bl += w_kadd;
+            }
           }
+          COMMIT(BAR(BAR_D_EMPTY + sd));
+        } else {
+          uint32_t al = (((h0 + sh * p.h_stage_bytes) >> 4) & 0x3FFFu) | h_lbo_bits;
+          for (int kc = 0; kc < nkc; ++kc) {
+            uint32_t bl = (((w0 + (uint32_t)(p.n_blk1 + kc) * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+#pragma unroll 4
+            for (int kk = 0; kk < ksteps; ++kk) {
+              MMA(dcol, al, bl, dhi, idesc, accum);
+              accum = 1;
+              al += h_kadd;
+              bl += w_kadd;
+            }
+          }
+          COMMIT(BAR(BAR_H_EMPTY + sh));
         }
-        COMMIT(BAR(BAR_H_EMPTY + sh));
         COMMIT(BAR(BAR_D2_FULL + sd));
         TRACE(t2, 5);
         ++t2;
@@ -1126,7 +1151,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
       auto gemm1_cg2 = [&](const Work& wk) {
         const uint32_t idesc2 = make_idesc_bf16(256, p.N_TILE);
         const uint32_t sd = rd1.idx;
-        mbar_wait_cl(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1);
+        mbar_wait_t<true>(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1, p.cg2_spin & 2);
         rd1.next(p.SD);
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols;
@@ -1136,7 +1161,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           uint64_t mask = mrow[kc];
           if (mask == 0) continue;
           const uint32_t sa = ra.idx;
-          mbar_wait_cl(BAR(BAR_A_FULL + sa), ra.ph);
+          mbar_wait_t<true>(BAR(BAR_A_FULL + sa), ra.ph, p.cg2_spin & 2);
           ra.next(p.SA);
           tc_fence_after();
           const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
@@ -1144,7 +1169,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
             const int j = __ffsll((long long)mask) - 1;
             mask &= mask - 1;
             const uint32_t sw = rw.idx;
-            mbar_wait_cl(BAR(BAR_W_FULL + sw), rw.ph);
+            mbar_wait_t<true>(BAR(BAR_W_FULL + sw), rw.ph, p.cg2_spin & 2);
             rw.next(p.SW);
             tc_fence_after();
             const uint32_t blo = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
@@ -1176,7 +1201,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
       auto relay_cg2 = [&](const Work& wk) {
         const uint32_t sd = rd1.idx;
         if (n_item >= (uint32_t)p.SD) {
-          mbar_wait_spin(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1);
+          mbar_wait_t<true>(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1, p.cg2_spin);
           if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_D_EMPTY + sd), 0));
         }
         ++n_item;
@@ -1186,12 +1211,12 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           uint64_t mask = mrow[kc];
           if (mask == 0) continue;
           const uint32_t sa = ra.idx;
-          mbar_wait_spin(BAR(BAR_A_FULL + sa), ra.ph);
+          mbar_wait_t<true>(BAR(BAR_A_FULL + sa), ra.ph, p.cg2_spin);
           ra.next(p.SA);
           if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_A_FULL + sa), 0));
           for (int nb = __popcll(mask); nb > 0; --nb) {
             const uint32_t sw = rw.idx;
-            mbar_wait_spin(BAR(BAR_W_FULL + sw), rw.ph);
+            mbar_wait_t<true>(BAR(BAR_W_FULL + sw), rw.ph, p.cg2_spin);
             rw.next(p.SW);
             if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_W_FULL + sw), 0));
           }
@@ -1259,23 +1284,24 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         const uint32_t sd = rd_.idx, sh = rh_.idx;
         mbar_wait(BAR(BAR_D_FULL + sd), rd_.ph);
         if (tr_warp) TRACE(ti, 6);
-        mbar_wait(BAR(BAR_H_EMPTY + sh), rh_.ph ^ 1);
+        if (!p.h_tmem) mbar_wait(BAR(BAR_H_EMPTY + sh), rh_.ph ^ 1);
         tc_fence_after();
-        uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
+        uint8_t* hb = p.h_tmem ? nullptr : h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
         for (int c0 = part * 32; c0 < C2; c0 += E1_PARTS * 32) {
           // rolled 16-column pieces: see drain_smem16 (instruction-cache footprint)
           const int c1 = C2 - c0 >= 32 ? c0 + 32 : c0 + 16;
 #pragma unroll 1
           for (int c = c0; c < c1; c += 16)
             h_chunk<ACT2, 16>(tmem + lane_base + sd * d_stage_cols + (uint32_t)c, bias_s + c, alpha2_s + c,
-                              hb + (size_t)(c >> 3) * 2048);
+                              hb ? hb + (size_t)(c >> 3) * 2048 : nullptr);
         }
-        fence_proxy_async();
+        if (p.h_tmem) tmem_st_wait();
+        else fence_proxy_async();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(BAR(BAR_H_FULL + sh));
-          mbar_arrive(BAR(BAR_D_EMPTY + sd));
+          if (!p.h_tmem) mbar_arrive(BAR(BAR_D_EMPTY + sd));    // h in TMEM: GEMM2 releases the stage (it reads h there)
         }
         if (tr_warp) TRACE(ti, 7);
       };

@@ -66,6 +66,7 @@ struct TcParams {
   int pair;                 // 1: clusters of two CTAs share each streamed weight block (half each, multicast)
   int cg2;                  // pair + 1: the pair runs tcgen05.mma.cta_group::2 (M = 256; w holds the N-split block layout,
                             // w_blk_bytes = one CTA's half block)
+  int cg2_spin;             // cta_group::2 waits: bit 0 producers / epilogue / relay spin, bit 1 the leader's MMA warp spins
   int dual_g1;              // resident + narrow: two warps issue GEMM1 of alternate work items
   // A tile TMA boxes (tensor map over the input view, see launch_tc_conv): a chunk of KC/8
   // channel groups x R_ALLOC rows is fetched as boxes of a_gb groups x a_box_rows rows
@@ -90,7 +91,9 @@ struct TcParams {
   const float* bias2;
   const float* alpha2;
   int n_blk1;               // weight blocks of GEMM1 (GEMM2 blocks follow)
-  int SH;                   // h stages
+  int SH;                   // h stages (h_tmem: = SD, the h ring follows the accumulator ring)
+  int h_tmem;               // fused: act(conv3 + b) is written back into the accumulator's own TMEM columns as packed
+                            // bf16 and the 1x1 conv reads its A operand from there (no h tile in shared memory)
   // shared memory carve-up (bytes from the 1024-aligned base)
   uint32_t off_bias, off_a, off_w, off_h, smem_bytes;
   uint32_t a_stage_bytes, w_blk_bytes, h_stage_bytes;

@@ -439,7 +439,14 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   const int acc_cols1 = L.fused ? 2 * L.N_TILE : L.N_TILE;
   const int sd_max = std::max(1, std::min(4, 512 / acc_cols1));
   p.SH = L.fused ? std::min(sd_max, p.res_smem ? 3 : 4) : 0;
-  p.h_stage_bytes = L.fused ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
+  // fused unit: h = act(conv3 + b) goes back into the accumulator's TMEM columns (packed bf16) and the 1x1 conv
+  // takes its A operand from there: no h tile in shared memory (its stores and the MMA's reads of it were a
+  // sixth of the L1 data-pipe wavefronts of a C = 128 unit) and no single h stage to queue behind.  Measured:
+  // C = 128 units 545 -> 531 kcycles; C = 64 units 790 -> 815 (issue-bound: the TMEM store + wait cost more
+  // instructions than the two shared-memory stores they replace), so only units wider than 64 channels use it.
+  p.h_tmem = (L.fused && L.N_TILE > 64 && !getenv("RB_TC_NOHTMEM")) ? 1 : 0;
+  if (L.fused && getenv("RB_TC_HTMEM_ALL")) p.h_tmem = 1;                       // experiments only
+  p.h_stage_bytes = (L.fused && !p.h_tmem) ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
   // resident weights when the whole layer fits beside >= 2 A stages, else a streamed ring
   for (int attempt = 0; attempt < 2; ++attempt) {
     const bool resident = attempt == 0 && (L.n_ntiles == 1) && w_total <= 160u * 1024u;
@@ -464,6 +471,8 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     p.cg2 = (!resident && !L.fused && L.w2 && L.N_TILE == 256 && p.pre_act == RB_ACT_NONE && p.y.n >= 256 &&
              sr_rows == 0 && !g_trace && !getenv("RB_TC_NOCG2")) ? 1 : 0;
     if (p.cg2) {
+      p.cg2_spin = 0;
+      if (const char* e = getenv("RB_TC_CG2_SPIN")) p.cg2_spin = atoi(e);   // experiments only
       p.pair = 1;
       // two sub-tiles per weight block (one accumulator stage of 512 columns) where a tile is long enough
       // (>= 8 K chunks x taps) that the un-overlapped epilogue is the smaller cost than streaming every weight
@@ -538,6 +547,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   const int acc_cols = L.fused ? 2 * L.N_TILE : p.MT * L.N_TILE;
   p.SD = std::max(1, std::min(4, 512 / acc_cols));
   if (L.fused) p.SD = std::min(sd_max, 4);
+  if (p.h_tmem) p.SH = p.SD;
   if (p.res_smem && p.SA < 5) p.res_smem = 0;           // too few A stages to hold tiles until E2
   RB_CHECK(!L.fused || p.SD >= 2, RB_ERR_UNSUPPORTED, "fused unit needs two accumulator stages");
   uint32_t cols = 32;

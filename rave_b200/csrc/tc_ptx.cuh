@@ -58,16 +58,28 @@ __device__ __forceinline__ uint32_t mbar_try_wait_hint(uint32_t bar, uint32_t pa
 // Bounded wait: a protocol bug traps (and surfaces as a CUDA error) instead of hanging the GPU.
 // The poll loop is ONE out-of-line copy shared by every wait site: inlined, the ~40 instructions
 // per site pushed the hot epilogue loops out of the ~6 KB L0 instruction cache.
+// Hand-written: a suspended waiter is woken by every mbarrier event of the CTA, not only by its own phase
+// (ncu on the narrow fused units: ~120 loop iterations per waiting warp and tile, 15 % of all issued
+// instructions while the issue slots were the bound), so the loop is as short as it can be -- the suspending
+// try_wait, one branch, a counter.  The counter bounds a wait at 2^20 wake-ups: >= 1 s of busy barrier traffic
+// or, with nothing happening at all, 2^20 x the 10 us suspend limit.
 __device__ __noinline__ void mbar_wait_slow(uint32_t bar, uint32_t parity) {
-  uint32_t n = 0;
-  long long t0 = 0;
-  while (!mbar_try_wait_hint(bar, parity, 100000u)) {
-    if ((++n & 63u) == 0) {                     // look at the clock only now and then
-      const long long t = clock64();
-      if (t0 == 0) t0 = t;
-      else if (t - t0 > 4000000000ll) __trap();
-    }
-  }
+  asm volatile(
+      "{\n"
+      ".reg .pred p, q;\n"
+      ".reg .u32 n;\n"
+      "mov.u32 n, 0;\n"
+      "RB_WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+      "@p bra RB_WAIT_DONE;\n"
+      "add.u32 n, n, 1;\n"
+      "setp.gt.u32 q, n, 1048576;\n"
+      "@!q bra RB_WAIT_LOOP;\n"
+      "trap;\n"
+      "RB_WAIT_DONE:\n"
+      "}\n" ::"r"(bar),
+      "r"(parity), "r"(10000u)
+      : "memory");
 }
 __device__ __forceinline__ uint32_t mbar_test_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
@@ -108,36 +120,21 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t local, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
-// Waits of the cta_group::2 kernels SPIN (test_wait).  The suspending try_wait of mbar_wait_slow is woken by
-// arrivals from the CTA's own threads, TMA and tcgen05.commit, but a waiter whose barrier is completed from the
-// peer CTA (multicast commit, mbarrier.arrive.shared::cluster) slept on towards its time limit: the first
-// cta_group::2 build ran the weight ring at ~1900 cycles per block -- half the speed of the one-CTA kernel -- with
-// 486 NANOSLEEP.SYNCS per peer CTA and launch (ncu source view), one per remotely released stage.
+// Spinning waits (test_wait), selectable for the cta_group::2 kernels with RB_TC_CG2_SPIN (experiments only).
+// The first cta_group::2 build ran at half the speed of the one-CTA kernel; the cause was not a wake-up
+// problem of the suspending try_wait (spinning changed nothing) but the `.acquire.cluster` / `.release.cluster`
+// qualifiers it used on every wait of the leader and every relayed arrive: with the default (CTA-scope)
+// semantics -- what CUTLASS uses for the same hand-overs -- the pair runs 5-17 % faster than two single CTAs,
+// and suspending waits measure slightly better than spinning ones (fewer issue slots, less power).
 __device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
   uint32_t n = 0;
   while (!mbar_test_wait(bar, parity)) {
     if (++n > (1u << 27)) __trap();
   }
 }
-// the same on a barrier that the peer arrives on with mbarrier.arrive.release.cluster: cluster-scope acquire
-__device__ __forceinline__ void mbar_wait_cl(uint32_t bar, uint32_t parity) {
-  uint32_t n = 0, ok = 0;
-  do {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n"
-        : "=r"(ok)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (++n > (1u << 27)) __trap();
-  } while (!ok);
-}
-template <bool SPIN>
-__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity) {
-  if (SPIN) mbar_wait_spin(bar, parity);
+template <bool CG2>
+__device__ __forceinline__ void mbar_wait_t(uint32_t bar, uint32_t parity, int spin) {
+  if (CG2 && spin) mbar_wait_spin(bar, parity);
   else mbar_wait(bar, parity);
 }
 
@@ -285,6 +282,21 @@ __device__ __forceinline__ void mma_bf16_lohi(uint32_t d_tmem, uint32_t a_lo, ui
       "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// D[tmem] (+)= A[tmem] * B[smem]^T: the A operand (M = 128 rows = lanes, K = 16 bf16 = 8 columns of two packed
+// elements each, lower K index in the lower half) is read from tensor memory at `a_tmem`.
+__device__ __forceinline__ void mma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t hi,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b64 db;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // cta_group::2: ONE thread of the pair's leader CTA issues for both SMs.  M = 256: rows 0-127 of D / A
 // live in the leader's TMEM / shared memory, rows 128-255 in the peer's, at the same addresses; each CTA
 // holds N/2 rows of B at the descriptor's address (tcgen05 reads both halves).
@@ -361,6 +373,15 @@ __device__ __forceinline__ void st_global_256(void* ptr, const uint4& a, const u
   asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(ptr), "r"(a.x), "r"(a.y), "r"(a.z),
                "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
                : "memory");
+}
+// 32 lanes x 8 consecutive 32-bit columns, registers -> TMEM (thread l of the warp writes row lane base + l)
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
