@@ -53,14 +53,29 @@ constexpr int W_LOAD0 = 12;      // activation-pass warps 12-15 (un-activated in
 constexpr int E1_WARPS = 8;      // fused: warps [0, 8) build the h tile, the other output warps store y
 
 template <int ACT>
-__device__ __forceinline__ float act_f(float v, float alpha) {
+__device__ __forceinline__ float act_f(float v, float alpha, float inv_alpha) {
   if (ACT == RB_ACT_LEAKY) return fmaxf(v, 0.2f * v);
   if (ACT == RB_ACT_SNAKE) {
-    // x + sin^2(a x) / (a + 1e-9)   (blocks.py:845-853); bf16 storage: fast sine is ample
+    // x + sin^2(a x) / (a + 1e-9)   (blocks.py:845-853); bf16 storage: fast sine is ample.  The reciprocal is a
+    // per-channel constant computed at load: one MUFU operation per element instead of two.
     const float s = __sinf(alpha * v);
-    return fmaf(__fdividef(1.0f, alpha + 1e-9f), s * s, v);
+    return fmaf(inv_alpha, s * s, v);
   }
   return v;
+}
+
+// Waveform head tanh(wave * sigmoid(amp)) (blocks.py:700-707) with the hardware tanh: sigmoid(a) = 0.5 +
+// 0.5 tanh(a / 2), so an output costs two MUFU operations instead of two exponentials and two reciprocals (the
+// last conv's epilogue was MUFU-bound: 4 x 4096 operations per tile at 16 per clock).  tanh.approx.f32 is good
+// to 2^-11 relative, a quarter of the bf16 rounding of the stored value.
+__device__ __forceinline__ float tanh_hw(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float head_value(float wave, float amp) {
+  const float g = fmaf(0.5f, tanh_hw(0.5f * amp), 0.5f);
+  return tanh_hw(wave * g);
 }
 
 __device__ __forceinline__ void unpack8(const uint4& q, float* f) {
@@ -235,10 +250,12 @@ __device__ __forceinline__ void finish_a_chunk(const TcParams& p, int kc, uint8_
       float f[8];
       unpack8(*q, f);
       const float4* al = reinterpret_cast<const float4*>(p.alpha + kc * p.KC + c8 * 8);
-      const float4 a0 = __ldg(al), a1 = __ldg(al + 1);
+      const float4* il = reinterpret_cast<const float4*>(p.alpha + p.alpha_n + kc * p.KC + c8 * 8);
+      const float4 a0 = __ldg(al), a1 = __ldg(al + 1), i0 = __ldg(il), i1 = __ldg(il + 1);
       const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float ia[8] = {i0.x, i0.y, i0.z, i0.w, i1.x, i1.y, i1.z, i1.w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) f[e] = act_f<PRE>(f[e], a[e]);
+      for (int e = 0; e < 8; ++e) f[e] = act_f<PRE>(f[e], a[e], ia[e]);
       *q = pack8(f);
     }
   });
@@ -600,9 +617,7 @@ __device__ __forceinline__ void drain(const TcParams& p, uint32_t bar_full, uint
         float o[16];
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
-          const float g = __fdividef(1.f, 1.f + __expf(-v[16 + e]));
-          const float x = v[e] * g;
-          const float th = 1.f - __fdividef(2.f, 1.f + __expf(2.f * x));
+          const float th = head_value(v[e], v[16 + e]);
           o[e] = ((e & 1) && even_row) ? -th : th;
         }
         uint4* hp = ys + (p.y.hist + t) * p.y.sT;
@@ -689,9 +704,7 @@ __device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full,
         for (int e = 0; e < 8; ++e) {
           const float wv = __uint_as_float(r[16 * sub + e]) + bw[e];
           const float am = __uint_as_float(r[16 * sub + 8 + e]) + bw[16 + e];
-          const float g = __fdividef(1.f, 1.f + __expf(-am));
-          const float x = wv * g;
-          const float th = 1.f - __fdividef(2.f, 1.f + __expf(2.f * x));
+          const float th = head_value(wv, am);
           o[8 * sub + e] = ((e & 1) && sub == 0) ? -th : th;
         }
       }
@@ -741,14 +754,14 @@ __device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full,
 // Fused E1 chunk: h = act2(D1 + bias) as bf16 into the h tile (core-matrix layout, 2048 B per
 // channel group).
 template <int ACT2, int NC>
-__device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const float* alpha2, uint8_t* hdst) {
+__device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const float* alpha2, int ia_off, uint8_t* hdst) {
   float v[NC];
   load_acc<NC>(taddr, bs, v);
   if (ACT2 == RB_ACT_LEAKY) {
     leaky_n<NC>(v);
   } else if (ACT2 == RB_ACT_SNAKE) {
 #pragma unroll
-    for (int e = 0; e < NC; ++e) v[e] = act_f<ACT2>(v[e], alpha2[e]);
+    for (int e = 0; e < NC; ++e) v[e] = act_f<ACT2>(v[e], alpha2[e], alpha2[e + ia_off]);
   }
   if (hdst) {
 #pragma unroll
@@ -854,6 +867,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
     for (int i = tid; i < p.N_TILE; i += N_THREADS) {
       bias2_s[i] = p.bias2 ? p.bias2[i] : 0.f;
       alpha2_s[i] = p.alpha2 ? p.alpha2[i] : 1.f;
+      alpha2_s[i + p.N_TILE] = p.alpha2 ? p.alpha2[i + p.N_TILE] : 1.f;
     }
   }
   if (warp == W_MMA) {
@@ -1292,7 +1306,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           const int c1 = C2 - c0 >= 32 ? c0 + 32 : c0 + 16;
 #pragma unroll 1
           for (int c = c0; c < c1; c += 16)
-            h_chunk<ACT2, 16>(tmem + lane_base + sd * d_stage_cols + (uint32_t)c, bias_s + c, alpha2_s + c,
+            h_chunk<ACT2, 16>(tmem + lane_base + sd * d_stage_cols + (uint32_t)c, bias_s + c, alpha2_s + c, C2,
                               hb ? hb + (size_t)(c >> 3) * 2048 : nullptr);
         }
         if (p.h_tmem) tmem_st_wait();

@@ -47,7 +47,9 @@ struct TcParams {
   const __nv_bfloat16* w;   // packed weight blocks, consumption order (see tc_engine.cu)
   const uint64_t* masks;    // [n_ntiles][n_kchunks] active-tap bit masks
   const float* bias;        // [N_total] or nullptr
-  const float* alpha;       // Snake alpha of the pre-activation per view channel, or nullptr
+  const float* alpha;       // Snake alpha of the pre-activation per view channel, then 1 / (alpha + 1e-9) (alpha_n
+                            // entries each), or nullptr; alpha2 likewise with N_TILE entries each
+  int alpha_n;
   const float* aff_a;       // AdaIN scale  [rows][c_in] applied before the pre-activation, or nullptr
   const float* aff_b;       // AdaIN shift
   int aff_C;                // channels of the affine tables (un-reshaped tensor)

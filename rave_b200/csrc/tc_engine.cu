@@ -81,6 +81,13 @@ static int dev_upload(const std::vector<T>& v, T** dev) {
 
 static inline __nv_bfloat16 f2bf(float f) { return __float2bfloat16_rn(f); }
 
+// Snake alpha of n channels, followed by 1 / (alpha + 1e-9) (blocks.py:845-853) so that the kernels multiply
+static int upload_alpha(const std::vector<float>& a, float** dev) {
+  std::vector<float> t(a);
+  for (float v : a) t.push_back(1.0f / (v + 1e-9f));
+  return dev_upload(t, dev);
+}
+
 // View-space weight of one op: Wv[n][c][j], n < N_total, c < cin_v, j < n_taps (zero padded).
 struct ViewWeight {
   int N_total, cin_v, n_taps, dil, off, fin, fout, out_mask;
@@ -330,7 +337,7 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
   }
   if ((rc = dev_upload(masks, &L.masks))) return rc;
   if (!v.bias.empty() && (rc = dev_upload(v.bias, &L.bias))) return rc;
-  if (!v.alpha.empty() && (rc = dev_upload(v.alpha, &L.alpha))) return rc;
+  if (!v.alpha.empty() && (rc = upload_alpha(v.alpha, &L.alpha))) return rc;
   L.valid = true;
   return RB_OK;
 }
@@ -411,7 +418,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       p.res_delay = 0;
     }
   }
-  p.w = L.w; p.masks = L.masks; p.bias = L.bias; p.alpha = L.alpha;
+  p.w = L.w; p.masks = L.masks; p.bias = L.bias; p.alpha = L.alpha; p.alpha_n = L.cin_v;
   p.pre_act = x_act ? RB_ACT_NONE : op.pre_act;
   p.out_act = out_act ? RB_ACT_LEAKY : RB_ACT_NONE;
   p.res_act = (res && res_act) ? 1 : 0;
@@ -434,7 +441,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   p.off_bias = 640 + TC_MAX_MASKS * 8;    // after the mbarriers, the TMEM address slot and the tap masks
   RB_CHECK(L.n_ntiles * L.n_kchunks <= TC_MAX_MASKS, RB_ERR_UNSUPPORTED, "too many (n-tile, K-chunk) pairs (%d x %d)",
            L.n_ntiles, L.n_kchunks);
-  const uint32_t fixed = align_up(p.off_bias + (uint32_t)(L.N_total + 2 * L.N_TILE) * 4, 128);
+  const uint32_t fixed = align_up(p.off_bias + (uint32_t)(L.N_total + 3 * L.N_TILE) * 4, 128);   // bias, bias2, alpha2, 1/alpha2
   // accumulator stages: as many as TMEM holds (<= 4); the fused unit keeps one h tile per stage
   const int acc_cols1 = L.fused ? 2 * L.N_TILE : L.N_TILE;
   const int sd_max = std::max(1, std::min(4, 512 / acc_cols1));
@@ -646,15 +653,31 @@ __global__ void concat_gm_kernel(Buf z, Buf y, CondArgs ca, int c_z, int B) {
     reinterpret_cast<uint4*>(y.p)[((size_t)b * G + g) * y.ld + y.hist + t] = v;
   }
 }
-// AdaIN transfer (blocks.py:885-891) as x = a[b][c]*x + b[b][c], in place
+// AdaIN transfer (blocks.py:885-891) as x = a[b][c]*x + b[b][c], in place.  One thread per 16-byte unit (8
+// channels of one row); consecutive threads take consecutive rows of one channel group: 512 contiguous bytes
+// per warp each way (the scalar version moved 2 bytes per thread and ran at 1 TB/s).
 __global__ void affine_gm_kernel(Buf x, const float* __restrict__ a, const float* __restrict__ bb, int C, int B) {
-  const size_t total = (size_t)B * x.n * x.cp;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    int b, t, c;
-    decode_gm(i, x, b, t, c);
-    if (c >= C) continue;
-    __nv_bfloat16* q = x.p + eidx(x, b, t, c);
-    *q = __float2bfloat16_rn(fmaf(__bfloat162float(*q), a[(size_t)b * C + c], bb[(size_t)b * C + c]));
+  const int G = x.cp >> 3;
+  const long long units = (long long)B * G * x.n;
+  for (long long u = blockIdx.x * (long long)blockDim.x + threadIdx.x; u < units; u += (long long)gridDim.x * blockDim.x) {
+    const int t = (int)(u % x.n);
+    const int r = (int)(u / x.n);
+    const int g = r % G, b = r / G;
+    uint4* q = reinterpret_cast<uint4*>(x.p) + (((size_t)b * G + g) * x.ld + x.hist + t);
+    uint4 v = *q;
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    const float* ap = a + (size_t)b * C + g * 8;
+    const float* bp = bb + (size_t)b * C + g * 8;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int c = g * 8 + 2 * k;
+      float lo = __uint_as_float(w[k] << 16), hi = __uint_as_float(w[k] & 0xffff0000u);
+      if (c < C) lo = fmaf(lo, __ldg(ap + 2 * k), __ldg(bp + 2 * k));
+      if (c + 1 < C) hi = fmaf(hi, __ldg(ap + 2 * k + 1), __ldg(bp + 2 * k + 1));
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(lo, hi);
+      w[k] = *reinterpret_cast<uint32_t*>(&h2);
+    }
+    *q = make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
 // AdaIN running statistics on a group-major tensor: one CTA per (stream, channel), two passes.
@@ -899,7 +922,7 @@ int tc_pack_weights(rb_handle* h) {
       if (fuse && S.valid) {
         S.fused = true; S.fused_with = i + 1; S.tail = i + 1; S.act2 = h->ops[i + 1].pre_act;
         if (!v2.bias.empty() && (rc = dev_upload(v2.bias, &S.bias2))) return rc;
-        if (!v2.alpha.empty() && (rc = dev_upload(v2.alpha, &S.alpha2))) return rc;
+        if (!v2.alpha.empty() && (rc = upload_alpha(v2.alpha, &S.alpha2))) return rc;
       }
     }
     // conv -> HEAD_V2 (no noise branch, amplitude modulation, 16 bands): the head runs in the epilogue
@@ -922,7 +945,7 @@ int tc_pack_weights(rb_handle* h) {
       L.tail = i + 1;
       L.act2 = h->ops[i + 1].pre_act;
       if (!v2.bias.empty() && (rc = dev_upload(v2.bias, &L.bias2))) return rc;
-      if (!v2.alpha.empty() && (rc = dev_upload(v2.alpha, &L.alpha2))) return rc;
+      if (!v2.alpha.empty() && (rc = upload_alpha(v2.alpha, &L.alpha2))) return rc;
       pl->skip[i + 1] = 1;
     }
   }
@@ -991,7 +1014,7 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
         return (int)RB_OK;
       }, &apply);
       if (rc) return rc;
-      if (apply) RB_LAUNCH_EW(affine_gm_kernel, (size_t)B * x.n * x.cp, s, x, w.aff_a + ro, w.aff_b + ro, op.c_in, B);
+      if (apply) RB_LAUNCH_EW(affine_gm_kernel, (size_t)B * x.n * (x.cp / 8), s, x, w.aff_a + ro, w.aff_b + ro, op.c_in, B);
       return RB_OK;
     }
     case RB_OP_HEAD_V2: {
