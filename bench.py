@@ -348,7 +348,7 @@ def run_ours(args):
         tp = os.path.join(ROOT, "profiles", name)
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get("dram_bytes_per_step")
-            traffic_src = f"profiles/{name} (ncu --set full capture of an earlier run of this command; not measured in this run)"
+            traffic_src = f"profiles/{name} (ncu dram__bytes_read + dram__bytes_write over the 46 launches of one step of this command, tools/traffic.py; an earlier run, not measured in this one)"
             break
     per_op_tf = conv_flops / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
     hbm_gbs = conv_bytes / (conv_ms / 1e3) / 1e9 if conv_ms > 0 else 0.0

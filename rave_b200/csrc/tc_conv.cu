@@ -753,7 +753,7 @@ __device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full,
 
 // Fused E1 chunk: h = act2(D1 + bias) as bf16 into the h tile (core-matrix layout, 2048 B per
 // channel group).
-template <int ACT2, int NC>
+template <int ACT2, int NC, bool HT>
 __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const float* alpha2, int ia_off, uint8_t* hdst) {
   float v[NC];
   load_acc<NC>(taddr, bs, v);
@@ -763,7 +763,7 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
 #pragma unroll
     for (int e = 0; e < NC; ++e) v[e] = act_f<ACT2>(v[e], alpha2[e], alpha2[e + ia_off]);
   }
-  if (hdst) {
+  if (!HT) {
 #pragma unroll
     for (int q = 0; q < NC / 8; ++q) *reinterpret_cast<uint4*>(hdst + (size_t)q * 2048) = pack8(v + q * 8);
   } else {
@@ -797,11 +797,14 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
 // each SM: the streamed wide layers were bound by the 128 B/clk shared-memory port (profiles/r01_ubench.txt), not
 // by the tensor pipe.  The leader (cluster rank 0) issues; the peer's MMA warp relays its barriers (below).
 // PTX wants one cta_group for every tcgen05 instruction of a kernel, hence a template parameter.
-template <int PRE, int ACT2, bool FUSED, int DR, bool TR, int NS, bool CG2>
+// HT: fused unit with h in tensor memory (TcParams::h_tmem) -- a template parameter because the narrow units are
+// bound by issue slots: the same choice as a run-time flag cost the C = 64 units 5 % (+16 M instructions).
+template <int PRE, int ACT2, bool FUSED, int DR, bool TR, int NS, bool CG2, bool HT>
 __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
     tc_conv_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcTmap tmx) {
   static_assert(NS == 2 || (NS == 3 && FUSED && PRE == RB_ACT_NONE), "three sets: fused units without activation pass");
   static_assert(!CG2 || (!FUSED && PRE == RB_ACT_NONE && NS == 2), "cta_group::2: plain streamed layers");
+  static_assert(!HT || FUSED, "h in tensor memory: fused units");
   constexpr int W_MMA = NS == 3 ? 24 : 16, W_WPROD = W_MMA + 1, W_APROD = W_MMA + 2, W_MMA2 = W_MMA + 3;
   constexpr int N_THREADS = NS == 3 ? 896 : TC_THREADS;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -853,7 +856,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
       // one arrival per WARP (lane 0 after __syncwarp): 32 per-thread arrivals on one mbarrier
       // serialise in the shared-memory atomic path -- at 768 arrivals per tile they, not the
       // math, set the tile rate of the narrow fused units
-      mbar_init(BAR(BAR_D_EMPTY + i), (FUSED ? (p.h_tmem ? 1 : E1_WARPS) : N_OUT / 32) + cg2_lead);
+      mbar_init(BAR(BAR_D_EMPTY + i), (FUSED ? (HT ? 1 : E1_WARPS) : N_OUT / 32) + cg2_lead);
       mbar_init(BAR(BAR_H_FULL + i), E1_WARPS);
       mbar_init(BAR(BAR_H_EMPTY + i), 1);
       mbar_init(BAR(BAR_D2_FULL + i), 1);
@@ -1117,7 +1120,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         const uint32_t dcol = tmem + sd * d_stage_cols + (uint32_t)C2;
         const int nkc = C2 / p.KC;
         uint32_t accum = 0;
-        if (p.h_tmem) {
+        if (HT) {
           // A operand from tensor memory: K step k of h sits at columns [16 k, 16 k + 8) of this stage's D1 region
           uint32_t at = tmem + sd * d_stage_cols;
           for (int kc = 0; kc < nkc; ++kc) {
@@ -1298,24 +1301,24 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         const uint32_t sd = rd_.idx, sh = rh_.idx;
         mbar_wait(BAR(BAR_D_FULL + sd), rd_.ph);
         if (tr_warp) TRACE(ti, 6);
-        if (!p.h_tmem) mbar_wait(BAR(BAR_H_EMPTY + sh), rh_.ph ^ 1);
+        if (!HT) mbar_wait(BAR(BAR_H_EMPTY + sh), rh_.ph ^ 1);
         tc_fence_after();
-        uint8_t* hb = p.h_tmem ? nullptr : h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
+        uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
         for (int c0 = part * 32; c0 < C2; c0 += E1_PARTS * 32) {
           // rolled 16-column pieces: see drain_smem16 (instruction-cache footprint)
           const int c1 = C2 - c0 >= 32 ? c0 + 32 : c0 + 16;
 #pragma unroll 1
           for (int c = c0; c < c1; c += 16)
-            h_chunk<ACT2, 16>(tmem + lane_base + sd * d_stage_cols + (uint32_t)c, bias_s + c, alpha2_s + c, C2,
-                              hb ? hb + (size_t)(c >> 3) * 2048 : nullptr);
+            h_chunk<ACT2, 16, HT>(tmem + lane_base + sd * d_stage_cols + (uint32_t)c, bias_s + c, alpha2_s + c, C2,
+                                  hb + (size_t)(c >> 3) * 2048);
         }
-        if (p.h_tmem) tmem_st_wait();
+        if (HT) tmem_st_wait();
         else fence_proxy_async();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(BAR(BAR_H_FULL + sh));
-          if (!p.h_tmem) mbar_arrive(BAR(BAR_D_EMPTY + sd));    // h in TMEM: GEMM2 releases the stage (it reads h there)
+          if (!HT) mbar_arrive(BAR(BAR_D_EMPTY + sd));    // h in TMEM: GEMM2 releases the stage (it reads h there)
         }
         if (tr_warp) TRACE(ti, 7);
       };
@@ -1395,11 +1398,11 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   }
 }
 
-template <int PRE, int ACT2, bool FUSED, int DR, bool TR = false, int NS = 2, bool CG2 = false>
+template <int PRE, int ACT2, bool FUSED, int DR, bool TR = false, int NS = 2, bool CG2 = false, bool HT = false>
 static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS, CG2>,
+    RB_CUDA(cudaFuncSetAttribute(tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS, CG2, HT>,
                                  cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
@@ -1418,7 +1421,7 @@ static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStr
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = p.pair ? 2 : 1;
-  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS, CG2>, p, tm));
+  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_conv_kernel<PRE, ACT2, FUSED, DR, TR, NS, CG2, HT>, p, tm));
   return RB_OK;
 }
 
@@ -1491,10 +1494,15 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
   // drain_fast: whole 32-column chunks whose four channel groups sit sA apart, plain stores
   const bool fast = !p.head && !p.out_mask && (p.N_TILE & 31) == 0 && (p.y.G1 & 3) == 0 &&
                     (p.res.p == nullptr || p.res_smem || (p.res.G1 & 3) == 0);
+  // h in tensor memory is compiled into one variant (and its traced twin): the fast fused unit of a LeakyReLU
+  // net with its residual in global memory -- tc_engine.cu sets h_tmem under the same conditions
+  RB_CHECK(!p.h_tmem || (p.fused && fast && p.res.p && !p.res_smem && p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_LEAKY),
+           RB_ERR_INVALID, "h_tmem set for a layer without that kernel variant");
   if (p.trace && p.pre_act == RB_ACT_NONE && fast && (!p.fused || (p.act2 == RB_ACT_LEAKY && p.res.p))) {
     // traced variants (debug hook): the headline kernels only
     if (!p.fused) rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 1, true>(p, tm, grid, s);
     else if (p.res_smem) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 2, true>(p, tm, grid, s);
+    else if (p.h_tmem) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 1, true, 2, false, true>(p, tm, grid, s);
     else rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 1, true>(p, tm, grid, s);
   } else if (!p.fused) {
     if (p.cg2) {
@@ -1522,6 +1530,8 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
       if (fast && p.res.p && p.res_smem && three)
         rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 2, false, 3>(p, tm, grid, s);
       else if (fast && p.res.p && p.res_smem) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 2>(p, tm, grid, s);
+      else if (fast && p.res.p && p.h_tmem)
+        rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 1, false, 2, false, true>(p, tm, grid, s);
       else if (fast && p.res.p) rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 1>(p, tm, grid, s);
       else rc = launch_variant<RB_ACT_NONE, RB_ACT_LEAKY, true, 0>(p, tm, grid, s);
     } else if (p.pre_act == RB_ACT_SNAKE && p.act2 == RB_ACT_SNAKE) {

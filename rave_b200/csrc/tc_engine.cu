@@ -451,8 +451,9 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   // sixth of the L1 data-pipe wavefronts of a C = 128 unit) and no single h stage to queue behind.  Measured:
   // C = 128 units 545 -> 531 kcycles; C = 64 units 790 -> 815 (issue-bound: the TMEM store + wait cost more
   // instructions than the two shared-memory stores they replace), so only units wider than 64 channels use it.
-  p.h_tmem = (L.fused && L.N_TILE > 64 && !getenv("RB_TC_NOHTMEM")) ? 1 : 0;
-  if (L.fused && getenv("RB_TC_HTMEM_ALL")) p.h_tmem = 1;                       // experiments only
+  // (one kernel variant carries it: LeakyReLU units on activated storage with the residual in global memory)
+  p.h_tmem = (L.fused && L.N_TILE > 64 && (L.N_TILE & 31) == 0 && p.pre_act == RB_ACT_NONE && L.act2 == RB_ACT_LEAKY &&
+              res && !p.res_smem && !getenv("RB_TC_NOHTMEM")) ? 1 : 0;
   p.h_stage_bytes = (L.fused && !p.h_tmem) ? (uint32_t)(L.N_TILE / 8) * 2048u : 0u;
   // resident weights when the whole layer fits beside >= 2 A stages, else a streamed ring
   for (int attempt = 0; attempt < 2; ++attempt) {
