@@ -410,10 +410,16 @@ __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full,
 __device__ __forceinline__ void drain_smem16(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                              const float* bs, const Work& wk, int rit, int part, int nparts,
                                              int NT, const uint8_t* res_s) {
+  // A fused unit's tensors are plain row views (one phase): channel group g sits g * sA units into the stream,
+  // so every address below advances by adds -- goff32()'s phase split (a division when G1 is not a power of
+  // two, compiled in either way) and the parameter reloads were ~25 of the ~160 instructions of a piece, and
+  // the narrow units are bound by issue slots.
   const int row = wk.t0 + rit;
-  const uint32_t yoff = (uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT);
-  uint4* const ybase = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p));
-  const uint4* const srow = reinterpret_cast<const uint4*>(res_s) + (rit + p.off);
+  const uint32_t ysA = (uint32_t)p.y.sA, RA = (uint32_t)p.R_ALLOC;
+  uint4* yp = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) +
+              ((uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT) + (uint32_t)(part * 4) * ysA);
+  const uint4* sp = reinterpret_cast<const uint4*>(res_s) + (rit + p.off) + (uint32_t)(part * 4) * RA;
+  const uint32_t ystep = (uint32_t)(nparts * 4 - 4) * ysA, sstep = (uint32_t)(nparts * 4 - 4) * RA;   // to the next chunk
   const bool valid = row < p.y.n;
   const bool ract = p.res_act != 0, oact = p.out_act != 0;
   mbar_wait(bar_full, parity);
@@ -421,8 +427,7 @@ __device__ __forceinline__ void drain_smem16(const TcParams& p, uint32_t bar_ful
   for (int c0 = part * 32; c0 < NT; c0 += nparts * 32) {
 #pragma unroll 1
     for (int c = c0; c < c0 + 32; c += 16) {
-      const uint4* sp = srow + (c >> 3) * p.R_ALLOC;
-      const uint4 r0 = sp[0], r1 = sp[p.R_ALLOC];
+      const uint4 r0 = sp[0], r1 = sp[RA];
       float v[16];
       load_acc<16>(tbase + (uint32_t)c, bs + c, v);
       const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
@@ -439,45 +444,49 @@ __device__ __forceinline__ void drain_smem16(const TcParams& p, uint32_t bar_ful
       }
       if (oact) leaky_n<16>(v);
       if (valid) {
-        const uint32_t o = yoff + (uint32_t)goff32(p.y, c >> 3);
-        ybase[o] = pack8(v);
-        ybase[o + (uint32_t)p.y.sA] = pack8(v + 8);
+        yp[0] = pack8(v);
+        yp[ysA] = pack8(v + 8);
       }
+      yp += 2 * ysA;
+      sp += 2 * RA;
     }
+    yp += ystep;
+    sp += sstep;
   }
   tc_fence_before();
 }
 
 // Fused unit whose residual comes from global memory (C = 96 / 128: the A tiles cannot wait in smem until
-// E2): 16-column pieces like drain_smem16, with the residual of the warp's first FOUR pieces (its whole share
-// of a C = 128 tile) requested BEFORE the accumulator barrier.  The event trace of the 32-column / one-chunk-
-// ahead drain showed E2 at 5200-6300 cycles per tile against ~1800 for E1 on the same amount of data: the
-// second chunk's residual load was only issued after the first chunk's math, so its full L2 / HBM latency
-// sat on the critical path of the output warps (and through D2_EMPTY / H_EMPTY on everything else).
+// E2): 16-column pieces like drain_smem16.  The residual of the warp's first two pieces is requested BEFORE the
+// accumulator barrier and each later piece two pieces ahead of its use (the tensor is this unit's own input, which
+// the A producer is pulling through L2 at the same time, so a piece of work covers the latency).  The event trace
+// of the first version -- 32-column chunks, one ahead -- showed E2 at 5200-6300 cycles per tile against ~1800 for E1
+// on the same amount of data: the second chunk's load was only issued after the first chunk's math.  (A four-deep
+// queue filled before the barrier worked as well but cost 24 register moves per piece in this rolled loop.)
 __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                             const float* bs, const Work& wk, int rit, int part, int nparts, int NT,
                                             uint32_t tr) {
   constexpr uint32_t tmask = 0;                             // `tr` already carries the trace mask
   const int row = wk.t0 + rit;
-  const uint32_t yoff = (uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT);
-  const uint32_t roff = (uint32_t)((long long)wk.b * p.res.sb) +
-                        (uint32_t)((p.res.hist - p.res_delay + row) * p.res.sT);
-  uint4* const ybase = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p));
-  const uint4* const rbase = reinterpret_cast<const uint4*>(p.res.p);
+  const uint32_t ysA = (uint32_t)p.y.sA, rsA = (uint32_t)p.res.sA;
+  uint4* yp = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) +
+              ((uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT) + (uint32_t)(part * 4) * ysA);
+  const uint4* rp = reinterpret_cast<const uint4*>(p.res.p) +
+                    ((uint32_t)((long long)wk.b * p.res.sb) + (uint32_t)((p.res.hist - p.res_delay + row) * p.res.sT) +
+                     (uint32_t)(part * 4) * rsA);
   const bool valid = row < p.y.n;
   const bool ract = p.res_act != 0, oact = p.out_act != 0;
   const int jump = 16 + (nparts - 1) * 32;                  // from the second piece of a chunk to the next chunk
-  uint4 rr[8];
+  const uint32_t yjump = (uint32_t)(nparts * 4 - 4) * ysA, rjump = (uint32_t)(nparts * 4 - 4) * rsA;
+  uint4 q0, q1, q2, q3;                                     // residual of the current piece (q0, q1) and the next (q2, q3)
+  q0 = q1 = q2 = q3 = make_uint4(0u, 0u, 0u, 0u);
   int cq = part * 32;                                       // column of the next piece to request
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    if (cq < NT && valid) {
-      const uint32_t o = roff + (uint32_t)goff32(p.res, cq >> 3);
-      rr[2 * i] = __ldg(rbase + o);
-      rr[2 * i + 1] = __ldg(rbase + (o + (uint32_t)p.res.sA));
-    }
-    cq += (cq & 16) ? jump : 16;
-  }
+  if (cq < NT && valid) { q0 = __ldg(rp); q1 = __ldg(rp + rsA); }
+  rp += 2 * rsA;
+  cq += 16;
+  if (cq < NT && valid) { q2 = __ldg(rp); q3 = __ldg(rp + rsA); }
+  rp += 2 * rsA + rjump;
+  cq += jump;
   mbar_wait(bar_full, parity);
   tc_fence_after();
   TRACE(tr, 12);
@@ -486,7 +495,12 @@ __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full
     float v[16];
     load_acc<16>(tbase + (uint32_t)c, bs + c, v);
     TRACE(tr, 13);
-    const uint32_t w[8] = {rr[0].x, rr[0].y, rr[0].z, rr[0].w, rr[1].x, rr[1].y, rr[1].z, rr[1].w};
+    const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    // the queue moves up and the piece two ahead is requested before this piece's math
+    q0 = q2;
+    q1 = q3;
+    if (cq < NT && valid) { q2 = __ldg(rp); q3 = __ldg(rp + rsA); }
+    if (cq & 16) { rp += 2 * rsA + rjump; cq += jump; } else { rp += 2 * rsA; cq += 16; }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
@@ -501,19 +515,10 @@ __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full
     if (oact) leaky_n<16>(v);
     TRACE(tr, 14);
     if (valid) {
-      const uint32_t o = yoff + (uint32_t)goff32(p.y, c >> 3);
-      ybase[o] = pack8(v);
-      ybase[o + (uint32_t)p.y.sA] = pack8(v + 8);
+      yp[0] = pack8(v);
+      yp[ysA] = pack8(v + 8);
     }
-    // shift the queue, request the piece four ahead
-#pragma unroll
-    for (int i = 0; i < 6; ++i) rr[i] = rr[i + 2];
-    if (cq < NT && valid) {
-      const uint32_t o = roff + (uint32_t)goff32(p.res, cq >> 3);
-      rr[6] = __ldg(rbase + o);
-      rr[7] = __ldg(rbase + (o + (uint32_t)p.res.sA));
-    }
-    cq += (cq & 16) ? jump : 16;
+    yp += (c & 16) ? 2 * ysA + yjump : 2 * ysA;
   }
   TRACE(tr, 15);
   tc_fence_before();
