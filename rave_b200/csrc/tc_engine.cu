@@ -1196,28 +1196,39 @@ __global__ void roll_gm_kernel(Buf b, int rows_per_stream_group, int n) {
 }
 // All group-major slots of a step in ONE launch (a step used to end with ~35 roll launches, 17 % of
 // its time): CTA -> (slot, stream, channel group) through the prefix table of the descriptor block.
-constexpr int ROLL_MAX = 56;
+constexpr int ROLL_MAX = 48;
 struct RollSet {
   uint4* base[ROLL_MAX];
-  int ld[ROLL_MAX], hist[ROLL_MAX], n[ROLL_MAX], first[ROLL_MAX + 1];
-  int skip[ROLL_MAX];     // hist is rounded up to 16 rows for alignment; only the last hist - skip rows are state
+  int ld[ROLL_MAX], hist[ROLL_MAX], n[ROLL_MAX];
+  int first[ROLL_MAX + 1];    // first WARP of each slot
+  int skip[ROLL_MAX];         // hist is rounded up to 16 rows for alignment; only the last hist - skip rows are state
+  int nblk[ROLL_MAX];         // (stream, channel group) blocks of the slot
+  int lpb[ROLL_MAX];          // lanes per block: a warp rolls 32 / lpb blocks at once (state is 2-18 rows per block)
   int count;
 };
 __global__ void __launch_bounds__(256) roll_many_kernel(const __grid_constant__ RollSet rs) {
-  // one WARP per (slot, stream, channel group) block of ld rows: 32 rows (512 B) per pass, read before write.
-  // blockIdx.y is the slot: with a flat index every one of the ~10^6 warps of a 1024-stream step walked the
-  // prefix table to find its slot (~30 steps on average) to then move 2-16 rows -- 0.2 ms per step for 86 MB.
-  const int k = (int)blockIdx.y;
+  // A warp takes 32 / lpb consecutive (stream, channel group) blocks of one slot, lpb lanes each; rows are read
+  // before they are written (the windows overlap when a chunk is shorter than the state).  The slot of a warp is
+  // found by bisection of the prefix table: the first version walked it linearly (~30 steps for each of the ~10^6
+  // one-block warps of a 1024-stream step, to then move 2-16 rows): 0.2 ms per step for 86 MB of state.
   const int gw = (int)((blockIdx.x * 256u + threadIdx.x) >> 5), lane = threadIdx.x & 31;
-  if (gw >= rs.first[k + 1] - rs.first[k]) return;
-  uint4* base = rs.base[k] + (size_t)gw * rs.ld[k];
+  if (gw >= rs.first[rs.count]) return;
+  int lo = 0, hi = rs.count;
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (gw >= rs.first[mid]) lo = mid; else hi = mid;
+  }
+  const int k = lo, lpb = rs.lpb[k];
+  const int blk = (gw - rs.first[k]) * (32 / lpb) + lane / lpb, l = lane % lpb;
+  const bool live = blk < rs.nblk[k];
+  uint4* base = rs.base[k] + (size_t)(live ? blk : 0) * rs.ld[k];
   const int hist = rs.hist[k], n = rs.n[k];
-  for (int r0 = rs.skip[k]; r0 < hist; r0 += 32) {
-    const int r = r0 + lane;
+  for (int r0 = rs.skip[k]; r0 < hist; r0 += lpb) {
+    const int r = r0 + l;
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (r < hist) v = base[r + n];
+    if (live && r < hist) v = base[r + n];
     __syncwarp();
-    if (r < hist) base[r] = v;
+    if (live && r < hist) base[r] = v;
     __syncwarp();
   }
 }
@@ -1342,9 +1353,7 @@ int tc_stream_run(rb_handle* h, int ob, int oe, int B, int F, const void* in, vo
   rs.first[0] = 0;
   auto flush = [&]() -> int {
     if (rs.count == 0) return RB_OK;
-    int most = 0;
-    for (int k = 0; k < rs.count; ++k) most = std::max(most, rs.first[k + 1] - rs.first[k]);
-    roll_many_kernel<<<dim3((most + 7) / 8, rs.count), 256, 0, s>>>(rs);
+    roll_many_kernel<<<(rs.first[rs.count] + 7) / 8, 256, 0, s>>>(rs);
     RB_CUDA(cudaGetLastError());
     ++g_launches;
     rs.count = 0;
@@ -1371,7 +1380,12 @@ int tc_stream_run(rb_handle* h, int ob, int oe, int B, int F, const void* in, vo
         rs.base[k] = reinterpret_cast<uint4*>(b.p);
         rs.ld[k] = b.ld; rs.hist[k] = b.hist; rs.n[k] = b.n;
         rs.skip[k] = std::max(0, b.hist - h->slots[u].hist);
-        rs.first[k + 1] = rs.first[k] + B * (b.cp / 8);
+        const int state = b.hist - rs.skip[k];
+        int lpb = 2;
+        while (lpb < 32 && lpb < state) lpb <<= 1;
+        rs.lpb[k] = lpb;
+        rs.nblk[k] = B * (b.cp / 8);
+        rs.first[k + 1] = rs.first[k] + (rs.nblk[k] + 32 / lpb - 1) / (32 / lpb);
         if (rs.count == ROLL_MAX) { int rc = flush(); if (rc) return rc; }
       }
     }
