@@ -348,13 +348,13 @@ def run_ours(args):
         tp = os.path.join(ROOT, "profiles", name)
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get("dram_bytes_per_step")
-            traffic_src = f"profiles/{name} (ncu dram__bytes_read + dram__bytes_write over the 46 launches of one step of this command, tools/traffic.py; an earlier run, not measured in this one)"
+            traffic_src = f"profiles/{name} (ncu dram__bytes_read + dram__bytes_write over the tc_conv / tc_du_pair launches of one step of this command, tools/traffic.py; an earlier run, not measured in this one)"
             break
     per_op_tf = conv_flops / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
     hbm_gbs = conv_bytes / (conv_ms / 1e3) / 1e9 if conv_ms > 0 else 0.0
     roofline = {"bound": "tensor", "achieved": achieved, "peak": pk["tf_sus"], "unit": "TFLOP/s",
                 "frac": achieved / pk["tf_sus"], "traffic": traffic, "traffic_source": traffic_src,
-                "kernel": "tc_conv_kernel: the %d launches of one step (%.2f of %.2f ms of per-op CUDA-event time); "
+                "kernel": "tc_conv_kernel / tc_du_pair_kernel: the %d launches of one step (%.2f of %.2f ms of per-op CUDA-event time); "
                           "achieved = algorithmic flops of the step / ms_per_step" % (n_launch, conv_ms, sum(op_ms)),
                 "peak_source": pk["src"] + ", sustained bf16",
                 "algorithmic_flops_per_step_per_gpu": flops_step,

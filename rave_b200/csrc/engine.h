@@ -128,6 +128,7 @@ struct rb_handle {
   std::vector<Ev> events;
 
   void* tc = nullptr;           // rb::tc::Plan of the bf16 engine (tc_engine.cu)
+  std::vector<int> tc_sact_hint;  // testing hook only: per-slot "stored activated" flags that replace the planner's
 
   std::atomic_flag busy = ATOMIC_FLAG_INIT;
   long long launches = 0;

@@ -1403,6 +1403,231 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Residual(DilatedUnit) at C = 256 in ONE launch (blocks.py:84-113 + :32-46): a cluster pair runs both GEMMs as
+// cta_group::2 MMAs (M = 256: each CTA's own 128-row tile, each CTA streams and holds 128 of the 256 rows of
+// every weight block), h never leaves the SM:
+//     GEMM1  D1 = conv3_d(z)            48 MMAs, A from shared memory (taps = start-row shifts), -> TMEM [0, 256)
+//     E1     h  = leaky(D1 + b3)        packed bf16 written back into D1's own columns (tcgen05.st)
+//     GEMM2  D2 = h W1^T                16 MMAs, A from TENSOR MEMORY                            -> TMEM [256, 512)
+//     E2     y  = leaky(D2 + b1 + x)    residual from global memory (the unit's input, L2-hot), 16-byte stores
+// Unfused, the 1x1 conv + residual launch sits at its HBM roofline (h written and read back: 0.54 GB per unit).
+// One warp issues both GEMMs: tcgen05.mma executes in issue order, so GEMM1 of the next tile may overwrite
+// D1 / h without a barrier; only D2 is handed back by the epilogue (D2_EMPTY).  The peer's MMA warp relays its
+// CTA's barriers to the leader like the CG2 kernel above.  Warps: 0-15 output (E1 then E2 of every tile), 16 MMA /
+// relay, 17 W producer, 18 A producer.  TMEM is full (512 columns): one tile in flight, E1 is exposed
+// (the tensor pipe waits for it), E2 runs under GEMM1 of the next tile.
+__global__ void __launch_bounds__(TC_THREADS, 1)
+    tc_du_pair_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcTmap tmx) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_COUNT * 8);
+  float* bias_s = reinterpret_cast<float*>(smem + p.off_bias);
+  float* bias2_s = bias_s + 256;
+  uint8_t* a_smem = smem + p.off_a;
+  uint8_t* w_smem = smem + p.off_w;
+  const uint32_t bar0 = smem_u32(bars);
+  auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+  int tid;
+  asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));
+  const int warp = tid >> 5, lane = tid & 31;
+  constexpr uint32_t tmask = 0xffffffffu;                 // no event trace in this kernel
+  asm volatile("griddepcontrol.launch_dependents;");
+  const uint32_t rank = cluster_ctarank();
+  const uint32_t lead = rank == 0 ? 1u : 0u;
+  constexpr int W_MMA = 16, W_WPROD = 17, W_APROD = 18;
+  constexpr int N = 256, NKC2 = 4;                        // channels; K chunks of the 1x1 conv (KC = 64)
+  if (tid == 0) {
+    for (int i = 0; i < MAX_SA; ++i) {
+      mbar_init(BAR(BAR_A_FULL + i), 1 + lead);
+      mbar_init(BAR(BAR_A_EMPTY + i), 1);
+    }
+    for (int i = 0; i < MAX_SW; ++i) {
+      mbar_init(BAR(BAR_W_FULL + i), 1 + lead);
+      mbar_init(BAR(BAR_W_EMPTY + i), 1);
+    }
+    mbar_init(BAR(BAR_D_FULL), 1);
+    mbar_init(BAR(BAR_H_FULL), 16 + lead);
+    mbar_init(BAR(BAR_D2_FULL), 1);
+    mbar_init(BAR(BAR_D2_EMPTY), 16 + lead);
+    fence_mbar_init();
+  }
+  for (int i = tid; i < N; i += TC_THREADS) {
+    bias_s[i] = p.bias ? p.bias[i] : 0.f;
+    bias2_s[i] = p.bias2 ? p.bias2[i] : 0.f;
+  }
+  if (warp == W_MMA) {
+    tmem_alloc2(smem_u32(tmem_slot), 512);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  cluster_sync();
+  if (warp != W_WPROD) asm volatile("griddepcontrol.wait;" ::: "memory");
+
+  const int ksteps = p.KC >> 4;                           // 4
+  const int nblk1 = p.n_kchunks * p.n_taps;               // weight blocks of GEMM1 per tile (12)
+  if (warp == W_APROD) {
+    if (lane == 0) prefetch_tmap(&tmx);
+    Ring ra;
+    WorkIter wi;
+    for (wi.init(p); wi.left > 0; wi.next(p)) {
+      const Work wk = wi.work(p);
+      for (int kc = 0; kc < p.n_kchunks; ++kc) {
+        const uint32_t sa = ra.idx;
+        mbar_wait(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1);
+        issue_a_tma(p, &tmx, wk.b, wk.t0 - p.off, kc, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes),
+                    BAR(BAR_A_FULL + sa), lane);
+        ra.next(p.SA);
+      }
+    }
+  } else if (warp == W_WPROD) {
+    if (lane == 0) {
+      Ring rw;
+      WorkIter wi;
+      for (wi.init(p); wi.left > 0; wi.next(p)) {
+        for (int blk = 0; blk < nblk1 + NKC2; ++blk) {     // conv3 blocks in (K chunk, tap) order, then the 1x1 conv's
+          const uint32_t sw = rw.idx;
+          mbar_wait(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
+          mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
+          bulk_g2s(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes),
+                   reinterpret_cast<const uint8_t*>(p.w) + ((size_t)blk * 2 + rank) * p.w_blk_bytes, p.w_blk_bytes,
+                   BAR(BAR_W_FULL + sw));
+          rw.next(p.SW);
+        }
+      }
+    }
+  } else if (warp == W_MMA) {
+    const bool leader = elect_one();
+    Ring ra, rw;
+    WorkIter wi;
+    uint32_t it = 0;
+    if (lead) {
+      const uint32_t idesc2 = make_idesc_bf16(256, N);
+      const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem);
+      const uint32_t dhi = desc_hi(128u);
+      const uint32_t lbo_a = (uint32_t)p.R_ALLOC * 16u, lbo_w = 128u * 16u;
+      const uint32_t a_lbo_bits = ((lbo_a >> 4) & 0x3FFFu) << 16, w_lbo_bits = ((lbo_w >> 4) & 0x3FFFu) << 16;
+      const uint32_t a_kadd = (2u * lbo_a) >> 4, w_kadd = (2u * lbo_w) >> 4;
+      for (wi.init(p); wi.left > 0; wi.next(p), ++it) {
+        // GEMM1 -> D1 (in issue order behind GEMM2 of the previous tile, which reads h from the same columns)
+        uint32_t acc = 0;
+        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+          const uint32_t sa = ra.idx;
+          mbar_wait(BAR(BAR_A_FULL + sa), ra.ph);
+          ra.next(p.SA);
+          tc_fence_after();
+          const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
+          for (int j = 0; j < p.n_taps; ++j) {
+            const uint32_t sw = rw.idx;
+            mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
+            rw.next(p.SW);
+            tc_fence_after();
+            uint32_t bl = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+            uint32_t al = alo0 + (uint32_t)(j * p.dil);
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              if (leader) mma2_bf16_lohi(tmem, al, bl, dhi, idesc2, acc);
+              acc = 1;
+              al += a_kadd;
+              bl += w_kadd;
+            }
+            if (leader) mma2_commit(BAR(BAR_W_EMPTY + sw));
+          }
+          if (leader) mma2_commit(BAR(BAR_A_EMPTY + sa));
+        }
+        if (leader) mma2_commit(BAR(BAR_D_FULL));
+        // GEMM2: A = h in tensor memory (K step k at columns [16 k, 16 k + 8) of D1), D2 at columns [256, 512)
+        mbar_wait(BAR(BAR_H_FULL), it & 1);
+        mbar_wait(BAR(BAR_D2_EMPTY), (it & 1) ^ 1);
+        tc_fence_after();
+        uint32_t at = tmem, acc2 = 0;
+        for (int kc = 0; kc < NKC2; ++kc) {
+          const uint32_t sw = rw.idx;
+          mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
+          rw.next(p.SW);
+          tc_fence_after();
+          uint32_t bl = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            if (leader) mma2_bf16_ts(tmem + (uint32_t)N, at, bl, dhi, idesc2, acc2);
+            acc2 = 1;
+            at += 16u;
+            bl += w_kadd;
+          }
+          if (leader) mma2_commit(BAR(BAR_W_EMPTY + sw));
+        }
+        if (leader) mma2_commit(BAR(BAR_D2_FULL));
+      }
+      (void)ksteps;
+    } else {
+      // relay: this CTA's stages, in the order the leader waits for them
+      auto fwd = [&](int b) { if (leader) mbar_arrive_cluster(mapa_shared(BAR(b), 0)); };
+      for (wi.init(p); wi.left > 0; wi.next(p), ++it) {
+        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+          const uint32_t sa = ra.idx;
+          mbar_wait(BAR(BAR_A_FULL + sa), ra.ph);
+          ra.next(p.SA);
+          fwd(BAR_A_FULL + sa);
+          for (int j = 0; j < p.n_taps; ++j) {
+            const uint32_t sw = rw.idx;
+            mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
+            rw.next(p.SW);
+            fwd(BAR_W_FULL + sw);
+          }
+        }
+        mbar_wait(BAR(BAR_H_FULL), it & 1);
+        fwd(BAR_H_FULL);
+        if (it > 0) {                                      // the first tile needs no drained D2 (see relay_cg2)
+          mbar_wait(BAR(BAR_D2_EMPTY), (it & 1) ^ 1);
+          fwd(BAR_D2_EMPTY);
+        }
+        for (int kc = 0; kc < NKC2; ++kc) {
+          const uint32_t sw = rw.idx;
+          mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
+          rw.next(p.SW);
+          fwd(BAR_W_FULL + sw);
+        }
+      }
+    }
+  } else if (warp < 16) {
+    const int rit = (warp & 3) * 32 + lane;
+    const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
+    const int part = warp >> 2;                            // 4 column parts
+    WorkIter wi;
+    uint32_t it = 0;
+    for (wi.init(p); wi.left > 0; wi.next(p), ++it) {
+      const Work wk = wi.work(p);
+      // E1: pieces 16 part + 64 i -- every warp finishes the lower K half of h before the upper one
+      mbar_wait(BAR(BAR_D_FULL), it & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int i = 0; i < 4; ++i) {
+        const int c = 16 * part + 64 * i;
+        h_chunk<RB_ACT_LEAKY, 16, true>(tmem + lane_base + (uint32_t)c, bias_s + c, nullptr, 0, nullptr);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(BAR(BAR_H_FULL));
+      // E2
+      drain_res16(p, BAR(BAR_D2_FULL), it & 1, tmem + lane_base + (uint32_t)N, bias2_s, wk, rit, part, 4, N,
+                  0xffffffffu);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(BAR(BAR_D2_EMPTY));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();
+  if (warp == W_MMA) {
+    tc_fence_after();
+    tmem_dealloc2(tmem, 512);
+  }
+}
+
 template <int PRE, int ACT2, bool FUSED, int DR, bool TR = false, int NS = 2, bool CG2 = false, bool HT = false>
 static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStream_t s) {
   static bool attr_set = false;
@@ -1465,6 +1690,56 @@ static int make_tmap(const TcParams& p, TcTmap* tm) {
            "cuTensorMapEncodeTiled failed (%d): dims {8,%d,%d,%d,%d} strides {%lld,%lld,%lld,%lld} box {%d,%d}", (int)r,
            phases, x.n - x.lo, g1, p.B, (long long)strides[0], (long long)strides[1], (long long)strides[2],
            (long long)strides[3], p.a_box_rows, p.a_gb);
+  return RB_OK;
+}
+
+// Launches tc_du_pair_kernel: p as for a plain cta_group::2 conv3 launch (x / y / res views, w = N-split weight
+// halves of conv3 followed by the 1x1 conv's, bias / bias2), geometry filled by the engine.
+int launch_tc_du_pair(TcParams& p, cudaStream_t s) {
+  if (p.n_work <= 0) return RB_OK;
+  static int n_sm = 0;
+  if (!n_sm) {
+    int dev = 0;
+    RB_CUDA(cudaGetDevice(&dev));
+    RB_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+  }
+  RB_CHECK(p.smem_bytes <= 227u * 1024u && p.N_TILE == 256 && p.KC == 64 && p.n_kchunks == 4 && p.n_ntiles == 1 &&
+               p.pair == 1 && p.MT == 1 && p.res.p && p.pre_act == RB_ACT_NONE && p.SW <= MAX_SW && p.SA <= MAX_SA,
+           RB_ERR_INVALID, "pair DilatedUnit launch outside its envelope");
+  const int slots = n_sm / 2;
+  const int stride = p.n_work < slots ? p.n_work : slots;
+  {
+    const int rt = stride / p.n_ntiles;
+    p.step_nt = stride - rt * p.n_ntiles;
+    p.step_b = rt / p.tiles_per_stream;
+    p.step_tile = rt - p.step_b * p.tiles_per_stream;
+  }
+  TcTmap tm;
+  int rc = make_tmap(p, &tm);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    RB_CUDA(cudaFuncSetAttribute(tc_du_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * stride);
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = p.smem_bytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  attr[1].id = cudaLaunchAttributeClusterDimension;
+  attr[1].val.clusterDim.x = 2;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_du_pair_kernel, p, tm));
+  ++g_launches;
+  RB_CUDA(cudaGetLastError());
   return RB_OK;
 }
 

@@ -110,6 +110,8 @@ struct alignas(64) TcTmap {
 
 // Fills the step_* fields and the tensor map from p.x, then launches.
 int launch_tc_conv(TcParams& p, cudaStream_t s);
+// Residual(DilatedUnit) at C = 256 as one cluster-pair launch (tc_conv.cu: tc_du_pair_kernel).
+int launch_tc_du_pair(TcParams& p, cudaStream_t s);
 
 }  // namespace tc
 }  // namespace rb

@@ -42,6 +42,7 @@ struct Layer {
   float* alpha = nullptr;         // device [cin_v]   (Snake pre-activation)
   // fused DilatedUnit: this layer also carries the 1x1 conv that follows it
   bool fused = false;
+  bool pairdu = false;            // C = 256 unit run by tc_du_pair_kernel (cluster pair, both convs in one launch)
   int fused_with = -1;            // op index of the 1x1 conv
   // op whose dst this launch writes: the fused 1x1 conv, or a HEAD_V2 op folded into the epilogue
   int tail = -1;
@@ -324,11 +325,13 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
   }
   int rc = dev_upload(blocks, &L.w);
   if (rc) return rc;
-  if (!extra && L.N_TILE == 256) {
+  if (L.N_TILE == 256) {
     // N-split twin for cta_group::2: block [n][c] -> half n / 128, then the same core-matrix order over 128 rows
+    // (a pair DilatedUnit's 1x1 conv blocks included)
     std::vector<__nv_bfloat16> b2(blocks.size());
     const size_t be = (size_t)L.N_TILE * L.KC, he = be / 2;
-    for (int b = 0; b < nblk; ++b)
+    const int nb_all = (int)(blocks.size() / be);
+    for (int b = 0; b < nb_all; ++b)
       for (int n = 0; n < L.N_TILE; ++n)
         for (int c = 0; c < L.KC; ++c)
           b2[b * be + (size_t)(n >> 7) * he + (size_t)(c >> 3) * (128 * 8) + (size_t)(n & 127) * 8 + (c & 7)] =
@@ -584,6 +587,63 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
             L.fout, L.KC, p.w_resident, p.fused, p.pair, p.cg2, p.MT, p.SA, p.SW, p.SD, p.pair_mode, p.y.n, p.n_work,
             p.smem_bytes);
   return launch_tc_conv(p, s);
+}
+
+// Residual(DilatedUnit) at C = 256 through tc_du_pair_kernel: x (activated storage) -> y, residual = x.
+static int run_pair_du(const Layer& L, const rb_op& op, const Buf& src, const Buf& dst, int B, cudaStream_t s,
+                       int res_act, int out_act) {
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  int rc = make_view(src, 1, &p.x);
+  if (rc) return rc;
+  if ((rc = make_view(dst, 1, &p.y))) return rc;
+  if ((rc = make_view(src, 1, &p.res))) return rc;
+  RB_CHECK(p.x.C == 256 && p.y.C == 256, RB_ERR_INVALID, "pair DilatedUnit: 256 channels expected");
+  p.w = L.w2; p.masks = L.masks; p.bias = L.bias; p.bias2 = L.bias2;
+  p.pre_act = RB_ACT_NONE; p.act2 = RB_ACT_LEAKY;
+  p.out_act = out_act ? RB_ACT_LEAKY : RB_ACT_NONE;
+  p.res_act = res_act ? 1 : 0;
+  p.B = B;
+  p.n_taps = L.n_taps; p.dil = L.dil; p.off = L.off;
+  p.KC = L.KC; p.n_kchunks = L.n_kchunks;
+  p.N_TILE = L.N_TILE; p.n_ntiles = 1;
+  p.nt_base[0] = 0; p.nt_base[1] = L.total_blocks;
+  p.MT = 1; p.pair = 1; p.cg2 = 1; p.fused = 1; p.h_tmem = 1; p.n_blk1 = L.total_blocks;
+  p.w_blk_bytes = L.blk_bytes / 2;
+  const int halo = (L.n_taps - 1) * L.dil;
+  p.R = 128 + halo;
+  {
+    const int c8n = L.KC / 8;
+    const int r8 = (p.R + 7) & ~7;
+    RB_CHECK(r8 <= 256, RB_ERR_UNSUPPORTED, "pair DilatedUnit: dilation too large");
+    p.R_ALLOC = r8; p.a_rsplit = 1; p.a_box_rows = r8;
+    int gb = c8n;
+    const int g1 = p.x.G1;
+    while (g1 % gb) --gb;
+    while (c8n % gb) --gb;
+    p.a_gb = gb;
+    p.a_tx_bytes = (uint32_t)c8n * p.R_ALLOC * 16u;
+    p.a_flat = (p.x.sT == 1) ? 1 : 0;
+  }
+  p.a_stage_bytes = (uint32_t)(L.KC / 8) * p.R_ALLOC * 16u;
+  const uint32_t budget = 224u * 1024u;
+  p.off_bias = 640 + TC_MAX_MASKS * 8;
+  const uint32_t fixed = align_up(p.off_bias + 512u * 4u, 128);
+  p.SW = 6;
+  if (const char* e = getenv("RB_TC_PD_SW")) p.SW = std::min(8, std::max(2, atoi(e)));   // experiments only
+  const uint32_t w_bytes = p.SW * p.w_blk_bytes;
+  p.SA = (int)std::min<uint32_t>(12, (budget - fixed - w_bytes) / p.a_stage_bytes);
+  RB_CHECK(p.SA >= 2, RB_ERR_UNSUPPORTED, "pair DilatedUnit does not fit in shared memory");
+  p.off_a = fixed;
+  p.off_w = p.off_a + p.SA * p.a_stage_bytes;
+  p.smem_bytes = p.off_w + w_bytes;
+  p.SD = 1; p.tmem_cols = 512;
+  p.tiles_per_stream = ((p.y.n + 127) / 128 + 1) / 2;     // work slots: one 128-row tile per CTA of a pair
+  p.n_work = B * p.tiles_per_stream;
+  if (getenv("RB_TC_PLAN_DEBUG"))
+    fprintf(stderr, "tc layer: pair DilatedUnit C 256 dil %d | SA %d SW %d rows %d work %d smem %u\n", L.dil, p.SA, p.SW,
+            p.y.n, p.n_work, p.smem_bytes);
+  return launch_tc_du_pair(p, s);
 }
 
 // ------------------------------------------------------------------- elementwise kernels
@@ -855,6 +915,7 @@ int tc_pack_weights(rb_handle* h) {
     bad(h->spec.noise_slot);
     pl->sact.assign(ns, 0);
     for (int sl = 0; sl < ns; ++sl) pl->sact[sl] = ok[sl] && conv_reads[sl] > 0 && conv_writes[sl] > 0;
+    if ((int)h->tc_sact_hint.size() == ns) pl->sact = h->tc_sact_hint;     // rb_debug_conv_bf16
   }
   for (int i = 0; i < nops; ++i) {
     const rb_op& op = h->ops[i];
@@ -864,7 +925,7 @@ int tc_pack_weights(rb_handle* h) {
     int rc = build_view_weight(h, i, *pl, v);
     if (rc) return rc;
     // DilatedUnit fusion: conv(k, dil) -> act -> conv(1x1) + residual of the unit's input
-    bool fuse = false;
+    bool fuse = false, pairdu = false;
     ViewWeight v2;
     if (op.kind == RB_OP_CONV && i + 1 < nops && i + 1 != h->spec.n_enc_ops) {
       const rb_op& o2 = h->ops[i + 1];
@@ -872,18 +933,37 @@ int tc_pack_weights(rb_handle* h) {
              op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 && o2.pre_act == op.pre_act &&
              v.N_total == v.cin_v && v.N_total <= 128 && pl->cp[o2.dst] == v.N_total &&
              (size_t)v.N_total * v.cin_v * (v.n_taps + 1) * 2 <= (size_t)128 * 1024;
-      if (fuse) {
+      // C = 256 (offline LeakyReLU nets on activated storage): both convs in one cluster-pair launch
+      pairdu = !fuse && o2.kind == RB_OP_CONV && o2.k == 1 && o2.stride == 1 && o2.ileave <= 1 && op.stride == 1 &&
+               op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 && o2.pre_act == op.pre_act &&
+               op.pre_act == RB_ACT_LEAKY && v.N_total == 256 && v.cin_v == 256 && v.n_taps == 3 &&
+               pl->cp[o2.dst] == 256 && !h->spec.streaming && pl->sact[op.src] && op.has_bias && o2.has_bias &&
+               !getenv("RB_TC_NOPAIRDU");
+      if (pairdu)
+        for (int j = 0; j < nops; ++j)                   // h must have no other reader
+          if (j != i + 1 && (h->ops[j].src == op.dst || h->ops[j].res == op.dst || h->ops[j].src2 == op.dst)) pairdu = false;
+      if (fuse || pairdu) {
         rc = build_view_weight(h, i + 1, *pl, v2);
         if (rc) return rc;
       }
     }
-    if (!fuse && op.res < 0 && !h->spec.streaming) {   // (streaming keeps plain row views: history alignment)
+    if (!fuse && !pairdu && op.res < 0 && !h->spec.streaming) {   // (streaming keeps plain row views: history alignment)
       const int F = choose_row_batch(v, h->slots[op.dst].per_frame / v.fout);
       if (F > 1) batch_rows(v, F);
     }
     Layer& L = pl->layers[i];
-    rc = pack_layer(v, 64, fuse ? &v2 : nullptr, L);
+    rc = pack_layer(v, 64, (fuse || pairdu) ? &v2 : nullptr, L);
     if (rc) return rc;
+    if (pairdu) {
+      RB_CHECK(L.w2 && L.N_TILE == 256 && L.KC == 64 && L.n_kchunks == 4 && L.total_blocks == 12, RB_ERR_STATE,
+               "pair DilatedUnit: unexpected packing");
+      L.pairdu = true;
+      L.fused_with = i + 1;
+      L.tail = i + 1;
+      L.act2 = h->ops[i + 1].pre_act;
+      if ((rc = dev_upload(v2.bias, &L.bias2))) return rc;
+      pl->skip[i + 1] = 1;
+    }
     if (h->spec.streaming && op.kind == RB_OP_CONV && v.out_mask == 0 &&
         pl->cp[op.src] != 1 && pl->cp[op.dst] != 1 &&
         h->slots[op.dst].per_frame / v.fout <= (fuse ? 32 : 8) &&      // fused units: also the 32-row C = 128 stage
@@ -964,6 +1044,11 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
     case RB_OP_PQMF_INV: {
       RB_CHECK(L.valid, RB_ERR_STATE, "op %d has no bf16 plan", i);
       const std::vector<int>& sa = pl->sact;
+      if (L.pairdu) {
+        const rb_op& o2 = h->ops[L.fused_with];
+        RB_CHECK(sa[op.src], RB_ERR_STATE, "pair DilatedUnit: input is not stored activated");
+        return run_pair_du(L, op, bufs[op.src], bufs[o2.dst], B, s, sa[o2.res], sa[o2.dst]);
+      }
       if (L.fused) {
         const rb_op& o2 = h->ops[L.fused_with];
         const Layer& S = pl->sr_layers[i];
@@ -1450,6 +1535,14 @@ extern "C" int rb_debug_conv_bf16(const rb_debug_conv* d) {
       h->w[i].alpha_host.assign(d->alpha[i], d->alpha[i] + op.c_in);
     }
   }
+  {
+    // activated-storage flags of the four slots, known to the planner (a C = 256 pair needs its input activated)
+    const int osl = d->n_ops == 2 ? 2 : 1;
+    h->tc_sact_hint.assign(h->slots.size(), 0);
+    h->tc_sact_hint[0] = (d->flags & 1) ? 1 : 0;
+    h->tc_sact_hint[osl] = (d->flags & 2) ? 1 : 0;
+    h->tc_sact_hint[3] = (d->flags & 4) ? 1 : 0;
+  }
   int rc = tc_pack_weights(h);
   if (rc) { tc_free(h); return rc; }
   Plan* pl = (Plan*)h->tc;
@@ -1513,7 +1606,7 @@ extern "C" int rb_debug_conv_bf16(const rb_debug_conv* d) {
       for (int c = 0; c < C; ++c)
         for (int t = 0; t < b.n; ++t)
           d->y[((size_t)bi * C + c) * b.n + t] = __bfloat162float(tmp[(((size_t)bi * (b.cp >> 3) + (c >> 3)) * b.n + t) * 8 + (c & 7)]);
-    if (d->fused_out) *d->fused_out = pl->layers[0].fused ? 1 : 0;
+    if (d->fused_out) *d->fused_out = pl->layers[0].pairdu ? 2 : (pl->layers[0].fused ? 1 : 0);
   }
   for (void* p : to_free) cudaFree(p);
   tc_free(h);

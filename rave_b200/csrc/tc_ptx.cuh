@@ -314,6 +314,20 @@ __device__ __forceinline__ void mma2_bf16_lohi(uint32_t d_tmem, uint32_t a_lo, u
       "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// the same with the A operand (each CTA's 128 rows) in tensor memory
+__device__ __forceinline__ void mma2_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t hi,
+                                             uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .b64 db;\n"
+      "setp.ne.b32 p, %5, 0;\n"
+      "mov.b64 db, {%2, %3};\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], db, %4, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // arrives on the mbarrier at this offset in BOTH CTAs once every MMA issued so far has completed
 __device__ __forceinline__ void mma2_commit(uint32_t bar) {
   asm volatile(
