@@ -1426,6 +1426,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   float* bias2_s = bias_s + 256;
   uint8_t* a_smem = smem + p.off_a;
   uint8_t* w_smem = smem + p.off_w;
+  uint8_t* w1_smem = smem + p.off_h;                      // this CTA's 128 rows of the 1x1 conv's four blocks, resident
   const uint32_t bar0 = smem_u32(bars);
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   int tid;
@@ -1446,8 +1447,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       mbar_init(BAR(BAR_W_FULL + i), 1 + lead);
       mbar_init(BAR(BAR_W_EMPTY + i), 1);
     }
+    mbar_init(BAR(BAR_RAW_FULL), 1 + lead);              // resident 1x1-conv weights landed (once)
     mbar_init(BAR(BAR_D_FULL), 1);
-    mbar_init(BAR(BAR_H_FULL), 16 + lead);
+    mbar_init(BAR(BAR_H_FULL), 16 + lead);               // lower K half of h (columns [0, 128) of D1)
+    mbar_init(BAR(BAR_H_FULL + 1), 16 + lead);           // upper K half
     mbar_init(BAR(BAR_D2_FULL), 1);
     mbar_init(BAR(BAR_D2_EMPTY), 16 + lead);
     fence_mbar_init();
@@ -1485,10 +1488,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     }
   } else if (warp == W_WPROD) {
     if (lane == 0) {
+      // the 1x1 conv's weights once (they follow conv3's blocks), then conv3's blocks of every tile through the ring:
+      // while E1 and GEMM2 of a tile run, the ring fills with the first blocks of the next tile's GEMM1
+      mbar_expect_tx(BAR(BAR_RAW_FULL), (uint32_t)NKC2 * p.w_blk_bytes);
+      for (int kc = 0; kc < NKC2; ++kc)
+        bulk_g2s(smem_u32(w1_smem + (size_t)kc * p.w_blk_bytes),
+                 reinterpret_cast<const uint8_t*>(p.w) + ((size_t)(nblk1 + kc) * 2 + rank) * p.w_blk_bytes, p.w_blk_bytes,
+                 BAR(BAR_RAW_FULL));
       Ring rw;
       WorkIter wi;
       for (wi.init(p); wi.left > 0; wi.next(p)) {
-        for (int blk = 0; blk < nblk1 + NKC2; ++blk) {     // conv3 blocks in (K chunk, tap) order, then the 1x1 conv's
+        for (int blk = 0; blk < nblk1; ++blk) {            // conv3 blocks in (K chunk, tap) order
           const uint32_t sw = rw.idx;
           mbar_wait(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
           mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
@@ -1506,7 +1516,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     uint32_t it = 0;
     if (lead) {
       const uint32_t idesc2 = make_idesc_bf16(256, N);
-      const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem);
+      const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem), w10 = smem_u32(w1_smem);
+      mbar_wait(BAR(BAR_RAW_FULL), 0);
+      tc_fence_after();
       const uint32_t dhi = desc_hi(128u);
       const uint32_t lbo_a = (uint32_t)p.R_ALLOC * 16u, lbo_w = 128u * 16u;
       const uint32_t a_lbo_bits = ((lbo_a >> 4) & 0x3FFFu) << 16, w_lbo_bits = ((lbo_w >> 4) & 0x3FFFu) << 16;
@@ -1540,16 +1552,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
         }
         if (leader) mma2_commit(BAR(BAR_D_FULL));
         // GEMM2: A = h in tensor memory (K step k at columns [16 k, 16 k + 8) of D1), D2 at columns [256, 512)
+        // (the lower K half as soon as E1 has written it: the upper half of E1 runs under these MMAs)
         mbar_wait(BAR(BAR_H_FULL), it & 1);
         mbar_wait(BAR(BAR_D2_EMPTY), (it & 1) ^ 1);
         tc_fence_after();
         uint32_t at = tmem, acc2 = 0;
         for (int kc = 0; kc < NKC2; ++kc) {
-          const uint32_t sw = rw.idx;
-          mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
-          rw.next(p.SW);
-          tc_fence_after();
-          uint32_t bl = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+          if (kc == NKC2 / 2) {
+            mbar_wait(BAR(BAR_H_FULL + 1), it & 1);
+            tc_fence_after();
+          }
+          uint32_t bl = (((w10 + (uint32_t)kc * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {
             if (leader) mma2_bf16_ts(tmem + (uint32_t)N, at, bl, dhi, idesc2, acc2);
@@ -1557,7 +1570,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
             at += 16u;
             bl += w_kadd;
           }
-          if (leader) mma2_commit(BAR(BAR_W_EMPTY + sw));
         }
         if (leader) mma2_commit(BAR(BAR_D2_FULL));
       }
@@ -1565,6 +1577,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     } else {
       // relay: this CTA's stages, in the order the leader waits for them
       auto fwd = [&](int b) { if (leader) mbar_arrive_cluster(mapa_shared(BAR(b), 0)); };
+      mbar_wait(BAR(BAR_RAW_FULL), 0);
+      fwd(BAR_RAW_FULL);
       for (wi.init(p); wi.left > 0; wi.next(p), ++it) {
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           const uint32_t sa = ra.idx;
@@ -1584,12 +1598,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
           mbar_wait(BAR(BAR_D2_EMPTY), (it & 1) ^ 1);
           fwd(BAR_D2_EMPTY);
         }
-        for (int kc = 0; kc < NKC2; ++kc) {
-          const uint32_t sw = rw.idx;
-          mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
-          rw.next(p.SW);
-          fwd(BAR_W_FULL + sw);
-        }
+        mbar_wait(BAR(BAR_H_FULL + 1), it & 1);
+        fwd(BAR_H_FULL + 1);
       }
     }
   } else if (warp < 16) {
@@ -1604,17 +1614,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       mbar_wait(BAR(BAR_D_FULL), it & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int i = 0; i < 4; ++i) {
-        const int c = 16 * part + 64 * i;
-        h_chunk<RB_ACT_LEAKY, 16, true>(tmem + lane_base + (uint32_t)c, bias_s + c, nullptr, 0, nullptr);
+      for (int half = 0; half < 2; ++half) {
+#pragma unroll 1
+        for (int i = 0; i < 2 && !(p.dbg & 1); ++i) {
+          const int c = 16 * part + 64 * (2 * half + i);
+          h_chunk<RB_ACT_LEAKY, 16, true>(tmem + lane_base + (uint32_t)c, bias_s + c, nullptr, 0, nullptr);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(BAR(BAR_H_FULL + half));
       }
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(BAR(BAR_H_FULL));
       // E2
-      drain_res16(p, BAR(BAR_D2_FULL), it & 1, tmem + lane_base + (uint32_t)N, bias2_s, wk, rit, part, 4, N,
-                  0xffffffffu);
+      if (p.dbg & 2) mbar_wait(BAR(BAR_D2_FULL), it & 1);   // (timing experiments: no drain)
+      else
+        drain_res16(p, BAR(BAR_D2_FULL), it & 1, tmem + lane_base + (uint32_t)N, bias2_s, wk, rit, part, 4, N,
+                    0xffffffffu);
       __syncwarp();
       if (lane == 0) mbar_arrive(BAR(BAR_D2_EMPTY));
     }

@@ -68,6 +68,7 @@ struct TcParams {
   int pair;                 // 1: clusters of two CTAs share each streamed weight block (half each, multicast)
   int cg2;                  // pair + 1: the pair runs tcgen05.mma.cta_group::2 (M = 256; w holds the N-split block layout,
                             // w_blk_bytes = one CTA's half block)
+  int dbg;                  // timing experiments only (RB_TC_PD_DBG): 1 skip E1 math, 2 skip E2 drain of the pair unit
   int cg2_spin;             // cta_group::2 waits: bit 0 producers / epilogue / relay spin, bit 1 the leader's MMA warp spins
   int dual_g1;              // resident + narrow: two warps issue GEMM1 of alternate work items
   // A tile TMA boxes (tensor map over the input view, see launch_tc_conv): a chunk of KC/8

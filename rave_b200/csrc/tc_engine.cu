@@ -629,15 +629,21 @@ static int run_pair_du(const Layer& L, const rb_op& op, const Buf& src, const Bu
   const uint32_t budget = 224u * 1024u;
   p.off_bias = 640 + TC_MAX_MASKS * 8;
   const uint32_t fixed = align_up(p.off_bias + 512u * 4u, 128);
+  // shared memory: the 1x1 conv's four half blocks resident (64 KB), a ring of conv3 half blocks deep enough to
+  // hold the first half of the next tile's weights while E1 / GEMM2 of this tile run, and >= 3 A stages
+  const uint32_t w1_bytes = 4u * p.w_blk_bytes;
   p.SW = 6;
   if (const char* e = getenv("RB_TC_PD_SW")) p.SW = std::min(8, std::max(2, atoi(e)));   // experiments only
+  while (p.SW > 2 && fixed + w1_bytes + p.SW * p.w_blk_bytes + 3 * p.a_stage_bytes > budget) --p.SW;
   const uint32_t w_bytes = p.SW * p.w_blk_bytes;
-  p.SA = (int)std::min<uint32_t>(12, (budget - fixed - w_bytes) / p.a_stage_bytes);
+  p.SA = (int)std::min<uint32_t>(12, (budget - fixed - w1_bytes - w_bytes) / p.a_stage_bytes);
   RB_CHECK(p.SA >= 2, RB_ERR_UNSUPPORTED, "pair DilatedUnit does not fit in shared memory");
   p.off_a = fixed;
   p.off_w = p.off_a + p.SA * p.a_stage_bytes;
-  p.smem_bytes = p.off_w + w_bytes;
+  p.off_h = p.off_w + w_bytes;                             // (resident 1x1-conv weights)
+  p.smem_bytes = p.off_h + w1_bytes;
   p.SD = 1; p.tmem_cols = 512;
+  if (const char* e = getenv("RB_TC_PD_DBG")) p.dbg = atoi(e);                           // experiments only
   p.tiles_per_stream = ((p.y.n + 127) / 128 + 1) / 2;     // work slots: one 128-row tile per CTA of a pair
   p.n_work = B * p.tiles_per_stream;
   if (getenv("RB_TC_PLAN_DEBUG"))
