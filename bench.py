@@ -146,8 +146,7 @@ def cpu_reference_pass(steps, warmup, T, budget_s=None):
 
 def parity_check(m, x, rows, first_stream, T):
     """Outside the timed region: rows `rows` of this rank's step output against OracleRAVE.forward (fp32
-    CPU) on the same rows.  BASELINE.json's bf16 bar is rel-L2 <= 1e-2 per program (encode, decode); the
-    forward chains both, so its bar is 2e-2 (as in tests/test_gpu_parity.py)."""
+    CPU) on the same rows, held to BASELINE.json's stated bars: rel-L2 <= 1e-2 (bf16) / 1e-3 (fp32)."""
     import numpy as np
     import torch
     from oracle.model import OracleRAVE
@@ -159,7 +158,7 @@ def parity_check(m, x, rows, first_stream, T):
     want = OracleRAVE(meta["cfg"], sd).forward(xin).numpy()
     rel = [float(np.linalg.norm(got[i].astype(np.float64) - want[i]) / np.linalg.norm(want[i]))
            for i in range(len(rows))]
-    tol = 2e-2 if x.dtype == torch.bfloat16 else 1e-3
+    tol = 1e-2 if x.dtype == torch.bfloat16 else 1e-3
     return {"rows": [int(first_stream + r) for r in rows], "rel_l2": rel, "tolerance": tol,
             "against": "OracleRAVE.forward (fp32 CPU port of the reference) on the same input rows, full length",
             "ok": bool(max(rel) < tol)}
