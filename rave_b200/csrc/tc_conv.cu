@@ -465,33 +465,34 @@ __device__ __forceinline__ void drain_smem16(const TcParams& p, uint32_t bar_ful
 // queue filled before the barrier worked as well but cost 24 register moves per piece in this rolled loop.)
 __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                             const float* bs, const Work& wk, int rit, int part, int nparts, int NT,
-                                            uint32_t tr) {
+                                            uint32_t tr, bool by16 = false) {
   constexpr uint32_t tmask = 0;                             // `tr` already carries the trace mask
   const int row = wk.t0 + rit;
   const uint32_t ysA = (uint32_t)p.y.sA, rsA = (uint32_t)p.res.sA;
+  // pieces of a warp: both halves of its 32-column chunks (part * 32, + 16, then the next chunk nparts * 32 on),
+  // or -- by16, units with fewer pieces than warps -- one 16-column piece every nparts * 16 columns
+  const int c_first = by16 ? part * 16 : part * 32;
+  const int jump = by16 ? nparts * 16 : 16 + (nparts - 1) * 32;   // from the second piece of a chunk to the next chunk
+  auto step = [&](int c) { return (by16 || (c & 16)) ? jump : 16; };
   uint4* yp = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) +
-              ((uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT) + (uint32_t)(part * 4) * ysA);
+              ((uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT) + (uint32_t)(c_first >> 3) * ysA);
   const uint4* rp = reinterpret_cast<const uint4*>(p.res.p) +
                     ((uint32_t)((long long)wk.b * p.res.sb) + (uint32_t)((p.res.hist - p.res_delay + row) * p.res.sT) +
-                     (uint32_t)(part * 4) * rsA);
+                     (uint32_t)(c_first >> 3) * rsA);
   const bool valid = row < p.y.n;
   const bool ract = p.res_act != 0, oact = p.out_act != 0;
-  const int jump = 16 + (nparts - 1) * 32;                  // from the second piece of a chunk to the next chunk
-  const uint32_t yjump = (uint32_t)(nparts * 4 - 4) * ysA, rjump = (uint32_t)(nparts * 4 - 4) * rsA;
   uint4 q0, q1, q2, q3;                                     // residual of the current piece (q0, q1) and the next (q2, q3)
   q0 = q1 = q2 = q3 = make_uint4(0u, 0u, 0u, 0u);
-  int cq = part * 32;                                       // column of the next piece to request
+  int cq = c_first;                                         // column of the next piece to request
   if (cq < NT && valid) { q0 = __ldg(rp); q1 = __ldg(rp + rsA); }
-  rp += 2 * rsA;
-  cq += 16;
+  { const int d = step(cq); rp += (uint32_t)(d >> 3) * rsA; cq += d; }
   if (cq < NT && valid) { q2 = __ldg(rp); q3 = __ldg(rp + rsA); }
-  rp += 2 * rsA + rjump;
-  cq += jump;
+  { const int d = step(cq); rp += (uint32_t)(d >> 3) * rsA; cq += d; }
   mbar_wait(bar_full, parity);
   tc_fence_after();
   TRACE(tr, 12);
 #pragma unroll 1
-  for (int c = part * 32; c < NT; c += (c & 16) ? jump : 16) {
+  for (int c = c_first; c < NT;) {
     float v[16];
     load_acc<16>(tbase + (uint32_t)c, bs + c, v);
     TRACE(tr, 13);
@@ -500,7 +501,7 @@ __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full
     q0 = q2;
     q1 = q3;
     if (cq < NT && valid) { q2 = __ldg(rp); q3 = __ldg(rp + rsA); }
-    if (cq & 16) { rp += 2 * rsA + rjump; cq += jump; } else { rp += 2 * rsA; cq += 16; }
+    { const int d = step(cq); rp += (uint32_t)(d >> 3) * rsA; cq += d; }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
@@ -518,7 +519,9 @@ __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full
       yp[0] = pack8(v);
       yp[ysA] = pack8(v + 8);
     }
-    yp += (c & 16) ? 2 * ysA + yjump : 2 * ysA;
+    const int d = step(c);
+    yp += (uint32_t)(d >> 3) * ysA;
+    c += d;
   }
   TRACE(tr, 15);
   tc_fence_before();
@@ -1404,19 +1407,23 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Residual(DilatedUnit) at C = 256 in ONE launch (blocks.py:84-113 + :32-46): a cluster pair runs both GEMMs as
-// cta_group::2 MMAs (M = 256: each CTA's own 128-row tile, each CTA streams and holds 128 of the 256 rows of
-// every weight block), h never leaves the SM:
-//     GEMM1  D1 = conv3_d(z)            48 MMAs, A from shared memory (taps = start-row shifts), -> TMEM [0, 256)
+// Residual(DilatedUnit) (blocks.py:84-113 + :32-46) at C = 64 / 128 / 256 in ONE launch by a cluster pair: both
+// GEMMs are cta_group::2 MMAs (M = 256: each CTA's own 128-row tile; each CTA holds N / 2 rows of every weight
+// block), h never leaves the SM:
+//     GEMM1  D1 = conv3_d(z)            A from shared memory (taps = start-row shifts)   -> TMEM stage s, [0, N)
 //     E1     h  = leaky(D1 + b3)        packed bf16 written back into D1's own columns (tcgen05.st)
-//     GEMM2  D2 = h W1^T                16 MMAs, A from TENSOR MEMORY                            -> TMEM [256, 512)
+//     GEMM2  D2 = h W1^T                A from TENSOR MEMORY                              -> TMEM stage s, [N, 2N)
 //     E2     y  = leaky(D2 + b1 + x)    residual from global memory (the unit's input, L2-hot), 16-byte stores
-// Unfused, the 1x1 conv + residual launch sits at its HBM roofline (h written and read back: 0.54 GB per unit).
-// One warp issues both GEMMs: tcgen05.mma executes in issue order, so GEMM1 of the next tile may overwrite
-// D1 / h without a barrier; only D2 is handed back by the epilogue (D2_EMPTY).  The peer's MMA warp relays its
-// CTA's barriers to the leader like the CG2 kernel above.  Warps: 0-15 output (E1 then E2 of every tile), 16 MMA /
-// relay, 17 W producer, 18 A producer.  TMEM is full (512 columns): one tile in flight, E1 is exposed
-// (the tensor pipe waits for it), E2 runs under GEMM1 of the next tile.
+// At C = 256 the unfused 1x1 conv + residual launch sat at its HBM roofline (h written and read back: 0.54 GB per
+// unit); at C <= 128 the one-CTA fused kernel above is bound by its output warps' latency chain (8 warps per phase,
+// E1 -> GEMM2 -> E2 in series).  Here all 16 output warps work on one phase at a time and, for C <= 128, TMEM
+// holds TWO tiles (2 x 2N <= 512 columns): the leader issues G1(t+1) before G2(t), so E1(t) runs under G1(t+1) and
+// E2(t) under the GEMMs after it.  One warp issues every MMA: tcgen05.mma executes in issue order, so G1(t+NS)
+// may overwrite D1 / h of tile t without a barrier; only D2 is handed back by the epilogue (D2_EMPTY).  The peer's MMA
+// warp relays its CTA's barriers to the leader like the CG2 kernel above.  Weights: conv1's half blocks resident;
+// conv3's resident too for C <= 128 (64 KB per CTA at C = 128), streamed through a ring at C = 256.
+// Warps: 0-15 output, 16 MMA / relay, 17 W producer, 18 A producer.
+template <int NS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
     tc_du_pair_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcTmap tmx) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -1425,8 +1432,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   float* bias_s = reinterpret_cast<float*>(smem + p.off_bias);
   float* bias2_s = bias_s + 256;
   uint8_t* a_smem = smem + p.off_a;
-  uint8_t* w_smem = smem + p.off_w;
-  uint8_t* w1_smem = smem + p.off_h;                      // this CTA's 128 rows of the 1x1 conv's four blocks, resident
+  uint8_t* w_smem = smem + p.off_w;                       // conv3 half blocks: ring (streamed) or all of them (resident)
+  uint8_t* w1_smem = smem + p.off_h;                      // conv1 half blocks, resident
   const uint32_t bar0 = smem_u32(bars);
   auto BAR = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   int tid;
@@ -1437,7 +1444,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   const uint32_t rank = cluster_ctarank();
   const uint32_t lead = rank == 0 ? 1u : 0u;
   constexpr int W_MMA = 16, W_WPROD = 17, W_APROD = 18;
-  constexpr int N = 256, NKC2 = 4;                        // channels; K chunks of the 1x1 conv (KC = 64)
+  const int N = p.N_TILE;                                 // channels of the unit
+  const int nkc = p.n_kchunks;                            // K chunks (KC = 64) of either GEMM
+  const int nblk1 = nkc * p.n_taps;                       // conv3 weight blocks per tile
+  const bool resident = p.w_resident != 0;
+  const uint32_t stage_cols = 2u * (uint32_t)N;
   if (tid == 0) {
     for (int i = 0; i < MAX_SA; ++i) {
       mbar_init(BAR(BAR_A_FULL + i), 1 + lead);
@@ -1447,12 +1458,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       mbar_init(BAR(BAR_W_FULL + i), 1 + lead);
       mbar_init(BAR(BAR_W_EMPTY + i), 1);
     }
-    mbar_init(BAR(BAR_RAW_FULL), 1 + lead);              // resident 1x1-conv weights landed (once)
-    mbar_init(BAR(BAR_D_FULL), 1);
-    mbar_init(BAR(BAR_H_FULL), 16 + lead);               // lower K half of h (columns [0, 128) of D1)
-    mbar_init(BAR(BAR_H_FULL + 1), 16 + lead);           // upper K half
-    mbar_init(BAR(BAR_D2_FULL), 1);
-    mbar_init(BAR(BAR_D2_EMPTY), 16 + lead);
+    mbar_init(BAR(BAR_RAW_FULL), 1 + lead);               // resident weights landed (once)
+    for (int st = 0; st < NS; ++st) {
+      mbar_init(BAR(BAR_D_FULL + st), 1);
+      mbar_init(BAR(BAR_H_FULL + 2 * st), 16 + lead);      // lower K half of h
+      mbar_init(BAR(BAR_H_FULL + 2 * st + 1), 16 + lead);  // upper K half
+      mbar_init(BAR(BAR_D2_FULL + st), 1);
+      mbar_init(BAR(BAR_D2_EMPTY + st), 16 + lead);
+    }
     fence_mbar_init();
   }
   for (int i = tid; i < N; i += TC_THREADS) {
@@ -1470,15 +1483,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   cluster_sync();
   if (warp != W_WPROD) asm volatile("griddepcontrol.wait;" ::: "memory");
 
-  const int ksteps = p.KC >> 4;                           // 4
-  const int nblk1 = p.n_kchunks * p.n_taps;               // weight blocks of GEMM1 per tile (12)
   if (warp == W_APROD) {
     if (lane == 0) prefetch_tmap(&tmx);
     Ring ra;
     WorkIter wi;
     for (wi.init(p); wi.left > 0; wi.next(p)) {
       const Work wk = wi.work(p);
-      for (int kc = 0; kc < p.n_kchunks; ++kc) {
+      for (int kc = 0; kc < nkc; ++kc) {
         const uint32_t sa = ra.idx;
         mbar_wait(BAR(BAR_A_EMPTY + sa), ra.ph ^ 1);
         issue_a_tma(p, &tmx, wk.b, wk.t0 - p.off, kc, smem_u32(a_smem + (size_t)sa * p.a_stage_bytes),
@@ -1488,24 +1499,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     }
   } else if (warp == W_WPROD) {
     if (lane == 0) {
-      // the 1x1 conv's weights once (they follow conv3's blocks), then conv3's blocks of every tile through the ring:
-      // while E1 and GEMM2 of a tile run, the ring fills with the first blocks of the next tile's GEMM1
-      mbar_expect_tx(BAR(BAR_RAW_FULL), (uint32_t)NKC2 * p.w_blk_bytes);
-      for (int kc = 0; kc < NKC2; ++kc)
-        bulk_g2s(smem_u32(w1_smem + (size_t)kc * p.w_blk_bytes),
-                 reinterpret_cast<const uint8_t*>(p.w) + ((size_t)(nblk1 + kc) * 2 + rank) * p.w_blk_bytes, p.w_blk_bytes,
-                 BAR(BAR_RAW_FULL));
-      Ring rw;
-      WorkIter wi;
-      for (wi.init(p); wi.left > 0; wi.next(p)) {
-        for (int blk = 0; blk < nblk1; ++blk) {            // conv3 blocks in (K chunk, tap) order
-          const uint32_t sw = rw.idx;
-          mbar_wait(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
-          mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
-          bulk_g2s(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes),
-                   reinterpret_cast<const uint8_t*>(p.w) + ((size_t)blk * 2 + rank) * p.w_blk_bytes, p.w_blk_bytes,
-                   BAR(BAR_W_FULL + sw));
-          rw.next(p.SW);
+      // resident: conv1's blocks (behind conv3's in the packed order) and, for C <= 128, conv3's as well, once
+      const int r0 = resident ? 0 : nblk1, rn = nblk1 + nkc - r0;
+      mbar_expect_tx(BAR(BAR_RAW_FULL), (uint32_t)rn * p.w_blk_bytes);
+      for (int i = 0; i < rn; ++i) {
+        const int blk = r0 + i;
+        uint8_t* dst = blk < nblk1 ? w_smem + (size_t)blk * p.w_blk_bytes : w1_smem + (size_t)(blk - nblk1) * p.w_blk_bytes;
+        bulk_g2s(smem_u32(dst), reinterpret_cast<const uint8_t*>(p.w) + ((size_t)blk * 2 + rank) * p.w_blk_bytes,
+                 p.w_blk_bytes, BAR(BAR_RAW_FULL));
+      }
+      if (!resident) {
+        // conv3's blocks of every tile through the ring: while E1 / GEMM2 of a tile run it fills with the first
+        // blocks of the next tile
+        Ring rw;
+        WorkIter wi;
+        for (wi.init(p); wi.left > 0; wi.next(p)) {
+          for (int blk = 0; blk < nblk1; ++blk) {          // (K chunk, tap) order
+            const uint32_t sw = rw.idx;
+            mbar_wait(BAR(BAR_W_EMPTY + sw), rw.ph ^ 1);
+            mbar_expect_tx(BAR(BAR_W_FULL + sw), p.w_blk_bytes);
+            bulk_g2s(smem_u32(w_smem + (size_t)sw * p.w_blk_bytes),
+                     reinterpret_cast<const uint8_t*>(p.w) + ((size_t)blk * 2 + rank) * p.w_blk_bytes, p.w_blk_bytes,
+                     BAR(BAR_W_FULL + sw));
+            rw.next(p.SW);
+          }
         }
       }
     }
@@ -1513,125 +1530,174 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     const bool leader = elect_one();
     Ring ra, rw;
     WorkIter wi;
-    uint32_t it = 0;
+    wi.init(p);
+    const int n_items = wi.left;
     if (lead) {
       const uint32_t idesc2 = make_idesc_bf16(256, N);
       const uint32_t a0 = smem_u32(a_smem), w0 = smem_u32(w_smem), w10 = smem_u32(w1_smem);
-      mbar_wait(BAR(BAR_RAW_FULL), 0);
-      tc_fence_after();
       const uint32_t dhi = desc_hi(128u);
-      const uint32_t lbo_a = (uint32_t)p.R_ALLOC * 16u, lbo_w = 128u * 16u;
+      const uint32_t lbo_a = (uint32_t)p.R_ALLOC * 16u, lbo_w = (uint32_t)(N / 2) * 16u;
       const uint32_t a_lbo_bits = ((lbo_a >> 4) & 0x3FFFu) << 16, w_lbo_bits = ((lbo_w >> 4) & 0x3FFFu) << 16;
       const uint32_t a_kadd = (2u * lbo_a) >> 4, w_kadd = (2u * lbo_w) >> 4;
-      for (wi.init(p); wi.left > 0; wi.next(p), ++it) {
-        // GEMM1 -> D1 (in issue order behind GEMM2 of the previous tile, which reads h from the same columns)
+      mbar_wait(BAR(BAR_RAW_FULL), 0);
+      tc_fence_after();
+      // GEMM1 of tile t -> D1 of stage t % NS
+      auto g1 = [&](int t) {
+        const uint32_t dcol = tmem + (uint32_t)(t % NS) * stage_cols;
         uint32_t acc = 0;
-        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+        for (int kc = 0; kc < nkc; ++kc) {
           const uint32_t sa = ra.idx;
           mbar_wait(BAR(BAR_A_FULL + sa), ra.ph);
           ra.next(p.SA);
           tc_fence_after();
           const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
           for (int j = 0; j < p.n_taps; ++j) {
-            const uint32_t sw = rw.idx;
-            mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
-            rw.next(p.SW);
-            tc_fence_after();
-            uint32_t bl = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+            uint32_t bl, sw = 0;
+            if (resident) {
+              bl = (((w0 + (uint32_t)(kc * p.n_taps + j) * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+            } else {
+              sw = rw.idx;
+              mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
+              rw.next(p.SW);
+              tc_fence_after();
+              bl = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+            }
             uint32_t al = alo0 + (uint32_t)(j * p.dil);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
-              if (leader) mma2_bf16_lohi(tmem, al, bl, dhi, idesc2, acc);
+              if (leader) mma2_bf16_lohi(dcol, al, bl, dhi, idesc2, acc);
               acc = 1;
               al += a_kadd;
               bl += w_kadd;
             }
-            if (leader) mma2_commit(BAR(BAR_W_EMPTY + sw));
+            if (!resident && leader) mma2_commit(BAR(BAR_W_EMPTY + sw));
           }
           if (leader) mma2_commit(BAR(BAR_A_EMPTY + sa));
         }
-        if (leader) mma2_commit(BAR(BAR_D_FULL));
-        // GEMM2: A = h in tensor memory (K step k at columns [16 k, 16 k + 8) of D1), D2 at columns [256, 512)
-        // (the lower K half as soon as E1 has written it: the upper half of E1 runs under these MMAs)
-        mbar_wait(BAR(BAR_H_FULL), it & 1);
-        mbar_wait(BAR(BAR_D2_EMPTY), (it & 1) ^ 1);
+        if (leader) mma2_commit(BAR(BAR_D_FULL + t % NS));
+      };
+      // GEMM2 of tile t: A = h in tensor memory (K step k at columns [16 k, 16 k + 8) of D1), D2 behind D1; the
+      // lower K half as soon as E1 has written it
+      auto g2 = [&](int t) {
+        const int st = t % NS;
+        const uint32_t par = (uint32_t)(t / NS) & 1u;
+        const uint32_t dcol = tmem + (uint32_t)st * stage_cols + (uint32_t)N;
+        mbar_wait(BAR(BAR_H_FULL + 2 * st), par);
+        mbar_wait(BAR(BAR_D2_EMPTY + st), par ^ 1);
         tc_fence_after();
-        uint32_t at = tmem, acc2 = 0;
-        for (int kc = 0; kc < NKC2; ++kc) {
-          if (kc == NKC2 / 2) {
-            mbar_wait(BAR(BAR_H_FULL + 1), it & 1);
+        uint32_t at = tmem + (uint32_t)st * stage_cols, acc2 = 0;
+        const int ks = nkc * 4;
+        for (int k = 0; k < ks; ++k) {
+          if (k == ks / 2) {
+            mbar_wait(BAR(BAR_H_FULL + 2 * st + 1), par);
             tc_fence_after();
           }
-          uint32_t bl = (((w10 + (uint32_t)kc * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
-#pragma unroll
-          for (int kk = 0; kk < 4; ++kk) {
-            if (leader) mma2_bf16_ts(tmem + (uint32_t)N, at, bl, dhi, idesc2, acc2);
-            acc2 = 1;
-            at += 16u;
-            bl += w_kadd;
-          }
+          const uint32_t bl = ((((w10 + (uint32_t)(k >> 2) * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits) +
+                              (uint32_t)(k & 3) * w_kadd;
+          if (leader) mma2_bf16_ts(dcol, at, bl, dhi, idesc2, acc2);
+          acc2 = 1;
+          at += 16u;
         }
-        if (leader) mma2_commit(BAR(BAR_D2_FULL));
+        if (leader) mma2_commit(BAR(BAR_D2_FULL + st));
+      };
+      if (NS == 1) {
+        for (int t = 0; t < n_items; ++t) { g1(t); g2(t); }
+      } else {
+        if (n_items > 0) g1(0);
+        for (int t = 0; t < n_items; ++t) {
+          if (t + 1 < n_items) g1(t + 1);
+          g2(t);
+        }
       }
-      (void)ksteps;
     } else {
       // relay: this CTA's stages, in the order the leader waits for them
       auto fwd = [&](int b) { if (leader) mbar_arrive_cluster(mapa_shared(BAR(b), 0)); };
       mbar_wait(BAR(BAR_RAW_FULL), 0);
       fwd(BAR_RAW_FULL);
-      for (wi.init(p); wi.left > 0; wi.next(p), ++it) {
-        for (int kc = 0; kc < p.n_kchunks; ++kc) {
+      auto r1 = [&](int) {
+        for (int kc = 0; kc < nkc; ++kc) {
           const uint32_t sa = ra.idx;
           mbar_wait(BAR(BAR_A_FULL + sa), ra.ph);
           ra.next(p.SA);
           fwd(BAR_A_FULL + sa);
-          for (int j = 0; j < p.n_taps; ++j) {
-            const uint32_t sw = rw.idx;
-            mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
-            rw.next(p.SW);
-            fwd(BAR_W_FULL + sw);
-          }
+          if (!resident)
+            for (int j = 0; j < p.n_taps; ++j) {
+              const uint32_t sw = rw.idx;
+              mbar_wait(BAR(BAR_W_FULL + sw), rw.ph);
+              rw.next(p.SW);
+              fwd(BAR_W_FULL + sw);
+            }
         }
-        mbar_wait(BAR(BAR_H_FULL), it & 1);
-        fwd(BAR_H_FULL);
-        if (it > 0) {                                      // the first tile needs no drained D2 (see relay_cg2)
-          mbar_wait(BAR(BAR_D2_EMPTY), (it & 1) ^ 1);
-          fwd(BAR_D2_EMPTY);
+      };
+      auto r2 = [&](int t) {
+        const int st = t % NS;
+        const uint32_t par = (uint32_t)(t / NS) & 1u;
+        mbar_wait(BAR(BAR_H_FULL + 2 * st), par);
+        fwd(BAR_H_FULL + 2 * st);
+        if (t >= NS) {                                     // the first use of a stage needs no drained D2 (see relay_cg2)
+          mbar_wait(BAR(BAR_D2_EMPTY + st), par ^ 1);
+          fwd(BAR_D2_EMPTY + st);
         }
-        mbar_wait(BAR(BAR_H_FULL + 1), it & 1);
-        fwd(BAR_H_FULL + 1);
+        mbar_wait(BAR(BAR_H_FULL + 2 * st + 1), par);
+        fwd(BAR_H_FULL + 2 * st + 1);
+      };
+      if (NS == 1) {
+        for (int t = 0; t < n_items; ++t) { r1(t); r2(t); }
+      } else {
+        if (n_items > 0) r1(0);
+        for (int t = 0; t < n_items; ++t) {
+          if (t + 1 < n_items) r1(t + 1);
+          r2(t);
+        }
       }
     }
   } else if (warp < 16) {
     const int rit = (warp & 3) * 32 + lane;
     const uint32_t lane_base = (uint32_t)((warp & 3) * 32) << 16;
     const int part = warp >> 2;                            // 4 column parts
+    const int ppw = N >> 6;                                // 16-column pieces per warp (1, 2 or 4)
     WorkIter wi;
-    uint32_t it = 0;
-    for (wi.init(p); wi.left > 0; wi.next(p), ++it) {
-      const Work wk = wi.work(p);
-      // E1: pieces 16 part + 64 i -- every warp finishes the lower K half of h before the upper one
-      mbar_wait(BAR(BAR_D_FULL), it & 1);
+    wi.init(p);
+    const int n_items = wi.left;
+    // E1 of tile t: pieces 16 part + 64 i -- every warp finishes the lower K half of h before the upper one
+    auto e1 = [&](int t) {
+      const int st = t % NS;
+      const uint32_t d1 = tmem + lane_base + (uint32_t)st * stage_cols;
+      mbar_wait(BAR(BAR_D_FULL + st), (uint32_t)(t / NS) & 1u);
       tc_fence_after();
+      int i = 0;
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
+        const int iend = half ? ppw : (ppw + 1) / 2;
 #pragma unroll 1
-        for (int i = 0; i < 2 && !(p.dbg & 1); ++i) {
-          const int c = 16 * part + 64 * (2 * half + i);
-          h_chunk<RB_ACT_LEAKY, 16, true>(tmem + lane_base + (uint32_t)c, bias_s + c, nullptr, 0, nullptr);
+        for (; i < iend && !(p.dbg & 1); ++i) {
+          const int c = 16 * part + 64 * i;
+          h_chunk<RB_ACT_LEAKY, 16, true>(d1 + (uint32_t)c, bias_s + c, nullptr, 0, nullptr);
         }
         tmem_st_wait();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(BAR(BAR_H_FULL + half));
+        if (lane == 0) mbar_arrive(BAR(BAR_H_FULL + 2 * st + half));
       }
-      // E2
-      if (p.dbg & 2) mbar_wait(BAR(BAR_D2_FULL), it & 1);   // (timing experiments: no drain)
+    };
+    auto e2 = [&](int t, const Work& wk) {
+      const int st = t % NS;
+      const uint32_t par = (uint32_t)(t / NS) & 1u;
+      if (p.dbg & 2) mbar_wait(BAR(BAR_D2_FULL + st), par);   // (timing experiments: no drain)
       else
-        drain_res16(p, BAR(BAR_D2_FULL), it & 1, tmem + lane_base + (uint32_t)N, bias2_s, wk, rit, part, 4, N,
-                    0xffffffffu);
+        drain_res16(p, BAR(BAR_D2_FULL + st), par, tmem + lane_base + (uint32_t)st * stage_cols + (uint32_t)N, bias2_s,
+                    wk, rit, part, 4, N, 0xffffffffu, N < 128);
       __syncwarp();
-      if (lane == 0) mbar_arrive(BAR(BAR_D2_EMPTY));
+      if (lane == 0) mbar_arrive(BAR(BAR_D2_EMPTY + st));
+    };
+    if (NS == 1) {
+      for (int t = 0; t < n_items; ++t, wi.next(p)) { e1(t); e2(t, wi.work(p)); }
+    } else {
+      if (n_items > 0) e1(0);
+      for (int t = 0; t < n_items; ++t, wi.next(p)) {
+        if (t + 1 < n_items) e1(t + 1);
+        e2(t, wi.work(p));
+      }
     }
   }
   tc_fence_before();
@@ -1718,9 +1784,11 @@ int launch_tc_du_pair(TcParams& p, cudaStream_t s) {
     RB_CUDA(cudaGetDevice(&dev));
     RB_CUDA(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
   }
-  RB_CHECK(p.smem_bytes <= 227u * 1024u && p.N_TILE == 256 && p.KC == 64 && p.n_kchunks == 4 && p.n_ntiles == 1 &&
-               p.pair == 1 && p.MT == 1 && p.res.p && p.pre_act == RB_ACT_NONE && p.SW <= MAX_SW && p.SA <= MAX_SA,
+  RB_CHECK(p.smem_bytes <= 227u * 1024u && (p.N_TILE == 256 || p.N_TILE == 128 || p.N_TILE == 64) && p.KC == 64 &&
+               p.n_kchunks * 64 == p.N_TILE && p.n_ntiles == 1 && p.pair == 1 && p.MT == 1 && p.res.p &&
+               p.pre_act == RB_ACT_NONE && p.SW <= MAX_SW && p.SA <= MAX_SA && (p.w_resident || p.N_TILE == 256),
            RB_ERR_INVALID, "pair DilatedUnit launch outside its envelope");
+  const bool two = p.N_TILE <= 128;                        // two tiles in TMEM
   const int slots = n_sm / 2;
   const int stride = p.n_work < slots ? p.n_work : slots;
   {
@@ -1734,7 +1802,8 @@ int launch_tc_du_pair(TcParams& p, cudaStream_t s) {
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    RB_CUDA(cudaFuncSetAttribute(tc_du_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    RB_CUDA(cudaFuncSetAttribute(tc_du_pair_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    RB_CUDA(cudaFuncSetAttribute(tc_du_pair_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg;
@@ -1752,7 +1821,8 @@ int launch_tc_du_pair(TcParams& p, cudaStream_t s) {
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 2;
-  RB_CUDA(cudaLaunchKernelEx(&cfg, tc_du_pair_kernel, p, tm));
+  if (two) RB_CUDA(cudaLaunchKernelEx(&cfg, tc_du_pair_kernel<2>, p, tm));
+  else RB_CUDA(cudaLaunchKernelEx(&cfg, tc_du_pair_kernel<1>, p, tm));
   ++g_launches;
   RB_CUDA(cudaGetLastError());
   return RB_OK;

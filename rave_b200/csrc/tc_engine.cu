@@ -258,7 +258,8 @@ static void free_layer(Layer& L) {
 
 // Pack Wv into [N_TILE][KC] blocks (UMMA K-major no-swizzle core-matrix order) in the order
 // the kernel consumes them: n-tile, K chunk, active tap.  `extra` (fused 1x1 conv) appended.
-static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, Layer& L, int ncap_arg = 0) {
+static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, Layer& L, int ncap_arg = 0,
+                      bool twin = false) {
   L.fin = v.fin; L.fout = v.fout; L.cin_v = v.cin_v; L.n_taps = v.n_taps; L.dil = v.dil; L.off = v.off;
   L.N_total = v.N_total; L.out_mask = v.out_mask;
   RB_CHECK(v.n_taps <= 64, RB_ERR_UNSUPPORTED, "conv with %d row taps (max 64)", v.n_taps);
@@ -325,16 +326,16 @@ static int pack_layer(const ViewWeight& v, int kc_cap, const ViewWeight* extra, 
   }
   int rc = dev_upload(blocks, &L.w);
   if (rc) return rc;
-  if (L.N_TILE == 256) {
-    // N-split twin for cta_group::2: block [n][c] -> half n / 128, then the same core-matrix order over 128 rows
-    // (a pair DilatedUnit's 1x1 conv blocks included)
+  if (L.N_TILE == 256 || twin) {
+    // N-split twin for cta_group::2: block [n][c] -> half n / (N / 2), then the same core-matrix order over the
+    // N / 2 rows of a half (a pair DilatedUnit's 1x1 conv blocks included)
     std::vector<__nv_bfloat16> b2(blocks.size());
     const size_t be = (size_t)L.N_TILE * L.KC, he = be / 2;
-    const int nb_all = (int)(blocks.size() / be);
+    const int nb_all = (int)(blocks.size() / be), H = L.N_TILE / 2;
     for (int b = 0; b < nb_all; ++b)
       for (int n = 0; n < L.N_TILE; ++n)
         for (int c = 0; c < L.KC; ++c)
-          b2[b * be + (size_t)(n >> 7) * he + (size_t)(c >> 3) * (128 * 8) + (size_t)(n & 127) * 8 + (c & 7)] =
+          b2[b * be + (size_t)(n / H) * he + (size_t)(c >> 3) * (H * 8) + (size_t)(n % H) * 8 + (c & 7)] =
               blocks[b * be + (size_t)(c >> 3) * (L.N_TILE * 8) + (size_t)n * 8 + (c & 7)];
     if ((rc = dev_upload(b2, &L.w2))) return rc;
   }
@@ -598,7 +599,7 @@ static int run_pair_du(const Layer& L, const rb_op& op, const Buf& src, const Bu
   if (rc) return rc;
   if ((rc = make_view(dst, 1, &p.y))) return rc;
   if ((rc = make_view(src, 1, &p.res))) return rc;
-  RB_CHECK(p.x.C == 256 && p.y.C == 256, RB_ERR_INVALID, "pair DilatedUnit: 256 channels expected");
+  RB_CHECK(p.x.C == L.N_TILE && p.y.C == L.N_TILE, RB_ERR_INVALID, "pair DilatedUnit: channel mismatch");
   p.w = L.w2; p.masks = L.masks; p.bias = L.bias; p.bias2 = L.bias2;
   p.pre_act = RB_ACT_NONE; p.act2 = RB_ACT_LEAKY;
   p.out_act = out_act ? RB_ACT_LEAKY : RB_ACT_NONE;
@@ -629,13 +630,15 @@ static int run_pair_du(const Layer& L, const rb_op& op, const Buf& src, const Bu
   const uint32_t budget = 224u * 1024u;
   p.off_bias = 640 + TC_MAX_MASKS * 8;
   const uint32_t fixed = align_up(p.off_bias + 512u * 4u, 128);
-  // shared memory: the 1x1 conv's four half blocks resident (64 KB), a ring of conv3 half blocks deep enough to
-  // hold the first half of the next tile's weights while E1 / GEMM2 of this tile run, and >= 3 A stages
-  const uint32_t w1_bytes = 4u * p.w_blk_bytes;
+  // shared memory: the 1x1 conv's half blocks resident; conv3's too when they fit (C <= 128: 48 KB per CTA at
+  // C = 128), else a ring of them deep enough to hold the first half of the next tile's weights while E1 / GEMM2
+  // of this tile run; and >= 3 A stages
+  const uint32_t w1_bytes = (uint32_t)L.n_kchunks * p.w_blk_bytes;
+  p.w_resident = (uint32_t)L.total_blocks * p.w_blk_bytes <= 64u * 1024u ? 1 : 0;
   p.SW = 6;
   if (const char* e = getenv("RB_TC_PD_SW")) p.SW = std::min(8, std::max(2, atoi(e)));   // experiments only
-  while (p.SW > 2 && fixed + w1_bytes + p.SW * p.w_blk_bytes + 3 * p.a_stage_bytes > budget) --p.SW;
-  const uint32_t w_bytes = p.SW * p.w_blk_bytes;
+  while (!p.w_resident && p.SW > 2 && fixed + w1_bytes + p.SW * p.w_blk_bytes + 3 * p.a_stage_bytes > budget) --p.SW;
+  const uint32_t w_bytes = p.w_resident ? (uint32_t)L.total_blocks * p.w_blk_bytes : p.SW * p.w_blk_bytes;
   p.SA = (int)std::min<uint32_t>(12, (budget - fixed - w1_bytes - w_bytes) / p.a_stage_bytes);
   RB_CHECK(p.SA >= 2, RB_ERR_UNSUPPORTED, "pair DilatedUnit does not fit in shared memory");
   p.off_a = fixed;
@@ -647,8 +650,8 @@ static int run_pair_du(const Layer& L, const rb_op& op, const Buf& src, const Bu
   p.tiles_per_stream = ((p.y.n + 127) / 128 + 1) / 2;     // work slots: one 128-row tile per CTA of a pair
   p.n_work = B * p.tiles_per_stream;
   if (getenv("RB_TC_PLAN_DEBUG"))
-    fprintf(stderr, "tc layer: pair DilatedUnit C 256 dil %d | SA %d SW %d rows %d work %d smem %u\n", L.dil, p.SA, p.SW,
-            p.y.n, p.n_work, p.smem_bytes);
+    fprintf(stderr, "tc layer: pair DilatedUnit C %d dil %d | resident %d SA %d SW %d rows %d work %d smem %u\n", L.N_TILE,
+            L.dil, p.w_resident, p.SA, p.SW, p.y.n, p.n_work, p.smem_bytes);
   return launch_tc_du_pair(p, s);
 }
 
@@ -939,15 +942,22 @@ int tc_pack_weights(rb_handle* h) {
              op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 && o2.pre_act == op.pre_act &&
              v.N_total == v.cin_v && v.N_total <= 128 && pl->cp[o2.dst] == v.N_total &&
              (size_t)v.N_total * v.cin_v * (v.n_taps + 1) * 2 <= (size_t)128 * 1024;
-      // C = 256 (offline LeakyReLU nets on activated storage): both convs in one cluster-pair launch
-      pairdu = !fuse && o2.kind == RB_OP_CONV && o2.k == 1 && o2.stride == 1 && o2.ileave <= 1 && op.stride == 1 &&
+      // offline LeakyReLU nets on activated storage, C = 256: both convs in one cluster-pair launch
+      // (tc_du_pair_kernel).  The kernel also runs C = 128 / 64 (two tiles in tensor memory, weights resident) but
+      // measured SLOWER there than the one-CTA fused kernel -- 517 vs 464 and 1296 vs 785 kcycles per launch: the
+      // narrow units are bound by the instructions of their output warps, not by the chain between them -- so
+      // those widths are behind RB_TC_PD128 / RB_TC_PD64 (experiments, and the tests of the two-stage path)
+      const bool pd_width = v.N_total == 256 || (v.N_total == 128 && getenv("RB_TC_PD128")) ||
+                            (v.N_total == 64 && getenv("RB_TC_PD64"));
+      pairdu = o2.kind == RB_OP_CONV && o2.k == 1 && o2.stride == 1 && o2.ileave <= 1 && op.stride == 1 &&
                op.ileave <= 1 && o2.src == op.dst && o2.res == op.src && op.res < 0 && o2.pre_act == op.pre_act &&
-               op.pre_act == RB_ACT_LEAKY && v.N_total == 256 && v.cin_v == 256 && v.n_taps == 3 &&
-               pl->cp[o2.dst] == 256 && !h->spec.streaming && pl->sact[op.src] && op.has_bias && o2.has_bias &&
+               op.pre_act == RB_ACT_LEAKY && pd_width && v.cin_v == v.N_total && v.n_taps == 3 &&
+               pl->cp[o2.dst] == v.N_total && !h->spec.streaming && pl->sact[op.src] && op.has_bias && o2.has_bias &&
                !getenv("RB_TC_NOPAIRDU");
       if (pairdu)
         for (int j = 0; j < nops; ++j)                   // h must have no other reader
           if (j != i + 1 && (h->ops[j].src == op.dst || h->ops[j].res == op.dst || h->ops[j].src2 == op.dst)) pairdu = false;
+      if (pairdu) fuse = false;
       if (fuse || pairdu) {
         rc = build_view_weight(h, i + 1, *pl, v2);
         if (rc) return rc;
@@ -958,11 +968,11 @@ int tc_pack_weights(rb_handle* h) {
       if (F > 1) batch_rows(v, F);
     }
     Layer& L = pl->layers[i];
-    rc = pack_layer(v, 64, (fuse || pairdu) ? &v2 : nullptr, L);
+    rc = pack_layer(v, 64, (fuse || pairdu) ? &v2 : nullptr, L, 0, pairdu);
     if (rc) return rc;
     if (pairdu) {
-      RB_CHECK(L.w2 && L.N_TILE == 256 && L.KC == 64 && L.n_kchunks == 4 && L.total_blocks == 12, RB_ERR_STATE,
-               "pair DilatedUnit: unexpected packing");
+      RB_CHECK(L.w2 && L.N_TILE == v.N_total && L.KC == 64 && L.n_kchunks * 64 == L.N_TILE &&
+                   L.total_blocks == 3 * L.n_kchunks, RB_ERR_STATE, "pair DilatedUnit: unexpected packing");
       L.pairdu = true;
       L.fused_with = i + 1;
       L.tail = i + 1;

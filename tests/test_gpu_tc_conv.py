@@ -201,10 +201,24 @@ def test_single_conv_activated_storage(c):
 @pytest.mark.parametrize("C_,dil,n", [(64, 9, 777), (32, 1, 256), (128, 3, 300), (128, 9, 2000),
                                       # C = 256: both convs in one cluster-pair launch (tc_du_pair_kernel): several
                                       # tiles per CTA, a pair whose second tile is past the end, one short tile
-                                      (256, 3, 2048), (256, 9, 900), (256, 1, 100), (256, 3, 4096)])
+                                      (256, 3, 2048), (256, 9, 900), (256, 1, 100), (256, 3, 4096),
+                                      (128, 1, 4096), (128, 9, 1100)])
 def test_dilated_unit_pair_activated_storage(C_, dil, n):
+    _dilated_unit_pair_activated(C_, dil, n, 2 if C_ == 256 else 1)
+
+
+@pytest.mark.parametrize("C_,dil,n", [(128, 1, 4096), (128, 9, 1100), (128, 3, 300), (64, 3, 2000), (64, 9, 130)])
+def test_dilated_unit_cluster_pair_two_tmem_stages(C_, dil, n, monkeypatch):
+    """tc_du_pair_kernel with two tiles in tensor memory (C <= 128; selected with RB_TC_PD128 / RB_TC_PD64 -- the
+    default for those widths is the one-CTA fused kernel, which measures faster): odd tile counts, one-item CTAs."""
+    monkeypatch.setenv("RB_TC_PD128", "1")
+    monkeypatch.setenv("RB_TC_PD64", "1")
+    _dilated_unit_pair_activated(C_, dil, n, 2)
+
+
+def _dilated_unit_pair_activated(C_, dil, n, want_fused):
     g = torch.Generator().manual_seed(C_ * 3 + dil)
-    B = 3 if C_ == 256 else 2
+    B = 3 if C_ >= 128 else 2
     z = _bf(F.leaky_relu(torch.randn(B, C_, n, generator=g), 0.2).numpy())
     w3 = _bf((torch.randn(C_, C_, 3, generator=g) / np.sqrt(3 * C_)).numpy())
     w1 = _bf((torch.randn(C_, C_, 1, generator=g) / np.sqrt(C_)).numpy())
@@ -215,6 +229,6 @@ def test_dilated_unit_pair_activated_storage(C_, dil, n):
     ops = [dict(c_in=C_, c_out=C_, k=3, stride=1, dilation=dil, off=dil, ileave=1, pre_act=1, has_bias=1, res_delay=0),
            dict(c_in=C_, c_out=C_, k=1, stride=1, dilation=1, off=0, ileave=1, pre_act=1, has_bias=1, res_delay=0)]
     y, fused = _run(ops, [w3.numpy(), w1.numpy()], [b3.numpy(), b1.numpy()], [None, None], z.numpy(), flags=3)
-    assert fused == (2 if C_ == 256 else 1)
+    assert fused == want_fused
     assert np.isfinite(y).all()
     assert _rel(y, ref.numpy()) < TOL
