@@ -129,6 +129,12 @@ struct WorkIter {
     --left;
   }
   __device__ __forceinline__ Work work(const TcParams& p) const {
+    if (p.pair_streams) {
+      // stream 2 b + rank; an odd stream count leaves the last slot's second CTA without a stream: its tile starts
+      // far past the end (TMA zero-fills the loads, the epilogue stores nothing)
+      const int bs = 2 * b + ((int)blockIdx.x & 1);
+      return Work{nt, bs < p.B ? bs : 0, bs < p.B ? tile * p.MT * 128 : (1 << 24)};
+    }
     return Work{nt, b, ((tile << p.pair) + ((int)blockIdx.x & p.pair)) * p.MT * 128};
   }
 };

@@ -167,6 +167,9 @@ ACT_CASES = [
     dict(c_in=256, c_out=256, k=1, stride=1, dil=1, off=0, ileave=1, res=1, B=5, n=2048, flags=7),
     dict(c_in=512, c_out=1024, k=4, stride=2, dil=1, off=1, ileave=1, res=0, B=2, n=1024, flags=3),
     dict(c_in=1024, c_out=1024, k=3, stride=1, dil=1, off=1, ileave=2, res=0, B=2, n=300, flags=3),
+    # short tensors: the pair takes two neighbouring streams (odd stream count: one CTA of the last pair idles)
+    dict(c_in=512, c_out=512, k=3, stride=1, dil=1, off=1, ileave=1, res=0, B=3, n=260, flags=3),
+    dict(c_in=512, c_out=1024, k=4, stride=2, dil=1, off=1, ileave=1, res=0, B=5, n=512, flags=3),
     # sector-complete stores of phase outputs (drain_pair), the second one also as a cta_group::2 pair
     dict(c_in=128, c_out=256, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=2, n=520, flags=3),
     dict(c_in=256, c_out=256, k=3, stride=1, dil=1, off=1, ileave=2, res=0, B=3, n=640, flags=3),
