@@ -87,3 +87,28 @@ def angles_to_unit_norm_vector(angles):
     capi.check(capi.load_library().rb_angles_to_unit_norm(a.data_ptr(), a.shape[0], a.shape[1] + 1, a.shape[2],
                                                           out.data_ptr(), _stream(a.device)))
     return out
+
+
+class DiscreteLatent:
+    """`DiscreteScriptedRAVE.post_process_latent / pre_process_latent` (scripts/export.py:503-517) on the model's
+    own RVQ (`model.encoder.rvq`, csrc/rvq.cu): the latent leaves as the residual-VQ indices cast to float and
+    comes back through a clamp to the codebook range, the index -> embedding sum and, when the encoder was
+    trained with noise augmentation, extra noise channels (the reference draws `randn`; here an argument)."""
+
+    def __init__(self, model):
+        if model.spec.rvq is None:
+            raise ValueError("DiscreteLatent needs a discrete config (encoder with an RVQ)")
+        self._m = model
+
+    def post_process_latent(self, z):
+        """z [B, D, F] (the encoder's latent channels, any float dtype) -> indices as float [B, Q, F]."""
+        return self._m.encoder.rvq.encode(z.float().contiguous()).float()
+
+    def pre_process_latent(self, z, noise=None):
+        """z [B, Q, F] float indices -> quantised latent [B, D (+ noise channels), F] fp32."""
+        k = self._m.spec.rvq["codebook_size"]
+        idx = torch.clamp(z, 0, k - 1).long()
+        zq = self._m.encoder.rvq.decode(idx)
+        if noise is not None:
+            zq = torch.cat([zq, noise.to(zq)], 1)
+        return zq

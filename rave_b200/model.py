@@ -324,6 +324,15 @@ class RAVE:
 
     __call__ = forward
 
+    @torch.no_grad()
+    def forward_stereo(self, x, f0=None):
+        """The export wrapper's fake stereo (scripts/export.py:399-411): the latent is duplicated along the batch,
+        decoded, and the two halves become the two output channels: [B, 1, T] -> [B, 2, T] (the channels differ only
+        through the noise branch)."""
+        z = self.encode(x, f0=f0)
+        y = self.decode(torch.cat([z, z], 0))
+        return torch.cat(y.chunk(2, 0), 1)
+
     def forward_host(self, x: np.ndarray) -> np.ndarray:
         """Host-buffer entry (rb_forward_host): H2D copy, forward, D2H copy, synchronous."""
         x = np.ascontiguousarray(x, dtype=np.float32)

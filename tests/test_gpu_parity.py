@@ -727,3 +727,38 @@ def test_stream_step_is_cuda_graph_capturable(name, dtype):
         g.replay()
         assert torch.equal(ys, ye)
     torch.cuda.synchronize()
+
+
+def test_discrete_latent_post_pre_processing_vs_oracle():
+    """DiscreteScriptedRAVE.post_process_latent / pre_process_latent (scripts/export.py:503-517): float indices out,
+    clamp + embedding sum back, against the oracle's RVQ (bit-exact indices, fp32 sums)."""
+    from oracle.model import OracleRAVE
+    from rave_b200.latent import DiscreteLatent
+    m, meta, a = _model("discrete_c8")
+    o = OracleRAVE(meta["cfg"], golden_state_dict(meta))
+    dl = DiscreteLatent(m)
+    z = torch.from_numpy(a["z"][:, :meta["cfg"]["latent_size"]]).contiguous()
+    zi = dl.post_process_latent(z.cuda())
+    assert zi.dtype == torch.float32 and zi.shape[1] == meta["cfg"]["num_quantizers"]
+    assert torch.equal(zi.cpu(), o.rvq_encode(z).float())
+    wild = zi.clone()
+    wild[:, 0, 0] = -7.0                         # out-of-range values are clamped like the reference's
+    wild[:, 1, 1] = 1e6
+    zq = dl.pre_process_latent(wild).cpu()
+    ref = o.rvq_decode(torch.clamp(wild.cpu(), 0, meta["cfg"]["codebook_size"] - 1).long())
+    assert rel_l2(zq.numpy(), ref.numpy()) < 1e-6
+    with pytest.raises(ValueError):
+        DiscreteLatent(_model("v2_c8")[0])
+
+
+def test_fake_stereo_forward_vs_oracle():
+    """scripts/export.py:399-411: `z = cat([z, z], 0)` before the decoder, `y = cat(y.chunk(2, 0), 1)` after it."""
+    from oracle.model import OracleRAVE
+    m, meta, a = _model("v2_c8")
+    o = OracleRAVE(meta["cfg"], golden_state_dict(meta))
+    x = torch.from_numpy(golden_input(a))
+    y = m.forward_stereo(x.cuda()).cpu()
+    zo = o.encode(x)
+    yo = torch.cat(o.decode(torch.cat([zo, zo], 0)).chunk(2, 0), 1)
+    assert y.shape == (x.shape[0], 2, x.shape[2])
+    assert rel_l2(y.numpy(), yo.numpy()) < 2 * F32_TOL
