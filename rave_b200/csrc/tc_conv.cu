@@ -112,8 +112,17 @@ struct WorkIter {
   // Pair mode (p.pair = 1): the two CTAs of a cluster walk the same work sequence -- same n-tile,
   // hence the same weight blocks in the same order, which lets each load half of every block and
   // multicast it to both -- and take the even / odd 128*MT-row tile of each slot.
+  // Flat mode (p.flat_units = u > 0; the cta_group::2 pairs): the (stream, 128*MT-row unit)
+  // pairs are numbered stream-major, u units per stream, and a work slot is 2^pair CONSECUTIVE units of one
+  // n-tile -- so a cluster spans neighbouring streams when a stream has fewer units than the cluster has CTAs
+  // (the deepest layers: 256 rows per stream).  `tile` holds the slot's linear index, `b` the grid stride.
   __device__ __forceinline__ void init(const TcParams& p) {
     const int w = (int)blockIdx.x >> p.pair, stride = (int)gridDim.x >> p.pair;
+    if (p.flat_units) {
+      nt = 0; tile = w; b = stride;
+      left = w < p.n_work ? (p.n_work - w + stride - 1) / stride : 0;
+      return;
+    }
     const int rt = w / p.n_ntiles;
     nt = w - rt * p.n_ntiles;
     b = rt / p.tiles_per_stream;
@@ -121,6 +130,7 @@ struct WorkIter {
     left = w < p.n_work ? (p.n_work - w + stride - 1) / stride : 0;
   }
   __device__ __forceinline__ void next(const TcParams& p) {
+    if (p.flat_units) { tile += b; --left; return; }
     nt += p.step_nt;
     if (nt >= p.n_ntiles) { nt -= p.n_ntiles; ++tile; }
     tile += p.step_tile;
@@ -129,11 +139,12 @@ struct WorkIter {
     --left;
   }
   __device__ __forceinline__ Work work(const TcParams& p) const {
-    if (p.pair_streams) {
-      // stream 2 b + rank; an odd stream count leaves the last slot's second CTA without a stream: its tile starts
-      // far past the end (TMA zero-fills the loads, the epilogue stores nothing)
-      const int bs = 2 * b + ((int)blockIdx.x & 1);
-      return Work{nt, bs < p.B ? bs : 0, bs < p.B ? tile * p.MT * 128 : (1 << 24)};
+    if (p.flat_units) {
+      // a CTA past the last unit gets a tile far beyond the end: TMA zero-fills its loads, its epilogue stores nothing
+      const int rt = tile / p.n_ntiles, nt_ = tile - rt * p.n_ntiles;
+      const int g = (rt << p.pair) + ((int)blockIdx.x & ((1 << p.pair) - 1));
+      const int bs = g / p.flat_units, tl = g - bs * p.flat_units;
+      return Work{nt_, bs < p.B ? bs : 0, bs < p.B ? tl * p.MT * 128 : (1 << 24)};
     }
     return Work{nt, b, ((tile << p.pair) + ((int)blockIdx.x & p.pair)) * p.MT * 128};
   }
@@ -294,6 +305,23 @@ __device__ __forceinline__ void load_acc(uint32_t taddr, const float* bias_s, fl
     }
   }
 }
+// Second half of a software-pipelined accumulator load: the tcgen05.ld of these 16 columns into r was issued a
+// piece of work earlier (the trace of the C = 128 unit showed ~450 of the ~1100 cycles of a 16-column E2 piece
+// waiting for the load it had just issued); waits, adds the bias.  r is free for the next load afterwards.
+__device__ __forceinline__ void acc_finish16(uint32_t* r, const float* bias_s, float* v) {
+  float4 b[4];
+#pragma unroll
+  for (int g = 0; g < 4; ++g) b[g] = *reinterpret_cast<const float4*>(bias_s + g * 4);
+  tmem_ld_wait16(r);
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    const int e = g * 4;
+    v[e + 0] = __uint_as_float(r[e + 0]); v[e + 1] = __uint_as_float(r[e + 1]);
+    v[e + 2] = __uint_as_float(r[e + 2]); v[e + 3] = __uint_as_float(r[e + 3]);
+    add2(v[e + 0], v[e + 1], b[g].x, b[g].y);
+    add2(v[e + 2], v[e + 3], b[g].z, b[g].w);
+  }
+}
 // LeakyReLU(0.2) on NC fp32 values: packed multiply + max.
 template <int NC>
 __device__ __forceinline__ void leaky_n(float* v) {
@@ -425,39 +453,41 @@ __device__ __forceinline__ void drain_smem16(const TcParams& p, uint32_t bar_ful
   uint4* yp = reinterpret_cast<uint4*>(const_cast<__nv_bfloat16*>(p.y.p)) +
               ((uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT) + (uint32_t)(part * 4) * ysA);
   const uint4* sp = reinterpret_cast<const uint4*>(res_s) + (rit + p.off) + (uint32_t)(part * 4) * RA;
-  const uint32_t ystep = (uint32_t)(nparts * 4 - 4) * ysA, sstep = (uint32_t)(nparts * 4 - 4) * RA;   // to the next chunk
+  const int jump = 16 + (nparts - 1) * 32;                  // from the second piece of a chunk to the next chunk
   const bool valid = row < p.y.n;
   const bool ract = p.res_act != 0, oact = p.out_act != 0;
   mbar_wait(bar_full, parity);
   tc_fence_after();
-  for (int c0 = part * 32; c0 < NT; c0 += nparts * 32) {
+  // the accumulator of a piece is requested before the math of the piece in front of it
+  uint32_t r[16];
+  if (part * 32 < NT) tmem_ld16(tbase + (uint32_t)(part * 32), r);
 #pragma unroll 1
-    for (int c = c0; c < c0 + 32; c += 16) {
-      const uint4 r0 = sp[0], r1 = sp[RA];
-      float v[16];
-      load_acc<16>(tbase + (uint32_t)c, bs + c, v);
-      const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+  for (int c = part * 32; c < NT;) {
+    const uint4 r0 = sp[0], r1 = sp[RA];
+    float v[16];
+    acc_finish16(r, bs + c, v);
+    const int d = (c & 16) ? jump : 16;
+    if (c + d < NT) tmem_ld16(tbase + (uint32_t)(c + d), r);
+    const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
-        if (ract) {                                         // stored as leaky(x): x = min(z, 5 z), exact in fp32
-          float l5, h5;
-          mul2(l5, h5, lo, hi, 5.f, 5.f);
-          lo = fminf(lo, l5);
-          hi = fminf(hi, h5);
-        }
-        add2(v[2 * e], v[2 * e + 1], lo, hi);
+    for (int e = 0; e < 8; ++e) {
+      float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
+      if (ract) {                                           // stored as leaky(x): x = min(z, 5 z), exact in fp32
+        float l5, h5;
+        mul2(l5, h5, lo, hi, 5.f, 5.f);
+        lo = fminf(lo, l5);
+        hi = fminf(hi, h5);
       }
-      if (oact) leaky_n<16>(v);
-      if (valid) {
-        yp[0] = pack8(v);
-        yp[ysA] = pack8(v + 8);
-      }
-      yp += 2 * ysA;
-      sp += 2 * RA;
+      add2(v[2 * e], v[2 * e + 1], lo, hi);
     }
-    yp += ystep;
-    sp += sstep;
+    if (oact) leaky_n<16>(v);
+    if (valid) {
+      yp[0] = pack8(v);
+      yp[ysA] = pack8(v + 8);
+    }
+    yp += (uint32_t)(d >> 3) * ysA;
+    sp += (uint32_t)(d >> 3) * RA;
+    c += d;
   }
   tc_fence_before();
 }
@@ -497,10 +527,15 @@ __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full
   mbar_wait(bar_full, parity);
   tc_fence_after();
   TRACE(tr, 12);
+  // the accumulator of a piece is requested before the math of the piece in front of it
+  uint32_t r[16];
+  if (c_first < NT) tmem_ld16(tbase + (uint32_t)c_first, r);
 #pragma unroll 1
   for (int c = c_first; c < NT;) {
     float v[16];
-    load_acc<16>(tbase + (uint32_t)c, bs + c, v);
+    acc_finish16(r, bs + c, v);
+    const int d = step(c);
+    if (c + d < NT) tmem_ld16(tbase + (uint32_t)(c + d), r);
     TRACE(tr, 13);
     const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
     // the queue moves up and the piece two ahead is requested before this piece's math
@@ -525,7 +560,6 @@ __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full
       yp[0] = pack8(v);
       yp[ysA] = pack8(v + 8);
     }
-    const int d = step(c);
     yp += (uint32_t)(d >> 3) * ysA;
     c += d;
   }
@@ -790,6 +824,30 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
   }
 }
 
+// The 16-column piece of E1, software-pipelined: r holds this piece's accumulator (tcgen05.ld issued a piece
+// earlier); the next piece (TMEM address t_next, 0 = none) is requested before this piece's math.
+template <int ACT2, bool HT>
+__device__ __forceinline__ void h_piece(uint32_t* r, uint32_t taddr, uint32_t t_next, const float* bs,
+                                        const float* alpha2, int ia_off, uint8_t* hdst) {
+  float v[16];
+  acc_finish16(r, bs, v);
+  if (t_next) tmem_ld16(t_next, r);
+  if (ACT2 == RB_ACT_LEAKY) {
+    leaky_n<16>(v);
+  } else if (ACT2 == RB_ACT_SNAKE) {
+#pragma unroll
+    for (int e = 0; e < 16; ++e) v[e] = act_f<ACT2>(v[e], alpha2[e], alpha2[e + ia_off]);
+  }
+  if (!HT) {
+    *reinterpret_cast<uint4*>(hdst) = pack8(v);
+    *reinterpret_cast<uint4*>(hdst + 2048) = pack8(v + 8);
+  } else {
+    const uint4 lo = pack8(v), hi = pack8(v + 8);
+    const uint32_t q[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+    tmem_st8(taddr, q);
+  }
+}
+
 }  // namespace
 
 // issued by the elected lane of the MMA warp only
@@ -854,7 +912,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   constexpr int E1_PARTS = E1_WARPS / 4;
 
   // cta_group::2: the leader's FULL / D_EMPTY barriers also count one relayed arrival from the peer
-  const uint32_t cg2_lead = (CG2 && cluster_ctarank() == 0) ? 1u : 0u;
+  const uint32_t cg2_lead = (CG2 && (cluster_ctarank() & 1u) == 0) ? 1u : 0u;
   if (tid == 0) {
     for (int i = 0; i < MAX_SA; ++i) {
       mbar_init(BAR(BAR_A_FULL + i), (PRE == RB_ACT_NONE ? 1 : N_LOAD / 32) + cg2_lead);
@@ -1318,13 +1376,19 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         if (!HT) mbar_wait(BAR(BAR_H_EMPTY + sh), rh_.ph ^ 1);
         tc_fence_after();
         uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
-        for (int c0 = part * 32; c0 < C2; c0 += E1_PARTS * 32) {
-          // rolled 16-column pieces: see drain_smem16 (instruction-cache footprint)
-          const int c1 = C2 - c0 >= 32 ? c0 + 32 : c0 + 16;
+        {
+          // rolled 16-column pieces (see drain_smem16: instruction-cache footprint), both halves of this warp's
+          // 32-column chunks; each piece's accumulator is requested before the math of the piece in front of it
+          const uint32_t tb1 = tmem + lane_base + sd * d_stage_cols;
+          uint32_t r[16];
+          if (part * 32 < C2) tmem_ld16(tb1 + (uint32_t)(part * 32), r);
 #pragma unroll 1
-          for (int c = c0; c < c1; c += 16)
-            h_chunk<ACT2, 16, HT>(tmem + lane_base + sd * d_stage_cols + (uint32_t)c, bias_s + c, alpha2_s + c, C2,
-                                  hb + (size_t)(c >> 3) * 2048);
+          for (int c = part * 32; c < C2;) {
+            const int cn = (c & 16) ? c - 16 + E1_PARTS * 32 : c + 16;
+            h_piece<ACT2, HT>(r, tb1 + (uint32_t)c, cn < C2 ? tb1 + (uint32_t)cn : 0u, bias_s + c, alpha2_s + c, C2,
+                              hb + (size_t)(c >> 3) * 2048);
+            c = cn;
+          }
         }
         if (HT) tmem_st_wait();
         else fence_proxy_async();
@@ -1672,13 +1736,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       mbar_wait(BAR(BAR_D_FULL + st), (uint32_t)(t / NS) & 1u);
       tc_fence_after();
       int i = 0;
+      const bool on = !(p.dbg & 1);
+      uint32_t r[16];                                       // each piece is requested one piece ahead (h_piece)
+      if (on) tmem_ld16(d1 + (uint32_t)(16 * part), r);
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
         const int iend = half ? ppw : (ppw + 1) / 2;
 #pragma unroll 1
-        for (; i < iend && !(p.dbg & 1); ++i) {
+        for (; i < iend && on; ++i) {
           const int c = 16 * part + 64 * i;
-          h_chunk<RB_ACT_LEAKY, 16, true>(d1 + (uint32_t)c, bias_s + c, nullptr, 0, nullptr);
+          h_piece<RB_ACT_LEAKY, true>(r, d1 + (uint32_t)c, i + 1 < ppw ? d1 + (uint32_t)(c + 64) : 0u, bias_s + c,
+                                      nullptr, 0, nullptr);
         }
         tmem_st_wait();
         tc_fence_before();
@@ -1733,7 +1801,7 @@ static int launch_variant(const TcParams& p, const TcTmap& tm, int grid, cudaStr
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   attr[1].id = cudaLaunchAttributeClusterDimension;
-  attr[1].val.clusterDim.x = 2;
+  attr[1].val.clusterDim.x = 1u << p.pair;
   attr[1].val.clusterDim.y = 1;
   attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
@@ -1849,9 +1917,9 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
   RB_CHECK(!p.pair || (!p.fused && !p.w_resident && p.pre_act == RB_ACT_NONE), RB_ERR_INVALID,
            "pair mode is for plain streamed layers");
   // pair mode: one cluster of two CTAs per work slot
-  const int slots = p.pair ? n_sm / 2 : n_sm;
+  const int slots = n_sm >> p.pair;
   const int stride = p.n_work < slots ? p.n_work : slots;
-  const int grid = p.pair ? 2 * stride : stride;
+  const int grid = stride << p.pair;
   {
     const int rt = stride / p.n_ntiles;                    // grid stride, decomposed (WorkIter::next)
     p.step_nt = stride - rt * p.n_ntiles;

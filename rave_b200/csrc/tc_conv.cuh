@@ -68,9 +68,8 @@ struct TcParams {
   int pair;                 // 1: clusters of two CTAs share each streamed weight block (half each, multicast)
   int cg2;                  // pair + 1: the pair runs tcgen05.mma.cta_group::2 (M = 256; w holds the N-split block layout,
                             // w_blk_bytes = one CTA's half block)
-  int pair_streams;         // pair: the two CTAs of a work slot take the same row tile of two NEIGHBOURING STREAMS
-                            // (slot b <-> streams 2 b, 2 b + 1) instead of two row tiles of one stream: short tensors
-                            // (256-511 rows) then still give each CTA two sub-tiles per weight block (MT = 2)
+  int flat_units;           // > 0 (cta_group::2 clusters): 128*MT-row units per stream; work slots are 2^pair consecutive
+                            // (stream, unit) pairs, stream-major -- see WorkIter
   int dbg;                  // timing experiments only (RB_TC_PD_DBG): 1 skip E1 math, 2 skip E2 drain of the pair unit
   int cg2_spin;             // cta_group::2 waits: bit 0 producers / epilogue / relay spin, bit 1 the leader's MMA warp spins
   int dual_g1;              // resident + narrow: two warps issue GEMM1 of alternate work items

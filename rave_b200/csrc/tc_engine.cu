@@ -492,12 +492,12 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       // profiles/r02_cg2_cycles.txt)
       p.MT = (p.y.n >= 512 && L.n_taps >= 2 && L.n_kchunks >= 8) ? 2 : 1;
       if (const char* e = getenv("RB_TC_CG2_MT")) p.MT = (atoi(e) == 2 && p.y.n >= 512) ? 2 : 1;   // experiments only
-      // short tensors (the deepest layers: 256 rows per stream): the pair takes two STREAMS, one per CTA, so that
-      // each CTA still runs two sub-tiles per weight block -- these layers stream their whole weight set from L2
-      // once per 128 rows otherwise, and that traffic is what bounds them
-      p.pair_streams = (p.MT == 1 && p.y.n >= 256 && p.y.n < 512 && B >= 2 && L.n_taps >= 2 && L.n_kchunks >= 8 &&
-                        !getenv("RB_TC_NOPAIRSTREAMS")) ? 1 : 0;
-      if (p.pair_streams) p.MT = 2;
+      // short tensors (the deepest layers: 256 rows per stream) too: the units of a cluster are numbered across
+      // streams (flat_units), so each CTA still runs two sub-tiles per weight block -- these layers stream their
+      // whole weight set from L2 once per 128 rows otherwise, and that traffic is what bounds them
+      if (p.MT == 1 && p.y.n >= 256 && p.y.n < 512 && B >= 2 && L.n_taps >= 2 && L.n_kchunks >= 8 &&
+          !getenv("RB_TC_NOPAIRSTREAMS"))
+        p.MT = 2;
     }
     if (p.pair && !p.cg2) p.MT = (2 * L.N_TILE <= 256 && p.y.n >= 512) ? 2 : 1;
     p.R = p.MT * 128 + halo;
@@ -586,8 +586,14 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     }
   }
   p.tiles_per_stream = (p.y.n + p.MT * 128 - 1) / (p.MT * 128);
-  if (p.pair && !p.pair_streams) p.tiles_per_stream = (p.tiles_per_stream + 1) / 2;   // work slots: two row tiles each
-  p.n_work = L.n_ntiles * (p.pair_streams ? (B + 1) / 2 : B) * p.tiles_per_stream;
+  if (p.cg2) {
+    p.flat_units = p.tiles_per_stream;
+    const long long units = (long long)B * p.flat_units, per = 1ll << p.pair;
+    p.n_work = L.n_ntiles * (int)((units + per - 1) / per);
+  } else {
+    if (p.pair) p.tiles_per_stream = (p.tiles_per_stream + 1) / 2;   // work slots: two row tiles each
+    p.n_work = L.n_ntiles * B * p.tiles_per_stream;
+  }
   if (getenv("RB_TC_PLAN_DEBUG"))
     fprintf(stderr, "tc layer: cin_v %d N %d x %d taps %d dil %d fin %d fout %d KC %d | resident %d fused %d pair %d cg2 %d MT %d "
             "SA %d SW %d SD %d pair_mode %d rows %d work %d smem %u\n", L.cin_v, L.N_TILE, L.n_ntiles, L.n_taps, L.dil, L.fin,

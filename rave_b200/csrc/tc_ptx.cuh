@@ -329,10 +329,10 @@ __device__ __forceinline__ void mma2_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, u
       : "memory");
 }
 // arrives on the mbarrier at this offset in BOTH CTAs once every MMA issued so far has completed
-__device__ __forceinline__ void mma2_commit(uint32_t bar) {
+__device__ __forceinline__ void mma2_commit(uint32_t bar, unsigned short cta_mask = 3) {
   asm volatile(
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-      "h"((unsigned short)3)
+      "h"(cta_mask)
       : "memory");
 }
 __device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo) {
@@ -399,6 +399,15 @@ __device__ __forceinline__ void tmem_st_wait() {
 }
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// The wait of a load issued EARLIER than just before its use (software-pipelined drains): the 16 registers are
+// in/out operands, so the compiler cannot read, move or spill them between the load and this wait.
+__device__ __forceinline__ void tmem_ld_wait16(uint32_t* r) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+               :
+               : "memory");
 }
 
 // ------------------------------------------------------------------- packed fp32 pairs
