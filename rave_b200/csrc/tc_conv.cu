@@ -354,10 +354,14 @@ __device__ __forceinline__ int goff32(const TcView& v, int g) {
 template <int RES, bool SPIN = false>
 __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                            const float* bs, const Work& wk, int rit, int part, int nparts, int ch0,
-                                           int MTn, int NT, const uint8_t* res_s, uint32_t tr) {
+                                           int MTn, int NT, const uint8_t* res_s, uint32_t tr,
+                                           uint32_t bar_full1 = 0, uint32_t bar_empty0 = 0) {
+  // bar_full1 != 0: split accumulator (gemm1_cg2) -- sub-tile 1 has its own FULL barrier, and sub-tile 0 is given
+  // back (bar_empty0) as soon as this warp has drained its share of it
   constexpr uint32_t tmask = 0;
   const int row = wk.t0 + rit;
   const int cstep = nparts * 32;
+  bool handed = bar_full1 == 0;
   // per-thread offsets in 16-byte units from the (warp-uniform) tensor bases: 32 bits cover 64 GB
   const uint32_t yoff = (uint32_t)((long long)wk.b * p.y.sb) + (uint32_t)((p.y.hist + row) * p.y.sT);
   const uint32_t roff = RES == 1 ? (uint32_t)((long long)wk.b * p.res.sb) +
@@ -429,8 +433,22 @@ __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full,
 #pragma unroll
       for (int q = 0; q < 4; ++q) ybase[o + (uint32_t)(q * p.y.sA)] = pack8(v + q * 8);
     }
+    if (!handed && mtn != mt) {
+      handed = true;
+      tc_fence_before();
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) mbar_arrive(bar_empty0);
+      if (mtn < MTn) {
+        mbar_wait_t<SPIN>(bar_full1, parity, p.cg2_spin);
+        tc_fence_after();
+      }
+    }
     mt = mtn;
     c0 = c0n;
+  }
+  if (!handed) {                                            // a warp without columns still hands sub-tile 0 back
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(bar_empty0);
   }
   TRACE(tr, 15);
   tc_fence_before();
@@ -1240,12 +1258,17 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
       auto gemm1_cg2 = [&](const Work& wk) {
         const uint32_t idesc2 = make_idesc_bf16(256, p.N_TILE);
         const uint32_t sd = rd1.idx;
-        mbar_wait_t<true>(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1, p.cg2_spin & 2);
+        const uint32_t phe = rd1.ph ^ 1;
+        if (!p.split) mbar_wait_t<true>(BAR(BAR_D_EMPTY + sd), phe, p.cg2_spin & 2);
         rd1.next(p.SD);
         tc_fence_after();
         const uint32_t dcol = tmem + sd * d_stage_cols;
         uint32_t acc = 0;
         const uint64_t* mrow = mask_s + wk.nt * p.n_kchunks;
+        int kf = -1, kl = -1;                                 // first / last chunk with work (split)
+        if (p.split)
+          for (int kc = 0; kc < p.n_kchunks; ++kc)
+            if (mrow[kc] != 0) { if (kf < 0) kf = kc; kl = kc; }
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           uint64_t mask = mrow[kc];
           if (mask == 0) continue;
@@ -1254,6 +1277,48 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           ra.next(p.SA);
           tc_fence_after();
           const uint32_t alo0 = (((a0 + sa * p.a_stage_bytes) >> 4) & 0x3FFFu) | a_lbo_bits;
+          if (p.split && (kc == kf || kc == kl)) {
+            // Split accumulator (MT = 2 fills tensor memory: one stage, the drain would be exposed).  The two
+            // sub-tiles have their own FULL / EMPTY barriers (indices 0, 1); the first and the last chunk of a
+            // work item run sub-tile-major, so sub-tile 0 is published one chunk-pass before sub-tile 1 and taken
+            // back one pass earlier: its drain overlaps the other's MMAs at both ends.  The weight stages of the
+            // chunk stay until the second pass has used them (taps <= SW).
+            Ring rw2 = rw;
+            for (int mt = 0; mt < 2; ++mt) {
+              if (kc == kf) {
+                mbar_wait_t<true>(BAR(BAR_D_EMPTY + mt), phe, p.cg2_spin & 2);
+                tc_fence_after();
+              }
+              rw2 = rw;
+              uint32_t acc2 = kc == kf ? 0u : 1u;
+              const uint32_t dc = dcol + (uint32_t)(mt * p.N_TILE);
+              for (uint64_t m2 = mask; m2; m2 &= m2 - 1) {
+                const int j = __ffsll((long long)m2) - 1;
+                const uint32_t sw = rw2.idx;
+                if (mt == 0) {
+                  mbar_wait_t<true>(BAR(BAR_W_FULL + sw), rw2.ph, p.cg2_spin & 2);
+                  tc_fence_after();
+                }
+                rw2.next(p.SW);
+                uint32_t al = alo0 + (uint32_t)j * tap_add + (uint32_t)mt * 128u;
+                uint32_t bl = (((w0 + sw * p.w_blk_bytes) >> 4) & 0x3FFFu) | w_lbo_bits;
+                if (leader) mma2_bf16_lohi(dc, al, bl, dhi, idesc2, acc2);
+#pragma unroll 4
+                for (int kk = 1; kk < ksteps; ++kk) {
+                  al += a_kadd;
+                  bl += w_kadd;
+                  if (leader) mma2_bf16_lohi(dc, al, bl, dhi, idesc2, 1u);
+                }
+                acc2 = 1;
+                if (mt == 1 && leader) mma2_commit(BAR(BAR_W_EMPTY + sw));   // second pass: the stage is done
+              }
+              if (kc == kl && leader) mma2_commit(BAR(BAR_D_FULL + mt));
+            }
+            rw = rw2;
+            acc = 1;
+            if (leader) mma2_commit(BAR(BAR_A_EMPTY + sa));
+            continue;
+          }
           while (mask) {
             const int j = __ffsll((long long)mask) - 1;
             mask &= mask - 1;
@@ -1280,7 +1345,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           }
           if (leader) mma2_commit(BAR(BAR_A_EMPTY + sa));
         }
-        if (leader) mma2_commit(BAR(BAR_D_FULL + sd));
+        if (!p.split && leader) mma2_commit(BAR(BAR_D_FULL + sd));
       };
       // The peer's MMA warp: follows the same sequence of stages and, as each of ITS stages becomes ready
       // (A tile landed, weight half landed, accumulator drained), arrives on the leader's barrier of the same
@@ -1289,12 +1354,15 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
       uint32_t n_item = 0;
       auto relay_cg2 = [&](const Work& wk) {
         const uint32_t sd = rd1.idx;
-        if (n_item >= (uint32_t)p.SD) {
-          mbar_wait_t<true>(BAR(BAR_D_EMPTY + sd), rd1.ph ^ 1, p.cg2_spin);
+        const bool hand = n_item >= (uint32_t)p.SD;
+        const uint32_t phe = rd1.ph ^ 1;
+        if (hand) {
+          mbar_wait_t<true>(BAR(BAR_D_EMPTY + sd), phe, p.cg2_spin);
           if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_D_EMPTY + sd), 0));
         }
         ++n_item;
         rd1.next(p.SD);
+        bool second = p.split && hand;                      // split: sub-tile 1 is handed over after the first chunk's stages
         const uint64_t* mrow = mask_s + wk.nt * p.n_kchunks;
         for (int kc = 0; kc < p.n_kchunks; ++kc) {
           uint64_t mask = mrow[kc];
@@ -1308,6 +1376,11 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
             mbar_wait_t<true>(BAR(BAR_W_FULL + sw), rw.ph, p.cg2_spin);
             rw.next(p.SW);
             if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_W_FULL + sw), 0));
+          }
+          if (second) {
+            second = false;
+            mbar_wait_t<true>(BAR(BAR_D_EMPTY + 1), phe, p.cg2_spin);
+            if (leader) mbar_arrive_cluster(mapa_shared(BAR(BAR_D_EMPTY + 1), 0));
           }
         }
       };
@@ -1352,12 +1425,12 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
                 p.N_TILE, nullptr, trc);
         else if (p.res.p)
           drain_fast<1, CG2>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
-                             p.N_TILE, nullptr, trc);
+                             p.N_TILE, nullptr, trc, CG2 && p.split ? BAR(BAR_D_FULL + 1) : 0u, BAR(BAR_D_EMPTY));
         else
           drain_fast<0, CG2>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
-                             p.N_TILE, nullptr, trc);
+                             p.N_TILE, nullptr, trc, CG2 && p.split ? BAR(BAR_D_FULL + 1) : 0u, BAR(BAR_D_EMPTY));
         __syncwarp();
-        if (lane == 0) mbar_arrive(BAR(BAR_D_EMPTY + sd));
+        if (lane == 0) mbar_arrive(BAR(BAR_D_EMPTY + (CG2 && p.split ? 1u : sd)));
         if (warp == 0) TRACE(ti, 9);
       }
     } else {

@@ -585,6 +585,9 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       p.pair_dcol = L.N_total / L.fout;
     }
   }
+  // MT = 2 leaves one accumulator stage: publish / take back its sub-tiles separately (tc_conv.cu gemm1_cg2)
+  p.split = (p.cg2 && p.MT == 2 && p.SD == 1 && !p.pair_mode && L.n_taps <= p.SW && !g_trace &&
+             !getenv("RB_TC_NOSPLIT")) ? 1 : 0;
   p.tiles_per_stream = (p.y.n + p.MT * 128 - 1) / (p.MT * 128);
   if (p.cg2) {
     p.flat_units = p.tiles_per_stream;

@@ -170,6 +170,10 @@ ACT_CASES = [
     # short tensors: the pair takes two neighbouring streams (odd stream count: one CTA of the last pair idles)
     dict(c_in=512, c_out=512, k=3, stride=1, dil=1, off=1, ileave=1, res=0, B=3, n=260, flags=3),
     dict(c_in=512, c_out=1024, k=4, stride=2, dil=1, off=1, ileave=1, res=0, B=5, n=512, flags=3),
+    # split accumulator (MT = 2: the sub-tiles are published / taken back separately), several work items per
+    # pair so that every barrier goes through both parities, with and without a residual
+    dict(c_in=512, c_out=512, k=3, stride=1, dil=3, off=3, ileave=1, res=1, B=40, n=1024, flags=7),
+    dict(c_in=256, c_out=512, k=4, stride=2, dil=1, off=1, ileave=1, res=0, B=64, n=2048, flags=3),
     # sector-complete stores of phase outputs (drain_pair), the second one also as a cta_group::2 pair
     dict(c_in=128, c_out=256, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=2, n=520, flags=3),
     dict(c_in=256, c_out=256, k=3, stride=1, dil=1, off=1, ileave=2, res=0, B=3, n=640, flags=3),
@@ -177,7 +181,7 @@ ACT_CASES = [
 ]
 
 
-@pytest.mark.parametrize("c", ACT_CASES, ids=lambda c: "ci{c_in}_co{c_out}_k{k}_s{stride}_il{ileave}_f{flags}".format(**c))
+@pytest.mark.parametrize("c", ACT_CASES, ids=lambda c: "ci{c_in}_co{c_out}_k{k}_s{stride}_il{ileave}_f{flags}_B{B}".format(**c))
 def test_single_conv_activated_storage(c):
     """LeakyReLU nets keep tensors as leaky(x): the conv input needs no pass, a residual is
     inverted with min(z, 5z), the output is activated in the epilogue before the bf16 store."""
