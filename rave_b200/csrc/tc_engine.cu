@@ -599,8 +599,8 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   }
   if (getenv("RB_TC_PLAN_DEBUG"))
     fprintf(stderr, "tc layer: cin_v %d N %d x %d taps %d dil %d fin %d fout %d KC %d | resident %d fused %d pair %d cg2 %d MT %d "
-            "SA %d SW %d SD %d pair_mode %d rows %d work %d smem %u\n", L.cin_v, L.N_TILE, L.n_ntiles, L.n_taps, L.dil, L.fin,
-            L.fout, L.KC, p.w_resident, p.fused, p.pair, p.cg2, p.MT, p.SA, p.SW, p.SD, p.pair_mode, p.y.n, p.n_work,
+            "SA %d SW %d SD %d pair_mode %d split %d rows %d work %d smem %u\n", L.cin_v, L.N_TILE, L.n_ntiles, L.n_taps, L.dil, L.fin,
+            L.fout, L.KC, p.w_resident, p.fused, p.pair, p.cg2, p.MT, p.SA, p.SW, p.SD, p.pair_mode, p.split, p.y.n, p.n_work,
             p.smem_bytes);
   return launch_tc_conv(p, s);
 }

@@ -174,6 +174,9 @@ ACT_CASES = [
     # pair so that every barrier goes through both parities, with and without a residual
     dict(c_in=512, c_out=512, k=3, stride=1, dil=3, off=3, ileave=1, res=1, B=40, n=1024, flags=7),
     dict(c_in=256, c_out=512, k=4, stride=2, dil=1, off=1, ileave=1, res=0, B=64, n=2048, flags=3),
+    # single-tap cta_group::2 layers: several items per pair, and fewer work slots than pairs
+    dict(c_in=512, c_out=512, k=1, stride=1, dil=1, off=0, ileave=1, res=1, B=48, n=1024, flags=7),
+    dict(c_in=512, c_out=1024, k=1, stride=1, dil=1, off=0, ileave=1, res=0, B=3, n=384, flags=3),
     # sector-complete stores of phase outputs (drain_pair), the second one also as a cta_group::2 pair
     dict(c_in=128, c_out=256, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=2, n=520, flags=3),
     dict(c_in=256, c_out=256, k=3, stride=1, dil=1, off=1, ileave=2, res=0, B=3, n=640, flags=3),
