@@ -536,8 +536,8 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     if (!resident && sr_rows > 0) {
       // stream-as-row: a CTA's work is one short pass over its slice of the weights, bound by the L2
       // round trip of each block -- keep as many blocks in flight as fit beside three A stages
-      int sw = 4;                                                               // the kernel has 4 W barriers
-      if (const char* e = getenv("RB_TC_SR_SW")) sw = std::min(4, std::max(2, atoi(e)));   // experiments only
+      int sw = 6;                                                               // 4 -> 6: C3 1.086 -> 1.051 ms / step
+      if (const char* e = getenv("RB_TC_SR_SW")) sw = std::min(8, std::max(2, atoi(e)));   // experiments only (<= MAX_SW)
       p.SW = sw;
       while (p.SW > 2 && fixed + p.SW * L.blk_bytes + 3 * p.a_stage_bytes > budget) --p.SW;
     }
