@@ -35,6 +35,15 @@ METRIC = "audio-sec/sec v2 encode+decode"
 REF_STREAMS = 32          # CPU sample: 32 of the 512 streams at the full 2^18 length
 
 
+_OUT = None
+
+
+def _emit(record):
+    out = _OUT if _OUT is not None else sys.stdout
+    out.write(json.dumps(record) + "\n")
+    out.flush()
+
+
 def _workload(B, T, streams, gathered):
     return (f"v2 encode+decode (BASELINE configs[1]), {streams} streams x {T} samples @44.1 kHz in all, {B} per GPU, " +
             ("NCCL all-gather of every step's outputs inside the timed region (overlapped with the next step's compute)"
@@ -203,7 +212,7 @@ def run_reference(args):
     val, dt, cores, n = cpu_reference_pass(args.steps, args.warmup, args.samples)
     sample = "each step = " + _cpu_sample(args.samples)
     strong = args.scaling == "strong"
-    print(json.dumps({
+    _emit(({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "audio-sec/sec", "n_gpus": args.gpus,
         "steps": n, "warmup": args.warmup, "ms_per_step": 1e3 * dt,
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
@@ -436,7 +445,7 @@ def run_ours(args):
             del x
             torch.cuda.empty_cache()
             out["eager_gpu"] = eager_gpu(T)
-        print(json.dumps(out))
+        _emit(out)
     if world > 1:
         dist.destroy_process_group()
 
@@ -460,6 +469,13 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the oracle legs (parity check, CPU baseline, eager GPU)")
     ap.add_argument("--dump-ops", default="", help="write per-op device times (JSON) to this file")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON record: whatever native libraries write to file descriptor 1
+    # (NCCL prints its "NCCL version ..." banner there whatever NCCL_DEBUG_FILE says) is sent to stderr, and the
+    # record goes out through a private copy of the original descriptor (_emit)
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -139,13 +139,18 @@ struct WorkIter {
     --left;
   }
   __device__ __forceinline__ Work work(const TcParams& p) const {
+    // p.reverse: the launch walks its row tiles from the END of the tensor.  Consecutive layers alternate, so a
+    // layer starts on the rows its producer wrote last -- the ~100 MB of them that are still in L2.
     if (p.flat_units) {
       // a CTA past the last unit gets a tile far beyond the end: TMA zero-fills its loads, its epilogue stores nothing
-      const int rt = tile / p.n_ntiles, nt_ = tile - rt * p.n_ntiles;
+      const int tl_ = p.reverse ? p.n_work - 1 - tile : tile;
+      const int rt = tl_ / p.n_ntiles, nt_ = tl_ - rt * p.n_ntiles;
       const int g = (rt << p.pair) + ((int)blockIdx.x & ((1 << p.pair) - 1));
       const int bs = g / p.flat_units, tl = g - bs * p.flat_units;
       return Work{nt_, bs < p.B ? bs : 0, bs < p.B ? tl * p.MT * 128 : (1 << 24)};
     }
+    if (p.reverse)
+      return Work{nt, p.B - 1 - b, (((p.tiles_per_stream - 1 - tile) << p.pair) + ((int)blockIdx.x & p.pair)) * p.MT * 128};
     return Work{nt, b, ((tile << p.pair) + ((int)blockIdx.x & p.pair)) * p.MT * 128};
   }
 };

@@ -70,6 +70,7 @@ struct TcParams {
                             // w_blk_bytes = one CTA's half block)
   int split;                // cta_group::2, MT = 2 (one accumulator stage fills tensor memory): the two sub-tiles are
                             // published and taken back separately so their drains overlap MMAs (gemm1_cg2)
+  int reverse;              // walk the row tiles from the end of the tensor (alternate launches: L2 reuse, see WorkIter)
   int flat_units;           // > 0 (cta_group::2 clusters): 128*MT-row units per stream; work slots are 2^pair consecutive
                             // (stream, unit) pairs, stream-major -- see WorkIter
   int dbg;                  // timing experiments only (RB_TC_PD_DBG): 1 skip E1 math, 2 skip E2 drain of the pair unit

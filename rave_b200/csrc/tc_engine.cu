@@ -375,6 +375,15 @@ static int make_view(const Buf& b, int f, TcView* v) {
 static uint32_t align_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
 
 static unsigned long long* g_trace = nullptr;   // debug hook only: device buffer [64][16] of clock stamps
+// Offline programs alternate the direction in which consecutive launches walk their row tiles (TcParams::reverse):
+// a layer then starts on the rows its producer wrote last, which are still in L2.  -1: off (streaming, debug hook).
+static thread_local int g_reverse = -1;
+static inline int next_direction() {
+  if (g_reverse < 0) return 0;
+  const int r = g_reverse;
+  g_reverse ^= 1;
+  return r;
+}
 
 // x_act / res_act / out_act: the tensor is (to be) stored LeakyReLU-activated (Plan::sact).
 // sr_rows > 0: L is a stream-as-row twin (Plan::sr_layers); computes the sr_rows rows of the chunk for all
@@ -602,6 +611,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
             "SA %d SW %d SD %d pair_mode %d split %d rows %d work %d smem %u\n", L.cin_v, L.N_TILE, L.n_ntiles, L.n_taps, L.dil, L.fin,
             L.fout, L.KC, p.w_resident, p.fused, p.pair, p.cg2, p.MT, p.SA, p.SW, p.SD, p.pair_mode, p.split, p.y.n, p.n_work,
             p.smem_bytes);
+  p.reverse = sr_rows == 0 ? next_direction() : 0;
   return launch_tc_conv(p, s);
 }
 
@@ -667,6 +677,7 @@ static int run_pair_du(const Layer& L, const rb_op& op, const Buf& src, const Bu
   if (getenv("RB_TC_PLAN_DEBUG"))
     fprintf(stderr, "tc layer: pair DilatedUnit C %d dil %d | resident %d SA %d SW %d rows %d work %d smem %u\n", L.N_TILE,
             L.dil, p.w_resident, p.SA, p.SW, p.y.n, p.n_work, p.smem_bytes);
+  p.reverse = next_direction();
   return launch_tc_du_pair(p, s);
 }
 
@@ -1243,6 +1254,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
                (long long)h->noise_numel, (long long)B * noise_bstride);
       noise = h->noise + (size_t)b0 * noise_bstride;
     }
+    tc::g_reverse = getenv("RB_TC_NOREVERSE") ? -1 : 0;
     for (int i = ob; i < oe; ++i) {
       if (i == n_enc && has_enc && has_dec) {      // latent stays on the device, group-major
         bufs[h->spec.dec_in_slot] = bufs[h->spec.enc_out_slot];
@@ -1280,6 +1292,7 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
     }
   }
   h->cur_b0 = 0;
+  tc::g_reverse = -1;
   adain_finalize(h, ob, oe);
   return RB_OK;
 }
