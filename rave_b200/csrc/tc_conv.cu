@@ -105,7 +105,11 @@ struct Work {
 };
 // The work items of one persistent CTA: w = blockIdx.x + i * gridDim.x, decoded once with
 // divisions and then advanced by the pre-decomposed grid stride (adds and compares only).
-struct WorkIter {
+// FLAT is a compile-time property (the cta_group::2 variants): its two integer divisions per work() -- inlined at
+// every call site -- spread the hot code of the narrow fused units over more instruction-cache lines when the
+// choice was a run-time branch (C = 64 units 776 -> 865 kcycles, icc hit rate 99.4 -> 93.7 %).
+template <bool FLAT>
+struct WorkIterT {
   int nt, b, tile, left;
   // w = (b * tiles_per_stream + tile) * n_ntiles + nt: the n-tiles of one row tile run at the same
   // time on neighbouring CTAs, so the A tile is read from HBM once and from L2 afterwards
@@ -118,7 +122,7 @@ struct WorkIter {
   // (the deepest layers: 256 rows per stream).  `tile` holds the slot's linear index, `b` the grid stride.
   __device__ __forceinline__ void init(const TcParams& p) {
     const int w = (int)blockIdx.x >> p.pair, stride = (int)gridDim.x >> p.pair;
-    if (p.flat_units) {
+    if (FLAT) {
       nt = 0; tile = w; b = stride;
       left = w < p.n_work ? (p.n_work - w + stride - 1) / stride : 0;
       return;
@@ -130,7 +134,7 @@ struct WorkIter {
     left = w < p.n_work ? (p.n_work - w + stride - 1) / stride : 0;
   }
   __device__ __forceinline__ void next(const TcParams& p) {
-    if (p.flat_units) { tile += b; --left; return; }
+    if (FLAT) { tile += b; --left; return; }
     nt += p.step_nt;
     if (nt >= p.n_ntiles) { nt -= p.n_ntiles; ++tile; }
     tile += p.step_tile;
@@ -141,7 +145,7 @@ struct WorkIter {
   __device__ __forceinline__ Work work(const TcParams& p) const {
     // p.reverse: the launch walks its row tiles from the END of the tensor.  Consecutive layers alternate, so a
     // layer starts on the rows its producer wrote last -- the ~100 MB of them that are still in L2.
-    if (p.flat_units) {
+    if (FLAT) {
       // a CTA past the last unit gets a tile far beyond the end: TMA zero-fills its loads, its epilogue stores nothing
       const int tl_ = p.reverse ? p.n_work - 1 - tile : tile;
       const int rt = tl_ / p.n_ntiles, nt_ = tl_ - rt * p.n_ntiles;
@@ -310,23 +314,6 @@ __device__ __forceinline__ void load_acc(uint32_t taddr, const float* bias_s, fl
     }
   }
 }
-// Second half of a software-pipelined accumulator load: the tcgen05.ld of these 16 columns into r was issued a
-// piece of work earlier (the trace of the C = 128 unit showed ~450 of the ~1100 cycles of a 16-column E2 piece
-// waiting for the load it had just issued); waits, adds the bias.  r is free for the next load afterwards.
-__device__ __forceinline__ void acc_finish16(uint32_t* r, const float* bias_s, float* v) {
-  float4 b[4];
-#pragma unroll
-  for (int g = 0; g < 4; ++g) b[g] = *reinterpret_cast<const float4*>(bias_s + g * 4);
-  tmem_ld_wait16(r);
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const int e = g * 4;
-    v[e + 0] = __uint_as_float(r[e + 0]); v[e + 1] = __uint_as_float(r[e + 1]);
-    v[e + 2] = __uint_as_float(r[e + 2]); v[e + 3] = __uint_as_float(r[e + 3]);
-    add2(v[e + 0], v[e + 1], b[g].x, b[g].y);
-    add2(v[e + 2], v[e + 3], b[g].z, b[g].w);
-  }
-}
 // LeakyReLU(0.2) on NC fp32 values: packed multiply + max.
 template <int NC>
 __device__ __forceinline__ void leaky_n(float* v) {
@@ -481,16 +468,13 @@ __device__ __forceinline__ void drain_smem16(const TcParams& p, uint32_t bar_ful
   const bool ract = p.res_act != 0, oact = p.out_act != 0;
   mbar_wait(bar_full, parity);
   tc_fence_after();
-  // the accumulator of a piece is requested before the math of the piece in front of it
-  uint32_t r[16];
-  if (part * 32 < NT) tmem_ld16(tbase + (uint32_t)(part * 32), r);
+  // (requesting a piece's accumulator one piece ahead was measured: +8 % instructions, no fewer cycles)
 #pragma unroll 1
   for (int c = part * 32; c < NT;) {
     const uint4 r0 = sp[0], r1 = sp[RA];
     float v[16];
-    acc_finish16(r, bs + c, v);
+    load_acc<16>(tbase + (uint32_t)c, bs + c, v);
     const int d = (c & 16) ? jump : 16;
-    if (c + d < NT) tmem_ld16(tbase + (uint32_t)(c + d), r);
     const uint32_t w[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
@@ -550,15 +534,11 @@ __device__ __forceinline__ void drain_res16(const TcParams& p, uint32_t bar_full
   mbar_wait(bar_full, parity);
   tc_fence_after();
   TRACE(tr, 12);
-  // the accumulator of a piece is requested before the math of the piece in front of it
-  uint32_t r[16];
-  if (c_first < NT) tmem_ld16(tbase + (uint32_t)c_first, r);
 #pragma unroll 1
   for (int c = c_first; c < NT;) {
     float v[16];
-    acc_finish16(r, bs + c, v);
+    load_acc<16>(tbase + (uint32_t)c, bs + c, v);
     const int d = step(c);
-    if (c + d < NT) tmem_ld16(tbase + (uint32_t)(c + d), r);
     TRACE(tr, 13);
     const uint32_t w[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
     // the queue moves up and the piece two ahead is requested before this piece's math
@@ -847,30 +827,6 @@ __device__ __forceinline__ void h_chunk(uint32_t taddr, const float* bs, const f
   }
 }
 
-// The 16-column piece of E1, software-pipelined: r holds this piece's accumulator (tcgen05.ld issued a piece
-// earlier); the next piece (TMEM address t_next, 0 = none) is requested before this piece's math.
-template <int ACT2, bool HT>
-__device__ __forceinline__ void h_piece(uint32_t* r, uint32_t taddr, uint32_t t_next, const float* bs,
-                                        const float* alpha2, int ia_off, uint8_t* hdst) {
-  float v[16];
-  acc_finish16(r, bs, v);
-  if (t_next) tmem_ld16(t_next, r);
-  if (ACT2 == RB_ACT_LEAKY) {
-    leaky_n<16>(v);
-  } else if (ACT2 == RB_ACT_SNAKE) {
-#pragma unroll
-    for (int e = 0; e < 16; ++e) v[e] = act_f<ACT2>(v[e], alpha2[e], alpha2[e + ia_off]);
-  }
-  if (!HT) {
-    *reinterpret_cast<uint4*>(hdst) = pack8(v);
-    *reinterpret_cast<uint4*>(hdst + 2048) = pack8(v + 8);
-  } else {
-    const uint4 lo = pack8(v), hi = pack8(v + 8);
-    const uint32_t q[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-    tmem_st8(taddr, q);
-  }
-}
-
 }  // namespace
 
 // issued by the elected lane of the MMA warp only
@@ -900,6 +856,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
   static_assert(NS == 2 || (NS == 3 && FUSED && PRE == RB_ACT_NONE), "three sets: fused units without activation pass");
   static_assert(!CG2 || (!FUSED && PRE == RB_ACT_NONE && NS == 2), "cta_group::2: plain streamed layers");
   static_assert(!HT || FUSED, "h in tensor memory: fused units");
+  using WorkIter = WorkIterT<CG2>;                          // cta_group::2 launches number their work flat
   constexpr int W_MMA = NS == 3 ? 24 : 16, W_WPROD = W_MMA + 1, W_APROD = W_MMA + 2, W_MMA2 = W_MMA + 3;
   constexpr int N_THREADS = NS == 3 ? 896 : TC_THREADS;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -1456,16 +1413,12 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         uint8_t* hb = h_smem + (size_t)sh * p.h_stage_bytes + (size_t)rit * 16;
         {
           // rolled 16-column pieces (see drain_smem16: instruction-cache footprint), both halves of this warp's
-          // 32-column chunks; each piece's accumulator is requested before the math of the piece in front of it
+          // 32-column chunks
           const uint32_t tb1 = tmem + lane_base + sd * d_stage_cols;
-          uint32_t r[16];
-          if (part * 32 < C2) tmem_ld16(tb1 + (uint32_t)(part * 32), r);
 #pragma unroll 1
           for (int c = part * 32; c < C2;) {
-            const int cn = (c & 16) ? c - 16 + E1_PARTS * 32 : c + 16;
-            h_piece<ACT2, HT>(r, tb1 + (uint32_t)c, cn < C2 ? tb1 + (uint32_t)cn : 0u, bias_s + c, alpha2_s + c, C2,
-                              hb + (size_t)(c >> 3) * 2048);
-            c = cn;
+            h_chunk<ACT2, 16, HT>(tb1 + (uint32_t)c, bias_s + c, alpha2_s + c, C2, hb + (size_t)(c >> 3) * 2048);
+            c = (c & 16) ? c - 16 + E1_PARTS * 32 : c + 16;
           }
         }
         if (HT) tmem_st_wait();
@@ -1574,6 +1527,7 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
 template <int NS>
 __global__ void __launch_bounds__(TC_THREADS, 1)
     tc_du_pair_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcTmap tmx) {
+  using WorkIter = WorkIterT<false>;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + BAR_COUNT * 8);
@@ -1815,16 +1769,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       tc_fence_after();
       int i = 0;
       const bool on = !(p.dbg & 1);
-      uint32_t r[16];                                       // each piece is requested one piece ahead (h_piece)
-      if (on) tmem_ld16(d1 + (uint32_t)(16 * part), r);
 #pragma unroll 1
       for (int half = 0; half < 2; ++half) {
         const int iend = half ? ppw : (ppw + 1) / 2;
 #pragma unroll 1
         for (; i < iend && on; ++i) {
           const int c = 16 * part + 64 * i;
-          h_piece<RB_ACT_LEAKY, true>(r, d1 + (uint32_t)c, i + 1 < ppw ? d1 + (uint32_t)(c + 64) : 0u, bias_s + c,
-                                      nullptr, 0, nullptr);
+          h_chunk<RB_ACT_LEAKY, 16, true>(d1 + (uint32_t)c, bias_s + c, nullptr, 0, nullptr);
         }
         tmem_st_wait();
         tc_fence_before();
@@ -1994,6 +1945,7 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
            "only LeakyReLU can be stored activated");
   RB_CHECK(!p.pair || (!p.fused && !p.w_resident && p.pre_act == RB_ACT_NONE), RB_ERR_INVALID,
            "pair mode is for plain streamed layers");
+  RB_CHECK((p.cg2 != 0) == (p.flat_units != 0), RB_ERR_INVALID, "flat work numbering is the cta_group::2 variants'");
   // pair mode: one cluster of two CTAs per work slot
   const int slots = n_sm >> p.pair;
   const int stride = p.n_work < slots ? p.n_work : slots;

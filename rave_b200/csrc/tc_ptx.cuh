@@ -400,16 +400,6 @@ __device__ __forceinline__ void tmem_st_wait() {
 __device__ __forceinline__ void tmem_ld_wait() {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
-// The wait of a load issued EARLIER than just before its use (software-pipelined drains): the 16 registers are
-// in/out operands, so the compiler cannot read, move or spill them between the load and this wait.
-__device__ __forceinline__ void tmem_ld_wait16(uint32_t* r) {
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
-                 "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
-               :
-               : "memory");
-}
-
 // ------------------------------------------------------------------- packed fp32 pairs
 // sm_100 executes add / mul / fma on two fp32 per instruction (f32x2): halves the epilogue math.
 __device__ __forceinline__ void add2(float& a0, float& a1, float b0, float b1) {
