@@ -142,6 +142,16 @@ struct WorkIterT {
     b += p.step_b;
     --left;
   }
+  // two items on in one step (the sets of output warps of a fused unit take alternate items)
+  __device__ __forceinline__ void next2(const TcParams& p) {
+    if (FLAT) { tile += 2 * b; left -= 2; return; }
+    nt += p.step2_nt;
+    if (nt >= p.n_ntiles) { nt -= p.n_ntiles; ++tile; }
+    tile += p.step2_tile;
+    if (tile >= p.tiles_per_stream) { tile -= p.tiles_per_stream; ++b; }
+    b += p.step2_b;
+    left -= 2;
+  }
   __device__ __forceinline__ Work work(const TcParams& p) const {
     // p.reverse: the launch walks its row tiles from the END of the tensor.  Consecutive layers alternate, so a
     // layer starts on the rows its producer wrote last -- the ~100 MB of them that are still in L2.
@@ -164,6 +174,11 @@ struct Ring {
   uint32_t idx = 0, ph = 0;
   __device__ __forceinline__ void next(int n) {
     if (++idx == (uint32_t)n) { idx = 0; ph ^= 1; }
+  }
+  // k positions on (any k, n >= 1)
+  __device__ __forceinline__ void advance(int k, int n) {
+    idx += (uint32_t)k;
+    while (idx >= (uint32_t)n) { idx -= (uint32_t)n; ph ^= 1; }
   }
 };
 
@@ -1474,15 +1489,19 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           if (t1 < n) {
             run_e1(rd, rh, (uint32_t)t1);
             t1 += NS;
-#pragma unroll
-            for (int i = 0; i < NS; ++i) { rd.next(p.SD); rh.next(p.SH); }
+            rd.advance(NS, p.SD);
+            rh.advance(NS, p.SH);
             did = true;
           }
           if (!skip2 && t2 < n) {
             run_e2(w2.work(p), rd2, ra, (uint32_t)t2);
             t2 += NS;
+            if (NS == 2) w2.next2(p);
+            else
 #pragma unroll
-            for (int i = 0; i < NS; ++i) { w2.next(p); rd2.next(p.SD); ra.next(p.SA); }
+              for (int i = 0; i < NS; ++i) w2.next(p);
+            rd2.advance(NS, p.SD);
+            ra.advance(NS, p.SA);
             did = true;
           }
           skip2 = false;
@@ -1899,6 +1918,10 @@ int launch_tc_du_pair(TcParams& p, cudaStream_t s) {
     p.step_nt = stride - rt * p.n_ntiles;
     p.step_b = rt / p.tiles_per_stream;
     p.step_tile = rt - p.step_b * p.tiles_per_stream;
+    const int rt2 = 2 * stride / p.n_ntiles;
+    p.step2_nt = 2 * stride - rt2 * p.n_ntiles;
+    p.step2_b = rt2 / p.tiles_per_stream;
+    p.step2_tile = rt2 - p.step2_b * p.tiles_per_stream;
   }
   TcTmap tm;
   int rc = make_tmap(p, &tm);
@@ -1955,6 +1978,10 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
     p.step_nt = stride - rt * p.n_ntiles;
     p.step_b = rt / p.tiles_per_stream;
     p.step_tile = rt - p.step_b * p.tiles_per_stream;
+    const int rt2 = 2 * stride / p.n_ntiles;
+    p.step2_nt = 2 * stride - rt2 * p.n_ntiles;
+    p.step2_b = rt2 / p.tiles_per_stream;
+    p.step2_tile = rt2 - p.step2_b * p.tiles_per_stream;
   }
   TcTmap tm;
   int rc = make_tmap(p, &tm);

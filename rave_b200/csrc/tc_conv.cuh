@@ -82,6 +82,7 @@ struct TcParams {
   int a_flat;               // unit-stride view: interior tiles are fetched as linear bulk copies per group
   uint32_t a_tx_bytes;      // bytes one chunk adds to its mbarrier
   int step_nt, step_b, step_tile;   // work-item increment of a persistent CTA (grid stride, decomposed)
+  int step2_nt, step2_b, step2_tile;   // twice the grid stride, decomposed (the output-warp sets advance two items at a time)
   int SA, SW, SD;           // A stages, W stages (streamed), accumulator stages
   int out_mask;             // 1: negate odd channels at even rows (pqmf.py:13-17 reverse_half)
   // > 0: every 32-column chunk is [16 wave | 16 amplitude] of one real row (head = chunks per view
