@@ -44,10 +44,10 @@ def _emit(record):
     out.flush()
 
 
-def _workload(B, T, streams, gathered):
+def _workload(B, T, streams, gathered, how=None):
     return (f"v2 encode+decode (BASELINE configs[1]), {streams} streams x {T} samples @44.1 kHz in all, {B} per GPU, " +
-            ("NCCL all-gather of every step's outputs inside the timed region (overlapped with the next step's compute)"
-             if gathered else "no data-path collective"))
+            (f"all-gather of every step's outputs inside the timed region, overlapped with the next step's compute "
+             f"({how or 'NCCL'})" if gathered else "no data-path collective"))
 
 
 def _peaks():
@@ -245,7 +245,8 @@ def run_ours(args):
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     esz = 2 if args.dtype == "bf16" else 4
     T = args.samples
-    from rave_b200.shard import OverlappedGather, max_over_ranks, stream_shard
+    from rave_b200.shard import OverlappedGather, PeerCopyGather, gather_outputs, max_over_ranks, stream_shard
+    gather_how = [None]
     m = RAVE.from_gin(["v2.gin"], device=f"cuda:{local}", dtype=dtype)
     m.load_state_dict(_state_dict()[1])
     if args.microbatch:
@@ -266,7 +267,17 @@ def run_ours(args):
         first, B = stream_shard(args.streams, world, rank, scaling)
         x = make_input(first, B)
         gathered = world > 1 and scaling == "strong"
-        gather = OverlappedGather(world) if gathered else None
+        gather = None
+        if gathered:
+            gather_how[0] = "nccl all_gather_into_tensor on a side stream"
+            if args.gather == "p2p":
+                try:
+                    gather = PeerCopyGather(world, rank, (B, 1, T), dtype, torch.device("cuda", local))
+                    gather_how[0] = "peer copies into symmetric buffers (copy engines) + one barrier per step, side stream"
+                except Exception as e:                       # no symmetric memory on this box: the NCCL collective
+                    sys.stderr.write(f"PeerCopyGather unavailable ({e!r}); using the NCCL all-gather\n")
+            if gather is None:
+                gather = OverlappedGather(world)
 
         def step():
             y = m(x)
@@ -289,6 +300,14 @@ def run_ours(args):
         barrier()
         if sampler is not None:
             sampler.stop = True
+        if gathered:
+            # outside the timed region: what the gather delivered against the NCCL collective on the same outputs
+            got = gather(m(x))
+            gather.finish()
+            torch.cuda.synchronize()
+            want = gather_outputs(m(x), world)
+            gather_how.append(bool(torch.equal(got, want)))
+            del got, want
         ms = max_over_ranks(ev0.elapsed_time(ev1), "cuda") / args.steps
         return ms, m.kernel_launches() - l0, first, B, B * world, x, gathered
 
@@ -420,7 +439,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": "audio-sec/sec", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": _workload(B, T, streams, gathered),
+            "config": {"workload": _workload(B, T, streams, gathered, gather_how[0]),
                        "l2": f"input {B * T * esz >> 20} MiB + layer activations (up to {B * T * esz * 4 >> 20} MiB each) "
                              "per GPU and step > 126 MB L2: no flush needed",
                        "weights": "random-init (name-keyed recipe), CAPACITY=64",
@@ -435,6 +454,8 @@ def run_ours(args):
         }
         if weak is not None:
             out["weak"] = weak
+        if gathered:
+            out["gather"] = {"how": gather_how[0], "equals_nccl_all_gather": gather_how[1] if len(gather_how) > 1 else None}
         if not args.no_cpu:
             # the oracle as the CHECKER: two rows of this rank's step output, outside the timed region
             out["parity_check"] = parity_check(m, x, [0, B - 1], first, T)
@@ -465,6 +486,9 @@ def main():
                     help="strong (default, the literal BASELINE configs[1]): --streams in all, sharded over the ranks, "
                          "NCCL all-gather of every step's outputs inside the timed region; weak: --streams per GPU, "
                          "no data-path collective (identical at N = 1)")
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"],
+                    help="strong scaling, N > 1: how every step's outputs reach all ranks (p2p: peer copies into "
+                         "symmetric buffers on the copy engines; nccl: all_gather_into_tensor)")
     ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the additional weak-scaling record")
     ap.add_argument("--no-cpu", action="store_true", help="skip the oracle legs (parity check, CPU baseline, eager GPU)")
     ap.add_argument("--dump-ops", default="", help="write per-op device times (JSON) to this file")
