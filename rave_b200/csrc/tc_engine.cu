@@ -474,7 +474,17 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     if (attempt == 0 && !resident) continue;
     RB_CHECK(resident || !L.fused, RB_ERR_UNSUPPORTED, "fused unit does not fit in shared memory");
     p.w_resident = resident ? 1 : 0;
-    p.dual_g1 = (resident && L.N_TILE <= 64 && !getenv("RB_TC_NODUAL")) ? 1 : 0;
+    {
+      // Two warps issue GEMM1 of alternate work items where one tile's MMAs are short: the issuing warp shares its
+      // scheduler with four busy output warps and needs ~140 cycles per tcgen05.mma (event trace of the C = 128
+      // unit: 3300 cycles to issue 24 MMAs that execute in 1536), so a single issuer sets the tile rate.
+      // N_TILE <= 64 always; N_TILE = 128 when a tile is at most 2048 tensor-pipe cycles (first conv 527 -> 425
+      // kcycles, C = 128 units 455 -> 446; the 64->128 strided conv, 3072 cycles of MMAs per tile, is left alone)
+      const int mma_clk = L.total_blocks * (L.KC / 16) * (L.N_TILE / 2);
+      int dual_max = 128;
+      if (const char* e = getenv("RB_TC_DUAL_MAXN")) dual_max = atoi(e);   // experiments only
+      p.dual_g1 = (resident && L.N_TILE <= dual_max && (L.N_TILE <= 64 || mma_clk <= 2048) && !getenv("RB_TC_NODUAL")) ? 1 : 0;
+    }
     p.MT = (!resident && p.y.n >= 256 && sr_rows == 0) ? 2 : 1;   // stream-as-row: few row tiles, keep them all busy
     // streamed transposed convs run as cluster pairs: the two CTAs split every weight block (half
     // the L2 -> SM weight traffic each), which pays for one sub-tile per accumulator stage and so
