@@ -1367,16 +1367,21 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
           if (cg2_lead) for (wi.init(p); wi.left > 0; wi.next(p)) gemm1_cg2(wi.work(p));
           else for (wi.init(p); wi.left > 0; wi.next(p)) relay_cg2(wi.work(p));
         }
-      } else if (warp == W_MMA2) {
-        if (FUSED)
-          for (wi.init(p); wi.left > 0; wi.next(p)) gemm2();
-      } else if (!p.dual_g1) {
+      } else if (FUSED && warp == W_MMA2) {
+        for (wi.init(p); wi.left > 0; wi.next(p)) gemm2();
+      } else if (p.dual_g1 <= 1) {
         if (warp == W_MMA)
           for (wi.init(p); wi.left > 0; wi.next(p)) gemm1(wi.work(p));
       } else {
-        bool mine = warp == W_MMA;
-        for (wi.init(p); wi.left > 0; wi.next(p), mine = !mine) {
-          if (mine) gemm1(wi.work(p)); else skip1(wi.work(p));
+        // dual_g1 = 2 or 3 issuers: W_MMA, the weight-producer warp (idle once the resident weights are in) and,
+        // in kernels without a second GEMM, W_MMA2 take the work items in turn
+        const int me = warp == W_MMA ? 0 : warp == W_WPROD ? 1 : 2;
+        if (me < p.dual_g1) {
+          int k = 0;
+          for (wi.init(p); wi.left > 0; wi.next(p)) {
+            if (k == me) gemm1(wi.work(p)); else skip1(wi.work(p));
+            if (++k == p.dual_g1) k = 0;
+          }
         }
       }
     }

@@ -75,7 +75,7 @@ struct TcParams {
                             // (stream, unit) pairs, stream-major -- see WorkIter
   int dbg;                  // timing experiments only (RB_TC_PD_DBG): 1 skip E1 math, 2 skip E2 drain of the pair unit
   int cg2_spin;             // cta_group::2 waits: bit 0 producers / epilogue / relay spin, bit 1 the leader's MMA warp spins
-  int dual_g1;              // resident + narrow: two warps issue GEMM1 of alternate work items
+  int dual_g1;              // resident + short tiles: 2 or 3 warps issue GEMM1 of the work items in turn (0 / 1: one issuer)
   // A tile TMA boxes (tensor map over the input view, see launch_tc_conv): a chunk of KC/8
   // channel groups x R_ALLOC rows is fetched as boxes of a_gb groups x a_box_rows rows
   int a_gb, a_box_rows, a_rsplit;

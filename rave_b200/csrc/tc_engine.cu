@@ -483,7 +483,10 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       const int mma_clk = L.total_blocks * (L.KC / 16) * (L.N_TILE / 2);
       int dual_max = 128;
       if (const char* e = getenv("RB_TC_DUAL_MAXN")) dual_max = atoi(e);   // experiments only
-      p.dual_g1 = (resident && L.N_TILE <= dual_max && (L.N_TILE <= 64 || mma_clk <= 2048) && !getenv("RB_TC_NODUAL")) ? 1 : 0;
+      p.dual_g1 = (resident && L.N_TILE <= dual_max && (L.N_TILE <= 64 || mma_clk <= 2048) && !getenv("RB_TC_NODUAL")) ? 2 : 0;
+      // (a third issuer -- the second-GEMM warp, idle in unfused kernels -- measured: PQMF banks 249 -> 247, last
+      // conv 587 -> 582 kcycles: two are enough.  RB_TC_TRI=1 turns it on for experiments.)
+      if (p.dual_g1 && !L.fused && L.N_TILE <= 64 && getenv("RB_TC_TRI")) p.dual_g1 = 3;
     }
     p.MT = (!resident && p.y.n >= 256 && sr_rows == 0) ? 2 : 1;   // stream-as-row: few row tiles, keep them all busy
     // streamed transposed convs run as cluster pairs: the two CTAs split every weight block (half
