@@ -1973,6 +1973,9 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
            "only LeakyReLU can be stored activated");
   RB_CHECK(!p.pair || (!p.fused && !p.w_resident && p.pre_act == RB_ACT_NONE), RB_ERR_INVALID,
            "pair mode is for plain streamed layers");
+  RB_CHECK(p.dual_g1 <= 1 || (p.w_resident && p.SA >= p.dual_g1 * p.n_kchunks && p.SD >= p.dual_g1), RB_ERR_INVALID,
+           "%d GEMM1 issuers need resident weights, %d A stages and as many accumulator stages", p.dual_g1,
+           p.dual_g1 * p.n_kchunks);
   RB_CHECK((p.cg2 != 0) == (p.flat_units != 0), RB_ERR_INVALID, "flat work numbering is the cta_group::2 variants'");
   // pair mode: one cluster of two CTAs per work slot
   const int slots = n_sm >> p.pair;

@@ -584,9 +584,16 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     break;
   }
   RB_CHECK(p.SA >= 1, RB_ERR_UNSUPPORTED, "conv tile does not fit in shared memory");
+  // Several GEMM1 issuers run up to one work item apart.  An issuer may wait for fill k + 1 of an A stage only
+  // when fill k is certainly complete (an mbarrier parity wait passes on a barrier that is TWO phases behind):
+  // true when the stage's previous fill belongs to the issuer's own previous item, i.e. the ring holds the
+  // chunks of as many items as there are issuers.  (The stream-as-row twin of a C = 128 unit has 6 chunks per
+  // item and 5 stages: with two issuers its second launch read stages that had not been filled.)
+  if (p.dual_g1 > 1 && p.SA < p.dual_g1 * L.n_kchunks) p.dual_g1 = 0;
   const int acc_cols = L.fused ? 2 * L.N_TILE : p.MT * L.N_TILE;
   p.SD = std::max(1, std::min(4, 512 / acc_cols));
   if (L.fused) p.SD = std::min(sd_max, 4);
+  if (p.dual_g1 > p.SD) p.dual_g1 = p.SD >= 2 ? p.SD : 0;   // same rule for the accumulator stages
   if (p.h_tmem) p.SH = p.SD;
   if (p.res_smem && p.SA < 5) p.res_smem = 0;           // too few A stages to hold tiles until E2
   RB_CHECK(!L.fused || p.SD >= 2, RB_ERR_UNSUPPORTED, "fused unit needs two accumulator stages");

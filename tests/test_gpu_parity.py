@@ -318,6 +318,16 @@ def test_streaming_bf16_many_streams_fill_row_tiles(name):
     y2 = torch.cat([m2(x2[..., c * 2 * n:(c + 1) * 2 * n].contiguous()) for c in range(x.shape[-1] // (2 * n))], -1)
     assert torch.equal(y2[2:], y2[:2].repeat(64, 1, 1))
     assert rel_l2(y2[:2].float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
+    if name == "v2causal_c64":
+        # the size of the C3 bench leg: 1024 streams -- the CTAs of the stream-as-row units run SEVERAL work
+        # items each, so every stage of their rings is reused (two GEMM1 issuers once read A stages there that had
+        # not been filled: six K chunks per item, five stages)
+        m3, _, _ = _model(name, streaming=True, dtype=torch.bfloat16)
+        m3.alloc_streams(1024, n)
+        x3 = x.repeat(4, 1, 1).contiguous()
+        y3 = torch.cat([m3(x3[..., c * n:(c + 1) * n].contiguous()) for c in range(x.shape[-1] // n)], -1)
+        assert torch.equal(y3[2:], y3[:2].repeat(511, 1, 1))
+        assert rel_l2(y3[:2].float().cpu().numpy(), a["y_stream"]) < 2 * BF16_TOL
 
 
 @pytest.mark.gpu
