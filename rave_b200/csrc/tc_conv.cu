@@ -793,11 +793,15 @@ __device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full,
     }
   } else {
     // phases: view channel n = ph * cpo + c; unit(group g, phase ph) = g * sA + ph
+    // (no divisions here: this preamble runs once per warp and tile, and these launches have one or two pieces
+    // per warp and tile -- the two divisions were ~50 of its 134 instructions)
     const int cpo = p.pair_dcol, kper = cpo >> 4;
-    const int units = (NT / (2 * cpo)) * kper;
+    const int units = p.pair_units;                           // (NT / (2 cpo)) * kper, from the host
+    int pp0 = 0, k0 = part;                                   // unit index = part, part + nparts, ...
+    while (k0 >= kper) { k0 -= kper; ++pp0; }
     for (int mt = 0; mt < MTn; ++mt) {
       const bool valid = row + mt * 128 < p.y.n;
-      int pp = part / kper, k = part - pp * kper;             // unit index = part, part + nparts, ...
+      int pp = pp0, k = k0;
       for (int u = part; u < units; u += nparts) {
         const int cA = 2 * pp * cpo + 16 * k;
         float v[32];

@@ -612,6 +612,7 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
     } else if (L.fout >= 2 && (L.fout & 1) == 0 && p.y.sB == 1 && (p.y.sA & 1) == 0) {
       p.pair_mode = 1;
       p.pair_dcol = L.N_total / L.fout;
+      p.pair_units = (L.N_TILE / (2 * p.pair_dcol)) * (p.pair_dcol >> 4);
     }
   }
   // MT = 2 leaves one accumulator stage: publish / take back its sub-tiles separately (tc_conv.cu gemm1_cg2)
