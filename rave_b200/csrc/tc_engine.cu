@@ -512,7 +512,8 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
       // (>= 8 K chunks x taps) that the un-overlapped epilogue is the smaller cost than streaming every weight
       // block twice as often; else one sub-tile and two accumulator stages (measured per layer,
       // profiles/r02_cg2_cycles.txt)
-      p.MT = (p.y.n >= 512 && L.n_taps >= 2 && L.n_kchunks >= 8) ? 2 : 1;
+      // (single-tap layers too since the accumulator is split: conv1 + res C = 512 321 -> 306 kcycles)
+      p.MT = (p.y.n >= 512 && L.n_kchunks >= 8) ? 2 : 1;
       if (const char* e = getenv("RB_TC_CG2_MT")) p.MT = (atoi(e) == 2 && p.y.n >= 512) ? 2 : 1;   // experiments only
       // short tensors (the deepest layers: 256 rows per stream) too: the units of a cluster are numbered across
       // streams (flat_units), so each CTA still runs two sub-tiles per weight block -- these layers stream their
