@@ -797,6 +797,8 @@ __device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full,
     // per warp and tile -- the two divisions were ~50 of its 134 instructions)
     const int cpo = p.pair_dcol, kper = cpo >> 4;
     const int units = p.pair_units;                           // (NT / (2 cpo)) * kper, from the host
+    bs += wk.nt * NT;                                         // this n-tile's bias columns ...
+    const uint32_t ph0 = (uint32_t)(wk.nt * p.pair_ph_tile);  // ... and its first phase
     int pp0 = 0, k0 = part;                                   // unit index = part, part + nparts, ...
     while (k0 >= kper) { k0 -= kper; ++pp0; }
     for (int mt = 0; mt < MTn; ++mt) {
@@ -808,7 +810,7 @@ __device__ __forceinline__ void drain_pair(const TcParams& p, uint32_t bar_full,
         load_acc2x16(tbase + (uint32_t)(mt * NT + cA), tbase + (uint32_t)(mt * NT + cA + cpo), bs + cA,
                      bs + cA + cpo, v);
         if (oact) leaky_n<32>(v);
-        uint4* yp = ybase + (yoff + (uint32_t)(mt * 128 * p.y.sT + 2 * k * p.y.sA + 2 * pp));
+        uint4* yp = ybase + (yoff + (uint32_t)(mt * 128 * p.y.sT + 2 * k * p.y.sA + 2 * pp) + ph0);
         if (valid) {
           st_global_256(yp, pack8(v), pack8(v + 16));
           st_global_256(yp + p.y.sA, pack8(v + 8), pack8(v + 24));

@@ -93,6 +93,7 @@ struct TcParams {
   // accumulator) are neighbours in memory and leave as one 32-byte store; 2 consecutive channel groups are
   // neighbours (audio rows); 3 waveform head with two real rows per view row
   int pair_mode, pair_dcol;
+  int pair_ph_tile;         // pair_mode 1 with several n-tiles: phases per n-tile (0: one n-tile)
   int pair_units;           // pair_mode 1: 32-byte units of a row tile, (N_TILE / (2 pair_dcol)) * (pair_dcol / 16)
   int tiles_per_stream, n_work;
   // fused DilatedUnit (blocks.py:84-113 + Residual :32-46): second GEMM k=1 on act(D1 + bias)

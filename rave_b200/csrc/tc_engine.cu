@@ -603,17 +603,24 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   p.tmem_cols = cols;
   // sector-complete stores (tc_conv.cu drain_pair): rows that interleave in memory leave in 32-byte pieces
   p.pair_mode = 0;
-  if (!L.fused && !res && sr_rows == 0 && p.pre_act == RB_ACT_NONE && L.n_ntiles == 1 && !L.out_mask &&
+  p.pair_ph_tile = 0;
+  if (!L.fused && !res && sr_rows == 0 && p.pre_act == RB_ACT_NONE && !L.out_mask &&
       (p.y.sT & 1) == 0 && (p.y.sb & 1) == 0 && ((p.y.hist * p.y.sT) & 1) == 0 &&
       (reinterpret_cast<uintptr_t>(p.y.p) & 31) == 0 && !getenv("RB_TC_NOPAIRST")) {
     if (L.head) {
-      if (L.head == 2 && L.N_total == 64 && p.MT == 1 && (p.y.sA & 1) == 0) p.pair_mode = 3;
+      if (L.n_ntiles == 1 && L.head == 2 && L.N_total == 64 && p.MT == 1 && (p.y.sA & 1) == 0) p.pair_mode = 3;
     } else if (dst.cp == 1) {
-      if ((L.N_total & 31) == 0) p.pair_mode = 2;
+      if (L.n_ntiles == 1 && (L.N_total & 31) == 0) p.pair_mode = 2;
     } else if (L.fout >= 2 && (L.fout & 1) == 0 && p.y.sB == 1 && (p.y.sA & 1) == 0) {
-      p.pair_mode = 1;
-      p.pair_dcol = L.N_total / L.fout;
-      p.pair_units = (L.N_TILE / (2 * p.pair_dcol)) * (p.pair_dcol >> 4);
+      // several n-tiles: each must hold whole pairs of phases (the 256->128 x4 transposed conv: 4 phases of 128
+      // channels in two tiles of 256 columns)
+      const int dcol = L.N_total / L.fout;
+      if (L.n_ntiles == 1 || (dcol % 16 == 0 && L.N_TILE % (2 * dcol) == 0 && L.N_TILE * L.n_ntiles == L.N_total)) {
+        p.pair_mode = 1;
+        p.pair_dcol = dcol;
+        p.pair_units = (L.N_TILE / (2 * dcol)) * (dcol >> 4);
+        p.pair_ph_tile = L.n_ntiles > 1 ? L.N_TILE / dcol : 0;
+      }
     }
   }
   // MT = 2 leaves one accumulator stage: publish / take back its sub-tiles separately (tc_conv.cu gemm1_cg2)

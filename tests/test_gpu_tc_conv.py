@@ -180,6 +180,8 @@ ACT_CASES = [
     # sector-complete stores of phase outputs (drain_pair), the second one also as a cta_group::2 pair
     dict(c_in=128, c_out=256, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=2, n=520, flags=3),
     dict(c_in=256, c_out=256, k=3, stride=1, dil=1, off=1, ileave=2, res=0, B=3, n=640, flags=3),
+    # ... and with two n-tiles that each hold two of the four phases (the 256->128 x4 transposed conv)
+    dict(c_in=256, c_out=512, k=3, stride=1, dil=1, off=1, ileave=4, res=0, B=3, n=520, flags=3),
     dict(c_in=6, c_out=64, k=7, stride=1, dil=1, off=3, ileave=1, res=0, B=2, n=4096, flags=2, pre=0),
 ]
 
