@@ -444,6 +444,7 @@ int rb_load_weights(rb_handle* h, const rb_tensor_desc* t, int n) {
                  "conditioning vector size");
         rc = upload(d.data, d.numel, &w.cond);
         w.cond_rows = 1;
+        ++h->cond_version;
         break;
       default:
         set_error("tensor %d: unknown role %d", i, d.role);
@@ -669,6 +670,7 @@ int rb_set_conditioning(rb_handle* h, const float* spk, int spk_rows, const floa
       w.cond_rows = spk_rows;
     }
     RB_CUDA(cudaMemcpyAsync(w.cond, spk, n * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    ++h->cond_version;
   }
   if (f0) {
     RB_CHECK(B >= 1 && f0_channels >= 1 && F >= 1, RB_ERR_INVALID, "f0 must be [B, f0_channels, F]");

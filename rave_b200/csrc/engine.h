@@ -92,6 +92,7 @@ struct rb_handle {
   int f0_B = 0, f0_C = 0, f0_F = 0;
 
   std::vector<rb::PoolBuf> pool;  // offline activation workspace
+  unsigned long long cond_version = 0;   // bumped whenever the speaker table changes (folded conditioning cache)
   int microbatch = 0;
   int cur_b0 = 0;               // first stream of the microbatch being executed (per-stream tables)
   bool adain_learn_x = false, adain_learn_y = false;   // export.py:248-265 learn_source / learn_target

@@ -358,7 +358,7 @@ __device__ __forceinline__ int goff32(const TcView& v, int g) {
 // The common case of drain() below, with the address arithmetic hoisted out of the chunk loop:
 // NT a multiple of 32, channel groups of a chunk sA apart in y (and in the residual), no waveform
 // head, no sign mask.  RES: 0 none, 1 global (L2-prefetched), 2 the A tile in smem (fused unit).
-template <int RES, bool SPIN = false>
+template <int RES, bool SPIN = false, bool SB = false>
 __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full, uint32_t parity, uint32_t tbase,
                                            const float* bs, const Work& wk, int rit, int part, int nparts, int ch0,
                                            int MTn, int NT, const uint8_t* res_s, uint32_t tr,
@@ -414,6 +414,18 @@ __device__ __forceinline__ void drain_fast(const TcParams& p, uint32_t bar_full,
     load_acc<32>(tbase + (uint32_t)(mt * NT + c0), bs + ch0 + c0, v);
     TRACE(tr, 13);
     const bool valid = row + mt * 128 < p.y.n;
+    if (SB) {
+      // per-stream bias of this row's class (TcParams::sbias); all lanes but the edge rows' read the same addresses
+      const int t = row + mt * 128;
+      const int cls = t == 0 ? 1 : (t == p.y.n - 1 ? 2 : 0);
+      const float4* sp = reinterpret_cast<const float4*>(p.sbias + ((size_t)wk.b * 3 + cls) * p.sbias_n + ch0 + c0);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float4 b4 = __ldg(sp + q);
+        add2(v[4 * q], v[4 * q + 1], b4.x, b4.y);
+        add2(v[4 * q + 2], v[4 * q + 3], b4.z, b4.w);
+      }
+    }
     if (RES != 0 && valid) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
@@ -1411,6 +1423,10 @@ __global__ void __launch_bounds__(NS == 3 ? 896 : TC_THREADS, 1)
         else if (DR == 0)
           drain(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
                 p.N_TILE, nullptr, trc);
+        else if (DR == 4)
+          drain_fast<0, CG2, true>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE,
+                                   p.MT, p.N_TILE, nullptr, trc, CG2 && p.split ? BAR(BAR_D_FULL + 1) : 0u,
+                                   BAR(BAR_D_EMPTY));
         else if (p.res.p)
           drain_fast<1, CG2>(p, BAR(BAR_D_FULL + sd), phd, tb, bias_s, wk, rit, part, OUT_PARTS, wk.nt * p.N_TILE, p.MT,
                              p.N_TILE, nullptr, trc, CG2 && p.split ? BAR(BAR_D_FULL + 1) : 0u, BAR(BAR_D_EMPTY));
@@ -2006,6 +2022,8 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
                     (p.res.p == nullptr || p.res_smem || (p.res.G1 & 3) == 0);
   // h in tensor memory is compiled into one variant (and its traced twin): the fast fused unit of a LeakyReLU
   // net with its residual in global memory -- tc_engine.cu sets h_tmem under the same conditions
+  RB_CHECK(!p.sbias || (fast && !p.fused && !p.res.p && !p.pair_mode && p.pre_act == RB_ACT_NONE && !p.trace &&
+                        (p.sbias_n & 3) == 0), RB_ERR_INVALID, "per-stream bias on a layer without that kernel variant");
   RB_CHECK(!p.h_tmem || (p.fused && fast && p.res.p && !p.res_smem && p.pre_act == RB_ACT_NONE && p.act2 == RB_ACT_LEAKY),
            RB_ERR_INVALID, "h_tmem set for a layer without that kernel variant");
   if (p.trace && p.pre_act == RB_ACT_NONE && fast && (!p.fused || (p.act2 == RB_ACT_LEAKY && p.res.p))) {
@@ -2019,7 +2037,10 @@ int launch_tc_conv(TcParams& p, cudaStream_t s) {
       RB_CHECK(p.pair && p.pre_act == RB_ACT_NONE && !p.w_resident && p.N_TILE == 256 &&
                    (fast || p.pair_mode), RB_ERR_INVALID, "cta_group::2 layer outside its envelope");
       rc = p.pair_mode ? launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 3, false, 2, true>(p, tm, grid, s)
+           : p.sbias   ? launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 4, false, 2, true>(p, tm, grid, s)
                        : launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 1, false, 2, true>(p, tm, grid, s);
+    } else if (p.pre_act == RB_ACT_NONE && p.sbias) {
+      rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 4>(p, tm, grid, s);
     } else if (p.pre_act == RB_ACT_NONE && p.pair_mode) {
       rc = launch_variant<RB_ACT_NONE, RB_ACT_NONE, false, 3>(p, tm, grid, s);
     } else if (p.pre_act == RB_ACT_NONE) {

@@ -92,6 +92,11 @@ struct TcParams {
   // (row batching, transposed-conv phases): the pieces of phase 2i and 2i+1 (pair_dcol columns apart in the
   // accumulator) are neighbours in memory and leave as one 32-byte store; 2 consecutive channel groups are
   // neighbours (audio rows); 3 waveform head with two real rows per view row
+  // Per-stream bias (the speaker channels of the decoder's first conv, folded: tc_engine.cu fold): [B][3][sbias_n]
+  // fp32 -- row classes 0 interior, 1 first row of the stream, 2 last row (zero padding drops one tap there).
+  // Kernel variants DR = 4 only.
+  const float* sbias;
+  int sbias_n;
   int pair_mode, pair_dcol;
   int pair_ph_tile;         // pair_mode 1 with several n-tiles: phases per n-tile (0: one n-tile)
   int pair_units;           // pair_mode 1: 32-byte units of a row tile, (N_TILE / (2 pair_dcol)) * (pair_dcol / 16)

@@ -66,7 +66,24 @@ struct Plan {
   // per slot: tensor is stored LeakyReLU-activated (every consumer wants act(x) as conv input, or
   // x as a residual, which min(z, 5z) recovers) -- consumers then load it straight into the MMA
   std::vector<int> sact;
+  // Folded conditioning (offline): the conv right behind CONCAT_COND, k = 3 with centred zero padding, reads only
+  // the latent channels; the time-constant speaker channels enter as a per-stream bias with the exact edge rows
+  // (the first row of a stream misses tap 0, the last row tap 2).  fold_layers[i]: the conv packed over the latent
+  // channels only; fold_wc[i]: its speaker-channel weights, bf16-rounded, fp32 [3][c_spk][N_total] on the device.
+  std::vector<Layer> fold_layers;
+  std::vector<float*> fold_wc;
+  float* fold_sbias = nullptr;    // [rows][3][N_total], recomputed when the speaker table or the batch changes
+  size_t fold_sbias_cap = 0;
+  const float* fold_key_spk = nullptr;
+  long long fold_key_stride = -1;
+  int fold_key_b0 = -1, fold_key_B = -1, fold_key_op = -1;
+  unsigned long long fold_key_version = ~0ull;
+  cudaStream_t fold_key_stream = nullptr;
+  int fold_now = -1;              // op whose folded form runs next (set by its CONCAT_COND, which then writes nothing)
+  int run_oe = 0;                 // end of the op range of the running program (tc_run_program)
 };
+static thread_local const float* g_sbias = nullptr;   // per-stream bias of the NEXT run_layer call (folded conditioning)
+static thread_local int g_sbias_n = 0;
 
 static int slot_cp(const rb_handle* h, int sl) {
   if (sl == h->spec.enc_in_slot || sl == h->spec.dec_out_slot) return 1;   // audio [B][T]
@@ -396,6 +413,8 @@ static int run_layer(const Layer& L, const rb_op& op, const rb_op* op2, const Bu
   int rc = make_view(src, L.fin, &p.x);
   if (rc) return rc;
   if ((rc = make_view(dst, L.fout, &p.y))) return rc;
+  p.sbias = g_sbias; p.sbias_n = g_sbias_n;
+  g_sbias = nullptr;
   const int n_streams = B;
   if (sr_rows > 0) {
     // rows = streams: row stride = the per-stream stride; tap j (and sub-row of a strided view) becomes
@@ -939,11 +958,18 @@ static inline int ew_grid(size_t total) {
 
 using namespace tc;
 
+static void free_fold(Plan* pl) {
+  for (auto& L : pl->fold_layers) free_layer(L);
+  for (float* p : pl->fold_wc) cudaFree(p);
+  cudaFree(pl->fold_sbias);
+}
+
 void tc_free(rb_handle* h) {
   Plan* pl = (Plan*)h->tc;
   if (!pl) return;
   for (auto& L : pl->layers) free_layer(L);
   for (auto& L : pl->sr_layers) free_layer(L);
+  free_fold(pl);
   delete pl;
   h->tc = nullptr;
 }
@@ -956,6 +982,8 @@ int tc_pack_weights(rb_handle* h) {
   const int nops = (int)h->ops.size();
   pl->layers.resize(nops);
   pl->sr_layers.resize(nops);
+  pl->fold_layers.resize(nops);
+  pl->fold_wc.assign(nops, nullptr);
   pl->skip.assign(nops, 0);
   pl->cp.resize(h->slots.size());
   for (size_t s = 0; s < h->slots.size(); ++s) pl->cp[s] = slot_cp(h, (int)s);
@@ -1025,6 +1053,48 @@ int tc_pack_weights(rb_handle* h) {
     Layer& L = pl->layers[i];
     rc = pack_layer(v, 64, (fuse || pairdu) ? &v2 : nullptr, L, 0, pairdu);
     if (rc) return rc;
+    if (getenv("RB_TC_PLAN_DEBUG") && op.kind == RB_OP_CONV && i > 0 && h->ops[i - 1].kind == RB_OP_CONCAT_COND)
+      fprintf(stderr, "fold candidate op %d: src match %d fuse %d pairdu %d streaming %d k %d stride %d dil %d ileave %d res %d "
+              "pre_act %d taps %d off %d fin %d fout %d cin_v %d N %d\n", i, (int)(h->ops[i - 1].dst == op.src), (int)fuse,
+              (int)pairdu, (int)h->spec.streaming, op.k, op.stride, op.dilation, op.ileave, op.res, op.pre_act, v.n_taps,
+              v.off, v.fin, v.fout, v.cin_v, v.N_total);
+    // folded conditioning (Plan::fold_layers): CONCAT_COND -> this conv, offline
+    // (in the reference's graph the concatenation is the LAST encoder op -- encode() returns the conditioned latent,
+    // model.py:615-620 -- and this conv the first decoder op: the fold applies to calls that span both programs)
+    if (op.kind == RB_OP_CONV && i > 0 && h->ops[i - 1].kind == RB_OP_CONCAT_COND &&
+        (h->ops[i - 1].dst == op.src || (i == h->spec.n_enc_ops && h->ops[i - 1].dst == h->spec.enc_out_slot &&
+                                         op.src == h->spec.dec_in_slot)) &&
+        !fuse && !pairdu && !h->spec.streaming && op.k == 3 && op.stride == 1 && op.dilation == 1 &&
+        std::max(op.ileave, 1) == 1 && op.res < 0 && op.pre_act == RB_ACT_NONE && v.n_taps == 3 && v.off == 1 &&
+        v.fin == 1 && v.fout == 1 && !getenv("RB_TC_NOFOLD")) {
+      const rb_op& cc = h->ops[i - 1];
+      const int c_z = cc.c_in, c_spk = h->spec.cond_channels;
+      bool only_reader = true;
+      for (int j = 0; j < nops; ++j)
+        if (j != i && (h->ops[j].src == op.src || h->ops[j].res == op.src || h->ops[j].src2 == op.src)) only_reader = false;
+      if (getenv("RB_TC_PLAN_DEBUG"))
+        fprintf(stderr, "  fold: only_reader %d c_z %d c_spk %d cp_src %d cp_dst %d\n", (int)only_reader, c_z, c_spk,
+                pl->cp[cc.src], pl->cp[op.dst]);
+      if (only_reader && c_spk > 0 && c_z % 16 == 0 && pl->cp[cc.src] == c_z && c_z + c_spk <= v.cin_v &&
+          v.N_total % 32 == 0 && (pl->cp[op.dst] / 8) % 4 == 0) {
+        ViewWeight vz;
+        vz.N_total = v.N_total; vz.cin_v = c_z; vz.n_taps = 3; vz.dil = 1; vz.off = 1; vz.fin = vz.fout = 1; vz.out_mask = 0;
+        vz.w.assign((size_t)vz.N_total * c_z * 3, 0.f);
+        for (int n = 0; n < v.N_total; ++n)
+          for (int c = 0; c < c_z; ++c)
+            for (int j = 0; j < 3; ++j) vz.at(n, c, j) = v.at(n, c, j);
+        vz.bias = v.bias;
+        if ((rc = pack_layer(vz, 64, nullptr, pl->fold_layers[i]))) return rc;
+        if (pl->fold_layers[i].N_TILE % 32 != 0) free_layer(pl->fold_layers[i]);   // needs the drain_fast variant
+        // the speaker channels' weights as the MMA would see them (bf16), [tap][channel][n]
+        std::vector<float> wc((size_t)3 * c_spk * v.N_total);
+        for (int j = 0; j < 3; ++j)
+          for (int c = 0; c < c_spk; ++c)
+            for (int n = 0; n < v.N_total; ++n)
+              wc[((size_t)j * c_spk + c) * v.N_total + n] = __bfloat162float(f2bf(v.at(n, c_z + c, j)));
+        if (pl->fold_layers[i].valid && (rc = dev_upload(wc, &pl->fold_wc[i]))) return rc;
+      }
+    }
     if (pairdu) {
       RB_CHECK(L.w2 && L.N_TILE == v.N_total && L.KC == 64 && L.n_kchunks * 64 == L.N_TILE &&
                    L.total_blocks == 3 * L.n_kchunks, RB_ERR_STATE, "pair DilatedUnit: unexpected packing");
@@ -1104,6 +1174,31 @@ int tc_pack_weights(rb_handle* h) {
   return RB_OK;
 }
 
+// Per-stream bias of a folded conditioning conv: V_j[n] = sum_c Wc[j][c][n] * bf16(spk[b][c]) for the three taps;
+// row classes: interior V0 + V1 + V2, first row of a stream (tap 0 falls on the zero padding) V1 + V2, last row
+// V0 + V1.  One block per stream, thread n-strided; the speaker row goes through shared memory.
+__global__ void cond_fold_kernel(const float* __restrict__ wc, const float* __restrict__ spk, long long spk_stride,
+                                 int b0, int c_spk, int N, float* __restrict__ out) {
+  extern __shared__ float srow[];
+  const int b = blockIdx.x;
+  for (int c = threadIdx.x; c < c_spk; c += blockDim.x)
+    srow[c] = __bfloat162float(__float2bfloat16_rn(spk[(size_t)(b0 + b) * spk_stride + c]));
+  __syncthreads();
+  for (int n = threadIdx.x; n < N; n += blockDim.x) {
+    float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+    for (int c = 0; c < c_spk; ++c) {
+      const float sv = srow[c];
+      v0 = fmaf(wc[((size_t)0 * c_spk + c) * N + n], sv, v0);
+      v1 = fmaf(wc[((size_t)1 * c_spk + c) * N + n], sv, v1);
+      v2 = fmaf(wc[((size_t)2 * c_spk + c) * N + n], sv, v2);
+    }
+    float* o = out + (size_t)b * 3 * N + n;
+    o[0] = v0 + v1 + v2;
+    o[N] = v1 + v2;
+    o[2 * N] = v0 + v1;
+  }
+}
+
 // ------------------------------------------------------------------- offline op interpreter
 static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int B, const float* noise,
                       int64_t noise_bstride, cudaStream_t s) {
@@ -1115,6 +1210,36 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
     case RB_OP_PQMF_INV: {
       RB_CHECK(L.valid, RB_ERR_STATE, "op %d has no bf16 plan", i);
       const std::vector<int>& sa = pl->sact;
+      if (pl->fold_now == i) {
+        pl->fold_now = -1;
+        const rb_op& cc = h->ops[i - 1];
+        const Layer& FL = pl->fold_layers[i];
+        CondArgs ca;
+        int rc = cond_args(h, i - 1, B, bufs[op.dst].n, &ca);
+        if (rc) return rc;
+        const int N = FL.N_total;
+        const size_t need = (size_t)B * 3 * N;
+        if (pl->fold_sbias_cap < need) {
+          RB_CUDA(cudaStreamSynchronize(s));
+          cudaFree(pl->fold_sbias);
+          pl->fold_sbias = nullptr; pl->fold_sbias_cap = 0;
+          RB_CUDA(cudaMalloc((void**)&pl->fold_sbias, need * sizeof(float)));
+          pl->fold_sbias_cap = need;
+          pl->fold_key_op = -1;
+        }
+        if (pl->fold_key_op != i || pl->fold_key_spk != ca.spk || pl->fold_key_stride != ca.spk_stride ||
+            pl->fold_key_b0 != ca.b0 || pl->fold_key_B != B || pl->fold_key_version != h->cond_version ||
+            pl->fold_key_stream != s) {
+          cond_fold_kernel<<<B, 256, (size_t)ca.c_spk * sizeof(float), s>>>(pl->fold_wc[i], ca.spk, ca.spk_stride, ca.b0,
+                                                                            ca.c_spk, N, pl->fold_sbias);
+          ++g_launches;
+          RB_CUDA(cudaGetLastError());
+          pl->fold_key_op = i; pl->fold_key_spk = ca.spk; pl->fold_key_stride = ca.spk_stride; pl->fold_key_b0 = ca.b0;
+          pl->fold_key_B = B; pl->fold_key_version = h->cond_version; pl->fold_key_stream = s;
+        }
+        g_sbias = pl->fold_sbias; g_sbias_n = N;
+        return run_layer(FL, op, nullptr, bufs[cc.src], bufs[op.dst], nullptr, B, s, sa[cc.src], 0, sa[op.dst]);
+      }
       if (L.pairdu) {
         const rb_op& o2 = h->ops[L.fused_with];
         RB_CHECK(sa[op.src], RB_ERR_STATE, "pair DilatedUnit: input is not stored activated");
@@ -1198,6 +1323,12 @@ static int tc_exec_op(rb_handle* h, Plan* pl, int i, std::vector<Buf>& bufs, int
       CondArgs ca;
       int rc = cond_args(h, i, B, y.n, &ca);
       if (rc) return rc;
+      pl->fold_now = -1;
+      if (i + 1 < pl->run_oe && pl->fold_layers[i + 1].valid && !ca.f0 && y.n >= 2 && !pl->skip[i + 1] &&
+          !getenv("RB_TC_NOFOLD")) {
+        pl->fold_now = i + 1;                 // the next conv reads the latent alone; nothing to materialise
+        return RB_OK;
+      }
       RB_LAUNCH_EW(concat_gm_kernel, (size_t)B * y.n * (y.cp / 8), s, bufs[op.src], y, ca, op.c_in, B);
       return RB_OK;
     }
@@ -1221,6 +1352,8 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
     RB_CHECK(pl->cp[h->spec.enc_out_slot] == pl->cp[h->spec.dec_in_slot], RB_ERR_INVALID,
              "encoder output and decoder input widths differ");
   std::vector<int> last_use(ns, -1), buf_of(ns, -1);
+  pl->run_oe = oe;
+  pl->fold_now = -1;
   for (int i = ob; i < oe; ++i) {
     if (pl->skip[i]) continue;
     const rb_op& op = h->ops[i];
@@ -1229,6 +1362,8 @@ int tc_run_program(rb_handle* h, int ob, int oe, const void* in, void* out, int 
     if (ol.res >= 0 && !pl->layers[i].head) last_use[ol.res] = i;
     if (op.src2 >= 0) last_use[op.src2] = i;
     last_use[ol.dst] = std::max(last_use[ol.dst], i);
+    // folded conditioning: the conv behind CONCAT_COND reads the concat's INPUT
+    if (pl->fold_layers[i].valid && i > ob) last_use[h->ops[i - 1].src] = std::max(last_use[h->ops[i - 1].src], i);
   }
   if (has_enc && has_dec) last_use[h->spec.enc_out_slot] = std::max(last_use[h->spec.enc_out_slot], last_use[h->spec.dec_in_slot]);
   auto slot_rows = [&](int sl) { return h->slots[sl].per_frame * F; };

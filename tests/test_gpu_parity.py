@@ -772,3 +772,39 @@ def test_fake_stereo_forward_vs_oracle():
     yo = torch.cat(o.decode(torch.cat([zo, zo], 0)).chunk(2, 0), 1)
     assert y.shape == (x.shape[0], 2, x.shape[2])
     assert rel_l2(y.numpy(), yo.numpy()) < 2 * F32_TOL
+
+
+@pytest.mark.gpu
+def test_folded_speaker_channels_vs_oracle():
+    """bf16, offline, forward(): the speaker channels never reach the decoder's first conv as data -- they enter
+    as a per-stream bias with the first / last row of each stream corrected for the zero padding (tc_engine.cu
+    fold; rave/blocks.py:631-638, rave/model.py:615-620).  Per-stream rows, a changed table between calls (the
+    bias is cached), stream micro-batches (row offsets), two-frame inputs (only edge rows) and one frame (the
+    unfolded path) against the oracle; encode() still returns the conditioned latent."""
+    from oracle.model import OracleRAVE
+    from rave_b200 import RAVE
+    from oracle.weights_recipe import recipe_input
+    meta, _ = load_golden("v2_c8")
+    sd = golden_state_dict(meta)
+    files, binds = GIN["v2_c8"]
+    m = RAVE.from_gin(files, binds, dtype=torch.bfloat16)
+    m.load_state_dict(sd)
+    o = OracleRAVE(meta["cfg"], sd)
+    B = 5
+    spk = torch.from_numpy(recipe_input((B, 256, 1), 192, scale=1.0))
+    for frames in (6, 2, 1):
+        T = 1024 * frames
+        x = torch.from_numpy(recipe_input((B, 1, T), 191))
+        xg = x.cuda().bfloat16()
+        m.set_speaker(spk.cuda())
+        y = m.forward(xg).float().cpu().numpy()
+        assert rel_l2(y, o.forward(x, speaker=spk).numpy()) < 1.5e-2
+        m.set_speaker(spk.flip(0).contiguous().cuda())        # same buffer, new contents
+        y2 = m.forward(xg).float().cpu().numpy()
+        assert rel_l2(y2, o.forward(x, speaker=spk.flip(0)).numpy()) < 1.5e-2
+        m.set_microbatch(2)                                    # streams 0-1, 2-3, 4
+        y3 = m.forward(xg).float().cpu().numpy()
+        m.set_microbatch(0)
+        assert np.array_equal(y3, y2)
+        z = m.encode(xg).float().cpu().numpy()
+        assert np.array_equal(z[:, 64:320, 0], spk.flip(0)[:, :, 0].bfloat16().float().numpy())
